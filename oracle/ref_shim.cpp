@@ -1,0 +1,566 @@
+// TEST INFRASTRUCTURE ONLY - not part of the product, never linked into libsrsran_ldpc_cuda.so.
+//
+// C-ABI shim (for ctypes) around the UNMODIFIED reference implementation of the PUSCH LDPC receive chain.
+// It is compiled together with the reference's own sources where they lie under /root/reference (see
+// oracle/Makefile) into oracle/_ref/libsrsran_ref.so and is used
+//   * by tests/ to pin the plain-C restatement (oracle/ldpc_oracle.c) and the CUDA path bit-for-bit,
+//   * by tools/ to dump the 3GPP base-graph tables and to generate tests/golden fixtures,
+//   * by bench.py (--impl reference / cpu_baseline) as the timed multi-threaded CPU baseline.
+//
+// Every function goes through the reference's public interfaces:
+//   create_ldpc_decoder_factory_sw / create_ldpc_rate_dematcher_factory_sw / create_ldpc_encoder_factory_sw /
+//   create_ldpc_rate_matcher_factory_sw / create_crc_calculator_factory_sw / create_ldpc_segmenter_*_factory_sw
+//   (include/srsran/phy/upper/channel_coding/channel_coding_factories.h:43-105) and pusch_decoder_impl
+//   (lib/phy/upper/channel_processors/pusch_decoder_impl.h) with the real rx_softbuffer_pool.
+
+#include "phy/upper/channel_coding/ldpc/ldpc_graph_impl.h"
+#include "phy/upper/channel_coding/ldpc/ldpc_luts_impl.h"
+#include "phy/upper/channel_processors/pusch_decoder_impl.h"
+#include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
+#include "srsran/phy/upper/log_likelihood_ratio.h"
+#include "srsran/phy/upper/rx_softbuffer_pool.h"
+#include "srsran/phy/upper/unique_rx_softbuffer.h"
+#include "srsran/ran/slot_point.h"
+#include "srsran/srsvec/bit.h"
+#include "srsran/support/cpu_features.h"
+
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+using namespace srsran;
+
+namespace {
+
+ldpc_base_graph_type to_bg(int bg)
+{
+  return bg == 2 ? ldpc_base_graph_type::BG2 : ldpc_base_graph_type::BG1;
+}
+
+// poly codes shared with include/ldpc_cuda.h: 0 = none, 1 = CRC16, 2 = CRC24A, 3 = CRC24B.
+bool to_poly(int code, crc_generator_poly& poly)
+{
+  switch (code) {
+    case 1:
+      poly = crc_generator_poly::CRC16;
+      return true;
+    case 2:
+      poly = crc_generator_poly::CRC24A;
+      return true;
+    case 3:
+      poly = crc_generator_poly::CRC24B;
+      return true;
+    default:
+      return false;
+  }
+}
+
+codeblock_metadata make_meta(int bg, int Z, int rv, int Qm, unsigned Nref, unsigned fillers, unsigned crc_bits)
+{
+  codeblock_metadata m            = {};
+  m.tb_common.base_graph          = to_bg(bg);
+  m.tb_common.lifting_size        = static_cast<ldpc::lifting_size_t>(Z);
+  m.tb_common.rv                  = rv;
+  m.tb_common.mod                 = static_cast<modulation_scheme>(Qm);
+  m.tb_common.Nref                = Nref;
+  m.cb_specific.nof_filler_bits   = fillers;
+  m.cb_specific.nof_crc_bits      = crc_bits;
+  m.cb_specific.full_length       = (bg == 2 ? 50 : 66) * Z;
+  return m;
+}
+
+struct decoder_handle {
+  std::unique_ptr<ldpc_decoder>   dec;
+  std::unique_ptr<crc_calculator> crc[4];
+};
+
+struct pusch_handle {
+  std::unique_ptr<pusch_decoder>      dec;
+  std::unique_ptr<rx_softbuffer_pool> pool;
+};
+
+} // namespace
+
+extern "C" {
+
+int ref_cpu_supports(const char* type)
+{
+  std::string t(type);
+  if (t == "generic") {
+    return 1;
+  }
+  if (t == "avx2") {
+    return cpu_supports_feature(cpu_feature::avx2) ? 1 : 0;
+  }
+  if (t == "avx512") {
+    return (cpu_supports_feature(cpu_feature::avx512f) && cpu_supports_feature(cpu_feature::avx512bw)) ? 1 : 0;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Graphs (ldpc_luts_impl.cpp: get_graph :4521-4544, get_adjacency_matrix; ldpc.h:41-104 lifting sizes).
+int ref_lifting_sizes(int* out51)
+{
+  int n = 0;
+  for (auto ls : ldpc::all_lifting_sizes) {
+    out51[n++] = static_cast<int>(ls);
+  }
+  return n;
+}
+
+int ref_lifting_index(int Z)
+{
+  return ldpc::get_lifting_index(static_cast<ldpc::lifting_size_t>(Z));
+}
+
+// pcm: [M][N_full] row-major, 0xffff = no edge, else shift % Z.  adj: [M][20], 0xffff-terminated.
+int ref_graph_dump(int bg, int Z, uint16_t* pcm, uint16_t* adj)
+{
+  ldpc::BG_matrix_t                  g = ldpc::get_graph(to_bg(bg), static_cast<ldpc::lifting_size_t>(Z));
+  const ldpc::BG_adjacency_matrix_t* a = ldpc::get_adjacency_matrix(to_bg(bg));
+  unsigned                           M = (bg == 2) ? ldpc::BG2_M : ldpc::BG1_M;
+  unsigned                           N = (bg == 2) ? ldpc::BG2_N_FULL : ldpc::BG1_N_FULL;
+  for (unsigned m = 0; m != M; ++m) {
+    for (unsigned n = 0; n != N; ++n) {
+      pcm[m * N + n] = g[m][n];
+    }
+    for (unsigned e = 0; e != ldpc::MAX_BG_CHECK_EDGES; ++e) {
+      adj[m * ldpc::MAX_BG_CHECK_EDGES + e] = (*a)[m][e];
+    }
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// LLR arithmetic (log_likelihood_ratio.cpp:38-85) and hard decision (:225-248).
+int ref_llr_add(int a, int b)
+{
+  return (log_likelihood_ratio(a) + log_likelihood_ratio(b)).to_value_type();
+}
+int ref_llr_sub(int a, int b)
+{
+  return (log_likelihood_ratio(a) - log_likelihood_ratio(b)).to_value_type();
+}
+int ref_llr_promotion_sum(int a, int b)
+{
+  return log_likelihood_ratio::promotion_sum(log_likelihood_ratio(a), log_likelihood_ratio(b)).to_value_type();
+}
+int ref_llr_quantize(float v, float range)
+{
+  return log_likelihood_ratio::quantize(v, range).to_value_type();
+}
+void ref_hard_decision(const int8_t* soft, unsigned n, uint8_t* out_packed)
+{
+  dynamic_bit_buffer bits(n);
+  hard_decision(bits, span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(soft), n));
+  std::memcpy(out_packed, bits.get_buffer().data(), (n + 7) / 8);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CRC (crc_calculator_lut_impl.cpp / crc_calculator_clmul_impl.cpp). impl in {"auto","lut","clmul"}.
+// Returns the checksum of the first nbits of the MSB-first packed buffer, or 0xffffffff on bad arguments.
+unsigned ref_crc_packed(const char* impl, int poly_code, const uint8_t* packed, unsigned nbits)
+{
+  crc_generator_poly poly;
+  if (!to_poly(poly_code, poly)) {
+    return 0xffffffffU;
+  }
+  auto factory = create_crc_calculator_factory_sw(impl);
+  if (!factory) {
+    return 0xffffffffU;
+  }
+  auto               crc = factory->create(poly);
+  dynamic_bit_buffer bits(nbits);
+  std::memcpy(bits.get_buffer().data(), packed, (nbits + 7) / 8);
+  return crc->calculate(bits);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Decoder (ldpc_decoder.h:44-74). One handle = one reference decoder object (stateful, not thread-safe).
+void* ref_decoder_create(const char* type)
+{
+  auto factory = create_ldpc_decoder_factory_sw(type);
+  if (!factory) {
+    return nullptr;
+  }
+  auto dec = factory->create();
+  if (!dec) {
+    return nullptr;
+  }
+  auto* h       = new decoder_handle;
+  h->dec        = std::move(dec);
+  auto crc_fact = create_crc_calculator_factory_sw("auto");
+  h->crc[1]     = crc_fact->create(crc_generator_poly::CRC16);
+  h->crc[2]     = crc_fact->create(crc_generator_poly::CRC24A);
+  h->crc[3]     = crc_fact->create(crc_generator_poly::CRC24B);
+  return h;
+}
+
+void ref_decoder_destroy(void* handle)
+{
+  delete static_cast<decoder_handle*>(handle);
+}
+
+// Returns the number of iterations if the reference returned a value, 0 if it returned nullopt.
+// out_packed must hold ceil(K/8) bytes, K = bg_K * Z; it is pre-filled by the caller (the reference leaves it
+// untouched on some paths, e.g. all-zero input with a CRC calculator).
+int ref_decoder_decode(void*         handle,
+                       int           bg,
+                       int           Z,
+                       unsigned      nof_filler_bits,
+                       int           crc_poly_code,
+                       unsigned      max_iterations,
+                       float         scaling_factor,
+                       const int8_t* llrs,
+                       unsigned      nof_llrs,
+                       uint8_t*      out_packed)
+{
+  auto*    h = static_cast<decoder_handle*>(handle);
+  unsigned K = ((bg == 2) ? 10 : 22) * Z;
+
+  dynamic_bit_buffer out(K);
+  std::memcpy(out.get_buffer().data(), out_packed, (K + 7) / 8);
+
+  ldpc_decoder::configuration cfg = {};
+  cfg.block_conf = make_meta(bg, Z, 0, 1, 0, nof_filler_bits, (crc_poly_code == 1) ? 16 : 24);
+  cfg.algorithm_conf.max_iterations = max_iterations;
+  cfg.algorithm_conf.scaling_factor = scaling_factor;
+
+  crc_calculator* crc = (crc_poly_code >= 1 && crc_poly_code <= 3) ? h->crc[crc_poly_code].get() : nullptr;
+
+  optional<unsigned> r = h->dec->decode(
+      out, span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs), crc, cfg);
+  std::memcpy(out_packed, out.get_buffer().data(), (K + 7) / 8);
+  return r.has_value() ? static_cast<int>(r.value()) : 0;
+}
+
+// Multi-threaded batch decode used as the timed CPU baseline (SURVEY.md 8(d) "CPU baseline timing"): nthreads
+// workers, one reference decoder object each, disjoint contiguous slices of the batch. Returns wall seconds of the
+// decode region only (objects are created before the clock starts). iters[i] = iterations or 0.
+double ref_decoder_decode_batch_mt(const char*   type,
+                                   unsigned      nthreads,
+                                   unsigned      ncb,
+                                   int           bg,
+                                   int           Z,
+                                   unsigned      nof_filler_bits,
+                                   int           crc_poly_code,
+                                   unsigned      max_iterations,
+                                   float         scaling_factor,
+                                   const int8_t* llrs,
+                                   unsigned      llr_stride,
+                                   unsigned      nof_llrs,
+                                   uint8_t*      out_packed,
+                                   unsigned      out_stride,
+                                   int*          iters)
+{
+  if (nthreads == 0) {
+    nthreads = 1;
+  }
+  std::vector<void*> handles(nthreads);
+  for (auto& h : handles) {
+    h = ref_decoder_create(type);
+    if (h == nullptr) {
+      return -1.0;
+    }
+  }
+  std::atomic<unsigned>    ready{0};
+  std::atomic<bool>        go{false};
+  std::vector<std::thread> workers;
+  for (unsigned t = 0; t != nthreads; ++t) {
+    workers.emplace_back([&, t]() {
+      unsigned begin = static_cast<unsigned>((static_cast<uint64_t>(ncb) * t) / nthreads);
+      unsigned end   = static_cast<unsigned>((static_cast<uint64_t>(ncb) * (t + 1)) / nthreads);
+      ready.fetch_add(1);
+      while (!go.load(std::memory_order_acquire)) {
+      }
+      for (unsigned i = begin; i != end; ++i) {
+        iters[i] = ref_decoder_decode(handles[t],
+                                      bg,
+                                      Z,
+                                      nof_filler_bits,
+                                      crc_poly_code,
+                                      max_iterations,
+                                      scaling_factor,
+                                      llrs + static_cast<size_t>(i) * llr_stride,
+                                      nof_llrs,
+                                      out_packed + static_cast<size_t>(i) * out_stride);
+      }
+    });
+  }
+  while (ready.load() != nthreads) {
+  }
+  auto t0 = std::chrono::steady_clock::now();
+  go.store(true, std::memory_order_release);
+  for (auto& w : workers) {
+    w.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  for (auto& h : handles) {
+    ref_decoder_destroy(h);
+  }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Rate dematcher (ldpc_rate_dematcher.h:52-55). out is the persistent in/out soft buffer of N_short * Z LLRs.
+void* ref_dematcher_create(const char* type)
+{
+  auto factory = create_ldpc_rate_dematcher_factory_sw(type);
+  if (!factory) {
+    return nullptr;
+  }
+  auto d = factory->create();
+  return d ? d.release() : nullptr;
+}
+
+void ref_dematcher_destroy(void* handle)
+{
+  delete static_cast<ldpc_rate_dematcher*>(handle);
+}
+
+void ref_dematcher_run(void*         handle,
+                       int8_t*       out,
+                       unsigned      out_len,
+                       const int8_t* in,
+                       unsigned      in_len,
+                       int           new_data,
+                       int           bg,
+                       int           Z,
+                       int           rv,
+                       int           Qm,
+                       unsigned      Nref,
+                       unsigned      nof_filler_bits)
+{
+  auto*              d    = static_cast<ldpc_rate_dematcher*>(handle);
+  codeblock_metadata meta = make_meta(bg, Z, rv, Qm, Nref, nof_filler_bits, 24);
+  d->rate_dematch(span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(out), out_len),
+                  span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), in_len),
+                  new_data != 0,
+                  meta);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Transmit side, used only to make test signals: encoder (ldpc_encoder.h) and rate matcher (ldpc_rate_matcher.h).
+// Bits are unpacked, one per byte; filler bits in the message are 254 (ldpc.h:113).
+int ref_encode(const char* type, int bg, int Z, const uint8_t* msg_bits, uint8_t* out_bits, unsigned out_len)
+{
+  auto factory = create_ldpc_encoder_factory_sw(type);
+  if (!factory) {
+    return -1;
+  }
+  auto enc = factory->create();
+  if (!enc) {
+    return -1;
+  }
+  unsigned                               K   = ((bg == 2) ? 10 : 22) * Z;
+  codeblock_metadata::tb_common_metadata cfg = make_meta(bg, Z, 0, 1, 0, 0, 24).tb_common;
+  enc->encode(span<uint8_t>(out_bits, out_len), span<const uint8_t>(msg_bits, K), cfg);
+  return 0;
+}
+
+int ref_rate_match(uint8_t*       out,
+                   unsigned       E,
+                   const uint8_t* in,
+                   unsigned       N,
+                   int            bg,
+                   int            Z,
+                   int            rv,
+                   int            Qm,
+                   unsigned       Nref,
+                   unsigned       nof_filler_bits)
+{
+  auto               rm   = create_ldpc_rate_matcher_factory_sw()->create();
+  codeblock_metadata meta = make_meta(bg, Z, rv, Qm, Nref, nof_filler_bits, 24);
+  rm->rate_match(span<uint8_t>(out, E), span<const uint8_t>(in, N), meta);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Segmenter, RX geometry (ldpc_segmenter_impl.cpp:226-308). Caller must make sure the TB has <= 52 codeblocks
+// (MAX_NOF_SEGMENTS, codeblock_metadata.h:88): beyond that the reference overflows a static_vector.
+// meta_out: per CB 6 unsigned {Z, full_length, rm_length, nof_filler_bits, cw_offset, nof_crc_bits}.
+int ref_segment_rx(unsigned  tbs,
+                   int       bg,
+                   int       rv,
+                   int       Qm,
+                   unsigned  Nref,
+                   unsigned  nof_layers,
+                   unsigned  nof_ch_symbols,
+                   unsigned* meta_out)
+{
+  if (ldpc::compute_nof_codeblocks(units::bits(tbs), to_bg(bg)) > MAX_NOF_SEGMENTS) {
+    return -1;
+  }
+  auto                              seg = create_ldpc_segmenter_rx_factory_sw()->create();
+  std::vector<log_likelihood_ratio> llrs(static_cast<size_t>(nof_ch_symbols) * Qm);
+  segmenter_config                  cfg = {};
+  cfg.base_graph                        = to_bg(bg);
+  cfg.rv                                = rv;
+  cfg.mod                               = static_cast<modulation_scheme>(Qm);
+  cfg.Nref                              = Nref;
+  cfg.nof_layers                        = nof_layers;
+  cfg.nof_ch_symbols                    = nof_ch_symbols;
+  static_vector<described_rx_codeblock, MAX_NOF_SEGMENTS> cbs;
+  seg->segment(cbs, llrs, tbs, cfg);
+  for (unsigned i = 0; i != cbs.size(); ++i) {
+    const codeblock_metadata& m = cbs[i].second;
+    meta_out[6 * i + 0]         = m.tb_common.lifting_size;
+    meta_out[6 * i + 1]         = m.cb_specific.full_length;
+    meta_out[6 * i + 2]         = m.cb_specific.rm_length;
+    meta_out[6 * i + 3]         = m.cb_specific.nof_filler_bits;
+    meta_out[6 * i + 4]         = m.cb_specific.cw_offset;
+    meta_out[6 * i + 5]         = m.cb_specific.nof_crc_bits;
+  }
+  return static_cast<int>(cbs.size());
+}
+
+// Segmenter, TX side (ldpc_segmenter_impl.cpp:89-222): TB bytes -> C segments of K unpacked bits (fillers = 254),
+// TB CRC, CB CRCs and zero padding attached. segs_out: [C][K] bytes. Returns C (<= 52) or -1.
+int ref_segment_tx(const uint8_t* tb,
+                   unsigned       tb_bytes,
+                   int            bg,
+                   int            rv,
+                   int            Qm,
+                   unsigned       Nref,
+                   unsigned       nof_layers,
+                   unsigned       nof_ch_symbols,
+                   uint8_t*       segs_out,
+                   unsigned       seg_stride)
+{
+  if (ldpc::compute_nof_codeblocks(units::bits(tb_bytes * 8), to_bg(bg)) > MAX_NOF_SEGMENTS) {
+    return -1;
+  }
+  auto             seg = create_ldpc_segmenter_tx_factory_sw(create_crc_calculator_factory_sw("auto"))->create();
+  segmenter_config cfg = {};
+  cfg.base_graph       = to_bg(bg);
+  cfg.rv               = rv;
+  cfg.mod              = static_cast<modulation_scheme>(Qm);
+  cfg.Nref             = Nref;
+  cfg.nof_layers       = nof_layers;
+  cfg.nof_ch_symbols   = nof_ch_symbols;
+  static_vector<described_segment, MAX_NOF_SEGMENTS> segments;
+  seg->segment(segments, span<const uint8_t>(tb, tb_bytes), cfg);
+  for (unsigned i = 0; i != segments.size(); ++i) {
+    const bit_buffer& data = segments[i].get_data();
+    unsigned          K    = data.size();
+    unsigned          F    = segments[i].get_metadata().cb_specific.nof_filler_bits;
+    uint8_t*          dst  = segs_out + static_cast<size_t>(i) * seg_stride;
+    for (unsigned b = 0; b != K; ++b) {
+      dst[b] = data.extract(b, 1);
+    }
+    // The TX chain marks filler bits for the encoder (pdsch_encoder_impl.cpp does the same substitution).
+    for (unsigned b = K - F; b != K; ++b) {
+      dst[b] = ldpc::FILLER_BIT;
+    }
+  }
+  return static_cast<int>(segments.size());
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pusch_decoder_impl + the real soft-buffer pool (pusch_decoder_impl.cpp:121-225, rx_softbuffer_pool_impl.cpp).
+void* ref_pusch_create(const char* decoder_type,
+                       const char* dematcher_type,
+                       unsigned    max_softbuffers,
+                       unsigned    max_nof_codeblocks,
+                       unsigned    expire_timeout_slots)
+{
+  auto dec_f   = create_ldpc_decoder_factory_sw(decoder_type);
+  auto dem_f   = create_ldpc_rate_dematcher_factory_sw(dematcher_type);
+  auto crc_f   = create_crc_calculator_factory_sw("auto");
+  auto seg_f   = create_ldpc_segmenter_rx_factory_sw();
+  auto decoder = dec_f ? dec_f->create() : nullptr;
+  auto demat   = dem_f ? dem_f->create() : nullptr;
+  if (!decoder || !demat) {
+    return nullptr;
+  }
+  pusch_decoder_impl::sch_crc crcs;
+  crcs.crc16  = crc_f->create(crc_generator_poly::CRC16);
+  crcs.crc24A = crc_f->create(crc_generator_poly::CRC24A);
+  crcs.crc24B = crc_f->create(crc_generator_poly::CRC24B);
+
+  auto* h = new pusch_handle;
+  h->dec  = std::make_unique<pusch_decoder_impl>(seg_f->create(), std::move(demat), std::move(decoder), std::move(crcs));
+  rx_softbuffer_pool_config pc = {};
+  pc.max_codeblock_size        = ldpc::MAX_CODEBLOCK_SIZE;
+  pc.max_softbuffers           = max_softbuffers;
+  pc.max_nof_codeblocks        = max_nof_codeblocks;
+  pc.expire_timeout_slots      = expire_timeout_slots;
+  h->pool                      = create_rx_softbuffer_pool(pc);
+  return h;
+}
+
+void ref_pusch_destroy(void* handle)
+{
+  delete static_cast<pusch_handle*>(handle);
+}
+
+// stats_out: {tb_crc_ok, nof_codeblocks_total, nof_observations, min_iters, max_iters, mean_iters*1000}.
+// Returns 0, or -1 if no soft buffer could be reserved. release_on_ok mirrors uplink_processor_impl.cpp:168-170.
+int ref_pusch_decode(void*         handle,
+                     unsigned      slot_count,
+                     unsigned      rnti,
+                     unsigned      harq_id,
+                     uint8_t*      tb_out,
+                     unsigned      tb_bytes,
+                     const int8_t* llrs,
+                     unsigned      nof_llrs,
+                     int           bg,
+                     int           rv,
+                     int           Qm,
+                     unsigned      Nref,
+                     unsigned      nof_layers,
+                     unsigned      nof_ldpc_iterations,
+                     int           use_early_stop,
+                     int           new_data,
+                     int           release_on_ok,
+                     unsigned*     stats_out)
+{
+  auto*    h       = static_cast<pusch_handle*>(handle);
+  unsigned nof_cbs = ldpc::compute_nof_codeblocks(units::bits(tb_bytes * 8), to_bg(bg));
+  if (nof_cbs > MAX_NOF_SEGMENTS) {
+    return -2;
+  }
+  slot_point               slot(1, slot_count % (1024 * 20));
+  rx_softbuffer_identifier id  = {static_cast<uint16_t>(rnti), static_cast<uint8_t>(harq_id)};
+  unique_rx_softbuffer     buf = h->pool->reserve_softbuffer(slot, id, nof_cbs);
+  if (!buf.is_valid()) {
+    return -1;
+  }
+  pusch_decoder::configuration cfg = {};
+  cfg.segmenter_cfg.base_graph     = to_bg(bg);
+  cfg.segmenter_cfg.rv             = rv;
+  cfg.segmenter_cfg.mod            = static_cast<modulation_scheme>(Qm);
+  cfg.segmenter_cfg.Nref           = Nref;
+  cfg.segmenter_cfg.nof_layers     = nof_layers;
+  cfg.segmenter_cfg.nof_ch_symbols = nof_llrs / Qm;
+  cfg.nof_ldpc_iterations          = nof_ldpc_iterations;
+  cfg.use_early_stop               = use_early_stop != 0;
+  cfg.new_data                     = new_data != 0;
+
+  pusch_decoder_result stats = {};
+  h->dec->decode(span<uint8_t>(tb_out, tb_bytes),
+                 stats,
+                 &buf.get(),
+                 span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs),
+                 cfg);
+  stats_out[0] = stats.tb_crc_ok ? 1 : 0;
+  stats_out[1] = stats.nof_codeblocks_total;
+  stats_out[2] = stats.ldpc_decoder_stats.get_nof_observations();
+  if (stats.ldpc_decoder_stats.get_nof_observations() > 0) {
+    stats_out[3] = stats.ldpc_decoder_stats.get_min();
+    stats_out[4] = stats.ldpc_decoder_stats.get_max();
+    stats_out[5] = static_cast<unsigned>(stats.ldpc_decoder_stats.get_mean() * 1000.0 + 0.5);
+  } else {
+    stats_out[3] = stats_out[4] = stats_out[5] = 0;
+  }
+  if (stats.tb_crc_ok && release_on_ok) {
+    buf.release();
+  }
+  h->pool->run_slot(slot);
+  return 0;
+}
+
+} // extern "C"

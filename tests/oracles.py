@@ -1,0 +1,320 @@
+"""ctypes bindings to the two parity oracles (TEST INFRASTRUCTURE, never imported by the product package).
+
+* ``port``  - oracle/liboracle_port.so, the plain-C restatement (always available once built).
+* ``ref``   - oracle/_ref/libsrsran_ref.so, the reference's own code compiled from /root/reference (None if not built).
+
+Also holds the synthetic test-signal helpers (random message -> encode -> BPSK/AWGN -> int8 LLR quantisation as
+log_likelihood_ratio::quantize, lib/phy/upper/log_likelihood_ratio.cpp:87-96).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+c_int, c_uint, c_float, c_void_p, c_char_p, c_double = (
+    ctypes.c_int, ctypes.c_uint, ctypes.c_float, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_double)
+
+BG_K = {1: 22, 2: 10}
+BG_N_SHORT = {1: 66, 2: 50}
+BG_M = {1: 46, 2: 42}
+LIFTING_SIZES = [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32, 36, 40, 44, 48,
+                 52, 56, 60, 64, 72, 80, 88, 96, 104, 112, 120, 128, 144, 160, 176, 192, 208, 224, 240, 256, 288, 320,
+                 352, 384]
+CRC_NONE, CRC16, CRC24A, CRC24B = 0, 1, 2, 3
+CRC_BITS = {CRC16: 16, CRC24A: 24, CRC24B: 24}
+SCALE_GENERIC, SCALE_AVX, SCALE_NEON = 0, 1, 2
+
+
+def _ptr(a):
+    return a.ctypes.data_as(c_void_p) if a is not None else None
+
+
+def build_port():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "port"])
+
+
+class PortOracle:
+    def __init__(self):
+        path = os.path.join(ORACLE_DIR, "liboracle_port.so")
+        if not os.path.exists(path):
+            build_port()
+        L = self.lib = ctypes.CDLL(path)
+        L.oracle_crc_packed.restype = c_uint
+        L.oracle_crc_packed.argtypes = [c_int, c_void_p, c_uint]
+        L.oracle_scale.argtypes = [c_int, c_float, c_int]
+        L.oracle_decode.argtypes = [c_int, c_int, c_uint, c_int, c_uint, c_float, c_int, c_void_p, c_uint, c_void_p]
+        L.oracle_rate_dematch.argtypes = [c_void_p, c_uint, c_void_p, c_uint, c_int, c_int, c_int, c_uint, c_uint]
+        L.oracle_segment_rx.argtypes = [c_uint, c_int, c_int, c_uint, c_uint, c_void_p, c_uint]
+        L.oracle_encode.argtypes = [c_int, c_int, c_void_p, c_void_p, c_uint]
+        L.oracle_rate_match.argtypes = [c_void_p, c_uint, c_void_p, c_uint, c_int, c_int, c_uint, c_uint]
+        L.oracle_hard_decision.argtypes = [c_void_p, c_uint, c_void_p]
+
+    def llr_add(self, a, b):
+        return self.lib.oracle_llr_add(int(a), int(b))
+
+    def llr_sub(self, a, b):
+        return self.lib.oracle_llr_sub(int(a), int(b))
+
+    def llr_promotion_sum(self, a, b):
+        return self.lib.oracle_llr_promotion_sum(int(a), int(b))
+
+    def hard_decision(self, soft):
+        soft = np.ascontiguousarray(soft, np.int8)
+        out = np.zeros((soft.size + 7) // 8, np.uint8)
+        self.lib.oracle_hard_decision(_ptr(soft), soft.size, _ptr(out))
+        return out
+
+    def crc(self, poly, packed, nbits):
+        packed = np.ascontiguousarray(packed, np.uint8)
+        return self.lib.oracle_crc_packed(poly, _ptr(packed), nbits)
+
+    def scale(self, m, sf=0.8, mode=SCALE_GENERIC):
+        return self.lib.oracle_scale(int(m), sf, mode)
+
+    def decode(self, bg, Z, llrs, fillers=0, crc=CRC_NONE, max_iters=6, sf=0.8, scale_mode=SCALE_GENERIC, out_init=0):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.full((BG_K[bg] * Z + 7) // 8, out_init, np.uint8)
+        it = self.lib.oracle_decode(bg, Z, fillers, crc, max_iters, sf, scale_mode, _ptr(llrs), llrs.size, _ptr(out))
+        return out, it
+
+    def rate_dematch(self, soft, llrs, new_data, rv=0, Qm=1, Nref=0, fillers=0):
+        """soft is modified in place (int8 array of N_short*Z)."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        assert soft.dtype == np.int8 and soft.flags.c_contiguous
+        r = self.lib.oracle_rate_dematch(_ptr(soft), soft.size, _ptr(llrs), llrs.size, int(new_data), rv, Qm, Nref,
+                                         fillers)
+        assert r == 0, r
+        return soft
+
+    def segment_rx(self, tbs, bg, Qm, nof_layers, nof_ch_symbols):
+        C = self.lib.oracle_segment_rx(tbs, bg, Qm, nof_layers, nof_ch_symbols, None, 0)
+        assert C > 0, C
+        meta = np.zeros((C, 6), np.uint32)
+        self.lib.oracle_segment_rx(tbs, bg, Qm, nof_layers, nof_ch_symbols, _ptr(meta), C)
+        return meta
+
+    def encode(self, bg, Z, msg_bits, out_len=None):
+        msg_bits = np.ascontiguousarray(msg_bits, np.uint8)
+        assert msg_bits.size == BG_K[bg] * Z
+        out_len = BG_N_SHORT[bg] * Z if out_len is None else out_len
+        out = np.zeros(out_len, np.uint8)
+        r = self.lib.oracle_encode(bg, Z, _ptr(msg_bits), _ptr(out), out_len)
+        assert r == 0, r
+        return out
+
+    def rate_match(self, cw, E, rv=0, Qm=1, Nref=0, fillers=0):
+        cw = np.ascontiguousarray(cw, np.uint8)
+        out = np.zeros(E, np.uint8)
+        r = self.lib.oracle_rate_match(_ptr(out), E, _ptr(cw), cw.size, rv, Qm, Nref, fillers)
+        assert r == 0, r
+        return out
+
+
+class RefOracle:
+    """The reference's own compiled code. One decoder / dematcher object per (type) is cached unless fresh=True."""
+
+    def __init__(self, path):
+        L = self.lib = ctypes.CDLL(path)
+        L.ref_cpu_supports.argtypes = [c_char_p]
+        L.ref_graph_dump.argtypes = [c_int, c_int, c_void_p, c_void_p]
+        L.ref_llr_quantize.argtypes = [c_float, c_float]
+        L.ref_hard_decision.argtypes = [c_void_p, c_uint, c_void_p]
+        L.ref_crc_packed.restype = c_uint
+        L.ref_crc_packed.argtypes = [c_char_p, c_int, c_void_p, c_uint]
+        L.ref_decoder_create.restype = c_void_p
+        L.ref_decoder_create.argtypes = [c_char_p]
+        L.ref_decoder_destroy.argtypes = [c_void_p]
+        L.ref_decoder_decode.argtypes = [c_void_p, c_int, c_int, c_uint, c_int, c_uint, c_float, c_void_p, c_uint,
+                                         c_void_p]
+        L.ref_decoder_decode_batch_mt.restype = c_double
+        L.ref_decoder_decode_batch_mt.argtypes = [c_char_p, c_uint, c_uint, c_int, c_int, c_uint, c_int, c_uint,
+                                                  c_float, c_void_p, c_uint, c_uint, c_void_p, c_uint, c_void_p]
+        L.ref_dematcher_create.restype = c_void_p
+        L.ref_dematcher_create.argtypes = [c_char_p]
+        L.ref_dematcher_destroy.argtypes = [c_void_p]
+        L.ref_dematcher_run.argtypes = [c_void_p, c_void_p, c_uint, c_void_p, c_uint, c_int, c_int, c_int, c_int,
+                                        c_int, c_uint, c_uint]
+        L.ref_encode.argtypes = [c_char_p, c_int, c_int, c_void_p, c_void_p, c_uint]
+        L.ref_rate_match.argtypes = [c_void_p, c_uint, c_void_p, c_uint, c_int, c_int, c_int, c_int, c_uint, c_uint]
+        L.ref_segment_rx.argtypes = [c_uint, c_int, c_int, c_int, c_uint, c_uint, c_uint, c_void_p]
+        L.ref_segment_tx.argtypes = [c_void_p, c_uint, c_int, c_int, c_int, c_uint, c_uint, c_uint, c_void_p, c_uint]
+        L.ref_pusch_create.restype = c_void_p
+        L.ref_pusch_create.argtypes = [c_char_p, c_char_p, c_uint, c_uint, c_uint]
+        L.ref_pusch_destroy.argtypes = [c_void_p]
+        L.ref_pusch_decode.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_int,
+                                       c_int, c_int, c_uint, c_uint, c_uint, c_int, c_int, c_int, c_void_p]
+        self._decoders = {}
+        self._dematchers = {}
+
+    def supports(self, kind):
+        return bool(self.lib.ref_cpu_supports(kind.encode()))
+
+    def llr_add(self, a, b):
+        return self.lib.ref_llr_add(int(a), int(b))
+
+    def llr_sub(self, a, b):
+        return self.lib.ref_llr_sub(int(a), int(b))
+
+    def llr_promotion_sum(self, a, b):
+        return self.lib.ref_llr_promotion_sum(int(a), int(b))
+
+    def quantize(self, v, rng):
+        return self.lib.ref_llr_quantize(float(v), float(rng))
+
+    def hard_decision(self, soft):
+        soft = np.ascontiguousarray(soft, np.int8)
+        out = np.zeros((soft.size + 7) // 8, np.uint8)
+        self.lib.ref_hard_decision(_ptr(soft), soft.size, _ptr(out))
+        return out
+
+    def crc(self, poly, packed, nbits, impl="auto"):
+        packed = np.ascontiguousarray(packed, np.uint8)
+        return self.lib.ref_crc_packed(impl.encode(), poly, _ptr(packed), nbits)
+
+    def graph(self, bg, Z):
+        M, N = BG_M[bg], BG_K[bg] + BG_M[bg]
+        pcm = np.zeros((M, N), np.uint16)
+        adj = np.zeros((M, 20), np.uint16)
+        self.lib.ref_graph_dump(bg, Z, _ptr(pcm), _ptr(adj))
+        return pcm, adj
+
+    def decode(self, bg, Z, llrs, fillers=0, crc=CRC_NONE, max_iters=6, sf=0.8, kind="generic", fresh=True,
+               out_init=0):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.full((BG_K[bg] * Z + 7) // 8, out_init, np.uint8)
+        if fresh:
+            h = self.lib.ref_decoder_create(kind.encode())
+        else:
+            h = self._decoders.get(kind) or self._decoders.setdefault(kind, self.lib.ref_decoder_create(kind.encode()))
+        assert h, "reference decoder type %s unavailable" % kind
+        it = self.lib.ref_decoder_decode(h, bg, Z, fillers, crc, max_iters, sf, _ptr(llrs), llrs.size, _ptr(out))
+        if fresh:
+            self.lib.ref_decoder_destroy(h)
+        return out, it
+
+    def decode_batch_mt(self, kind, nthreads, bg, Z, llrs2d, fillers=0, crc=CRC_NONE, max_iters=6, sf=0.8):
+        llrs2d = np.ascontiguousarray(llrs2d, np.int8)
+        ncb, n = llrs2d.shape
+        kb = (BG_K[bg] * Z + 7) // 8
+        out = np.zeros((ncb, kb), np.uint8)
+        iters = np.zeros(ncb, np.int32)
+        secs = self.lib.ref_decoder_decode_batch_mt(kind.encode(), nthreads, ncb, bg, Z, fillers, crc, max_iters, sf,
+                                                    _ptr(llrs2d), n, n, _ptr(out), kb, _ptr(iters))
+        assert secs >= 0, "reference decoder type %s unavailable" % kind
+        return secs, out, iters
+
+    def rate_dematch(self, soft, llrs, new_data, bg, Z, rv=0, Qm=1, Nref=0, fillers=0, kind="generic"):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        assert soft.dtype == np.int8 and soft.flags.c_contiguous
+        h = self._dematchers.get(kind) or self._dematchers.setdefault(kind,
+                                                                      self.lib.ref_dematcher_create(kind.encode()))
+        assert h
+        self.lib.ref_dematcher_run(h, _ptr(soft), soft.size, _ptr(llrs), llrs.size, int(new_data), bg, Z, rv, Qm, Nref,
+                                   fillers)
+        return soft
+
+    def encode(self, bg, Z, msg_bits, out_len=None, kind="auto"):
+        msg_bits = np.ascontiguousarray(msg_bits, np.uint8)
+        out_len = BG_N_SHORT[bg] * Z if out_len is None else out_len
+        out = np.zeros(out_len, np.uint8)
+        r = self.lib.ref_encode(kind.encode(), bg, Z, _ptr(msg_bits), _ptr(out), out_len)
+        assert r == 0
+        return out
+
+    def rate_match(self, cw, E, bg, Z, rv=0, Qm=1, Nref=0, fillers=0):
+        cw = np.ascontiguousarray(cw, np.uint8)
+        out = np.zeros(E, np.uint8)
+        self.lib.ref_rate_match(_ptr(out), E, _ptr(cw), cw.size, bg, Z, rv, Qm, Nref, fillers)
+        return out
+
+    def segment_rx(self, tbs, bg, Qm, nof_layers, nof_ch_symbols, rv=0, Nref=0):
+        meta = np.zeros((52, 6), np.uint32)
+        C = self.lib.ref_segment_rx(tbs, bg, rv, Qm, Nref, nof_layers, nof_ch_symbols, _ptr(meta))
+        return None if C < 0 else meta[:C].copy()
+
+    def segment_tx(self, tb_bytes, bg, Qm, nof_layers, nof_ch_symbols, rv=0, Nref=0):
+        tb_bytes = np.ascontiguousarray(tb_bytes, np.uint8)
+        segs = np.zeros((52, 8448), np.uint8)
+        C = self.lib.ref_segment_tx(_ptr(tb_bytes), tb_bytes.size, bg, rv, Qm, Nref, nof_layers, nof_ch_symbols,
+                                    _ptr(segs), 8448)
+        return None if C < 0 else segs[:C].copy()
+
+
+_port = None
+_ref = None
+_ref_tried = False
+
+
+def port():
+    global _port
+    if _port is None:
+        _port = PortOracle()
+    return _port
+
+
+def ref():
+    """Returns the compiled-reference oracle or None when oracle/_ref was never built (no /root/reference)."""
+    global _ref, _ref_tried
+    if not _ref_tried:
+        _ref_tried = True
+        path = os.path.join(ORACLE_DIR, "_ref", "libsrsran_ref.so")
+        if os.path.exists(path):
+            try:
+                _ref = RefOracle(path)
+            except OSError:
+                _ref = None
+    return _ref
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Synthetic signals.
+def quantize_llr(x, range_limit):
+    """log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip, scale to +-120, std::round (half away)."""
+    x = np.clip(np.asarray(x, np.float32), -range_limit, range_limit) / np.float32(range_limit) * np.float32(120)
+    return (np.sign(x) * np.floor(np.abs(x) + np.float32(0.5))).astype(np.int8)
+
+
+def random_message(rng, bg, Z, fillers=0):
+    K = BG_K[bg] * Z
+    msg = rng.integers(0, 2, K).astype(np.uint8)
+    if fillers:
+        msg[K - fillers:] = 254
+    return msg
+
+
+def attach_crc(msg, poly, fillers=0):
+    """Overwrites the last CRC_BITS[poly] payload bits (before the fillers) with the CRC of what precedes them."""
+    nb = CRC_BITS[poly]
+    K = msg.size - fillers
+    payload = msg[:K - nb]
+    packed = np.packbits(payload)
+    c = port().crc(poly, packed, payload.size)
+    msg[K - nb:K] = [(c >> (nb - 1 - i)) & 1 for i in range(nb)]
+    return msg
+
+
+def awgn_llrs(rng, code_bits, esn0_db, range_limit=20.0):
+    """BPSK (0 -> +1) over AWGN, LLR = 2y/sigma^2 quantised to int8 as SURVEY.md 8(d) cfg 1. Filler (254) -> +127."""
+    code_bits = np.asarray(code_bits)
+    sigma2 = 10.0 ** (-esn0_db / 10.0) / 2.0
+    s = 1.0 - 2.0 * (code_bits & 1).astype(np.float32)
+    y = s + rng.normal(0.0, np.sqrt(sigma2), code_bits.shape).astype(np.float32)
+    llr = quantize_llr(2.0 * y / sigma2, range_limit)
+    llr[code_bits == 254] = 127
+    return llr
+
+
+def make_codeword(rng, bg, Z, fillers=0, crc=CRC_NONE):
+    msg = random_message(rng, bg, Z, fillers)
+    if crc != CRC_NONE:
+        attach_crc(msg, crc, fillers)
+    cw = port().encode(bg, Z, msg)
+    return msg, cw
+
+
+def msg_to_packed(msg):
+    return np.packbits(np.where(msg == 254, 0, msg).astype(np.uint8))
