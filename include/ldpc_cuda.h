@@ -1,0 +1,217 @@
+/*
+ * ldpc_cuda.h - C ABI of the B200 (sm_100a) PUSCH LDPC receive chain: rate dematching with HARQ soft combining,
+ * layered normalised min-sum decoding of 3GPP BG1/BG2 over all 51 lifting sizes, CRC16/24A/24B early stop.
+ *
+ * This is the drop-in boundary. The entry points are exactly what a "cuda" variant of the reference's factories binds
+ * (paths relative to the srsRAN Project 23.5 tree):
+ *
+ *   ldpc_cuda_decode           <->  ldpc_decoder::decode
+ *                                   include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:44-74
+ *                                   (lib/phy/upper/channel_coding/ldpc/ldpc_decoder_impl.cpp:60-146)
+ *   ldpc_cuda_rate_dematch     <->  ldpc_rate_dematcher::rate_dematch
+ *                                   include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:52-55
+ *                                   (lib/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher_impl.cpp:43-198)
+ *   ldpc_cuda_create/destroy   <->  ldpc_decoder_factory::create / ldpc_rate_dematcher_factory::create
+ *                                   include/srsran/phy/upper/channel_coding/channel_coding_factories.h:52-77
+ *   ldpc_cuda_decode_batch*    <->  the per-codeblock loop of pusch_decoder_impl::decode
+ *                                   lib/phy/upper/channel_processors/pusch_decoder_impl.cpp:156-201
+ *                                   (rate_dematch :182, decode_cblk :94-118/:186, CRC flags :188-195) - new batched entry
+ *   ldpc_cuda_softbuffer_*     <->  rx_softbuffer::get_codeblock_soft_bits / get_codeblocks_crc storage
+ *                                   include/srsran/phy/upper/rx_softbuffer.h:42-72 (HBM-resident equivalent)
+ *   ldpc_cuda_segment          <->  ldpc_segmenter_rx::segment geometry
+ *                                   lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_impl.cpp:226-308 (no 52-CB cap)
+ *
+ * Conventions
+ *   - Plain C, no CUDA or torch types. "_d" suffix = device pointer on the handle's device; everything else is host
+ *     memory owned by the caller, not retained after the call returns.
+ *   - LLRs are int8 in {-127} u [-120,120] u {127} (log_likelihood_ratio, log_likelihood_ratio.h:234,239).
+ *   - Hard bits are packed MSB first: bit i -> byte i/8, mask 0x80 >> (i%8) (bit_buffer, adt/bit_buffer.h:95-139).
+ *   - Error convention: the reference asserts/aborts on invalid arguments and has no error codes
+ *     (support/srsran_assert.h:60-105). The C ABI returns 0 on success and a negative ldpc_cuda_status otherwise; the C++
+ *     adaptor (srsran_project_23.5_b200/host) turns a non-zero status into the reference's assert/abort. A decode that does
+ *     not pass its CRC is NOT an error: it is reported as data (iterations == 0 <-> nullopt).
+ *   - There is no CPU fallback: every compute entry point fails with LDPC_CUDA_ERR_CUDA if no sm_100 device is usable.
+ *   - A handle is not thread-safe (same as one reference decoder object); use one handle per host thread / per GPU.
+ */
+#ifndef LDPC_CUDA_H
+#define LDPC_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LDPC_CUDA_ABI_VERSION 1
+
+typedef struct ldpc_cuda_handle ldpc_cuda_handle;
+
+typedef enum {
+  LDPC_CUDA_OK            = 0,
+  LDPC_CUDA_ERR_ARG       = -1, /* invalid argument (where the reference would assert) */
+  LDPC_CUDA_ERR_CUDA      = -2, /* CUDA runtime error, no device, or not an sm_100 device */
+  LDPC_CUDA_ERR_CAPACITY  = -3, /* batch larger than the handle was created for */
+  LDPC_CUDA_ERR_UNSUPPORTED = -4
+} ldpc_cuda_status;
+
+/* CRC polynomials the PUSCH decoder can hand to the LDPC decoder (pusch_decoder_impl.cpp:44-56 select_crc). */
+typedef enum { LDPC_CUDA_CRC_NONE = 0, LDPC_CUDA_CRC16 = 1, LDPC_CUDA_CRC24A = 2, LDPC_CUDA_CRC24B = 3 } ldpc_cuda_crc;
+
+/* Check-to-variable scaling arithmetic. GENERIC is the parity target (ldpc_decoder_generic.cpp:80-89:
+ * round(float(m)*sf)); AVX reproduces avx2_support.h:82-91 / avx512_support.h:82-91 ((m*uint16(sf*65536))>>16);
+ * NEON reproduces neon_support.h:73-86 ((m*uint8(sf*256))>>8). */
+typedef enum { LDPC_CUDA_SCALE_GENERIC = 0, LDPC_CUDA_SCALE_AVX = 1, LDPC_CUDA_SCALE_NEON = 2 } ldpc_cuda_scale_mode;
+
+/* Decoder algorithm parameters = ldpc_decoder::configuration::algorithm_details (ldpc_decoder.h:46-51) + scale mode. */
+typedef struct {
+  uint32_t max_iterations; /* > 0, default 6 */
+  float    scaling_factor; /* in (0,1), default 0.8f */
+  uint32_t scale_mode;     /* ldpc_cuda_scale_mode */
+  uint32_t reserved;
+} ldpc_cuda_algorithm;
+
+/* One codeblock = codeblock_metadata (include/srsran/phy/upper/codeblock_metadata.h:38-73) reduced to what the path
+ * reads, plus the buffer locations for the batched entries. */
+typedef struct {
+  uint8_t  base_graph;      /* 1 or 2                                   tb_common.base_graph   */
+  uint8_t  crc_poly;        /* ldpc_cuda_crc used for early stop / check; NONE = run max_iterations, no check */
+  uint8_t  rv;              /* 0..3                                     tb_common.rv       (dematch) */
+  uint8_t  mod_order;       /* bits per symbol Qm: 1, 2, 4, 6, 8        tb_common.mod      (dematch) */
+  uint16_t lifting_size;    /* Z, one of the 51 sizes                   tb_common.lifting_size */
+  uint16_t nof_filler_bits; /* F                                        cb_specific.nof_filler_bits */
+  uint32_t Nref;            /* LBRM buffer limit, 0 = none              tb_common.Nref     (dematch) */
+  uint32_t rm_length;       /* E: rate-matched LLRs of this codeblock   cb_specific.rm_length (dematch) */
+  uint32_t in_length;       /* decode-only entries: number of input LLRs, (bg_K+2)Z <= in_length <= N_short*Z */
+  uint8_t  new_data;        /* 1: first transmission (copy), 0: retransmission (combine)   (dematch) */
+  uint8_t  skip_decode;     /* 1: CRC already OK from an earlier transmission - dematch/combine only
+                               (pusch_decoder_impl.cpp:184) */
+  uint8_t  early_stop;      /* 1: check the CRC after every iteration; 0: run max_iterations then check once
+                               (pusch_decoder_impl.cpp:104-117). Ignored when crc_poly == NONE. */
+  uint8_t  reserved;
+  uint64_t in_offset;       /* byte offset of this codeblock's input LLRs inside the batch input buffer */
+  uint64_t soft_offset;     /* byte offset of its N_short*Z soft buffer inside the soft-buffer arena (fused entries) */
+  uint64_t out_offset;      /* byte offset of its ceil(bg_K*Z/8) output bytes inside the batch output buffer */
+} ldpc_cuda_cb_desc;
+
+/* Per-codeblock result = optional<unsigned> of ldpc_decoder::decode + the CRC flag the PUSCH decoder keeps. */
+typedef struct {
+  uint16_t iterations; /* iterations run; with a CRC: value of the optional when crc_ok, else max_iterations run */
+  uint8_t  crc_ok;     /* 1 iff the optional has a value */
+  uint8_t  flags;      /* bit0: all-zero input shortcut taken (ldpc_decoder_impl.cpp:88-94) */
+} ldpc_cuda_cb_result;
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Life cycle.
+ */
+int         ldpc_cuda_abi_version(void);
+const char* ldpc_cuda_status_string(int status);
+/* Number of usable sm_100 devices (0 when there is none / no driver). Never fails. */
+int         ldpc_cuda_device_count(void);
+
+/* device: CUDA ordinal. max_codeblocks: largest batch a single call may carry (device scratch and pinned staging are
+ * sized for it: max_codeblocks * (25344 + 1056 + descriptors) bytes). */
+int  ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblocks, uint32_t flags);
+void ldpc_cuda_destroy(ldpc_cuda_handle* handle);
+int  ldpc_cuda_set_algorithm(ldpc_cuda_handle* handle, const ldpc_cuda_algorithm* alg);
+/* The handle's CUDA stream as an opaque pointer (cudaStream_t) so callers can order their own work after it. */
+void* ldpc_cuda_stream(ldpc_cuda_handle* handle);
+int   ldpc_cuda_synchronize(ldpc_cuda_handle* handle);
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches claim). */
+uint64_t ldpc_cuda_launch_count(const ldpc_cuda_handle* handle);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Drop-in, one codeblock per call, host buffers, synchronous (what the reference interfaces need).
+ */
+
+/* ldpc_decoder::decode. llrs: desc->in_length int8. out_bits: ceil(bg_K*Z/8) bytes, in/out (left untouched where the
+ * reference leaves it untouched: all-zero input with a CRC). *iterations = N >= 1 when the CRC passed after N iterations
+ * (optional has a value), 0 otherwise (nullopt). Uses desc->{base_graph,lifting_size,nof_filler_bits,crc_poly,in_length};
+ * early stop is always on when crc_poly != NONE, as in the reference interface. */
+int ldpc_cuda_decode(ldpc_cuda_handle*        handle,
+                     const ldpc_cuda_cb_desc* desc,
+                     const int8_t*            llrs,
+                     uint8_t*                 out_bits,
+                     uint32_t*                iterations);
+
+/* ldpc_rate_dematcher::rate_dematch. soft_inout: N_short*Z int8, persistent HARQ buffer (in/out). in: desc->rm_length
+ * int8. Uses desc->{base_graph,lifting_size,nof_filler_bits,rv,mod_order,Nref,rm_length,new_data}. */
+int ldpc_cuda_rate_dematch(ldpc_cuda_handle* handle, const ldpc_cuda_cb_desc* desc, int8_t* soft_inout, const int8_t* in);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Batched entries. All codeblocks of a call may differ in every descriptor field; internally they are grouped by
+ * (base_graph, lifting_size) and each group is one kernel launch.
+ */
+
+/* Decode-only, HOST buffers: H2D of descriptors + LLRs, kernels, D2H of bits + results, all inside the call. */
+int ldpc_cuda_decode_batch(ldpc_cuda_handle*        handle,
+                           uint32_t                 nof_codeblocks,
+                           const ldpc_cuda_cb_desc* descs,
+                           const int8_t*            llrs,     /* base; codeblock i at llrs + descs[i].in_offset */
+                           uint8_t*                 out_bits, /* base; codeblock i at out_bits + descs[i].out_offset */
+                           ldpc_cuda_cb_result*     results);
+
+/* Decode-only, DEVICE buffers, asynchronous on the handle's stream. descs are host memory (copied at enqueue);
+ * results_d / out_bits_d / llrs_d are device memory. Call ldpc_cuda_synchronize (or use the stream) before reading. */
+int ldpc_cuda_decode_batch_device(ldpc_cuda_handle*        handle,
+                                  uint32_t                 nof_codeblocks,
+                                  const ldpc_cuda_cb_desc* descs,
+                                  const int8_t*            llrs_d,
+                                  uint8_t*                 out_bits_d,
+                                  ldpc_cuda_cb_result*     results_d);
+
+/* Fused rate-dematch (+HARQ combine) + decode + CRC, soft buffers resident in a device arena (see below).
+ * HOST input/output: rm_llrs = rate-matched LLRs (codeblock i: descs[i].rm_length bytes at in_offset). For each
+ * codeblock: dematch/combine into arena[soft_offset .. +N_short*Z) exactly as rate_dematch would, then (unless
+ * skip_decode) decode from that soft buffer. */
+int ldpc_cuda_dematch_decode_batch(ldpc_cuda_handle*        handle,
+                                   uint32_t                 nof_codeblocks,
+                                   const ldpc_cuda_cb_desc* descs,
+                                   const int8_t*            rm_llrs,
+                                   uint8_t*                 out_bits,
+                                   ldpc_cuda_cb_result*     results);
+/* Same, DEVICE input/output, asynchronous on the handle's stream. */
+int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle*        handle,
+                                          uint32_t                 nof_codeblocks,
+                                          const ldpc_cuda_cb_desc* descs,
+                                          const int8_t*            rm_llrs_d,
+                                          uint8_t*                 out_bits_d,
+                                          ldpc_cuda_cb_result*     results_d);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,
+ * rx_softbuffer_codeblock_pool.h). Offsets in ldpc_cuda_cb_desc::soft_offset index into it.
+ */
+int ldpc_cuda_softbuffer_reserve(ldpc_cuda_handle* handle, uint64_t nof_bytes); /* (re)allocates and zeroes */
+int ldpc_cuda_softbuffer_zero(ldpc_cuda_handle* handle, uint64_t offset, uint64_t nof_bytes);
+int ldpc_cuda_softbuffer_read(ldpc_cuda_handle* handle, uint64_t offset, int8_t* dst, uint64_t nof_bytes);
+int ldpc_cuda_softbuffer_write(ldpc_cuda_handle* handle, uint64_t offset, const int8_t* src, uint64_t nof_bytes);
+/* Device address of the arena (NULL before reserve). */
+void* ldpc_cuda_softbuffer_ptr(ldpc_cuda_handle* handle);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Host-side geometry helpers (no GPU needed).
+ */
+
+/* TB -> codeblock geometry of ldpc_segmenter_rx::segment. Fills up to max_cbs descriptors (base_graph, lifting_size,
+ * nof_filler_bits, rm_length, mod_order, rv, Nref, crc_poly per pusch_decoder_impl.cpp:44-56, in_offset = cw_offset);
+ * nof_crc_bits_out (optional) receives cb_specific.nof_crc_bits. Returns the number of codeblocks C (> 0) or a negative
+ * status; when C > max_cbs nothing is written and C is still returned. */
+int ldpc_cuda_segment(uint32_t           tbs_bits,
+                      int                base_graph,
+                      int                rv,
+                      int                mod_order,
+                      uint32_t           Nref,
+                      uint32_t           nof_layers,
+                      uint32_t           nof_ch_symbols,
+                      ldpc_cuda_cb_desc* descs,
+                      uint32_t           max_cbs,
+                      uint32_t*          nof_crc_bits_out);
+
+/* Circulant shift of base-graph edge (row m, column n) for lifting size Z, or -1 when there is no edge. */
+int ldpc_cuda_graph_shift(int base_graph, int lifting_size, int m, int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LDPC_CUDA_H */
