@@ -109,6 +109,9 @@ const char* ldpc_cuda_status_string(int status);
 /* Number of usable sm_100 devices (0 when there is none / no driver). Never fails. */
 int         ldpc_cuda_device_count(void);
 
+/* flags for ldpc_cuda_create */
+#define LDPC_CUDA_FLAG_FORCE_SCALAR 1u /* always use the general one-lane-per-thread kernel (cross-check / debugging) */
+
 /* device: CUDA ordinal. max_codeblocks: largest batch a single call may carry (device scratch and pinned staging are
  * sized for it: max_codeblocks * (25344 + 1056 + descriptors) bytes). */
 int  ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblocks, uint32_t flags);

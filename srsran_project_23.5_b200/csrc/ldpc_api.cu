@@ -1,0 +1,586 @@
+// C ABI of the B200 LDPC receive chain (include/ldpc_cuda.h): handle life cycle, batching/grouping, launches.
+// No CPU fallback: every compute entry point needs an sm_100 device and fails with LDPC_CUDA_ERR_CUDA otherwise.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <new>
+#include <vector>
+
+#include "ldpc_host_util.h"
+#include "ldpc_kernels_scalar.cuh"
+#include "ldpc_dematch.cuh"
+#include "ldpc_kernels_packed.cuh"
+
+using namespace ldpc_b200;
+
+#define CUDA_TRY(expr)                                                                                       \
+  do {                                                                                                       \
+    cudaError_t err__ = (expr);                                                                              \
+    if (err__ != cudaSuccess) {                                                                              \
+      std::fprintf(stderr, "ldpc_cuda: %s failed: %s (%s:%d)\n", #expr, cudaGetErrorString(err__), __FILE__, \
+                   __LINE__);                                                                                \
+      return LDPC_CUDA_ERR_CUDA;                                                                             \
+    }                                                                                                        \
+  } while (0)
+
+struct ldpc_cuda_handle {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  uint32_t max_cbs = 0;
+  uint32_t flags = 0;
+  ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
+  unsigned char scale_lut[121];
+  int packed_scale = PACKED_SCALE_NONE;  // closed-form scaling usable by the packed kernel
+  CbWork* d_work = nullptr;
+  CbWork* h_work = nullptr;  // pinned
+  CbResult* d_results = nullptr;
+  int8_t* d_in = nullptr;
+  size_t d_in_cap = 0;
+  uint8_t* d_out = nullptr;
+  size_t d_out_cap = 0;
+  int8_t* arena = nullptr;
+  size_t arena_bytes = 0;
+  uint64_t launches = 0;
+  std::vector<uint32_t> order;
+  std::vector<uint32_t> group_begin;
+};
+
+namespace {
+
+int usable_device(int device)
+{
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+    return 0;
+  }
+  return prop.major == 10;
+}
+
+int upload_constants()
+{
+  static GraphTables gt;
+  std::memset(&gt, 0, sizeof(gt));
+  std::memcpy(gt.row_ptr[0], LDPC_BG1_ROW_PTR, sizeof(LDPC_BG1_ROW_PTR));
+  std::memcpy(gt.row_ptr[1], LDPC_BG2_ROW_PTR, sizeof(LDPC_BG2_ROW_PTR));
+  std::memcpy(gt.col[0], LDPC_BG1_COL, sizeof(LDPC_BG1_COL));
+  std::memcpy(gt.col[1], LDPC_BG2_COL, sizeof(LDPC_BG2_COL));
+  for (int s = 0; s != LDPC_NOF_LIFTING_SETS; ++s) {
+    std::memcpy(gt.shift[0][s], LDPC_BG1_SHIFT[s], sizeof(LDPC_BG1_SHIFT[s]));
+    std::memcpy(gt.shift[1][s], LDPC_BG2_SHIFT[s], sizeof(LDPC_BG2_SHIFT[s]));
+  }
+  CUDA_TRY(cudaMemcpyToSymbol(c_graphs, &gt, sizeof(gt)));
+  static CrcTables ct;
+  std::memset(&ct, 0, sizeof(ct));
+  for (int code = 1; code <= 3; ++code) {
+    build_crc_tables(code, ct.table[code], ct.pow8[code], 1057);
+    crc_params(code, ct.poly[code], ct.order[code]);
+  }
+  CUDA_TRY(cudaMemcpyToSymbol(c_crc, &ct, sizeof(ct)));
+  return LDPC_CUDA_OK;
+}
+
+int ensure_capacity(ldpc_cuda_handle* h, size_t in_bytes, size_t out_bytes)
+{
+  if (in_bytes > h->d_in_cap) {
+    if (h->d_in) {
+      CUDA_TRY(cudaFree(h->d_in));
+      h->d_in = nullptr, h->d_in_cap = 0;
+    }
+    size_t cap = in_bytes + (in_bytes >> 3) + 4096;
+    CUDA_TRY(cudaMalloc(&h->d_in, cap));
+    h->d_in_cap = cap;
+  }
+  if (out_bytes > h->d_out_cap) {
+    if (h->d_out) {
+      CUDA_TRY(cudaFree(h->d_out));
+      h->d_out = nullptr, h->d_out_cap = 0;
+    }
+    size_t cap = out_bytes + (out_bytes >> 3) + 4096;
+    CUDA_TRY(cudaMalloc(&h->d_out, cap));
+    h->d_out_cap = cap;
+  }
+  return LDPC_CUDA_OK;
+}
+
+// Sort codeblock indices by (base graph, lifting size); every group becomes one launch.
+void group_codeblocks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs)
+{
+  h->order.resize(n);
+  for (uint32_t i = 0; i != n; ++i) {
+    h->order[i] = i;
+  }
+  auto key = [&](uint32_t i) { return (unsigned)descs[i].base_graph * 1024u + descs[i].lifting_size; };
+  bool sorted = true;
+  for (uint32_t i = 1; i < n && sorted; ++i) {
+    sorted = key(i - 1) <= key(i);
+  }
+  if (!sorted) {
+    std::stable_sort(h->order.begin(), h->order.end(), [&](uint32_t a, uint32_t b) { return key(a) < key(b); });
+  }
+  h->group_begin.clear();
+  for (uint32_t i = 0; i != n; ++i) {
+    if (i == 0 || key(h->order[i]) != key(h->order[i - 1])) {
+      h->group_begin.push_back(i);
+    }
+  }
+  h->group_begin.push_back(n);
+}
+
+GroupParams make_group(const ldpc_cuda_handle* h, int bg, int Z)
+{
+  GroupParams gp;
+  std::memset(&gp, 0, sizeof(gp));
+  gp.bg = bg;
+  gp.Z = Z;
+  gp.lifting_set = lifting_set_of(Z);
+  gp.max_iterations = (int)h->alg.max_iterations;
+  std::memcpy(gp.scale_lut, h->scale_lut, sizeof(gp.scale_lut));
+  return gp;
+}
+
+int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_llr,
+                        uint8_t* d_out, CbResult* d_res)
+{
+  GroupParams gp = make_group(h, bg, Z);
+  if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != PACKED_SCALE_NONE) {
+    int rc = launch_packed_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, h->sm_count, h->stream);
+    if (rc == 0) {
+      h->launches += 1;
+      return LDPC_CUDA_OK;
+    }
+    if (rc < 0) {
+      return LDPC_CUDA_ERR_CUDA;
+    }
+    // rc > 0: configuration not covered by the packed kernel -> general kernel below
+  }
+  const size_t smem = scalar_kernel_smem_bytes(bg, Z);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(ldpc_decode_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  const int threads = std::max(32, ((Z + 31) / 32) * 32);
+  const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 8u);
+  ldpc_decode_scalar_kernel<<<grid, threads, smem, h->stream>>>(gp, d_work, n, d_llr, d_out, d_res);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_rm)
+{
+  const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 16u);
+  ldpc_dematch_kernel<<<grid, 256, 0, h->stream>>>(bg, Z, d_work, n, d_rm, h->arena);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+// Fills the pinned work array in group order and uploads it. fused: in_offset = soft_offset, in_length = N.
+int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused)
+{
+  if (n > h->max_cbs) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  for (uint32_t i = 0; i != n; ++i) {
+    const ldpc_cuda_cb_desc& d = descs[i];
+    int rc = fused ? validate_dematch_desc(d) : validate_decode_desc(d);
+    if (rc != LDPC_CUDA_OK) {
+      return rc;
+    }
+    if (fused) {
+      const uint64_t N = (uint64_t)bg_N_short(d.base_graph) * d.lifting_size;
+      if (d.crc_poly > LDPC_CUDA_CRC24B || d.soft_offset + N > h->arena_bytes ||
+          d.nof_filler_bits >= bg_K(d.base_graph) * d.lifting_size) {
+        return LDPC_CUDA_ERR_ARG;
+      }
+    }
+  }
+  group_codeblocks(h, n, descs);
+  for (uint32_t k = 0; k != n; ++k) {
+    const uint32_t i = h->order[k];
+    const ldpc_cuda_cb_desc& d = descs[i];
+    CbWork& w = h->h_work[k];
+    std::memset(&w, 0, sizeof(w));
+    w.in_offset = fused ? d.soft_offset : d.in_offset;
+    w.out_offset = d.out_offset;
+    w.rm_offset = d.in_offset;
+    w.in_length = fused ? bg_N_short(d.base_graph) * d.lifting_size : d.in_length;
+    w.rm_length = d.rm_length;
+    w.Nref = d.Nref;
+    w.nof_filler_bits = d.nof_filler_bits;
+    w.crc_poly = d.crc_poly;
+    w.early_stop = d.early_stop;
+    w.rv = d.rv;
+    w.mod_order = d.mod_order;
+    w.new_data = d.new_data;
+    w.skip_decode = fused ? d.skip_decode : 0;
+    w.result_index = i;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work, sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int run_groups(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused, const int8_t* d_in,
+               uint8_t* d_out, CbResult* d_res)
+{
+  CUDA_TRY(cudaMemsetAsync(d_res, 0, sizeof(CbResult) * n, h->stream));
+  for (size_t g = 0; g + 1 < h->group_begin.size(); ++g) {
+    const uint32_t b = h->group_begin[g], e = h->group_begin[g + 1];
+    const ldpc_cuda_cb_desc& d0 = descs[h->order[b]];
+    int rc;
+    if (fused) {
+      rc = launch_dematch_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in);
+      if (rc != LDPC_CUDA_OK) {
+        return rc;
+      }
+      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, h->arena, d_out, d_res);
+    } else {
+      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, d_out, d_res);
+    }
+    if (rc != LDPC_CUDA_OK) {
+      return rc;
+    }
+  }
+  return LDPC_CUDA_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int ldpc_cuda_abi_version(void) { return LDPC_CUDA_ABI_VERSION; }
+
+const char* ldpc_cuda_status_string(int status)
+{
+  switch (status) {
+    case LDPC_CUDA_OK:
+      return "ok";
+    case LDPC_CUDA_ERR_ARG:
+      return "invalid argument";
+    case LDPC_CUDA_ERR_CUDA:
+      return "CUDA error or no sm_100 device (there is no CPU fallback)";
+    case LDPC_CUDA_ERR_CAPACITY:
+      return "batch exceeds the capacity the handle was created with";
+    case LDPC_CUDA_ERR_UNSUPPORTED:
+      return "unsupported";
+    default:
+      return "unknown status";
+  }
+}
+
+int ldpc_cuda_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int usable = 0;
+  for (int d = 0; d != n; ++d) {
+    usable += usable_device(d);
+  }
+  return usable;
+}
+
+int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblocks, uint32_t flags)
+{
+  if (handle == nullptr || max_codeblocks == 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  *handle = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n || !usable_device(device)) {
+    cudaGetLastError();
+    return LDPC_CUDA_ERR_CUDA;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  ldpc_cuda_handle* h = new (std::nothrow) ldpc_cuda_handle;
+  if (h == nullptr) {
+    return LDPC_CUDA_ERR_CUDA;
+  }
+  h->device = device;
+  h->max_cbs = max_codeblocks;
+  h->flags = flags;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  h->sm_count = prop.multiProcessorCount;
+  int rc = upload_constants();
+  if (rc != LDPC_CUDA_OK) {
+    delete h;
+    return rc;
+  }
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaMalloc(&h->d_work, sizeof(CbWork) * max_codeblocks));
+  CUDA_TRY(cudaMallocHost(&h->h_work, sizeof(CbWork) * max_codeblocks));
+  CUDA_TRY(cudaMalloc(&h->d_results, sizeof(CbResult) * max_codeblocks));
+  ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
+  *handle = h;
+  return ldpc_cuda_set_algorithm(h, &alg);
+}
+
+void ldpc_cuda_destroy(ldpc_cuda_handle* h)
+{
+  if (h == nullptr) {
+    return;
+  }
+  cudaSetDevice(h->device);
+  if (h->stream) {
+    cudaStreamSynchronize(h->stream);
+  }
+  cudaFree(h->d_work);
+  cudaFreeHost(h->h_work);
+  cudaFree(h->d_results);
+  cudaFree(h->d_in);
+  cudaFree(h->d_out);
+  cudaFree(h->arena);
+  if (h->stream) {
+    cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+int ldpc_cuda_set_algorithm(ldpc_cuda_handle* h, const ldpc_cuda_algorithm* alg)
+{
+  // asserts of ldpc_decoder_impl::init, ldpc_decoder_impl.cpp:46-50
+  if (h == nullptr || alg == nullptr || alg->max_iterations == 0 || alg->max_iterations > 65535 ||
+      !(alg->scaling_factor > 0.f && alg->scaling_factor < 1.f) || alg->scale_mode > LDPC_CUDA_SCALE_NEON) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  h->alg = *alg;
+  build_scale_lut(alg->scaling_factor, alg->scale_mode, h->scale_lut);
+  h->packed_scale = packed_scale_variant(h->scale_lut);
+  return LDPC_CUDA_OK;
+}
+
+void* ldpc_cuda_stream(ldpc_cuda_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+int ldpc_cuda_synchronize(ldpc_cuda_handle* h)
+{
+  if (h == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+uint64_t ldpc_cuda_launch_count(const ldpc_cuda_handle* h) { return h ? h->launches : 0; }
+
+// ---- batched, device buffers ----------------------------------------------------------------------------------------
+int ldpc_cuda_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* llrs_d,
+                                  uint8_t* out_bits_d, ldpc_cuda_cb_result* results_d)
+{
+  if (h == nullptr || descs == nullptr || llrs_d == nullptr || out_bits_d == nullptr || results_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  // The pinned work array is reused by every call: wait for the previous upload to be consumed.
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  int rc = stage_work(h, n, descs, false);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  return run_groups(h, n, descs, false, llrs_d, out_bits_d, reinterpret_cast<CbResult*>(results_d));
+}
+
+int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs,
+                                          const int8_t* rm_llrs_d, uint8_t* out_bits_d, ldpc_cuda_cb_result* results_d)
+{
+  if (h == nullptr || descs == nullptr || rm_llrs_d == nullptr || out_bits_d == nullptr || results_d == nullptr ||
+      h->arena == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  int rc = stage_work(h, n, descs, true);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  return run_groups(h, n, descs, true, rm_llrs_d, out_bits_d, reinterpret_cast<CbResult*>(results_d));
+}
+
+// ---- batched, host buffers ------------------------------------------------------------------------------------------
+static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in, uint8_t* out,
+                      ldpc_cuda_cb_result* results, bool fused)
+{
+  if (h == nullptr || descs == nullptr || in == nullptr || out == nullptr || results == nullptr ||
+      (fused && h->arena == nullptr)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  int rc = stage_work(h, n, descs, fused);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  // One H2D for the span of inputs and one D2H for the span of outputs (callers lay codeblocks out densely).
+  uint64_t in_lo = ~0ull, in_hi = 0, out_lo = ~0ull, out_hi = 0;
+  for (uint32_t i = 0; i != n; ++i) {
+    const ldpc_cuda_cb_desc& d = descs[i];
+    const uint64_t len = fused ? d.rm_length : d.in_length;
+    const uint64_t ob = ((uint64_t)bg_K(d.base_graph) * d.lifting_size + 7) / 8;
+    in_lo = std::min(in_lo, d.in_offset), in_hi = std::max(in_hi, d.in_offset + len);
+    out_lo = std::min(out_lo, d.out_offset), out_hi = std::max(out_hi, d.out_offset + ob);
+  }
+  rc = ensure_capacity(h, in_hi - in_lo, out_hi - out_lo);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  if (in_hi > in_lo) {
+    CUDA_TRY(cudaMemcpyAsync(h->d_in, in + in_lo, in_hi - in_lo, cudaMemcpyHostToDevice, h->stream));
+  }
+  // Output bytes a codeblock does not write (skip_decode, all-zero input with a CRC) must keep the caller's contents.
+  bool preserve = false;
+  for (uint32_t i = 0; i != n && !preserve; ++i) {
+    preserve = descs[i].skip_decode || descs[i].crc_poly != LDPC_CUDA_CRC_NONE;
+  }
+  if (preserve) {
+    CUDA_TRY(cudaMemcpyAsync(h->d_out, out + out_lo, out_hi - out_lo, cudaMemcpyHostToDevice, h->stream));
+  }
+  rc = run_groups(h, n, descs, fused, h->d_in - in_lo, h->d_out - out_lo, h->d_results);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(out + out_lo, h->d_out, out_hi - out_lo, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_decode_batch(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* llrs,
+                           uint8_t* out_bits, ldpc_cuda_cb_result* results)
+{
+  return batch_host(h, n, descs, llrs, out_bits, results, false);
+}
+
+int ldpc_cuda_dematch_decode_batch(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* rm_llrs,
+                                   uint8_t* out_bits, ldpc_cuda_cb_result* results)
+{
+  return batch_host(h, n, descs, rm_llrs, out_bits, results, true);
+}
+
+// ---- drop-in single codeblock ---------------------------------------------------------------------------------------
+int ldpc_cuda_decode(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, const int8_t* llrs, uint8_t* out_bits,
+                     uint32_t* iterations)
+{
+  if (desc == nullptr || iterations == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  ldpc_cuda_cb_desc d = *desc;
+  d.in_offset = 0, d.out_offset = 0, d.skip_decode = 0;
+  d.early_stop = 1;  // ldpc_decoder::decode with a CRC calculator always stops early (ldpc_decoder_impl.cpp:125-133)
+  ldpc_cuda_cb_result r = {0, 0, 0};
+  int rc = batch_host(h, 1, &d, llrs, out_bits, &r, false);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  *iterations = r.crc_ok ? r.iterations : 0;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_rate_dematch(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, int8_t* soft_inout, const int8_t* in)
+{
+  if (h == nullptr || desc == nullptr || soft_inout == nullptr || (in == nullptr && desc->rm_length != 0)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  int rc = validate_dematch_desc(*desc);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  const size_t N = (size_t)bg_N_short(desc->base_graph) * desc->lifting_size;
+  rc = ensure_capacity(h, N + desc->rm_length + 64, 16);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  int8_t* d_soft = h->d_in;
+  int8_t* d_rm = h->d_in + ((N + 63) & ~(size_t)63);
+  rc = ensure_capacity(h, ((N + 63) & ~(size_t)63) + desc->rm_length + 64, 16);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  d_soft = h->d_in, d_rm = h->d_in + ((N + 63) & ~(size_t)63);
+  CbWork& w = h->h_work[0];
+  std::memset(&w, 0, sizeof(w));
+  w.rm_length = desc->rm_length, w.Nref = desc->Nref, w.nof_filler_bits = desc->nof_filler_bits;
+  w.rv = desc->rv, w.mod_order = desc->mod_order, w.new_data = desc->new_data;
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work, sizeof(CbWork), cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_soft, soft_inout, N, cudaMemcpyHostToDevice, h->stream));
+  if (desc->rm_length) {
+    CUDA_TRY(cudaMemcpyAsync(d_rm, in, desc->rm_length, cudaMemcpyHostToDevice, h->stream));
+  }
+  ldpc_dematch_kernel<<<1, 256, 0, h->stream>>>(desc->base_graph, desc->lifting_size, h->d_work, 1, d_rm, d_soft);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  CUDA_TRY(cudaMemcpyAsync(soft_inout, d_soft, N, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+// ---- HBM-resident soft-buffer arena ---------------------------------------------------------------------------------
+int ldpc_cuda_softbuffer_reserve(ldpc_cuda_handle* h, uint64_t nof_bytes)
+{
+  if (h == nullptr || nof_bytes == 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (h->arena) {
+    CUDA_TRY(cudaFree(h->arena));
+    h->arena = nullptr, h->arena_bytes = 0;
+  }
+  CUDA_TRY(cudaMalloc(&h->arena, nof_bytes));
+  h->arena_bytes = nof_bytes;
+  // zero-initialised once, like the reference pool (rx_softbuffer_codeblock_pool.h)
+  CUDA_TRY(cudaMemsetAsync(h->arena, 0, nof_bytes, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_softbuffer_zero(ldpc_cuda_handle* h, uint64_t offset, uint64_t nof_bytes)
+{
+  if (h == nullptr || h->arena == nullptr || offset + nof_bytes > h->arena_bytes) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaMemsetAsync(h->arena + offset, 0, nof_bytes, h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_softbuffer_read(ldpc_cuda_handle* h, uint64_t offset, int8_t* dst, uint64_t nof_bytes)
+{
+  if (h == nullptr || h->arena == nullptr || dst == nullptr || offset + nof_bytes > h->arena_bytes) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaMemcpyAsync(dst, h->arena + offset, nof_bytes, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_softbuffer_write(ldpc_cuda_handle* h, uint64_t offset, const int8_t* src, uint64_t nof_bytes)
+{
+  if (h == nullptr || h->arena == nullptr || src == nullptr || offset + nof_bytes > h->arena_bytes) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaMemcpyAsync(h->arena + offset, src, nof_bytes, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+void* ldpc_cuda_softbuffer_ptr(ldpc_cuda_handle* h) { return h ? h->arena : nullptr; }
+
+}  // extern "C"

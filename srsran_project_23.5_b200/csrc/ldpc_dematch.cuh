@@ -1,0 +1,148 @@
+// Rate dematching (bit de-interleave + circular-buffer de-selection + HARQ soft combining) as a closed form per soft-buffer
+// position, so that every position is produced by one independent thread with coalesced soft-buffer traffic.
+//
+// Reference: ldpc_rate_dematcher_impl.cpp:43-110 (rate_dematch), :125-198 (allot_llrs), :113-123 (combine_softbits),
+// :200-254 (deinterleave). allot_llrs walks the circular buffer [0, Ncb) from k0 in "laps": a lap runs from the current
+// index to the end of the buffer, skipping the filler range [info, sys). The first lap copies when new_data is set, every
+// later lap (and every lap of a retransmission) saturating-adds. The literal range operations of the reference - and
+// therefore which bytes keep their PREVIOUS contents - are reproduced exactly (SURVEY.md 8a row R3, quirks i-v):
+//   new data: out[0, min(k0, info)) = 0 (or out[0, info) = 0 when k0 >= info); fillers = +127; positions reached in the
+//   first lap are copied; positions before the start are first reached in lap 1 and ADDED to what is there (0 if zeroed
+//   above, stale otherwise); if the input ends inside the first lap, the LAST (Ncb - idx_end) bytes of the N-long span
+//   are zeroed (not [idx_end, Ncb)); bytes never named keep their contents.
+#pragma once
+
+#include "ldpc_device.cuh"
+
+namespace ldpc_b200 {
+
+struct DematchGeom {
+  unsigned N;      // N_short * Z, soft-buffer length
+  unsigned Ncb;    // circular buffer length
+  unsigned info;   // (bg_K - 2) Z - F : first filler position
+  unsigned sys;    // (bg_K - 2) Z     : first parity position
+  unsigned k0;     // start position
+  unsigned E;      // rate-matched length
+  unsigned Qm;     // bits per symbol
+  unsigned new_data;
+  // derived
+  unsigned s0;     // effective start (k0, or sys when k0 falls in the filler range)
+  unsigned V;      // valid positions per full lap
+  unsigned Ls0;    // linear rank of s0
+  unsigned zero_from;  // new data, input ended in lap 0: [zero_from, N) is zeroed; N when nothing is
+};
+
+__host__ __device__ inline unsigned dematch_linear(const DematchGeom& g, unsigned p)
+{
+  return (p < g.info) ? p : p - (g.sys - g.info);
+}
+
+// k0 = floor(c_rv * Ncb / N) * Z computed in double as the reference does (ldpc_rate_dematcher_impl.cpp:101-102).
+__host__ __device__ inline DematchGeom make_dematch_geom(int bg, unsigned Z, unsigned F, unsigned rv, unsigned Qm,
+                                                         unsigned Nref, unsigned E, unsigned new_data)
+{
+  DematchGeom g;
+  const unsigned n_short = (bg == 2) ? 50 : 66, K = (bg == 2) ? 10 : 22;
+  g.N = n_short * Z;
+  g.Ncb = (Nref > 0) ? (Nref < g.N ? Nref : g.N) : g.N;
+  g.sys = (K - 2) * Z;
+  g.info = g.sys - F;
+  const double f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
+  const double factor = (bg == 2) ? f2[rv & 3] : f1[rv & 3];
+  g.k0 = (unsigned)((unsigned short)floor((factor * g.Ncb) / g.N)) * Z;
+  g.E = E;
+  g.Qm = Qm;
+  g.new_data = new_data;
+  g.s0 = (g.k0 >= g.info && g.k0 < g.sys) ? g.sys : g.k0;
+  g.V = g.info + (g.Ncb - g.sys);
+  g.Ls0 = dematch_linear(g, g.s0);
+  g.zero_from = g.N;
+  if (new_data) {
+    const unsigned lap0 = g.V - g.Ls0;  // positions from s0 to the end of the buffer
+    if (E < lap0 || E == 0) {
+      // index left by steps A-D of the first loop pass (allot_llrs :137-191)
+      unsigned end;
+      if (E == 0) {
+        end = g.k0;  // loop never ran: zero(out.last(Ncb - k0)) when k0 != 0
+      } else if (g.s0 < g.info) {
+        const unsigned n = (g.info - g.s0 < E) ? (g.info - g.s0) : E;  // systematic chunk
+        end = g.sys + (E - n);                                        // then jump to sys and take the rest
+      } else {
+        end = g.s0 + E;
+      }
+      end %= g.Ncb;
+      if (end != 0) {
+        g.zero_from = g.N - (g.Ncb - end);
+      }
+    }
+  }
+  return g;
+}
+
+// De-interleaved input element x (deinterleave_llrs :200-210): aux[(E/Qm) j + i] = in[i Qm + j].
+__device__ __forceinline__ int dematch_input(const DematchGeom& g, const int8_t* __restrict__ in, unsigned x)
+{
+  if (g.Qm == 1) {
+    return in[x];
+  }
+  const unsigned Kq = g.E / g.Qm;
+  const unsigned j = x / Kq, i = x - j * Kq;
+  return in[i * g.Qm + j];
+}
+
+// Final content of soft-buffer position p given its previous content.
+__device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8_t* __restrict__ in, unsigned p, int prev)
+{
+  int v = prev;
+  const bool is_filler = (p >= g.info && p < g.sys);
+  if (g.new_data && g.E != 0) {
+    if (is_filler) {
+      return LLR_INF;
+    }
+    // zeroing done by the first loop pass before it copies
+    if (p < g.info && (g.k0 >= g.info || p < g.k0)) {
+      v = 0;
+    }
+  }
+  if (!is_filler && p < g.Ncb) {
+    const unsigned L = dematch_linear(g, p);
+    const bool before_start = L < g.Ls0;
+    unsigned r = before_start ? (L + g.V - g.Ls0) : (L - g.Ls0);
+    bool first = true;
+    for (; r < g.E; r += g.V) {
+      const int x = dematch_input(g, in, r);
+      if (first && g.new_data && !before_start) {
+        v = x;  // copy in the first lap
+      } else {
+        v = llr_add(v, x);
+      }
+      first = false;
+    }
+  }
+  if (p >= g.zero_from) {
+    v = 0;
+  }
+  return v;
+}
+
+// Standalone kernel: one block per codeblock, threads stride over the N positions (coalesced read-modify-write).
+__global__ void __launch_bounds__(256) ldpc_dematch_kernel(int bg, int Z, const CbWork* __restrict__ work, unsigned nof_cbs,
+                                                            const int8_t* __restrict__ rm_base, int8_t* __restrict__ soft_base)
+{
+  for (unsigned cb = blockIdx.x; cb < nof_cbs; cb += gridDim.x) {
+    const CbWork w = work[cb];
+    const DematchGeom g = make_dematch_geom(bg, (unsigned)Z, w.nof_filler_bits, w.rv, w.mod_order, w.Nref, w.rm_length,
+                                            w.new_data);
+    const int8_t* in = rm_base + w.rm_offset;
+    int8_t* soft = soft_base + w.in_offset;
+    for (unsigned p = threadIdx.x; p < g.N; p += blockDim.x) {
+      const int prev = soft[p];
+      const int v = dematch_position(g, in, p, prev);
+      if (v != prev) {
+        soft[p] = (int8_t)v;
+      }
+    }
+  }
+}
+
+}  // namespace ldpc_b200

@@ -1,0 +1,244 @@
+"""ctypes binding of include/ldpc_cuda.h. Names and argument meaning follow the reference interfaces:
+ldpc_decoder::decode (ldpc_decoder.h:44-74), ldpc_rate_dematcher::rate_dematch (ldpc_rate_dematcher.h:52-55),
+codeblock_metadata (codeblock_metadata.h:38-73). Buffers are numpy arrays (host entries) or raw device pointers
+(device entries, e.g. ``torch.Tensor.data_ptr()``)."""
+import ctypes
+import os
+
+import numpy as np
+
+CRC_NONE, CRC16, CRC24A, CRC24B = 0, 1, 2, 3
+SCALE_GENERIC, SCALE_AVX, SCALE_NEON = 0, 1, 2
+FLAG_FORCE_SCALAR = 1
+
+BG_K = {1: 22, 2: 10}
+BG_N_SHORT = {1: 66, 2: 50}
+
+# numpy mirror of ldpc_cuda_cb_desc (48 bytes) and ldpc_cuda_cb_result (4 bytes)
+CB_DESC = np.dtype([("base_graph", "u1"), ("crc_poly", "u1"), ("rv", "u1"), ("mod_order", "u1"),
+                    ("lifting_size", "<u2"), ("nof_filler_bits", "<u2"), ("Nref", "<u4"), ("rm_length", "<u4"),
+                    ("in_length", "<u4"), ("new_data", "u1"), ("skip_decode", "u1"), ("early_stop", "u1"),
+                    ("reserved", "u1"), ("in_offset", "<u8"), ("soft_offset", "<u8"), ("out_offset", "<u8")],
+                   align=True)
+CB_RESULT = np.dtype([("iterations", "<u2"), ("crc_ok", "u1"), ("flags", "u1")], align=True)
+assert CB_DESC.itemsize == 48 and CB_RESULT.itemsize == 4
+
+
+class LdpcCudaError(RuntimeError):
+    def __init__(self, status, where):
+        self.status = status
+        super().__init__("%s: %s (status %d)" % (where, library().ldpc_cuda_status_string(status).decode(), status))
+
+
+class _Algorithm(ctypes.Structure):
+    _fields_ = [("max_iterations", ctypes.c_uint32), ("scaling_factor", ctypes.c_float),
+                ("scale_mode", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+
+
+_lib = None
+
+
+def library_path():
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libsrsran_ldpc_cuda.so")
+
+
+def library():
+    """Loads the CUDA extension. Fails loudly when it has not been built - there is no fallback path."""
+    global _lib
+    if _lib is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise ImportError("CUDA extension %s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)" % path)
+        L = ctypes.CDLL(path)
+        vp, u32, u64, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_int
+        L.ldpc_cuda_status_string.restype = ctypes.c_char_p
+        L.ldpc_cuda_status_string.argtypes = [i32]
+        L.ldpc_cuda_create.argtypes = [ctypes.POINTER(vp), i32, u32, u32]
+        L.ldpc_cuda_destroy.argtypes = [vp]
+        L.ldpc_cuda_destroy.restype = None
+        L.ldpc_cuda_set_algorithm.argtypes = [vp, ctypes.POINTER(_Algorithm)]
+        L.ldpc_cuda_stream.argtypes = [vp]
+        L.ldpc_cuda_stream.restype = vp
+        L.ldpc_cuda_synchronize.argtypes = [vp]
+        L.ldpc_cuda_launch_count.argtypes = [vp]
+        L.ldpc_cuda_launch_count.restype = u64
+        L.ldpc_cuda_decode.argtypes = [vp, vp, vp, vp, ctypes.POINTER(u32)]
+        L.ldpc_cuda_rate_dematch.argtypes = [vp, vp, vp, vp]
+        for name in ("ldpc_cuda_decode_batch", "ldpc_cuda_decode_batch_device", "ldpc_cuda_dematch_decode_batch",
+                     "ldpc_cuda_dematch_decode_batch_device"):
+            getattr(L, name).argtypes = [vp, u32, vp, vp, vp, vp]
+        L.ldpc_cuda_softbuffer_reserve.argtypes = [vp, u64]
+        L.ldpc_cuda_softbuffer_zero.argtypes = [vp, u64, u64]
+        L.ldpc_cuda_softbuffer_read.argtypes = [vp, u64, vp, u64]
+        L.ldpc_cuda_softbuffer_write.argtypes = [vp, u64, vp, u64]
+        L.ldpc_cuda_softbuffer_ptr.argtypes = [vp]
+        L.ldpc_cuda_softbuffer_ptr.restype = vp
+        L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
+        L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
+        _lib = L
+    return _lib
+
+
+def device_count():
+    return library().ldpc_cuda_device_count()
+
+
+def graph_shift(bg, Z, m, n):
+    return library().ldpc_cuda_graph_shift(bg, Z, m, n)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def segment(tbs, bg, mod_order, nof_layers, nof_ch_symbols, rv=0, Nref=0):
+    """ldpc_segmenter_rx::segment geometry. Returns (descs[C], nof_crc_bits[C])."""
+    L = library()
+    C = L.ldpc_cuda_segment(tbs, bg, rv, mod_order, Nref, nof_layers, nof_ch_symbols, None, 0, None)
+    if C <= 0:
+        raise LdpcCudaError(C, "ldpc_cuda_segment")
+    descs = np.zeros(C, CB_DESC)
+    crc_bits = np.zeros(C, np.uint32)
+    L.ldpc_cuda_segment(tbs, bg, rv, mod_order, Nref, nof_layers, nof_ch_symbols, _ptr(descs), C, _ptr(crc_bits))
+    return descs, crc_bits
+
+
+def make_descs(n, bg, Z, **fields):
+    """n descriptors of one (base graph, lifting size) with dense default offsets for decode-only batches."""
+    d = np.zeros(n, CB_DESC)
+    d["base_graph"], d["lifting_size"] = bg, Z
+    d["mod_order"] = 1
+    d["early_stop"] = 1
+    d["new_data"] = 1
+    in_len = fields.get("in_length", BG_N_SHORT[bg] * Z)
+    d["in_length"] = in_len
+    out_bytes = (BG_K[bg] * Z + 7) // 8
+    d["in_offset"] = np.arange(n, dtype=np.uint64) * np.uint64(fields.pop("in_stride", in_len))
+    d["out_offset"] = np.arange(n, dtype=np.uint64) * np.uint64(fields.pop("out_stride", out_bytes))
+    for k, v in fields.items():
+        d[k] = v
+    return d
+
+
+class LdpcCuda:
+    """One handle = one GPU stream + scratch, like one reference decoder/dematcher object (not thread-safe)."""
+
+    def __init__(self, device=0, max_codeblocks=1024, flags=0, max_iterations=6, scaling_factor=0.8,
+                 scale_mode=SCALE_GENERIC):
+        self._L = library()
+        h = ctypes.c_void_p()
+        rc = self._L.ldpc_cuda_create(ctypes.byref(h), device, max_codeblocks, flags)
+        if rc != 0:
+            raise LdpcCudaError(rc, "ldpc_cuda_create")
+        self._h = h
+        self.device = device
+        self.set_algorithm(max_iterations, scaling_factor, scale_mode)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ldpc_cuda_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, where):
+        if rc != 0:
+            raise LdpcCudaError(rc, where)
+
+    def set_algorithm(self, max_iterations=6, scaling_factor=0.8, scale_mode=SCALE_GENERIC):
+        alg = _Algorithm(max_iterations, scaling_factor, scale_mode, 0)
+        self._check(self._L.ldpc_cuda_set_algorithm(self._h, ctypes.byref(alg)), "ldpc_cuda_set_algorithm")
+        self.max_iterations = max_iterations
+
+    @property
+    def stream(self):
+        return self._L.ldpc_cuda_stream(self._h)
+
+    def synchronize(self):
+        self._check(self._L.ldpc_cuda_synchronize(self._h), "ldpc_cuda_synchronize")
+
+    @property
+    def launch_count(self):
+        return self._L.ldpc_cuda_launch_count(self._h)
+
+    # -- drop-in, one codeblock ----------------------------------------------------------------------------------------
+    def decode(self, bg, Z, llrs, fillers=0, crc=CRC_NONE, out=None):
+        """ldpc_decoder::decode. Returns (packed bits, iterations) with iterations == 0 <-> nullopt."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        d = make_descs(1, bg, Z, in_length=llrs.size, nof_filler_bits=fillers, crc_poly=crc)
+        if out is None:
+            out = np.zeros((BG_K[bg] * Z + 7) // 8, np.uint8)
+        it = ctypes.c_uint32(0)
+        self._check(self._L.ldpc_cuda_decode(self._h, _ptr(d), _ptr(llrs), _ptr(out), ctypes.byref(it)),
+                    "ldpc_cuda_decode")
+        return out, it.value
+
+    def rate_dematch(self, soft, llrs, new_data, bg, Z, rv=0, mod_order=1, Nref=0, fillers=0):
+        """ldpc_rate_dematcher::rate_dematch; soft (int8[N_short*Z]) is updated in place."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        assert soft.dtype == np.int8 and soft.flags.c_contiguous and soft.size == BG_N_SHORT[bg] * Z
+        d = make_descs(1, bg, Z, rm_length=llrs.size, rv=rv, mod_order=mod_order, Nref=Nref, nof_filler_bits=fillers,
+                       new_data=int(bool(new_data)))
+        self._check(self._L.ldpc_cuda_rate_dematch(self._h, _ptr(d), _ptr(soft), _ptr(llrs)), "ldpc_cuda_rate_dematch")
+        return soft
+
+    # -- batched -------------------------------------------------------------------------------------------------------
+    def decode_batch(self, descs, llrs, out=None, results=None):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        n = descs.size
+        if out is None:
+            span = int((descs["out_offset"] + (descs["lifting_size"].astype(np.uint64) *
+                                               np.where(descs["base_graph"] == 2, 10, 22).astype(np.uint64) + 7) // 8
+                        ).max()) if n else 0
+            out = np.zeros(span, np.uint8)
+        if results is None:
+            results = np.zeros(n, CB_RESULT)
+        self._check(self._L.ldpc_cuda_decode_batch(self._h, n, _ptr(descs), _ptr(llrs), _ptr(out), _ptr(results)),
+                    "ldpc_cuda_decode_batch")
+        return out, results
+
+    def decode_batch_device(self, descs, llrs_ptr, out_ptr, results_ptr):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_decode_batch_device(self._h, descs.size, _ptr(descs), llrs_ptr, out_ptr,
+                                                          results_ptr), "ldpc_cuda_decode_batch_device")
+
+    def dematch_decode_batch(self, descs, rm_llrs, out, results=None):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        rm_llrs = np.ascontiguousarray(rm_llrs, np.int8)
+        if results is None:
+            results = np.zeros(descs.size, CB_RESULT)
+        self._check(self._L.ldpc_cuda_dematch_decode_batch(self._h, descs.size, _ptr(descs), _ptr(rm_llrs), _ptr(out),
+                                                           _ptr(results)), "ldpc_cuda_dematch_decode_batch")
+        return out, results
+
+    def dematch_decode_batch_device(self, descs, rm_ptr, out_ptr, results_ptr):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_dematch_decode_batch_device(self._h, descs.size, _ptr(descs), rm_ptr, out_ptr,
+                                                                  results_ptr), "ldpc_cuda_dematch_decode_batch_device")
+
+    # -- soft-buffer arena ---------------------------------------------------------------------------------------------
+    def softbuffer_reserve(self, nbytes):
+        self._check(self._L.ldpc_cuda_softbuffer_reserve(self._h, nbytes), "ldpc_cuda_softbuffer_reserve")
+
+    def softbuffer_zero(self, offset, nbytes):
+        self._check(self._L.ldpc_cuda_softbuffer_zero(self._h, offset, nbytes), "ldpc_cuda_softbuffer_zero")
+
+    def softbuffer_read(self, offset, nbytes):
+        dst = np.zeros(nbytes, np.int8)
+        self._check(self._L.ldpc_cuda_softbuffer_read(self._h, offset, _ptr(dst), nbytes), "ldpc_cuda_softbuffer_read")
+        return dst
+
+    def softbuffer_write(self, offset, src):
+        src = np.ascontiguousarray(src, np.int8)
+        self._check(self._L.ldpc_cuda_softbuffer_write(self._h, offset, _ptr(src), src.size),
+                    "ldpc_cuda_softbuffer_write")
+
+    @property
+    def softbuffer_ptr(self):
+        return self._L.ldpc_cuda_softbuffer_ptr(self._h)

@@ -1,0 +1,149 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the plain-C oracle on identical inputs.
+Bar: hard bits, CRC pass/fail and iteration counts bit-exact (integer path). Marked gpu; run on the B200 box."""
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+import oracles as O
+
+pkg = ge.load_package()
+pytestmark = pytest.mark.gpu
+
+VARIANTS = [0, pkg.FLAG_FORCE_SCALAR]
+
+
+@pytest.fixture(scope="module", params=VARIANTS, ids=["auto", "scalar"])
+def dec(request):
+    d = pkg.LdpcCuda(device=0, max_codeblocks=4096, flags=request.param)
+    yield d
+    d.close()
+
+
+def check_decode(dec, bg, Z, llr, fillers=0, crc=O.CRC_NONE, max_iters=6, scale_mode=O.SCALE_GENERIC, out_init=0):
+    dec.set_algorithm(max_iters, 0.8, scale_mode)
+    want_bits, want_it = O.port().decode(bg, Z, llr, fillers=fillers, crc=crc, max_iters=max_iters,
+                                         scale_mode=scale_mode, out_init=out_init)
+    out = np.full((O.BG_K[bg] * Z + 7) // 8, out_init, np.uint8)
+    got_bits, got_it = dec.decode(bg, Z, llr, fillers=fillers, crc=crc, out=out)
+    assert got_it == want_it, (bg, Z, crc, max_iters, got_it, want_it)
+    assert (got_bits == want_bits).all(), (bg, Z, crc, max_iters)
+    return got_bits, got_it
+
+
+@pytest.mark.parametrize("bg", [1, 2])
+def test_decode_all_lifting_sizes(dec, bg):
+    """BASELINE config 2: every (BG, Z); noiseless 1-iteration decode (ldpc_enc_dec_test.cpp:249-279) and a noisy
+    CRC early-stop decode at a shortened length with filler bits."""
+    rng = np.random.default_rng(10 + bg)
+    K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+    for Z in O.LIFTING_SIZES:
+        msg, cw = O.make_codeword(rng, bg, Z)
+        llr = (10 * (1 - 2 * cw.astype(np.int16))).astype(np.int8)
+        for nodes in (K + 2, Ns):
+            bits, _ = check_decode(dec, bg, Z, llr[:nodes * Z], max_iters=1)
+            assert (bits == O.msg_to_packed(msg)).all()
+        F = min(Z - 1, 12) if Z > 3 else 0
+        crc = O.CRC16 if K * Z - F <= 40 else O.CRC24B
+        msg, cw = O.make_codeword(rng, bg, Z, F, crc)
+        noisy = O.awgn_llrs(rng, cw, -1.0 if bg == 1 else -3.5)
+        n = (K + 2 + int(rng.integers(2, Ns - K - 1))) * Z
+        check_decode(dec, bg, Z, noisy[:n], fillers=F, crc=crc, max_iters=6)
+
+
+@pytest.mark.parametrize("bg,Z", [(1, 384), (1, 208), (2, 384), (2, 30)])
+@pytest.mark.parametrize("crc", [O.CRC_NONE, O.CRC16, O.CRC24A, O.CRC24B])
+def test_decode_noisy_iterations_and_rates(dec, bg, Z, crc):
+    rng = np.random.default_rng(1000 * bg + Z + crc)
+    K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+    for esn0, iters, fillers, nodes in [(-1.5, 6, 0, Ns), (-2.5, 10, 28, Ns), (1.5, 1, 0, K + 2), (-4.5, 6, 12, Ns),
+                                        (0.5, 3, 0, K + 9), (-0.8, 6, 0, Ns)]:
+        msg, cw = O.make_codeword(rng, bg, Z, fillers, crc)
+        llr = O.awgn_llrs(rng, cw, esn0 - (2.5 if bg == 2 else 0.0))
+        check_decode(dec, bg, Z, llr[:nodes * Z], fillers=fillers, crc=crc, max_iters=iters)
+
+
+def test_decode_zero_almost_zero_and_untouched_output(dec):
+    for bg, Z in [(1, 384), (2, 7), (1, 22)]:
+        K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+        zero = np.zeros(Ns * Z, np.int8)
+        bits, it = check_decode(dec, bg, Z, zero)  # LDPCDecTestZeroLLR
+        assert it == 0 and (np.unpackbits(bits)[:K * Z] == 1).all()
+        bits, it = check_decode(dec, bg, Z, zero, crc=O.CRC16, out_init=0x5A)  # output left untouched
+        assert it == 0 and (bits == 0x5A).all()
+        x = zero.copy()  # LDPCDecTestAlmostZeroLLR
+        for i in range((K + 2) * Z + 2, Ns * Z, 3):
+            x[i] = 1 if i % 2 == 0 else -1
+        bits, _ = check_decode(dec, bg, Z, x)
+        assert (np.unpackbits(bits)[:K * Z] == 1).all()
+
+
+def test_decode_trailing_zeros_and_ragged_lengths(dec):
+    rng = np.random.default_rng(7)
+    for bg, Z in [(1, 96), (2, 72)]:
+        K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+        msg, cw = O.make_codeword(rng, bg, Z, 0, O.CRC24B)
+        llr = O.awgn_llrs(rng, cw, -1.0 - (2.5 if bg == 2 else 0))
+        for cut in [(K + 8) * Z, (K + 8) * Z + 5, (K + 19) * Z - 1]:
+            x = llr.copy()
+            x[cut:] = 0
+            check_decode(dec, bg, Z, x, crc=O.CRC24B)
+            check_decode(dec, bg, Z, x)
+        for n in [(K + 2) * Z + 1, (K + 18) * Z + 17, Ns * Z - 1]:
+            check_decode(dec, bg, Z, llr[:n], crc=O.CRC24B)
+
+
+def test_decode_saturated_and_infinite_inputs(dec):
+    rng = np.random.default_rng(8)
+    vals = np.array([-127, -120, -119, -60, -1, 0, 1, 60, 119, 120, 127], np.int8)
+    for bg, Z in [(2, 52), (1, 128), (1, 15)]:
+        for _ in range(4):
+            llr = rng.choice(vals, O.BG_N_SHORT[bg] * Z)
+            check_decode(dec, bg, Z, llr, max_iters=4)
+            check_decode(dec, bg, Z, llr, max_iters=4, crc=O.CRC16)
+
+
+def test_decode_avx_and_neon_scaling_modes(dec):
+    rng = np.random.default_rng(9)
+    for bg, Z in [(1, 384), (2, 160)]:
+        msg, cw = O.make_codeword(rng, bg, Z, 0, O.CRC24A)
+        llr = O.awgn_llrs(rng, cw, -1.2 - (2.5 if bg == 2 else 0))
+        for mode in (O.SCALE_AVX, O.SCALE_NEON, O.SCALE_GENERIC):
+            check_decode(dec, bg, Z, llr, crc=O.CRC24A, scale_mode=mode)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+
+
+def test_invalid_arguments_return_status(dec):
+    llr = np.zeros(66 * 384, np.int8)
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.decode(1, 385, llr)  # not a lifting size
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.decode(1, 384, llr[:23 * 384])  # shorter than (bg_K + 2) Z, ldpc_decoder_impl.cpp:78-83
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.set_algorithm(0, 0.8)  # max_iterations > 0
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.set_algorithm(6, 1.0)  # 0 < sf < 1
+    dec.set_algorithm(6, 0.8)
+
+
+RM_CASES = [  # (bg, Z, E, rv, Qm, Nref, fillers): ldpc_rm_test.cpp's spread + the cfg-3 shapes + LBRM quirk triggers
+    (1, 16, 208, 0, 1, 0, 0), (1, 16, 300, 0, 2, 0, 12), (1, 16, 2000, 0, 2, 700, 12), (1, 16, 300, 2, 2, 0, 12),
+    (1, 16, 300, 0, 2, 700, 12), (1, 16, 1200, 1, 4, 0, 28), (1, 16, 1536, 3, 6, 0, 28), (1, 16, 9240, 3, 8, 700, 12),
+    (2, 12, 600, 0, 4, 0, 28), (2, 12, 704, 2, 8, 0, 0), (2, 12, 1200, 1, 6, 430, 12), (1, 384, 8960, 0, 8, 0, 16),
+    (1, 384, 8992, 2, 8, 0, 16), (1, 384, 30000, 0, 6, 0, 0), (1, 384, 30000, 3, 2, 16896, 40),
+    (2, 384, 19200, 1, 1, 0, 300), (1, 16, 0, 1, 2, 0, 4), (1, 16, 4, 3, 2, 0, 0), (1, 16, 1056 - 4, 0, 2, 0, 4),
+]
+
+
+@pytest.mark.parametrize("case", RM_CASES)
+def test_rate_dematch_matches_oracle(dec, case):
+    bg, Z, E, rv, Qm, Nref, F = case
+    rng = np.random.default_rng(abs(hash(case)) % (1 << 31))
+    N = O.BG_N_SHORT[bg] * Z
+    llr_in = rng.integers(-120, 121, E).astype(np.int8)
+    for new_data in (True, False):
+        prior = rng.integers(-120, 121, N).astype(np.int8)  # arbitrary prior contents: stale-byte quirks must match
+        prior[(O.BG_K[bg] - 2) * Z - F:(O.BG_K[bg] - 2) * Z] = 127
+        want, got = prior.copy(), prior.copy()
+        O.port().rate_dematch(want, llr_in, new_data, rv, Qm, Nref, F)
+        dec.rate_dematch(got, llr_in, new_data, bg, Z, rv, Qm, Nref, F)
+        assert (want == got).all(), (case, new_data, np.nonzero(want != got)[0][:10])
