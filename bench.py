@@ -1,0 +1,302 @@
+#!/usr/bin/env python3
+"""bench.py - decoded info-bit throughput of the B200 LDPC receive chain on BASELINE.json's metric/config.
+
+Workload (config 4 of BASELINE.json): 65536 BG1 Z=384 R=1/3 codeblocks per GPU (N=25344 int8 LLRs each, 1.66 GB, larger
+than L2), AWGN-corrupted codewords, max 6 iterations. A step = one pass of the batched decode over that batch.
+  value  : device-resident inputs, CUDA events on the library's stream (fixed 6 iterations, no CRC: workload-independent)
+  e2e    : same through the public C-ABI host entry (pinned host LLRs -> H2D -> decode -> D2H bits + results)
+  extra  : CRC24B early-stop run on the same LLRs (what pusch_decoder drives), reported beside the fixed-6 number
+`--impl reference` times the reference's own CPU decoder (oracle/_ref, all host threads) on a bounded sample.
+One process per GPU under torchrun; codeblocks are independent so ranks share nothing on the data path (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+BG, Z = 1, 384
+K_BITS, N_LLR = 22 * Z, 66 * Z
+OUT_BYTES = K_BITS // 8
+EDGES_BG1 = 316
+ALG_BYTES_PER_CB = N_LLR + OUT_BYTES  # 25344 B in + 1056 B out = 26400 B / codeblock
+INT_OPS_PER_EMU = 20                  # SURVEY.md 8(d) canonical cost of one edge-message update
+METRIC = "LDPC decoded info Gb/s (BG1 Z=384, 6 iters)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--codeblocks", type=int, default=65536, help="codeblocks per GPU per step")
+    ap.add_argument("--esn0", type=float, default=-1.0, help="Es/N0 in dB of the synthetic AWGN channel")
+    ap.add_argument("--max-iters", type=int, default=6)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), float(p.get("sm_max_mhz", 1965.0)), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, 1965.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        reasons = [name for i, name in ((2, "hw_slowdown"), (3, "hw_thermal_slowdown"), (4, "sw_thermal_slowdown"),
+                                        (5, "sw_power_cap")) if any(s[i] == "Active" for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": int(self.samples[0][1]),
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def make_workload_gpu(torch, dev, n_cb, esn0_db, seed):
+    """n_cb AWGN-corrupted BG1 Z=384 codewords as int8 LLRs on the GPU (256 distinct codewords carrying a CRC24B,
+    independent noise per codeblock), quantised as log_likelihood_ratio::quantize(2y/sigma^2, 20)."""
+    import oracles as O
+    rng = np.random.default_rng(seed)
+    n_distinct = 256
+    cws = np.stack([O.make_codeword(rng, BG, Z, 0, O.CRC24B)[1] for _ in range(n_distinct)])
+    cw_d = torch.from_numpy(cws.astype(np.int8)).to(dev)
+    sigma2 = 10.0 ** (-esn0_db / 10.0) / 2.0
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    llr = torch.empty((n_cb, N_LLR), dtype=torch.int8, device=dev)
+    chunk = 4096
+    for b in range(0, n_cb, chunk):
+        e = min(n_cb, b + chunk)
+        idx = torch.arange(b, e, device=dev) % n_distinct
+        s = 1.0 - 2.0 * cw_d[idx].float()
+        y = s + torch.randn(s.shape, generator=g, device=dev) * (sigma2 ** 0.5)
+        x = torch.clamp(2.0 * y / sigma2, -20.0, 20.0) / 20.0 * 120.0
+        llr[b:e] = (torch.sign(x) * torch.floor(torch.abs(x) + 0.5)).to(torch.int8)
+    return llr
+
+
+def make_workload_cpu(n_cb, esn0_db, seed):
+    import oracles as O
+    rng = np.random.default_rng(seed)
+    cws = [O.make_codeword(rng, BG, Z, 0, O.CRC24B)[1] for _ in range(min(n_cb, 64))]
+    return np.stack([O.awgn_llrs(rng, cws[i % len(cws)], esn0_db) for i in range(n_cb)])
+
+
+def cpu_reference_run(llrs, max_iters, reps):
+    """Times the reference decoder (oracle/_ref, fastest variant the host supports, one decoder object per thread,
+    disjoint slices) on `llrs`. Returns (best Gb/s, kind, threads, description)."""
+    import oracles as O
+    ref = O.ref()
+    threads = len(os.sched_getaffinity(0))
+    n = llrs.shape[0]
+    if ref is not None:
+        kind = "avx512" if ref.supports("avx512") else ("avx2" if ref.supports("avx2") else "generic")
+        best = None
+        for _ in range(reps):
+            secs, _, _ = ref.decode_batch_mt(kind, threads, BG, Z, llrs, crc=O.CRC_NONE, max_iters=max_iters)
+            best = secs if best is None else min(best, secs)
+        return n * K_BITS / best / 1e9, "reference", threads, "reference %s decoder, %d threads" % (kind, threads)
+    # oracle/_ref was never built: time the plain-C port, single thread
+    n = min(n, 8)
+    t0 = time.perf_counter()
+    for i in range(n):
+        O.port().decode(BG, Z, llrs[i], max_iters=max_iters)
+    secs = time.perf_counter() - t0
+    return n * K_BITS / secs / 1e9, "port", 1, "plain-C oracle port, 1 thread"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = 2048
+    llrs = make_workload_cpu(sample, args.esn0, 1234)
+    vals = []
+    for step in range(args.warmup + args.steps):
+        gbps, kind, threads, desc = cpu_reference_run(llrs, args.max_iters, 1)
+        if step >= args.warmup:
+            vals.append(gbps)
+    value = float(np.mean(vals))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Gb/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sample * K_BITS / value / 1e6,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": "BG1 Z=384 R=1/3 codeblocks (N=25344 int8 LLRs), AWGN Es/N0=%.1f dB, fixed %d "
+                                   "iterations (no CRC); bounded sample of %d codeblocks per step" %
+                                   (args.esn0, args.max_iters, sample)},
+            "cpu_baseline": {"value": value, "unit": "Gb/s", "cores": threads, "kind": kind,
+                             "sample": "%d codeblocks per step, %s" % (sample, desc)},
+            "e2e": {"value": value, "unit": "Gb/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if pkg.device_count() < 1:
+        raise RuntimeError("bench.py needs an sm_100 GPU: the LDPC path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n_cb = args.codeblocks
+    dec = pkg.LdpcCuda(device=local, max_codeblocks=n_cb, max_iterations=args.max_iters)
+    stream = torch.cuda.ExternalStream(dec.stream, device=dev)
+    llr_d = make_workload_gpu(torch, dev, n_cb, args.esn0, 1000 + rank)
+    out_d = torch.zeros((n_cb, OUT_BYTES), dtype=torch.uint8, device=dev)
+    res_d = torch.zeros((n_cb,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    descs_fixed = pkg.make_descs(n_cb, BG, Z, crc_poly=pkg.CRC_NONE)
+    descs_crc = pkg.make_descs(n_cb, BG, Z, crc_poly=pkg.CRC24B, early_stop=1)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_device(descs, steps):
+        """K launches of the device-resident batch, CUDA events on the library's stream; returns ms (max over ranks)."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        launches0 = dec.launch_count
+        e0.record(stream)
+        for _ in range(steps):
+            dec.decode_batch_device(descs, llr_d.data_ptr(), out_d.data_ptr(), res_d.data_ptr())
+        e1.record(stream)
+        dec.synchronize()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, dec.launch_count - launches0
+
+    # warm-up, then the timed region (fixed 6 iterations, no CRC)
+    timed_device(descs_fixed, max(args.warmup, 3))
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_total, launches = timed_device(descs_fixed, args.steps)
+    clocks = sampler.summary()
+    ms_step = ms_total / args.steps
+    total_bits = float(n_cb) * K_BITS * world
+    value = total_bits / (ms_step * 1e-3) / 1e9
+    kernel_ms = ms_step  # one kernel per step for a single (BG, Z) group: the step IS the dominant kernel
+
+    # CRC24B early-stop variant on the same LLRs (extra, not the headline)
+    timed_device(descs_crc, 1)
+    ms_es, _ = timed_device(descs_crc, args.steps)
+    res_h = res_d.cpu().numpy().view(pkg.CB_RESULT)
+    es = {"value": total_bits / (ms_es / args.steps * 1e-3) / 1e9, "unit": "Gb/s",
+          "mean_iterations": float(res_h["iterations"].mean()), "crc_pass_rate": float(res_h["crc_ok"].mean()),
+          "what": "same LLRs, CRC24B early stop after every iteration (pusch_decoder default), max %d" % args.max_iters}
+
+    # end to end through the public host entry: pinned host LLRs -> H2D -> decode -> D2H bits + results
+    e2e = None
+    if not args.no_e2e:
+        llr_h = torch.empty((n_cb, N_LLR), dtype=torch.int8, pin_memory=True)
+        llr_h.copy_(llr_d)
+        out_h = torch.empty((n_cb, OUT_BYTES), dtype=torch.uint8, pin_memory=True)
+        res_hh = np.zeros(n_cb, pkg.CB_RESULT)
+        torch.cuda.synchronize()
+        for _ in range(2):
+            dec.decode_batch(descs_fixed, llr_h.numpy(), out_h.numpy(), res_hh)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            dec.decode_batch(descs_fixed, llr_h.numpy(), out_h.numpy(), res_hh)
+        barrier()
+        secs = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([secs], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            secs = float(t.item())
+        e2e = {"value": total_bits * args.steps / secs / 1e9, "unit": "Gb/s",
+               "h2d_bytes_per_step": int(n_cb) * N_LLR + n_cb * 48, "d2h_bytes_per_step": int(n_cb) * (OUT_BYTES + 4),
+               "timer": "host wall clock around the synchronous C-ABI call (copies inside)"}
+
+    hbm_peak, sm_max_mhz, peak_src = peaks()
+    alg_bytes = float(n_cb) * ALG_BYTES_PER_CB
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    emu = float(n_cb) * args.max_iters * EDGES_BG1 * Z
+    emu_per_s = emu / (kernel_ms * 1e-3)
+    sm_mhz = clocks.get("sm_mhz") or sm_max_mhz
+    alu_peak = 148 * 64 * sm_mhz * 1e6  # measured: 64 ALU-pipe thread-instr / clk / SM (profiles/r01_pipes_microbench.md)
+    line = {"metric": METRIC, "value": value, "unit": "Gb/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": "65536 BG1 Z=384 R=1/3 codeblocks per GPU (N=25344 int8 LLRs each), AWGN Es/N0=%.1f dB,"
+                                   " fixed %d iterations (no CRC)" % (args.esn0, args.max_iters),
+                       "codeblocks_per_gpu": n_cb, "sharding": "independent codeblocks per rank, no collective",
+                       "l2": "inputs (%.2f GB) larger than L2" % (n_cb * N_LLR / 1e9)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "decode kernel of the (BG1, Z=384) group, %d launch(es) per step" % (launches // args.steps),
+                         "note": "the path is integer-ALU-issue bound, not HBM bound: see roofline_alu"},
+            "roofline_alu": {"emu_per_s": emu_per_s, "int_ops_per_s_canonical": emu_per_s * INT_OPS_PER_EMU,
+                             "alu_pipe_peak_instr_per_s": alu_peak,
+                             "canonical_ops_over_alu_peak": emu_per_s * INT_OPS_PER_EMU / alu_peak},
+            "early_stop": es, "clocks": clocks, "gpu_launches": int(launches)}
+    if e2e is not None:
+        line["e2e"] = e2e
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sample = 2048
+        llrs = llr_d[:sample].cpu().numpy()
+        gbps, kind, threads, desc = cpu_reference_run(llrs, args.max_iters, 3)
+        line["cpu_baseline"] = {"value": gbps, "unit": "Gb/s", "cores": threads, "kind": kind,
+                                "sample": "first %d codeblocks of the same workload, best of 3, %s" % (sample, desc)}
+    if rank == 0:
+        print(json.dumps(line))
+    dec.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
