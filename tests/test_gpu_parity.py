@@ -147,3 +147,70 @@ def test_rate_dematch_matches_oracle(dec, case):
         O.port().rate_dematch(want, llr_in, new_data, rv, Qm, Nref, F)
         dec.rate_dematch(got, llr_in, new_data, bg, Z, rv, Qm, Nref, F)
         assert (want == got).all(), (case, new_data, np.nonzero(want != got)[0][:10])
+
+
+def test_batch_heterogeneous_codeblocks(dec):
+    """Batched entry: codeblocks of different (BG, Z), lengths, fillers, CRCs and early-stop modes in one call,
+    including an all-zero and a saturated codeblock; every codeblock must match the oracle individually."""
+    rng = np.random.default_rng(21)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    shapes = [(1, 384), (2, 384), (1, 384), (1, 56), (2, 56), (1, 384), (1, 384), (2, 20), (1, 384), (1, 56), (1, 384)]
+    llrs, descs, want = [], [], []
+    in_off = out_off = 0
+    for i, (bg, Z) in enumerate(shapes):
+        K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+        crc = [O.CRC24B, O.CRC_NONE, O.CRC24A, O.CRC16][i % 4]
+        F = [0, 12, 5, 0][i % 4] if Z > 20 else 0
+        early = 0 if i % 5 == 4 else 1
+        msg, cw = O.make_codeword(rng, bg, Z, F, crc if crc else O.CRC24B)
+        x = O.awgn_llrs(rng, cw, [-1.2, 0.5, -2.5, 3.0][i % 4] - (2.5 if bg == 2 else 0))
+        n = Ns * Z if i % 3 else (K + 2 + int(rng.integers(2, Ns - K - 1))) * Z
+        x = x[:n].copy()
+        if i == 5:
+            x[:] = 0
+        if i == 8:
+            x = rng.choice(np.array([-127, -120, 0, 1, 120, 127], np.int8), n)
+        d = pkg.make_descs(1, bg, Z, in_length=n, nof_filler_bits=F, crc_poly=crc, early_stop=early)
+        d["in_offset"], d["out_offset"] = in_off, out_off
+        kb = (K * Z + 7) // 8
+        in_off += n
+        out_off += kb
+        llrs.append(x)
+        descs.append(d)
+        if crc and not early:  # decode without CRC for max iterations, then check once (pusch_decoder_impl.cpp:104-117)
+            bits, _ = O.port().decode(bg, Z, x, fillers=F, crc=O.CRC_NONE, out_init=0x33)
+            ok = O.port().crc(crc, bits, K * Z - F) == 0 and x.any()
+            want.append((bits, 6 if x.any() else 0, ok))
+        else:
+            bits, it = O.port().decode(bg, Z, x, fillers=F, crc=crc, out_init=0x33)
+            want.append((bits, it if it else (6 if x.any() else 0), it > 0))
+    descs = np.concatenate(descs)
+    out = np.full(out_off, 0x33, np.uint8)
+    out, res = dec.decode_batch(descs, np.concatenate(llrs), out=out)
+    for i, (bits, it, ok) in enumerate(want):
+        o = int(descs["out_offset"][i])
+        assert (out[o:o + bits.size] == bits).all(), i
+        assert int(res["crc_ok"][i]) == int(ok), i
+        assert int(res["iterations"][i]) == it, (i, res[i], it)
+
+
+def test_batch_many_pairs_iteration_counts(dec):
+    """200 BG1 Z=384 codeblocks around the waterfall: iteration counts differ inside pairs."""
+    rng = np.random.default_rng(22)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    bg, Z, n = 1, 384, 200
+    N = 66 * Z
+    llrs = np.zeros((n, N), np.int8)
+    for i in range(n):
+        msg, cw = O.make_codeword(rng, bg, Z, 0, O.CRC24B)
+        llrs[i] = O.awgn_llrs(rng, cw, -2.2 + 1.6 * (i % 7) / 6)
+    descs = pkg.make_descs(n, bg, Z, crc_poly=pkg.CRC24B)
+    out, res = dec.decode_batch(descs, llrs)
+    kb = 22 * Z // 8
+    its = []
+    for i in range(0, n, 3):
+        bits, it = O.port().decode(bg, Z, llrs[i], crc=O.CRC24B)
+        assert (out[i * kb:(i + 1) * kb] == bits).all(), i
+        assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, i
+        its.append(it)
+    assert len(set(its)) >= 3
