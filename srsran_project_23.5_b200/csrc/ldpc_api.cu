@@ -9,7 +9,7 @@
 #include "ldpc_host_util.h"
 #include "ldpc_kernels_scalar.cuh"
 #include "ldpc_dematch.cuh"
-#include "ldpc_kernels_packed.cuh"  // needs c_crc / crc_warp from the scalar header
+#include "ldpc_kernels_tmem.cuh"  // needs c_crc / crc_warp from the scalar header
 
 using namespace ldpc_b200;
 
@@ -31,7 +31,7 @@ struct ldpc_cuda_handle {
   uint32_t flags = 0;
   ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
   unsigned char scale_lut[121];
-  int packed_scale = PACKED_SCALE_NONE;  // closed-form scaling usable by the packed kernel
+  int packed_scale = TM_SCALE_NONE;  // closed-form scaling usable by the packed (TMEM-message) kernel
   CbWork* d_work = nullptr;
   CbWork* h_work = nullptr;  // pinned
   CbResult* d_results = nullptr;
@@ -41,7 +41,7 @@ struct ldpc_cuda_handle {
   size_t d_out_cap = 0;
   int8_t* arena = nullptr;
   size_t arena_bytes = 0;
-  unsigned* ext_scratch = nullptr;  // packed kernel: extension-node soft values, L2 resident
+  unsigned* pair_counter = nullptr;  // packed kernel: dynamic work distribution
   uint64_t launches = 0;
   std::vector<uint32_t> order;
   std::vector<uint32_t> group_begin;
@@ -144,8 +144,8 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
                         uint8_t* d_out, CbResult* d_res)
 {
   GroupParams gp = make_group(h, bg, Z);
-  if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != PACKED_SCALE_NONE) {
-    int rc = launch_packed_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, h->ext_scratch, h->sm_count, h->stream);
+  if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != TM_SCALE_NONE) {
+    int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, h->pair_counter, h->sm_count, h->stream);
     if (rc == 0) {
       h->launches += 1;
       return LDPC_CUDA_OK;
@@ -317,7 +317,7 @@ int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblo
   CUDA_TRY(cudaMalloc(&h->d_work, sizeof(CbWork) * max_codeblocks));
   CUDA_TRY(cudaMallocHost(&h->h_work, sizeof(CbWork) * max_codeblocks));
   CUDA_TRY(cudaMalloc(&h->d_results, sizeof(CbResult) * max_codeblocks));
-  CUDA_TRY(cudaMalloc(&h->ext_scratch, packed_ext_scratch_words(h->sm_count) * sizeof(unsigned)));
+  CUDA_TRY(cudaMalloc(&h->pair_counter, 64));
   ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
   *handle = h;
   return ldpc_cuda_set_algorithm(h, &alg);
@@ -338,7 +338,7 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
   cudaFree(h->d_in);
   cudaFree(h->d_out);
   cudaFree(h->arena);
-  cudaFree(h->ext_scratch);
+  cudaFree(h->pair_counter);
   if (h->stream) {
     cudaStreamDestroy(h->stream);
   }
@@ -354,17 +354,17 @@ int ldpc_cuda_set_algorithm(ldpc_cuda_handle* h, const ldpc_cuda_algorithm* alg)
   }
   h->alg = *alg;
   build_scale_lut(alg->scaling_factor, alg->scale_mode, h->scale_lut);
-  h->packed_scale = packed_scale_variant(h->scale_lut);
-  if (h->packed_scale != PACKED_SCALE_NONE) {
+  h->packed_scale = tm_scale_variant(h->scale_lut);
+  if (h->packed_scale != TM_SCALE_NONE) {
     // the fp16 closed form must reproduce the reference table for every magnitude, or the general kernel is used
     CUDA_TRY(cudaSetDevice(h->device));
-    const int chk = packed_scale_selfcheck(h->packed_scale, h->scale_lut, h->stream);
+    const int chk = tm_scale_selfcheck(h->packed_scale, h->scale_lut, h->stream);
     if (chk < 0) {
       return LDPC_CUDA_ERR_CUDA;
     }
     if (chk > 0) {
       std::fprintf(stderr, "ldpc_cuda: packed scaling self-check failed, using the general kernel\n");
-      h->packed_scale = PACKED_SCALE_NONE;
+      h->packed_scale = TM_SCALE_NONE;
     }
   }
   return LDPC_CUDA_OK;

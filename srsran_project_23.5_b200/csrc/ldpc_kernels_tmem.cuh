@@ -1,0 +1,780 @@
+// Layered normalised min-sum decoder for sm_100a, "TMEM-message" formulation.
+//
+// Work split: one thread per lifted lane, TWO codeblocks per thread (half2: low half = codeblock A, high half = B; both
+// share base graph and lifting size so addresses, rotations and control flow are common). A thread block holds
+// G = 384 / roundup32(Z) independent codeblock pairs ("groups"), each with its own named barrier.
+//
+// Where the data live (per SM, Z = 384: everything on chip, nothing but the input LLRs and output bits touches HBM):
+//   * a-posteriori soft values of the high-rate nodes (bg_K + 4 columns)            shared memory, half2 per lane
+//   * soft value and check-to-variable message of the extension nodes (one private
+//     lane per row, shift 0)                                                        shared memory, thread-private words
+//   * check-to-variable messages of all other edges (the reference's check_to_var
+//     array, ldpc_decoder_impl.h:204-210), one biased byte per codeblock and edge   TENSOR MEMORY (tcgen05.ld / .st,
+//                                                                                   32x32b shape: one TMEM lane per
+//                                                                                   thread, <= 170 private columns)
+// Keeping the messages explicitly (instead of the compressed min1/min2/index/sign state of the first packed kernel)
+// removes the per-edge reconstruction and the index/sign bookkeeping from the instruction stream, and moving them to
+// TMEM frees shared memory for the extension nodes (no L2 round trips inside an iteration).
+//
+// Arithmetic (bit-exact with lib/phy/upper/channel_coding/ldpc/ldpc_decoder_impl.cpp:116-135 + ldpc_decoder_generic.cpp
+// :30-130 + lib/phy/upper/log_likelihood_ratio.cpp:38-85): all values are integers of magnitude <= 336, exact in fp16;
+// the LLR "infinity" (+-127, sticky) is the fp16 infinity.
+//   v2c   u = soft - c_old                     (inf stays inf)
+//   min1/min2 over |u|, capped at 120 (the reference initialises both to 120 and compares strictly, so values >= 120
+//         never win); computed as a tree of sorted pairs with VIMNMX.U16x2 / VIMNMX3.U16x2 on the (order-preserving)
+//         bit patterns of the non-negative halves
+//   c2v   c_new = sign * (|u| == min1 ? Q(min2) : Q(min1))  == the reference's argmin-index rule, because a tie for
+//         the minimum implies min2 == min1
+//   soft  promote(c_new + clamp(u, +-120)): |sum| > 120 -> +-inf; lanes with u = +-inf keep u
+// Row structure (degrees, columns, shifts) comes from a per-launch table in the kernel parameters (constant bank,
+// uniform loads); the row bodies are instantiated per number of high-rate edges so that the per-edge loops unroll
+// while the code stays small enough for the instruction cache (the first packed kernel unrolled all 316 edges and was
+// instruction-fetch bound, profiles/r01_ncu_packed_v1_summary.txt).
+#pragma once
+
+#include <cuda_fp16.h>
+
+#include "ldpc_device.cuh"
+
+namespace ldpc_b200 {
+
+enum { TM_SCALE_NONE = 0, TM_SCALE_GENERIC_08 = 1, TM_SCALE_AVX_08 = 2 };
+
+constexpr int TM_THREADS = 384;       // threads per block at full occupancy of the TMEM lanes (12 warps)
+constexpr int TM_COLS_PER_WARP = 170; // 512 TMEM columns / 3 warps per lane quadrant
+
+struct __align__(8) TmEdge {
+  unsigned s4;  // 4 * (shift % Z): rotation in bytes
+  unsigned cb;  // byte offset of the column's soft values inside the group's soft array: col * 4 * Z
+};
+
+struct TmemParams {
+  const CbWork* work;
+  const int8_t* llr_base;
+  uint8_t* out_base;
+  CbResult* results;
+  unsigned* pair_counter;  // dynamic distribution of codeblock pairs over the groups of all blocks
+  unsigned nof_cbs;
+  int Z;
+  int Z4;           // 4 * Z
+  int zpad;         // threads per group = roundup32(Z)
+  int groups;       // codeblock pairs processed concurrently by one block
+  int max_iterations;
+  unsigned group_stride;  // bytes of shared memory per group
+  unsigned char rowcls[LDPC_BG1_M];    // per row: 2 * (number of high-rate edges) + (1 if the row has an extension node)
+  unsigned short rowedge[LDPC_BG1_M];  // per row: index of its first entry in edge[]
+  unsigned short rowtm[LDPC_BG1_M];    // per row: first TMEM word (relative to the warp's column block)
+  unsigned short tm_words;             // TMEM words used per thread
+  TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
+};
+
+// ---- small helpers on raw half2 bit patterns -------------------------------------------------------------------------
+namespace tm {
+
+__device__ __forceinline__ __half2 h2(unsigned x) { return *reinterpret_cast<__half2*>(&x); }
+__device__ __forceinline__ unsigned un(__half2 x) { return *reinterpret_cast<unsigned*>(&x); }
+__device__ __forceinline__ unsigned hc(float v) { return un(__float2half2_rn(v)); }
+__device__ __forceinline__ unsigned hadd(unsigned a, unsigned b) { return un(__hadd2(h2(a), h2(b))); }
+__device__ __forceinline__ unsigned hsub(unsigned a, unsigned b) { return un(__hsub2(h2(a), h2(b))); }
+__device__ __forceinline__ unsigned hfma(unsigned a, unsigned b, unsigned c) { return un(__hfma2(h2(a), h2(b), h2(c))); }
+__device__ __forceinline__ unsigned hfma_sat(unsigned a, unsigned b, unsigned c) { return un(__hfma2_sat(h2(a), h2(b), h2(c))); }
+__device__ __forceinline__ unsigned hmin(unsigned a, unsigned b) { return un(__hmin2(h2(a), h2(b))); }
+__device__ __forceinline__ unsigned hmax(unsigned a, unsigned b) { return un(__hmax2(h2(a), h2(b))); }
+// |a| inside the consumer (HMNMX2 / HFMA2 take |R| operands for free)
+__device__ __forceinline__ unsigned hmin_abs(unsigned a, unsigned b) { return un(__hmin2(__habs2(h2(a)), __habs2(h2(b)))); }
+__device__ __forceinline__ unsigned hmax_abs(unsigned a, unsigned b) { return un(__hmax2(__habs2(h2(a)), __habs2(h2(b)))); }
+__device__ __forceinline__ unsigned hadd_sat_abs(unsigned a, unsigned b) { return un(__hadd2_sat(__habs2(h2(a)), h2(b))); }
+__device__ __forceinline__ unsigned hfma_relu_abs(unsigned a, unsigned b, unsigned c)
+{
+  return un(__hfma2_relu(__habs2(h2(a)), h2(b), h2(c)));
+}
+__device__ __forceinline__ unsigned hfma_relu(unsigned a, unsigned b, unsigned c) { return un(__hfma2_relu(h2(a), h2(b), h2(c))); }
+// integer min / max on the two non-negative 16-bit halves (fp16 bit patterns of non-negative values order like integers)
+__device__ __forceinline__ unsigned umin2(unsigned a, unsigned b)
+{
+  unsigned r;
+  asm("min.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned umax2(unsigned a, unsigned b)
+{
+  unsigned r;
+  asm("max.u16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned umin3(unsigned a, unsigned b, unsigned c) { return umin2(umin2(a, b), c); }
+
+__device__ __forceinline__ unsigned lds32(unsigned addr)
+{
+  unsigned r;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts32(unsigned addr, unsigned v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
+__device__ __forceinline__ void group_barrier(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+// ---- tensor memory as thread-private message storage (shape 32x32b: thread i of the warp <-> TMEM lane base + i) -----
+__device__ __forceinline__ void tm_ld8(unsigned ta, unsigned* r)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(ta));
+}
+__device__ __forceinline__ void tm_ld2(unsigned ta, unsigned* r)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(ta));
+}
+__device__ __forceinline__ void tm_ld4(unsigned ta, unsigned* r)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(ta));
+}
+__device__ __forceinline__ void tm_ld1(unsigned ta, unsigned* r)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[0]) : "r"(ta));
+}
+template <int W>
+__device__ __forceinline__ void tm_load(unsigned ta, unsigned* r)
+{
+  if constexpr (W >= 8) {
+    tm_ld8(ta, r);
+    tm_load<W - 8>(ta + 8, r + 8);
+  } else if constexpr (W >= 4) {
+    tm_ld4(ta, r);
+    tm_load<W - 4>(ta + 4, r + 4);
+  } else if constexpr (W >= 2) {
+    tm_ld2(ta, r);
+    tm_load<W - 2>(ta + 2, r + 2);
+  } else if constexpr (W == 1) {
+    tm_ld1(ta, r);
+  }
+}
+__device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tm_st1(unsigned ta, const unsigned* r)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(ta), "r"(r[0]) : "memory");
+}
+__device__ __forceinline__ void tm_st2(unsigned ta, const unsigned* r)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1,%2};" ::"r"(ta), "r"(r[0]), "r"(r[1]) : "memory");
+}
+__device__ __forceinline__ void tm_st4(unsigned ta, const unsigned* r)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(ta), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3])
+               : "memory");
+}
+__device__ __forceinline__ void tm_st8(unsigned ta, const unsigned* r)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(ta), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+               "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+template <int W>
+__device__ __forceinline__ void tm_store(unsigned ta, const unsigned* r)
+{
+  if constexpr (W >= 8) {
+    tm_st8(ta, r);
+    tm_store<W - 8>(ta + 8, r + 8);
+  } else if constexpr (W >= 4) {
+    tm_st4(ta, r);
+    tm_store<W - 4>(ta + 4, r + 4);
+  } else if constexpr (W >= 2) {
+    tm_st2(ta, r);
+    tm_store<W - 2>(ta + 2, r + 2);
+  } else if constexpr (W == 1) {
+    tm_st1(ta, r);
+  }
+}
+
+constexpr unsigned SIGN2 = 0x80008000u;
+
+// Scaled magnitude Q(m), m integer-valued half2 in [0,120] (closed forms checked against the host table for every m by
+// tm_scale_selfcheck() when the algorithm is set):
+//  GENERIC 0.8: round(0.8 m) = m - round(m / 5)   (0.2 m is never at a tie, one FMA rounding is exact)
+//  AVX     0.8: (m * 52428) >> 16 = m - floor(m / 5) - [m > 0], floor(m / 5) = round((m - 2) / 5)
+// The magic constant 1536 keeps the sum in [1024, 2048) where the fp16 ulp is 1.
+template <int SCALE>
+__device__ __forceinline__ unsigned scale_q(unsigned m)
+{
+  const unsigned magic = hc(1536.f), fifth = hc(0.2f);
+  if (SCALE == TM_SCALE_GENERIC_08) {
+    const unsigned r = hsub(hfma(m, fifth, magic), magic);
+    return hsub(m, r);
+  } else {
+    const unsigned r = hsub(hfma(hsub(m, hc(2.f)), fifth, magic), magic);
+    const unsigned nz = hfma_sat(m, hc(1.f), hc(0.f));
+    return hsub(hsub(m, r), nz);
+  }
+}
+
+// (min1, min2) of a set kept as a sorted pair of non-negative bit patterns.
+struct MinPair {
+  unsigned m1, m2;
+};
+__device__ __forceinline__ MinPair merge(MinPair a, MinPair b)
+{
+  MinPair r;
+  r.m1 = umin2(a.m1, b.m1);
+  r.m2 = umin3(umax2(a.m1, b.m1), a.m2, b.m2);
+  return r;
+}
+// Tree reduction over N sorted pairs.
+template <int N>
+__device__ __forceinline__ MinPair reduce_pairs(MinPair* p)
+{
+  if constexpr (N == 1) {
+    return p[0];
+  } else {
+    constexpr int H = N / 2;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      p[i] = merge(p[2 * i], p[2 * i + 1]);
+    }
+    if constexpr (N & 1) {
+      p[H] = p[N - 1];
+      return reduce_pairs<H + 1>(p);
+    } else {
+      return reduce_pairs<H>(p);
+    }
+  }
+}
+
+// Per-thread context of the row loop.
+struct Ctx {
+  unsigned soft_base;  // shared address of the group's high-rate soft array (uniform per warp)
+  unsigned ext_soft;   // shared address of this thread's extension soft word of row 4 (row r: + (r - 4) * zpad4)
+  unsigned ext_c2v;    // same for the extension message
+  unsigned t4;         // 4 * lane
+  unsigned Z4;
+  unsigned zpad4;
+  unsigned tm_addr;    // TMEM address of this warp's column block (lane base in the upper half)
+  bool active;         // lane < Z
+};
+
+// One check row: D high-rate edges (rotated accesses to shared soft values, messages in cw[]) plus, when EXT, the row's
+// private extension node. e0 / r / tmw are warp-uniform.
+template <int D, bool EXT, int SCALE>
+__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
+{
+  constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
+  constexpr int W = (D + 1) / 2;         // message words of the row
+  unsigned addr[D], u[NV], cw[W];
+  // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads below
+  tm_load<W>(c.tm_addr + tmw, cw);
+  // addresses and soft values: lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66)
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    const TmEdge ed = p.edge[e0 + k];
+    const unsigned a = c.t4 + ed.s4;
+    addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
+    u[k] = lds32(addr[k]);
+  }
+  unsigned xaddr = 0, caddr = 0;
+  if constexpr (EXT) {
+    const unsigned ro = (unsigned)(r - 4) * c.zpad4;
+    xaddr = c.ext_soft + ro;
+    caddr = c.ext_c2v + ro;
+    u[D] = hsub(lds32(xaddr), lds32(caddr));
+  }
+  // previous messages: byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
+  tm_wait_ld();
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    const unsigned tb = __byte_perm(cw[k >> 1], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+    u[k] = hadd(hsub(u[k], tb), hc(1152.f));  // variable-to-check message (compute_var_to_check_msgs)
+  }
+  // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
+  constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
+  MinPair pr[NP];
+  const unsigned c120 = hc(120.f);
+#pragma unroll
+  for (int i = 0; i < NV / 2; ++i) {
+    pr[i].m1 = hmin_abs(u[2 * i], u[2 * i + 1]);
+    pr[i].m2 = hmax_abs(u[2 * i], u[2 * i + 1]);
+  }
+  if constexpr (NV & 1) {
+    pr[NP - 1].m1 = hmin_abs(u[NV - 1], c120);
+    pr[NP - 1].m2 = c120;
+  } else {
+    pr[NP - 1].m1 = c120;
+    pr[NP - 1].m2 = c120;
+  }
+  const MinPair mm = reduce_pairs<NP>(pr);
+  unsigned S = 0;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    S ^= u[k];
+  }
+  const unsigned T = S & SIGN2;
+  // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
+  const unsigned Q1 = scale_q<SCALE>(mm.m1), Q2 = scale_q<SCALE>(mm.m2);
+  const unsigned Q2s = Q2 ^ T;
+  const unsigned nD = hsub(Q1, Q2) ^ T;
+  const unsigned nM1 = mm.m1 ^ SIGN2;
+  // compute_check_to_var_msgs (:93-116) + compute_soft_bits (:118-130)
+  unsigned tn[D + 1];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const unsigned uk = u[k];
+    const unsigned indp = hadd_sat_abs(uk, nM1);  // 0 where |u| == min1, 1 elsewhere
+    const unsigned cm = hfma(indp, nD, Q2s);
+    const unsigned cn = cm ^ (uk & SIGN2);
+    const unsigned v = hmax(hmin(uk, c120), hc(-120.f));
+    const unsigned s = hadd(v, cn);
+    const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
+    const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
+    const unsigned ru = hfma_relu(uk, uk, hc(-46656.f));             // inf iff u is inf
+    const unsigned n = hfma(ru, uk, n1);                             // lanes frozen at +-inf stay there
+    if (k < D) {
+      if (c.active) {
+        sts32(addr[k], n);
+      }
+      tn[k] = hadd(cn, hc(1152.f));
+    } else {
+      sts32(xaddr, n);
+      sts32(caddr, cn);
+    }
+  }
+  if constexpr (D & 1) {
+    tn[D] = tn[D - 1];
+  }
+  unsigned wv[W];
+#pragma unroll
+  for (int i = 0; i < W; ++i) {
+    wv[i] = __byte_perm(tn[2 * i], tn[2 * i + 1], 0x6420);
+  }
+  tm_store<W>(c.tm_addr + tmw, wv);
+}
+
+template <int SCALE>
+__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r)
+{
+  const int cls = p.rowcls[r];
+  const int e0 = p.rowedge[r];
+  const unsigned tmw = p.rowtm[r];
+  switch (cls) {
+#define LDPC_TM_CASE(D, EXT)                        \
+  case 2 * (D) + (EXT):                             \
+    row_body<D, (EXT) != 0, SCALE>(c, p, r, e0, tmw); \
+    break;
+    LDPC_TM_CASE(2, 1)
+    LDPC_TM_CASE(3, 1)
+    LDPC_TM_CASE(4, 1)
+    LDPC_TM_CASE(5, 1)
+    LDPC_TM_CASE(6, 1)
+    LDPC_TM_CASE(7, 1)
+    LDPC_TM_CASE(8, 1)
+    LDPC_TM_CASE(9, 1)
+    LDPC_TM_CASE(8, 0)
+    LDPC_TM_CASE(10, 0)
+    LDPC_TM_CASE(19, 0)
+#undef LDPC_TM_CASE
+    default:
+      break;
+  }
+}
+
+__device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, v, 0); }
+
+}  // namespace tm
+
+// Shared memory: [crc tables 3 x 256 words][group 0][group 1]...; group = soft[HRR * Z] | ext_soft[(M-4) * zpad] |
+// ext_c2v[(M-4) * zpad] | hard[2][msg_bytes16] | flags[8].
+struct TmLayout {
+  unsigned soft, ext_soft, ext_c2v, hard, flags, total;
+};
+__host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
+{
+  const unsigned hrr = (bg == 2) ? 14 : 26, M = (bg == 2) ? LDPC_BG2_M : LDPC_BG1_M, K = (bg == 2) ? 10 : 22;
+  const unsigned msg_bytes16 = (((unsigned)(K * Z + 7) / 8) + 15) & ~15u;
+  TmLayout l;
+  l.soft = 0;
+  l.ext_soft = l.soft + hrr * Z * 4;
+  l.ext_c2v = l.ext_soft + (M - 4) * zpad * 4;
+  l.hard = l.ext_c2v + (M - 4) * zpad * 4;
+  l.flags = l.hard + 2 * msg_bytes16;
+  l.total = (l.flags + 8 * 4 + 15) & ~15u;
+  return l;
+}
+constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base address written by tcgen05.alloc
+
+template <int BG, int SCALE>
+__global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
+{
+  constexpr int K = (BG == 2) ? 10 : 22, M = (BG == 2) ? LDPC_BG2_M : LDPC_BG1_M, HRR = K + 4;
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int Z = p.Z, zpad = p.zpad, tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int grp = tm::uniform(tid / zpad);
+  const int t = tid - grp * zpad;
+  const int wig = tm::uniform(t >> 5);   // warp index inside the group
+  const int nwg = zpad >> 5;             // warps per group
+  const int bar_id = 1 + grp;
+  const unsigned msg_len = (unsigned)(K * Z), msg_bytes = (msg_len + 7) / 8, msg_bytes16 = (msg_bytes + 15) & ~15u;
+  const TmLayout lay = tm_layout(BG, Z, zpad);
+
+  // tensor memory: the whole 512 columns (one block per SM), released at the end
+  if (warp == 0) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smem + 3 * 256 * 4);
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  unsigned* s_crc = reinterpret_cast<unsigned*>(smem);
+  for (int i = tid; i < 3 * 256; i += blockDim.x) {
+    s_crc[i] = c_crc.table[1 + i / 256][i & 255];
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+
+  unsigned char* gsm = smem + TM_CRC_TABLE_BYTES + (size_t)grp * p.group_stride;
+  unsigned* soft_w = reinterpret_cast<unsigned*>(gsm + lay.soft);
+  unsigned* ext_soft_w = reinterpret_cast<unsigned*>(gsm + lay.ext_soft);
+  unsigned* ext_c2v_w = reinterpret_cast<unsigned*>(gsm + lay.ext_c2v);
+  unsigned char* hard = gsm + lay.hard;
+  volatile unsigned* flags = reinterpret_cast<volatile unsigned*>(gsm + lay.flags);  // 0,1: last non-zero + 1; 2,3: crc ok; 4: pair
+
+  tm::Ctx c;
+  c.soft_base = (unsigned)__cvta_generic_to_shared(soft_w);
+  c.ext_soft = (unsigned)__cvta_generic_to_shared(ext_soft_w + t);
+  c.ext_c2v = (unsigned)__cvta_generic_to_shared(ext_c2v_w + t);
+  c.t4 = 4u * (unsigned)t;
+  c.Z4 = (unsigned)p.Z4;
+  c.zpad4 = 4u * (unsigned)zpad;
+  const unsigned tmem_base = *reinterpret_cast<volatile unsigned*>(smem + 3 * 256 * 4);
+  c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * TM_COLS_PER_WARP;
+  c.active = t < Z;
+
+  for (;;) {
+    // next pair of codeblocks for this group
+    if (t == 0) {
+      flags[4] = atomicAdd(p.pair_counter, 1u);
+      flags[0] = 0, flags[1] = 0, flags[2] = 0, flags[3] = 0;
+    }
+    tm::group_barrier(bar_id, zpad);
+    const unsigned pair = (unsigned)tm::uniform((int)flags[4]);
+    if (2 * pair >= p.nof_cbs) {
+      break;
+    }
+    const bool hasB = 2 * pair + 1 < p.nof_cbs;
+    const CbWork wA = p.work[2 * pair];
+    const CbWork wB = p.work[hasB ? 2 * pair + 1 : 2 * pair];
+    const bool useA = !wA.skip_decode, useB = hasB && !wB.skip_decode;
+    if (!useA && !useB) {
+      tm::group_barrier(bar_id, zpad);
+      continue;
+    }
+    // load_soft_bits (ldpc_decoder_impl.cpp:148-173) for both codeblocks: int8 -> fp16, +-127 -> +-inf; punctured and
+    // missing nodes 0. Messages start at zero (first visit of a layer, ldpc_decoder_impl.cpp:181-185).
+    const int8_t* inA = p.llr_base + wA.in_offset;
+    const int8_t* inB = p.llr_base + wB.in_offset;
+    unsigned lastA = 0, lastB = 0;
+    if (c.active) {
+#pragma unroll 4
+      for (int n = 0; n < K + M; ++n) {
+        int a = 0, b = 0;
+        if (n >= 2) {
+          const unsigned i = (unsigned)(n - 2) * Z + t;
+          if (useA && i < wA.in_length) {
+            a = inA[i];
+            lastA = a ? i + 1 : lastA;
+          }
+          if (useB && i < wB.in_length) {
+            b = inB[i];
+            lastB = b ? i + 1 : lastB;
+          }
+        }
+        float fa = (float)a, fb = (float)b;
+        fa = (a > LLR_MAX) ? __int_as_float(0x7f800000) : ((a < -LLR_MAX) ? __int_as_float(0xff800000) : fa);
+        fb = (b > LLR_MAX) ? __int_as_float(0x7f800000) : ((b < -LLR_MAX) ? __int_as_float(0xff800000) : fb);
+        const unsigned v = tm::un(__floats2half2_rn(fa, fb));
+        if (n < HRR) {
+          soft_w[n * Z + t] = v;
+        } else {
+          ext_soft_w[(n - HRR) * zpad + t] = v;
+        }
+      }
+    }
+    for (int n = 0; n < M - 4; ++n) {
+      ext_c2v_w[n * zpad + t] = 0;
+    }
+    {
+      unsigned init[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        init[i] = 0x80808080u;
+      }
+      for (int w = 0; w < p.tm_words; w += 8) {
+        tm::tm_st8(c.tm_addr + w, init);
+      }
+      tm::tm_wait_st();
+    }
+    if (lastA) {
+      atomicMax(const_cast<unsigned*>(&flags[0]), lastA);
+    }
+    if (lastB) {
+      atomicMax(const_cast<unsigned*>(&flags[1]), lastB);
+    }
+    tm::group_barrier(bar_id, zpad);
+    const unsigned inszA = flags[0], inszB = flags[1];  // one past the last non-zero LLR (ldpc_decoder_impl.cpp:86-94)
+    bool doneA = !useA, doneB = !useB;
+    CbResult resA = {0, 0, 0}, resB = {0, 0, 0};
+    auto zero_shortcut = [&](const CbWork& w, CbResult& res) {
+      if (!w.crc_poly) {  // output.one()
+        uint8_t* out = p.out_base + w.out_offset;
+        for (unsigned i = t; i < msg_bytes; i += zpad) {
+          out[i] = (i == msg_bytes - 1 && (msg_len & 7)) ? (unsigned char)(0xff << (8 - (msg_len & 7))) : 0xff;
+        }
+      }
+      res.flags = 1;
+      if (t == 0) {
+        p.results[w.result_index] = res;
+      }
+    };
+    if (useA && inszA == 0) {
+      zero_shortcut(wA, resA);
+      doneA = true;
+    }
+    if (useB && inszB == 0) {
+      zero_shortcut(wB, resB);
+      doneB = true;
+    }
+    // number of layers (ldpc_decoder_impl.cpp:105-114); the pair runs the larger count - surplus layers of the shorter
+    // codeblock see an all-zero extension node, which leaves its high-rate nodes untouched
+    auto layers_of = [&](unsigned insz) {
+      unsigned cb_len = max(insz + 2u * Z, msg_len + 4u * Z);
+      cb_len = ((cb_len + Z - 1) / Z) * Z;
+      return (int)(cb_len / Z) - K;
+    };
+    const int nof_layers = tm::uniform(max(doneA ? 4 : layers_of(inszA), doneB ? 4 : layers_of(inszB)));
+
+    int it = 0;
+    while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
+      for (int r = 0; r < nof_layers; ++r) {
+        tm::row_dispatch<SCALE>(c, p, r);
+        tm::group_barrier(bar_id, zpad);
+      }
+      tm::tm_wait_st();
+      ++it;
+      const bool last = (it == p.max_iterations);
+      const bool chkA = !doneA && ((wA.crc_poly && wA.early_stop) || last);
+      const bool chkB = !doneB && ((wB.crc_poly && wB.early_stop) || last);
+      if (chkA || chkB) {
+        // get_hard_bits (ldpc_decoder_generic.cpp:132-138): bit = soft <= 0, MSB first, both halves at once
+        for (unsigned i = t; i < msg_bytes; i += zpad) {
+          unsigned ba = 0, bb = 0;
+#pragma unroll
+          for (unsigned k = 0; k < 8; ++k) {
+            const unsigned b = 8 * i + k;
+            if (b < msg_len) {
+              const unsigned v = soft_w[b];
+              ba |= (((v & 0x7fffu) == 0 || (v & 0x8000u)) ? 0x80u : 0u) >> k;
+              bb |= (((v & 0x7fff0000u) == 0 || (v & 0x80000000u)) ? 0x80u : 0u) >> k;
+            }
+          }
+          if (chkA) {
+            hard[i] = (unsigned char)ba;
+          }
+          if (chkB) {
+            hard[msg_bytes16 + i] = (unsigned char)bb;
+          }
+        }
+        tm::group_barrier(bar_id, zpad);
+        if (wig == 0 && chkA && wA.crc_poly) {
+          const unsigned rr = crc_warp(hard, msg_len - wA.nof_filler_bits, wA.crc_poly, s_crc + 256 * (wA.crc_poly - 1));
+          if ((t & 31) == 0) {
+            flags[2] = (rr == 0);
+          }
+        }
+        if (wig == (nwg > 1 ? 1 : 0) && chkB && wB.crc_poly) {
+          const unsigned rr =
+              crc_warp(hard + msg_bytes16, msg_len - wB.nof_filler_bits, wB.crc_poly, s_crc + 256 * (wB.crc_poly - 1));
+          if ((t & 31) == 0) {
+            flags[3] = (rr == 0);
+          }
+        }
+        tm::group_barrier(bar_id, zpad);
+        auto finish = [&](const CbWork& w, CbResult& res, bool& done, const unsigned char* bits, bool ok) {
+          if (ok || last) {
+            uint8_t* out = p.out_base + w.out_offset;
+            for (unsigned i = t; i < msg_bytes; i += zpad) {
+              out[i] = bits[i];
+            }
+            res.iterations = (unsigned short)it;
+            res.crc_ok = ok ? 1 : 0;
+            if (t == 0) {
+              p.results[w.result_index] = res;
+            }
+            done = true;
+          }
+        };
+        if (chkA) {
+          finish(wA, resA, doneA, hard, wA.crc_poly && flags[2]);
+        }
+        if (chkB) {
+          finish(wB, resB, doneB, hard + msg_bytes16, wB.crc_poly && flags[3]);
+        }
+        tm::group_barrier(bar_id, zpad);
+      }
+    }
+    tm::group_barrier(bar_id, zpad);  // flags / hard bits are reused by the next pair
+  }
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------------
+static inline int tm_scale_variant(const unsigned char* lut)
+{
+  bool gen = true, avx = true;
+  for (int m = 0; m <= LLR_MAX; ++m) {
+    const int r5 = (2 * m + 5) / 10;  // round(m / 5), never at a tie
+    gen = gen && (lut[m] == m - r5);
+    avx = avx && (lut[m] == m - m / 5 - (m > 0 ? 1 : 0));
+  }
+  return gen ? TM_SCALE_GENERIC_08 : (avx ? TM_SCALE_AVX_08 : TM_SCALE_NONE);
+}
+
+template <int SCALE>
+__global__ void tm_scale_selfcheck_kernel(unsigned char* out)
+{
+  const int m = threadIdx.x;
+  if (m <= LLR_MAX) {
+    const unsigned q = tm::scale_q<SCALE>(tm::hc((float)m));
+    out[m] = (unsigned char)__half2float(__low2half(tm::h2(q)));
+  }
+}
+
+// Runs the fp16 closed form for every magnitude on the device and compares with the host table. 0 = identical.
+static inline int tm_scale_selfcheck(int variant, const unsigned char* lut, cudaStream_t stream)
+{
+  unsigned char* d = nullptr;
+  unsigned char h[LLR_MAX + 1];
+  if (cudaMalloc(&d, LLR_MAX + 1) != cudaSuccess) {
+    return -1;
+  }
+  if (variant == TM_SCALE_GENERIC_08) {
+    tm_scale_selfcheck_kernel<TM_SCALE_GENERIC_08><<<1, 128, 0, stream>>>(d);
+  } else {
+    tm_scale_selfcheck_kernel<TM_SCALE_AVX_08><<<1, 128, 0, stream>>>(d);
+  }
+  cudaError_t e = cudaMemcpyAsync(h, d, LLR_MAX + 1, cudaMemcpyDeviceToHost, stream);
+  e = (e == cudaSuccess) ? cudaStreamSynchronize(stream) : e;
+  cudaFree(d);
+  if (e != cudaSuccess) {
+    return -1;
+  }
+  for (int m = 0; m <= LLR_MAX; ++m) {
+    if (h[m] != lut[m]) {
+      return 1;
+    }
+  }
+  return 0;
+}
+
+// Fills the row / edge tables of a (base graph, lifting size) group. Returns false when a row shape has no kernel case.
+static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p)
+{
+  const int M = (bg == 2) ? LDPC_BG2_M : LDPC_BG1_M, K = (bg == 2) ? 10 : 22, hrr = K + 4;
+  const uint16_t* row_ptr = (bg == 2) ? LDPC_BG2_ROW_PTR : LDPC_BG1_ROW_PTR;
+  const uint8_t* col = (bg == 2) ? LDPC_BG2_COL : LDPC_BG1_COL;
+  const uint16_t* shift = (bg == 2) ? LDPC_BG2_SHIFT[lifting_set] : LDPC_BG1_SHIFT[lifting_set];
+  unsigned ne = 0, tmw = 0;
+  for (int r = 0; r != M; ++r) {
+    unsigned d = 0, ext = 0;
+    p.rowedge[r] = (unsigned short)ne;
+    p.rowtm[r] = (unsigned short)tmw;
+    for (int e = row_ptr[r]; e != row_ptr[r + 1]; ++e) {
+      if (col[e] < hrr) {
+        p.edge[ne].s4 = 4u * (shift[e] % (unsigned)Z);
+        p.edge[ne].cb = 4u * (unsigned)Z * col[e];
+        ++ne, ++d;
+      } else {
+        // the row's private extension node: last edge, identity circulant
+        if (col[e] != K + r || shift[e] % (unsigned)Z != 0 || e + 1 != row_ptr[r + 1] || r < 4) {
+          return false;
+        }
+        ext = 1;
+      }
+    }
+    const bool ok = ext ? (d >= 2 && d <= 9) : (d == 8 || d == 10 || d == 19);
+    if (!ok) {
+      return false;
+    }
+    p.rowcls[r] = (unsigned char)(2 * d + ext);
+    tmw += (d + 1) / 2;
+  }
+  p.tm_words = (unsigned short)tmw;
+  return ((tmw + 7) & ~7u) <= (unsigned)TM_COLS_PER_WARP;
+}
+
+constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100
+constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block per SM owns all 512 TMEM columns
+
+template <int BG, int SCALE>
+static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, cudaStream_t stream)
+{
+  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM_LIMIT);
+    if (e != cudaSuccess) {
+      std::fprintf(stderr, "ldpc_cuda: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(e));
+      return -1;
+    }
+    attr_set = true;
+  }
+  kernel<<<grid, p.groups * p.zpad, smem, stream>>>(p);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    std::fprintf(stderr, "ldpc_cuda: packed decode launch failed: %s\n", cudaGetErrorString(e));
+    return -1;
+  }
+  return 0;
+}
+
+// Returns 0 when launched, > 0 when the configuration is not covered (caller uses the general kernel), < 0 on CUDA error.
+static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, const CbWork* d_work, unsigned n,
+                                     const int8_t* d_llr, uint8_t* d_out, CbResult* d_res, unsigned* d_pair_counter,
+                                     int sm_count, cudaStream_t stream)
+{
+  if (scale_variant == TM_SCALE_NONE || d_pair_counter == nullptr) {
+    return 1;
+  }
+  TmemParams p;
+  std::memset(&p, 0, sizeof(p));
+  if (!tm_build_tables(gp.bg, gp.Z, gp.lifting_set, p)) {
+    return 1;
+  }
+  p.work = d_work, p.llr_base = d_llr, p.out_base = d_out, p.results = d_res, p.pair_counter = d_pair_counter;
+  p.nof_cbs = n, p.Z = gp.Z, p.Z4 = 4 * gp.Z, p.max_iterations = gp.max_iterations;
+  p.zpad = ((gp.Z + 31) / 32) * 32;
+  p.groups = TM_THREADS / p.zpad;
+  const TmLayout lay = tm_layout(gp.bg, gp.Z, p.zpad);
+  p.group_stride = lay.total;
+  const unsigned n_pairs = (n + 1) / 2;
+  if ((unsigned)p.groups > n_pairs) {
+    p.groups = (int)n_pairs;
+  }
+  size_t smem = TM_CRC_TABLE_BYTES + (size_t)p.groups * lay.total;
+  if (smem > TM_SMEM_LIMIT) {
+    return 1;
+  }
+  smem = std::max(smem, TM_SMEM_MIN);
+  const unsigned grid = std::min<unsigned>((n_pairs + p.groups - 1) / p.groups, (unsigned)sm_count);
+  if (cudaMemsetAsync(d_pair_counter, 0, sizeof(unsigned), stream) != cudaSuccess) {
+    return -1;
+  }
+  const bool gen = scale_variant == TM_SCALE_GENERIC_08;
+  if (gp.bg == 1) {
+    return gen ? tm_launch_variant<1, TM_SCALE_GENERIC_08>(p, smem, grid, stream)
+               : tm_launch_variant<1, TM_SCALE_AVX_08>(p, smem, grid, stream);
+  }
+  return gen ? tm_launch_variant<2, TM_SCALE_GENERIC_08>(p, smem, grid, stream)
+             : tm_launch_variant<2, TM_SCALE_AVX_08>(p, smem, grid, stream);
+}
+
+}  // namespace ldpc_b200
