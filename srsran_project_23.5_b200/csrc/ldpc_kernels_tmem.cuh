@@ -42,21 +42,10 @@ enum { TM_SCALE_NONE = 0, TM_SCALE_GENERIC_08 = 1, TM_SCALE_AVX_08 = 2 };
 
 constexpr int TM_THREADS = 384;       // threads per block at full occupancy of the TMEM lanes (12 warps)
 constexpr int TM_COLS_PER_WARP = 170; // 512 TMEM columns / 3 warps per lane quadrant
-constexpr int TM_BIG_ROW = 12;        // rows with at least this many high-rate edges take the looping path
-constexpr int TM_STASH_WORDS = 20;    // TMEM words that park the v2c messages of a big row
 
 struct __align__(8) TmEdge {
   unsigned s4;  // 4 * (shift % Z): rotation in bytes
   unsigned cb;  // byte offset of the column's soft values inside the group's soft array: col * 4 * Z
-};
-
-// Row descriptor (uniform): number of high-rate edges D (20 for the padded 19-edge rows), extension flag, first edge
-// entry, first TMEM word.
-struct __align__(8) TmRow {
-  unsigned short deg;
-  unsigned short ext;
-  unsigned short e0;
-  unsigned short tmw;
 };
 
 struct TmemParams {
@@ -72,11 +61,11 @@ struct TmemParams {
   int groups;       // codeblock pairs processed concurrently by one block
   int max_iterations;
   unsigned group_stride;  // bytes of shared memory per group
-  unsigned short tm_words;             // TMEM words per thread that hold messages
-  unsigned short stash;                // first of the TM_STASH_WORDS words that park the v2c messages of a big row
-  TmRow row[LDPC_BG1_M];
-  TmEdge edge[LDPC_BG1_EDGES + 4];     // high-rate edges only, row after row (extension edges are implicit; 19-edge
-                                       // rows carry one padding edge to the dummy column)
+  unsigned char rowcls[LDPC_BG1_M];    // per row: 2 * (number of high-rate edges) + (1 if the row has an extension node)
+  unsigned short rowedge[LDPC_BG1_M];  // per row: index of its first entry in edge[]
+  unsigned short rowtm[LDPC_BG1_M];    // per row: first TMEM word (relative to the warp's column block)
+  unsigned short tm_words;             // TMEM words used per thread
+  TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
 };
 
 // ---- small helpers on raw half2 bit patterns -------------------------------------------------------------------------
@@ -230,6 +219,27 @@ __device__ __forceinline__ MinPair merge(MinPair a, MinPair b)
   r.m2 = umin3(umax2(a.m1, b.m1), a.m2, b.m2);
   return r;
 }
+// Tree reduction over N sorted pairs.
+template <int N>
+__device__ __forceinline__ MinPair reduce_pairs(MinPair* p)
+{
+  if constexpr (N == 1) {
+    return p[0];
+  } else {
+    constexpr int H = N / 2;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      p[i] = merge(p[2 * i], p[2 * i + 1]);
+    }
+    if constexpr (N & 1) {
+      p[H] = p[N - 1];
+      return reduce_pairs<H + 1>(p);
+    } else {
+      return reduce_pairs<H>(p);
+    }
+  }
+}
+
 // Per-thread context of the row loop.
 struct Ctx {
   unsigned soft_base;  // shared address of the group's high-rate soft array (uniform per warp)
@@ -242,109 +252,93 @@ struct Ctx {
   bool active;         // lane < Z
 };
 
-// The row engine. The hot loop must fit the ~8 KB level-0 instruction cache (profiles/r01_icache_microbench.md: beyond
-// it the issue rate of 12 warps drops from 3.9 to 2.0 warp-instructions/clk/SM), so there is ONE row routine for all
-// rows instead of one unrolled body per row shape: the D high-rate edges of a row are processed in chunks of 4, 2 and 1
-// edges whose registers are static ("slots"): slot A (4 edges), slot B (4 edges), a 2-edge and a 1-edge tail cover rows
-// of up to 11 edges; the four 19-edge rows of BG1 (padded to 20 with one edge to a dummy column frozen at +inf) loop
-// five times over slot A and park their variable-to-check messages in spare TMEM columns between the two passes.
-template <int C>
-struct Chunk {
-  unsigned u[C];     // soft value, then variable-to-check message
-  unsigned addr[C];  // shared address of the rotated soft value
-};
-
-// lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66): address of the soft value
-template <int C>
-__device__ __forceinline__ void chunk_addr(const Ctx& c, const TmemParams& p, int e, Chunk<C>& ch)
+// One check row: D high-rate edges (rotated accesses to shared soft values, messages in cw[]) plus, when EXT, the row's
+// private extension node. e0 / r / tmw are warp-uniform.
+template <int D, bool EXT, int SCALE>
+__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
 {
-#pragma unroll
-  for (int k = 0; k < C; ++k) {
-    const TmEdge ed = p.edge[e + k];
-    const unsigned a = c.t4 + ed.s4;
-    ch.addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
-  }
-}
-
-// First pass over a chunk: previous messages from TMEM, soft values from shared memory, v2c messages, running
-// (min1, min2) and sign parity (compute_var_to_check_msgs + analyze_var_to_check_msgs, ldpc_decoder_generic.cpp:30-78).
-template <int C>
-__device__ __forceinline__ void chunk_pass1(const Ctx& c, const TmemParams& p, int e, unsigned tmw, Chunk<C>& ch, MinPair& run,
-                                            unsigned& S)
-{
-  constexpr int W = (C + 1) / 2;
-  unsigned cw[W];
+  constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
+  constexpr int W = (D + 1) / 2;         // message words of the row
+  unsigned addr[D], u[NV], cw[W];
+  // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads below
   tm_load<W>(c.tm_addr + tmw, cw);
-  chunk_addr<C>(c, p, e, ch);
+  // addresses and soft values: lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66)
 #pragma unroll
-  for (int k = 0; k < C; ++k) {
-    ch.u[k] = lds32(ch.addr[k]);
+  for (int k = 0; k < D; ++k) {
+    const TmEdge ed = p.edge[e0 + k];
+    const unsigned a = c.t4 + ed.s4;
+    addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
+    u[k] = lds32(addr[k]);
   }
+  unsigned xaddr = 0, caddr = 0;
+  if constexpr (EXT) {
+    const unsigned ro = (unsigned)(r - 4) * c.zpad4;
+    xaddr = c.ext_soft + ro;
+    caddr = c.ext_c2v + ro;
+    u[D] = hsub(lds32(xaddr), lds32(caddr));
+  }
+  // previous messages: byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
   tm_wait_ld();
 #pragma unroll
-  for (int k = 0; k < C; ++k) {
-    // byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
+  for (int k = 0; k < D; ++k) {
     const unsigned tb = __byte_perm(cw[k >> 1], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
-    ch.u[k] = hadd(hsub(ch.u[k], tb), hc(1152.f));
+    u[k] = hadd(hsub(u[k], tb), hc(1152.f));  // variable-to-check message (compute_var_to_check_msgs)
   }
-  if constexpr (C == 4) {
-    MinPair a, b;
-    a.m1 = hmin_abs(ch.u[0], ch.u[1]), a.m2 = hmax_abs(ch.u[0], ch.u[1]);
-    b.m1 = hmin_abs(ch.u[2], ch.u[3]), b.m2 = hmax_abs(ch.u[2], ch.u[3]);
-    run = merge(run, merge(a, b));
-    S ^= ch.u[0] ^ ch.u[1];
-    S ^= ch.u[2] ^ ch.u[3];
-  } else if constexpr (C == 2) {
-    MinPair a;
-    a.m1 = hmin_abs(ch.u[0], ch.u[1]), a.m2 = hmax_abs(ch.u[0], ch.u[1]);
-    run = merge(run, a);
-    S ^= ch.u[0] ^ ch.u[1];
-  } else {
-    const unsigned t = hmax_abs(ch.u[0], run.m1);
-    run.m1 = hmin_abs(ch.u[0], run.m1);
-    run.m2 = umin2(run.m2, t);
-    S ^= ch.u[0];
-  }
-}
-
-// Values of a row that every edge needs in the second pass.
-struct RowConst {
-  unsigned Q2s;  // scaled min2, sign parity folded in
-  unsigned nD;   // (scaled min1 - scaled min2), sign parity folded in
-  unsigned nM1;  // -min1
-};
-
-// New check-to-variable message and new soft value of one edge (compute_check_to_var_msgs :93-116, compute_soft_bits
-// :118-130). Returns the soft value; cn receives the message.
-__device__ __forceinline__ unsigned edge_update(unsigned uk, const RowConst& rc, unsigned& cn)
-{
-  const unsigned indp = hadd_sat_abs(uk, rc.nM1);  // 0 where |u| == min1, 1 elsewhere
-  const unsigned cm = hfma(indp, rc.nD, rc.Q2s);
-  cn = cm ^ (uk & SIGN2);
-  const unsigned v = hmax(hmin(uk, hc(120.f)), hc(-120.f));
-  const unsigned s = hadd(v, cn);
-  const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
-  const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
-  const unsigned ru = hfma_relu(uk, uk, hc(-46656.f));             // inf iff u is inf
-  return hfma(ru, uk, n1);                                         // lanes frozen at +-inf stay there
-}
-
-template <int C>
-__device__ __forceinline__ void chunk_pass2(const Ctx& c, unsigned tmw, const Chunk<C>& ch, const RowConst& rc)
-{
-  constexpr int W = (C + 1) / 2;
-  unsigned tn[2 * W];
+  // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
+  constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
+  MinPair pr[NP];
+  const unsigned c120 = hc(120.f);
 #pragma unroll
-  for (int k = 0; k < C; ++k) {
-    unsigned cn;
-    const unsigned n = edge_update(ch.u[k], rc, cn);
-    if (c.active) {
-      sts32(ch.addr[k], n);
-    }
-    tn[k] = hadd(cn, hc(1152.f));
+  for (int i = 0; i < NV / 2; ++i) {
+    pr[i].m1 = hmin_abs(u[2 * i], u[2 * i + 1]);
+    pr[i].m2 = hmax_abs(u[2 * i], u[2 * i + 1]);
   }
-  if constexpr (C & 1) {
-    tn[C] = tn[C - 1];
+  if constexpr (NV & 1) {
+    pr[NP - 1].m1 = hmin_abs(u[NV - 1], c120);
+    pr[NP - 1].m2 = c120;
+  } else {
+    pr[NP - 1].m1 = c120;
+    pr[NP - 1].m2 = c120;
+  }
+  const MinPair mm = reduce_pairs<NP>(pr);
+  unsigned S = 0;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    S ^= u[k];
+  }
+  const unsigned T = S & SIGN2;
+  // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
+  const unsigned Q1 = scale_q<SCALE>(mm.m1), Q2 = scale_q<SCALE>(mm.m2);
+  const unsigned Q2s = Q2 ^ T;
+  const unsigned nD = hsub(Q1, Q2) ^ T;
+  const unsigned nM1 = mm.m1 ^ SIGN2;
+  // compute_check_to_var_msgs (:93-116) + compute_soft_bits (:118-130)
+  unsigned tn[D + 1];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const unsigned uk = u[k];
+    const unsigned indp = hadd_sat_abs(uk, nM1);  // 0 where |u| == min1, 1 elsewhere
+    const unsigned cm = hfma(indp, nD, Q2s);
+    const unsigned cn = cm ^ (uk & SIGN2);
+    const unsigned v = hmax(hmin(uk, c120), hc(-120.f));
+    const unsigned s = hadd(v, cn);
+    const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
+    const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
+    // lanes frozen at +-inf stay there (HSET2.BM + LOP3 on the ALU pipe: the FP16 pipe is the busier one in this pass)
+    const unsigned isinf = __heq2_mask(__habs2(h2(uk)), h2(0x7c007c00u));
+    const unsigned n = (uk & isinf) | (n1 & ~isinf);
+    if (k < D) {
+      if (c.active) {
+        sts32(addr[k], n);
+      }
+      tn[k] = hadd(cn, hc(1152.f));
+    } else {
+      sts32(xaddr, n);
+      sts32(caddr, cn);
+    }
+  }
+  if constexpr (D & 1) {
+    tn[D] = tn[D - 1];
   }
   unsigned wv[W];
 #pragma unroll
@@ -354,90 +348,31 @@ __device__ __forceinline__ void chunk_pass2(const Ctx& c, unsigned tmw, const Ch
   tm_store<W>(c.tm_addr + tmw, wv);
 }
 
-
 template <int SCALE>
-__device__ __forceinline__ void process_row(const Ctx& c, const TmemParams& p, int r, unsigned stash)
+__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r)
 {
-  const TmRow row = p.row[r];
-  const int D = row.deg, e0 = row.e0;
-  const unsigned tmw = row.tmw;
-  const bool big = D >= TM_BIG_ROW;
-  MinPair run;
-  run.m1 = hc(120.f), run.m2 = hc(120.f);  // the reference initialises both minima to 120 (ldpc_decoder_impl.cpp:239-240)
-  unsigned S = 0;
-  Chunk<4> A, B;
-  Chunk<2> T2;
-  Chunk<1> T1;
-  const int nq = D >> 2;
-  // ---- first pass
-  if (nq >= 1) {
-    int q = 0;
-#pragma unroll 1
-    do {
-      chunk_pass1<4>(c, p, e0 + 4 * q, tmw + 2 * q, A, run, S);
-      if (!big) {
-        break;
-      }
-      tm_store<4>(c.tm_addr + stash + 4 * q, A.u);
-    } while (++q < nq);
-  }
-  if (!big && nq >= 2) {
-    chunk_pass1<4>(c, p, e0 + 4, tmw + 2, B, run, S);
-  }
-  if (D & 2) {
-    chunk_pass1<2>(c, p, e0 + 4 * nq, tmw + 2 * nq, T2, run, S);
-  }
-  if (D & 1) {
-    chunk_pass1<1>(c, p, e0 + (D & ~1), tmw + (D >> 1), T1, run, S);
-  }
-  unsigned ue = 0, xaddr = 0, caddr = 0;
-  if (row.ext) {
-    const unsigned ro = (unsigned)(r - 4) * c.zpad4;
-    xaddr = c.ext_soft + ro;
-    caddr = c.ext_c2v + ro;
-    ue = hsub(lds32(xaddr), lds32(caddr));
-    const unsigned t = hmax_abs(ue, run.m1);
-    run.m1 = hmin_abs(ue, run.m1);
-    run.m2 = umin2(run.m2, t);
-    S ^= ue;
-  }
-  // ---- scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
-  const unsigned T = S & SIGN2;
-  const unsigned Q1 = scale_q<SCALE>(run.m1), Q2 = scale_q<SCALE>(run.m2);
-  RowConst rc;
-  rc.Q2s = Q2 ^ T;
-  rc.nD = hsub(Q1, Q2) ^ T;
-  rc.nM1 = run.m1 ^ SIGN2;
-  // ---- second pass
-  if (nq >= 1) {
-    int q = 0;
-    if (big) {
-      tm_wait_st();
-    }
-#pragma unroll 1
-    do {
-      if (big) {
-        tm_load<4>(c.tm_addr + stash + 4 * q, A.u);
-        chunk_addr<4>(c, p, e0 + 4 * q, A);
-        tm_wait_ld();
-      }
-      chunk_pass2<4>(c, tmw + 2 * q, A, rc);
-    } while (big && ++q < nq);
-  }
-  if (!big && nq >= 2) {
-    chunk_pass2<4>(c, tmw + 2, B, rc);
-  }
-  if (D & 2) {
-    chunk_pass2<2>(c, tmw + 2 * nq, T2, rc);
-  }
-  if (D & 1) {
-    chunk_pass2<1>(c, tmw + (D >> 1), T1, rc);
-  }
-  if (row.ext) {
-    unsigned cn;
-    const unsigned n = edge_update(ue, rc, cn);
-    sts32(xaddr, n);
-    sts32(caddr, cn);
+  const int cls = p.rowcls[r];
+  const int e0 = p.rowedge[r];
+  const unsigned tmw = p.rowtm[r];
+  switch (cls) {
+#define LDPC_TM_CASE(D, EXT)                        \
+  case 2 * (D) + (EXT):                             \
+    row_body<D, (EXT) != 0, SCALE>(c, p, r, e0, tmw); \
+    break;
+    LDPC_TM_CASE(2, 1)
+    LDPC_TM_CASE(3, 1)
+    LDPC_TM_CASE(4, 1)
+    LDPC_TM_CASE(5, 1)
+    LDPC_TM_CASE(6, 1)
+    LDPC_TM_CASE(7, 1)
+    LDPC_TM_CASE(8, 1)
+    LDPC_TM_CASE(9, 1)
+    LDPC_TM_CASE(8, 0)
+    LDPC_TM_CASE(10, 0)
+    LDPC_TM_CASE(19, 0)
+#undef LDPC_TM_CASE
+    default:
+      break;
   }
 }
 
@@ -456,7 +391,7 @@ __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
   const unsigned msg_bytes16 = (((unsigned)(K * Z + 7) / 8) + 15) & ~15u;
   TmLayout l;
   l.soft = 0;
-  l.ext_soft = l.soft + (hrr + 1) * Z * 4;  // + the dummy column (frozen at +inf) that padding edges point to
+  l.ext_soft = l.soft + hrr * Z * 4;
   l.ext_c2v = l.ext_soft + (M - 4) * zpad * 4;
   l.hard = l.ext_c2v + (M - 4) * zpad * 4;
   l.flags = l.hard + 2 * msg_bytes16;
@@ -565,9 +500,6 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     for (int n = 0; n < M - 4; ++n) {
       ext_c2v_w[n * zpad + t] = 0;
     }
-    if (c.active) {
-      soft_w[HRR * Z + t] = 0x7c007c00u;  // dummy column of the padding edges: +inf, never changes
-    }
     {
       unsigned init[8];
 #pragma unroll
@@ -621,7 +553,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
       for (int r = 0; r < nof_layers; ++r) {
-        tm::process_row<SCALE>(c, p, r, p.stash);
+        tm::row_dispatch<SCALE>(c, p, r);
         tm::group_barrier(bar_id, zpad);
       }
       tm::tm_wait_st();
@@ -754,8 +686,8 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
   unsigned ne = 0, tmw = 0;
   for (int r = 0; r != M; ++r) {
     unsigned d = 0, ext = 0;
-    p.row[r].e0 = (unsigned short)ne;
-    p.row[r].tmw = (unsigned short)tmw;
+    p.rowedge[r] = (unsigned short)ne;
+    p.rowtm[r] = (unsigned short)tmw;
     for (int e = row_ptr[r]; e != row_ptr[r + 1]; ++e) {
       if (col[e] < hrr) {
         p.edge[ne].s4 = 4u * (shift[e] % (unsigned)Z);
@@ -769,28 +701,15 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
         ext = 1;
       }
     }
-    if (d >= (unsigned)TM_BIG_ROW) {
-      // looping path: chunks of 4 only; pad with edges to the dummy column (soft value frozen at +inf: never the
-      // minimum, positive sign, rewritten with +inf)
-      while (d % 4 != 0) {
-        p.edge[ne].s4 = 0;
-        p.edge[ne].cb = 4u * (unsigned)Z * hrr;
-        ++ne, ++d;
-      }
-      if (d > 4u * (TM_STASH_WORDS / 4)) {
-        return false;
-      }
-    }
-    if (d < 1 || ne > sizeof(p.edge) / sizeof(p.edge[0])) {
+    const bool ok = ext ? (d >= 2 && d <= 9) : (d == 8 || d == 10 || d == 19);
+    if (!ok) {
       return false;
     }
-    p.row[r].deg = (unsigned short)d;
-    p.row[r].ext = (unsigned short)ext;
+    p.rowcls[r] = (unsigned char)(2 * d + ext);
     tmw += (d + 1) / 2;
   }
   p.tm_words = (unsigned short)tmw;
-  p.stash = (unsigned short)((tmw + 3) & ~3u);
-  return ((tmw + 7) & ~7u) <= (unsigned)TM_COLS_PER_WARP && p.stash + TM_STASH_WORDS <= TM_COLS_PER_WARP;
+  return ((tmw + 7) & ~7u) <= (unsigned)TM_COLS_PER_WARP;
 }
 
 constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100

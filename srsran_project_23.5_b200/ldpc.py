@@ -39,6 +39,9 @@ _lib = None
 
 
 def library_path():
+    override = os.environ.get("SRSRAN_LDPC_CUDA_LIB")  # development only: A/B runs of two builds of the same library
+    if override:
+        return override
     return os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libsrsran_ldpc_cuda.so")
 
 

@@ -7,8 +7,8 @@
 #define I64 I16 I16 I16 I16
 #define I256 I64 I64 I64 I64
 #define I1024 I256 I256 I256 I256
-#define BLK1024 asm volatile(I64 : "+r"(a), "+r"(b), "+r"(c), "+r"(d), "+r"(e), "+r"(f), "+r"(g), "+r"(h) : "r"(k1), "r"(k2));
-template <int NK, int TH>  // body = NK * 64 instructions
+#define BLK1024 if (SYNC && (i & 3) == 3) __syncthreads(); asm volatile(I64 : "+r"(a), "+r"(b), "+r"(c), "+r"(d), "+r"(e), "+r"(f), "+r"(g), "+r"(h) : "r"(k1), "r"(k2));
+template <int NK, int TH, bool SYNC>  // body = NK * 64 instructions, optional barrier every 256
 __global__ void __launch_bounds__(TH, 1) k(unsigned* out, int reps, long long* cyc)
 {
   unsigned a = threadIdx.x, b = a * 3 + 1, c = a ^ 0x55, d = a + 7, e = a + 9, f = a * 5, g = a ^ 0x77, h = a + 100, k1 = a | 0x3c003c00, k2 = a >> 3;
@@ -23,23 +23,23 @@ __global__ void __launch_bounds__(TH, 1) k(unsigned* out, int reps, long long* c
   out[blockIdx.x * TH + threadIdx.x] = a ^ b ^ c ^ d ^ e ^ f ^ g ^ h;
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
-template <int NK, int TH>
+template <int NK, int TH, bool SYNC>
 void run(unsigned* out, long long* cyc)
 {
   int reps = 32768 / NK;
-  k<NK, TH><<<148, TH>>>(out, reps, cyc);
+  k<NK, TH, SYNC><<<148, TH>>>(out, reps, cyc);
   cudaDeviceSynchronize();
-  k<NK, TH><<<148, TH>>>(out, reps, cyc);
+  k<NK, TH, SYNC><<<148, TH>>>(out, reps, cyc);
   cudaError_t e = cudaDeviceSynchronize();
   long long h[148];
   cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost);
   double instr = (double)reps * NK * 64 * (TH / 32);  // warp-instructions per SM
-  printf("threads %d body %6d instr = %6.1f KB: %.3f warp-instr/clk/SM (%s)\n", TH, NK * 64, NK * 1.0, instr / h[0], cudaGetErrorString(e));
+  printf("sync %d threads %d body %6d instr = %6.1f KB: %.3f warp-instr/clk/SM (%s)\n", (int)SYNC, TH, NK * 64, NK * 1.0, instr / h[0], cudaGetErrorString(e));
 }
 int main()
 {
   unsigned* out; long long* cyc;
   cudaMalloc(&out, 148 * 1024 * 4); cudaMalloc(&cyc, 148 * 8);
-  run<8,384>(out, cyc); run<9,384>(out, cyc); run<10,384>(out, cyc); run<11,384>(out, cyc); run<12,384>(out, cyc); run<13,384>(out, cyc); run<14,384>(out,cyc); run<15,384>(out,cyc); run<16,384>(out,cyc); run<20,384>(out,cyc);
+  run<24,384,true>(out, cyc); run<40,384,true>(out, cyc); run<48,384,true>(out, cyc); run<56,384,true>(out, cyc); run<64,384,true>(out, cyc); run<72,384,true>(out, cyc); run<80,384,true>(out, cyc); run<96,384,true>(out, cyc); run<112,384,true>(out, cyc); run<128,384,true>(out, cyc); run<144,384,true>(out, cyc); run<160,384,true>(out, cyc); run<192,384,true>(out, cyc); run<224,384,true>(out, cyc); run<256,384,true>(out, cyc); run<320,384,true>(out, cyc); run<384,384,true>(out, cyc);
   return 0;
 }
