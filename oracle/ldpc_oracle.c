@@ -74,7 +74,9 @@ int oracle_llr_promotion_sum(int a, int b)
   return t;
 }
 
-/* hard_decision, log_likelihood_ratio.cpp:225-248 + to_hard_bit log_likelihood_ratio.h:86: bit = (llr <= 0), MSB first. */
+/* hard_decision, log_likelihood_ratio.cpp:225-248 + to_hard_bit log_likelihood_ratio.h:86: bit = (llr <= 0), MSB first.
+ * The bits are written with bit_buffer::insert (adt/bit_buffer.h:95-140), which keeps the bits of the last byte that lie
+ * beyond the n-th bit as the caller left them. */
 void oracle_hard_decision(const int8_t* soft, unsigned n, uint8_t* out_packed)
 {
   unsigned nbytes = (n + 7) / 8;
@@ -85,6 +87,10 @@ void oracle_hard_decision(const int8_t* soft, unsigned n, uint8_t* out_packed)
       if (soft[8 * i + k] <= 0) {
         byte |= (uint8_t)(0x80U >> k);
       }
+    }
+    if (lim < 8) {
+      uint8_t keep = (uint8_t)(0xffU >> lim);
+      byte         = (uint8_t)(byte | (out_packed[i] & keep));
     }
     out_packed[i] = byte;
   }

@@ -24,6 +24,13 @@
 #include "srsran/srsvec/bit.h"
 #include "srsran/support/cpu_features.h"
 
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+// Second build of this shim (oracle/_ref/libdropin.so, see oracle/Makefile): the same test entry points, but the
+// variant name "cuda" selects the product's factories (srsran_project_23.5_b200/host/ldpc_cuda_factories.h), so that the
+// reference's UNMODIFIED pusch_decoder_impl / interfaces run on top of the B200 kernels. Used by tests/test_gpu_dropin.py.
+#include "../srsran_project_23.5_b200/host/ldpc_cuda_factories.h"
+#endif
+
 #include <atomic>
 #include <chrono>
 #include <cstring>
@@ -33,6 +40,26 @@
 using namespace srsran;
 
 namespace {
+
+std::shared_ptr<ldpc_decoder_factory> decoder_factory_of(const char* type)
+{
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (std::strcmp(type, "cuda") == 0) {
+    return create_ldpc_decoder_factory_cuda(0);
+  }
+#endif
+  return create_ldpc_decoder_factory_sw(type);
+}
+
+std::shared_ptr<ldpc_rate_dematcher_factory> dematcher_factory_of(const char* type)
+{
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (std::strcmp(type, "cuda") == 0) {
+    return create_ldpc_rate_dematcher_factory_cuda(0);
+  }
+#endif
+  return create_ldpc_rate_dematcher_factory_sw(type);
+}
 
 ldpc_base_graph_type to_bg(int bg)
 {
@@ -182,7 +209,7 @@ unsigned ref_crc_packed(const char* impl, int poly_code, const uint8_t* packed, 
 // Decoder (ldpc_decoder.h:44-74). One handle = one reference decoder object (stateful, not thread-safe).
 void* ref_decoder_create(const char* type)
 {
-  auto factory = create_ldpc_decoder_factory_sw(type);
+  auto factory = decoder_factory_of(type);
   if (!factory) {
     return nullptr;
   }
@@ -308,7 +335,7 @@ double ref_decoder_decode_batch_mt(const char*   type,
 // Rate dematcher (ldpc_rate_dematcher.h:52-55). out is the persistent in/out soft buffer of N_short * Z LLRs.
 void* ref_dematcher_create(const char* type)
 {
-  auto factory = create_ldpc_rate_dematcher_factory_sw(type);
+  auto factory = dematcher_factory_of(type);
   if (!factory) {
     return nullptr;
   }
@@ -467,8 +494,8 @@ void* ref_pusch_create(const char* decoder_type,
                        unsigned    max_nof_codeblocks,
                        unsigned    expire_timeout_slots)
 {
-  auto dec_f   = create_ldpc_decoder_factory_sw(decoder_type);
-  auto dem_f   = create_ldpc_rate_dematcher_factory_sw(dematcher_type);
+  auto dec_f   = decoder_factory_of(decoder_type);
+  auto dem_f   = dematcher_factory_of(dematcher_type);
   auto crc_f   = create_crc_calculator_factory_sw("auto");
   auto seg_f   = create_ldpc_segmenter_rx_factory_sw();
   auto decoder = dec_f ? dec_f->create() : nullptr;

@@ -455,10 +455,12 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   if (in_hi > in_lo) {
     CUDA_TRY(cudaMemcpyAsync(h->d_in, in + in_lo, in_hi - in_lo, cudaMemcpyHostToDevice, h->stream));
   }
-  // Output bytes a codeblock does not write (skip_decode, all-zero input with a CRC) must keep the caller's contents.
+  // Output bytes / bits a codeblock does not write (skip_decode, all-zero input with a CRC, the bits of the last byte
+  // beyond a message that is not a whole number of bytes) must keep the caller's contents.
   bool preserve = false;
   for (uint32_t i = 0; i != n && !preserve; ++i) {
-    preserve = descs[i].skip_decode || descs[i].crc_poly != LDPC_CUDA_CRC_NONE;
+    preserve = descs[i].skip_decode || descs[i].crc_poly != LDPC_CUDA_CRC_NONE ||
+               (bg_K(descs[i].base_graph) * descs[i].lifting_size) % 8 != 0;
   }
   if (preserve) {
     CUDA_TRY(cudaMemcpyAsync(h->d_out, out + out_lo, out_hi - out_lo, cudaMemcpyHostToDevice, h->stream));

@@ -254,8 +254,14 @@ __global__ void __launch_bounds__(384) ldpc_decode_scalar_kernel(GroupParams gp,
       }
     }
     // Output: the reference rewrites the bits after every checked iteration, so the last computed bits stand.
+    // bit_buffer::insert keeps the bits of the last byte beyond the message as the caller left them
     for (unsigned i = tid; i < msg_bytes; i += blockDim.x) {
-      out[i] = hard[i];
+      unsigned char v = hard[i];
+      if (i == msg_bytes - 1 && (msg_len & 7)) {
+        const unsigned char keep = (unsigned char)(0xffU >> (msg_len & 7));
+        v = (unsigned char)((v & ~keep) | (out[i] & keep));
+      }
+      out[i] = v;
     }
     if (tid == 0) {
       res.iterations = (unsigned short)it;

@@ -599,8 +599,14 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         auto finish = [&](const CbWork& w, CbResult& res, bool& done, const unsigned char* bits, bool ok) {
           if (ok || last) {
             uint8_t* out = p.out_base + w.out_offset;
+            // bit_buffer::insert keeps the bits of the last byte beyond the message as the caller left them
             for (unsigned i = t; i < msg_bytes; i += zpad) {
-              out[i] = bits[i];
+              unsigned char v = bits[i];
+              if (i == msg_bytes - 1 && (msg_len & 7)) {
+                const unsigned char keep = (unsigned char)(0xffU >> (msg_len & 7));
+                v = (unsigned char)((v & ~keep) | (out[i] & keep));
+              }
+              out[i] = v;
             }
             res.iterations = (unsigned short)it;
             res.crc_ok = ok ? 1 : 0;

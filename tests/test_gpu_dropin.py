@@ -1,0 +1,133 @@
+"""Drop-in tests: the reference's UNMODIFIED interfaces and pusch_decoder_impl, compiled from /root/reference into
+oracle/_ref/libdropin.so, run on top of the product's "cuda" factories (srsran_project_23.5_b200/host) and are compared
+with the same reference code on its own software factories. They follow the reference's own test procedures:
+  ldpc_enc_dec_test.cpp:249-320 (decode through ldpc_decoder::decode, zero / almost-zero LLRs),
+  ldpc_rm_test.cpp:176-192      (rate_dematch through ldpc_rate_dematcher::rate_dematch),
+  pusch_decoder_test.cpp:60-175 (real rx_softbuffer_pool, 4 HARQ transmissions rv {0,2,3,1}, iteration statistics).
+Marked gpu; needs oracle/_ref/libdropin.so (built in the build container, shipped to the GPU box)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import oracles as O
+
+pytestmark = pytest.mark.gpu
+
+DROPIN = os.path.join(O.ORACLE_DIR, "_ref", "libdropin.so")
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(DROPIN):
+        pytest.skip("oracle/_ref/libdropin.so was not built (no reference tree in the build container)")
+    return O.RefOracle(DROPIN)
+
+
+def test_factory_creates_decoder_and_dematcher(lib):
+    h = lib.lib.ref_decoder_create(b"cuda")
+    assert h, "create_ldpc_decoder_factory_cuda()->create() returned nullptr on a GPU box"
+    lib.lib.ref_decoder_destroy(h)
+    h = lib.lib.ref_dematcher_create(b"cuda")
+    assert h
+    lib.lib.ref_dematcher_destroy(h)
+
+
+@pytest.mark.parametrize("bg,Z", [(1, 384), (1, 52), (2, 384), (2, 9), (1, 2)])
+def test_ldpc_decoder_interface(lib, bg, Z):
+    """LDPCDecTest: noiseless +-10 LLRs, 1 iteration, several codeblock lengths -> decoded == message; then noisy
+    codewords with every CRC through optional<unsigned> decode(...): value / nullopt, iterations and bits identical."""
+    rng = np.random.default_rng(100 * bg + Z)
+    K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+    msg, cw = O.make_codeword(rng, bg, Z)
+    llr = (10 * (1 - 2 * cw.astype(np.int16))).astype(np.int8)
+    for nodes in (K + 2, (K + 2 + Ns) // 2, Ns):
+        want, wit = lib.decode(bg, Z, llr[:nodes * Z], max_iters=1, kind="generic")
+        got, git = lib.decode(bg, Z, llr[:nodes * Z], max_iters=1, kind="cuda")
+        assert (got == want).all() and git == wit
+        assert (got == O.msg_to_packed(msg)).all()
+    for crc in (O.CRC16, O.CRC24A, O.CRC24B):
+        if K * Z <= 48:
+            continue
+        for esn0 in (-0.5, -2.0, -6.0):
+            msg, cw = O.make_codeword(rng, bg, Z, 0, crc)
+            x = O.awgn_llrs(rng, cw, esn0 - (2.5 if bg == 2 else 0.0))
+            want, wit = lib.decode(bg, Z, x, crc=crc, kind="generic", out_init=0x11)
+            got, git = lib.decode(bg, Z, x, crc=crc, kind="cuda", out_init=0x11)
+            assert git == wit, (bg, Z, crc, esn0, git, wit)
+            assert (got == want).all()
+    # LDPCDecTestZeroLLR / AlmostZeroLLR
+    zero = np.zeros(Ns * Z, np.int8)
+    got, git = lib.decode(bg, Z, zero, kind="cuda")
+    assert git == 0 and (np.unpackbits(got)[:K * Z] == 1).all()
+    x = zero.copy()
+    x[(K + 2) * Z + 2::3] = 1
+    want, _ = lib.decode(bg, Z, x, kind="generic")
+    got, _ = lib.decode(bg, Z, x, kind="cuda")
+    assert (got == want).all()
+
+
+@pytest.mark.parametrize("case", [(1, 16, 300, 0, 2, 0, 12), (1, 16, 2000, 0, 2, 700, 12), (1, 16, 1536, 3, 6, 0, 28),
+                                  (2, 12, 704, 2, 8, 0, 0), (1, 384, 8960, 0, 8, 0, 16), (1, 384, 30000, 3, 2, 16896, 40)])
+def test_ldpc_rate_dematcher_interface(lib, case):
+    bg, Z, E, rv, Qm, Nref, F = case
+    rng = np.random.default_rng(sum(case))
+    N = O.BG_N_SHORT[bg] * Z
+    llr_in = rng.integers(-120, 121, E).astype(np.int8)
+    a, b = np.zeros(N, np.int8), np.zeros(N, np.int8)  # pool memory starts at zero (rx_softbuffer_codeblock_pool.h)
+    for new_data in (True, False, False):
+        lib.rate_dematch(a, llr_in, new_data, bg, Z, rv, Qm, Nref, F, kind="generic")
+        lib.rate_dematch(b, llr_in, new_data, bg, Z, rv, Qm, Nref, F, kind="cuda")
+        assert (a == b).all(), (case, new_data)
+
+
+def _pusch(lib, h, slot, tb_bytes, llrs, bg, rv, Qm, nof_layers, iters, early_stop, new_data, rnti=0x4601, harq=3):
+    tb = np.zeros(tb_bytes, np.uint8)
+    stats = np.zeros(6, np.uint32)
+    llrs = np.ascontiguousarray(llrs, np.int8)
+    rc = lib.lib.ref_pusch_decode(h, slot, rnti, harq, tb.ctypes.data_as(ctypes.c_void_p), tb_bytes,
+                                  llrs.ctypes.data_as(ctypes.c_void_p), llrs.size, bg, rv, Qm, 0, nof_layers, iters,
+                                  int(early_stop), int(new_data), 1, stats.ctypes.data_as(ctypes.c_void_p))
+    assert rc == 0
+    return tb, stats
+
+
+# Transport block sizes follow TS 38.214 5.1.3.2 (TBS + 24 is a multiple of 8 C): srsvec::copy_offset of the reference
+# (lib/srsvec/bit.cpp:333-358) restarts at bit 0 after its byte-aligned fast path, so pusch_decoder_impl loses the last
+# (payload % 8) bits of the first codeblock for any other size - 3GPP sizes never trigger it.
+@pytest.mark.parametrize("bg,tbs_bytes,Qm,nsym,esn0", [(1, 4001, 4, 12000, -1.0), (2, 300, 2, 2400, -4.5),
+                                                      (1, 20004, 6, 42588, 2.0), (2, 1905, 4, 6000, -3.0)])
+@pytest.mark.parametrize("early_stop", [True, False])
+def test_pusch_decoder_harq_through_reference_pusch_decoder_impl(lib, bg, tbs_bytes, Qm, nsym, esn0, early_stop):
+    """pusch_decoder_test.cpp:144-175 with the reference's pusch_decoder_impl on top of (a) its own generic factories and
+    (b) the cuda factories: TB bytes, tb_crc_ok and the iteration statistics must agree for every transmission."""
+    rng = np.random.default_rng(tbs_bytes + Qm)
+    nof_layers = 1
+    tb = rng.integers(0, 256, tbs_bytes).astype(np.uint8)
+    segs = lib.segment_tx(tb, bg, Qm, nof_layers, nsym)
+    meta = lib.segment_rx(tbs_bytes * 8, bg, Qm, nof_layers, nsym)
+    assert segs is not None and meta is not None and len(meta) == len(segs)
+    h_sw = lib.lib.ref_pusch_create(b"generic", b"generic", 4, 64, 100)
+    h_cu = lib.lib.ref_pusch_create(b"cuda", b"cuda", 4, 64, 100)
+    assert h_sw and h_cu
+    seen_fail = seen_ok = False
+    for i, rv in enumerate([0, 2, 3, 1]):
+        parts = []
+        for c in range(len(segs)):
+            Z, N, E, F = int(meta[c, 0]), int(meta[c, 1]), int(meta[c, 2]), int(meta[c, 3])
+            K = O.BG_K[bg] * Z
+            cw = lib.encode(bg, Z, segs[c, :K])
+            parts.append(lib.rate_match(cw, E, bg, Z, rv, Qm, 0, F))
+        llrs = O.awgn_llrs(rng, np.concatenate(parts), esn0)
+        want_tb, want_st = _pusch(lib, h_sw, 10 + i, tbs_bytes, llrs, bg, rv, Qm, nof_layers, 6, early_stop, i == 0)
+        got_tb, got_st = _pusch(lib, h_cu, 10 + i, tbs_bytes, llrs, bg, rv, Qm, nof_layers, 6, early_stop, i == 0)
+        assert (want_st == got_st).all(), (i, rv, want_st, got_st)
+        if want_st[0]:
+            assert (got_tb == want_tb).all() and (got_tb == tb).all()
+            seen_ok = True
+            break  # the soft buffer is released on success (uplink_processor_impl.cpp:168-170)
+        seen_fail = True
+    assert seen_ok
+    lib.lib.ref_pusch_destroy(h_sw)
+    lib.lib.ref_pusch_destroy(h_cu)

@@ -77,6 +77,15 @@ def test_decode_zero_almost_zero_and_untouched_output(dec):
         assert (np.unpackbits(bits)[:K * Z] == 1).all()
 
 
+def test_decode_keeps_padding_bits_of_last_output_byte(dec):
+    rng = np.random.default_rng(6)
+    for bg, Z in [(2, 9), (1, 2), (2, 3), (1, 6), (2, 15)]:
+        msg, cw = O.make_codeword(rng, bg, Z)
+        llr = O.awgn_llrs(rng, cw, 0.0)
+        for out_init in (0x00, 0xFF, 0x5A):
+            check_decode(dec, bg, Z, llr, out_init=out_init)
+
+
 def test_decode_trailing_zeros_and_ragged_lengths(dec):
     rng = np.random.default_rng(7)
     for bg, Z in [(1, 96), (2, 72)]:

@@ -102,6 +102,19 @@ def _decode_both(bg, Z, llr, **kw):
     return out_p, it_p
 
 
+def test_decoder_keeps_padding_bits_of_last_output_byte():
+    # bit_buffer::insert (adt/bit_buffer.h:95-140) leaves the bits beyond bg_K * Z in the last byte as the caller had them.
+    rng = np.random.default_rng(6)
+    for bg, Z in [(2, 9), (1, 2), (2, 3), (1, 6), (2, 15)]:
+        assert (O.BG_K[bg] * Z) % 8 != 0
+        msg, cw = O.make_codeword(rng, bg, Z)
+        llr = O.awgn_llrs(rng, cw, 0.0)
+        for out_init in (0x00, 0xFF, 0x5A):
+            out, _ = _decode_both(bg, Z, llr, out_init=out_init)
+            pad = 8 - (O.BG_K[bg] * Z) % 8
+            assert out[-1] & ((1 << pad) - 1) == out_init & ((1 << pad) - 1)
+
+
 @pytest.mark.parametrize("bg", [1, 2])
 def test_decoder_noiseless_all_lifting_sizes(bg):
     # LDPCDecTest, ldpc_enc_dec_test.cpp:249-279: +-10 LLRs, 1 iteration, several shortened lengths.
