@@ -23,6 +23,8 @@ using namespace ldpc_b200;
     }                                                                                                        \
   } while (0)
 
+constexpr unsigned MAX_CHUNKS = 16;
+
 struct ldpc_cuda_handle {
   int device = 0;
   int sm_count = 0;
@@ -33,7 +35,12 @@ struct ldpc_cuda_handle {
   unsigned char scale_lut[121];
   int packed_scale = TM_SCALE_NONE;  // closed-form scaling usable by the packed (TMEM-message) kernel
   CbWork* d_work = nullptr;
-  CbWork* h_work = nullptr;  // pinned
+  CbWork* h_work[2] = {nullptr, nullptr};  // pinned, double-buffered: staging of call k overlaps the kernels of call k-1
+  cudaEvent_t ev_work[2] = {nullptr, nullptr};
+  unsigned work_slot = 0;
+  // host-buffer entries: input copies, kernels and output copies of consecutive chunks overlap
+  cudaStream_t stream2 = nullptr, h2d_stream = nullptr, d2h_stream = nullptr;
+  cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_done[MAX_CHUNKS] = {}, ev_misc = nullptr;
   CbResult* d_results = nullptr;
   int8_t* d_in = nullptr;
   size_t d_in_cap = 0;
@@ -141,11 +148,11 @@ GroupParams make_group(const ldpc_cuda_handle* h, int bg, int Z)
 }
 
 int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_llr,
-                        uint8_t* d_out, CbResult* d_res)
+                        uint8_t* d_out, CbResult* d_res, cudaStream_t stream, unsigned* pair_counter)
 {
   GroupParams gp = make_group(h, bg, Z);
   if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != TM_SCALE_NONE) {
-    int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, h->pair_counter, h->sm_count, h->stream);
+    int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, pair_counter, h->sm_count, stream);
     if (rc == 0) {
       h->launches += 1;
       return LDPC_CUDA_OK;
@@ -163,16 +170,17 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
   }
   const int threads = std::max(32, ((Z + 31) / 32) * 32);
   const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 8u);
-  ldpc_decode_scalar_kernel<<<grid, threads, smem, h->stream>>>(gp, d_work, n, d_llr, d_out, d_res);
+  ldpc_decode_scalar_kernel<<<grid, threads, smem, stream>>>(gp, d_work, n, d_llr, d_out, d_res);
   CUDA_TRY(cudaGetLastError());
   h->launches += 1;
   return LDPC_CUDA_OK;
 }
 
-int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_rm)
+int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_rm,
+                         cudaStream_t stream)
 {
   const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 16u);
-  ldpc_dematch_kernel<<<grid, 256, 0, h->stream>>>(bg, Z, d_work, n, d_rm, h->arena);
+  ldpc_dematch_kernel<<<grid, 256, 0, stream>>>(bg, Z, d_work, n, d_rm, h->arena);
   CUDA_TRY(cudaGetLastError());
   h->launches += 1;
   return LDPC_CUDA_OK;
@@ -199,10 +207,14 @@ int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
     }
   }
   group_codeblocks(h, n, descs);
+  // The pinned work array of this slot was last read by the upload of the call before the previous one.
+  const unsigned slot = (h->work_slot++) & 1u;
+  CUDA_TRY(cudaEventSynchronize(h->ev_work[slot]));
+  CbWork* h_work = h->h_work[slot];
   for (uint32_t k = 0; k != n; ++k) {
     const uint32_t i = h->order[k];
     const ldpc_cuda_cb_desc& d = descs[i];
-    CbWork& w = h->h_work[k];
+    CbWork& w = h_work[k];
     std::memset(&w, 0, sizeof(w));
     w.in_offset = fused ? d.soft_offset : d.in_offset;
     w.out_offset = d.out_offset;
@@ -219,7 +231,8 @@ int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
     w.skip_decode = fused ? d.skip_decode : 0;
     w.result_index = i;
   }
-  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work, sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h_work, sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaEventRecord(h->ev_work[slot], h->stream));
   return LDPC_CUDA_OK;
 }
 
@@ -232,13 +245,15 @@ int run_groups(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
     const ldpc_cuda_cb_desc& d0 = descs[h->order[b]];
     int rc;
     if (fused) {
-      rc = launch_dematch_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in);
+      rc = launch_dematch_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, h->stream);
       if (rc != LDPC_CUDA_OK) {
         return rc;
       }
-      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, h->arena, d_out, d_res);
+      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, h->arena, d_out, d_res, h->stream,
+                               h->pair_counter);
     } else {
-      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, d_out, d_res);
+      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, d_out, d_res, h->stream,
+                               h->pair_counter);
     }
     if (rc != LDPC_CUDA_OK) {
       return rc;
@@ -315,7 +330,18 @@ int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblo
   }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaMalloc(&h->d_work, sizeof(CbWork) * max_codeblocks));
-  CUDA_TRY(cudaMallocHost(&h->h_work, sizeof(CbWork) * max_codeblocks));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+  for (int i = 0; i != 2; ++i) {
+    CUDA_TRY(cudaMallocHost(&h->h_work[i], sizeof(CbWork) * max_codeblocks));
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_work[i], cudaEventDisableTiming));
+  }
+  for (unsigned i = 0; i != MAX_CHUNKS; ++i) {
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+  }
+  CUDA_TRY(cudaEventCreateWithFlags(&h->ev_misc, cudaEventDisableTiming));
   CUDA_TRY(cudaMalloc(&h->d_results, sizeof(CbResult) * max_codeblocks));
   CUDA_TRY(cudaMalloc(&h->pair_counter, 64));
   ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
@@ -333,7 +359,29 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
     cudaStreamSynchronize(h->stream);
   }
   cudaFree(h->d_work);
-  cudaFreeHost(h->h_work);
+  for (cudaStream_t st : {h->stream2, h->h2d_stream, h->d2h_stream}) {
+    if (st) {
+      cudaStreamSynchronize(st);
+      cudaStreamDestroy(st);
+    }
+  }
+  for (int i = 0; i != 2; ++i) {
+    cudaFreeHost(h->h_work[i]);
+    if (h->ev_work[i]) {
+      cudaEventDestroy(h->ev_work[i]);
+    }
+  }
+  for (unsigned i = 0; i != MAX_CHUNKS; ++i) {
+    if (h->ev_in[i]) {
+      cudaEventDestroy(h->ev_in[i]);
+    }
+    if (h->ev_done[i]) {
+      cudaEventDestroy(h->ev_done[i]);
+    }
+  }
+  if (h->ev_misc) {
+    cudaEventDestroy(h->ev_misc);
+  }
   cudaFree(h->d_results);
   cudaFree(h->d_in);
   cudaFree(h->d_out);
@@ -394,8 +442,6 @@ int ldpc_cuda_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cu
     return LDPC_CUDA_OK;
   }
   CUDA_TRY(cudaSetDevice(h->device));
-  // The pinned work array is reused by every call: wait for the previous upload to be consumed.
-  CUDA_TRY(cudaStreamSynchronize(h->stream));
   int rc = stage_work(h, n, descs, false);
   if (rc != LDPC_CUDA_OK) {
     return rc;
@@ -414,7 +460,6 @@ int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const
     return LDPC_CUDA_OK;
   }
   CUDA_TRY(cudaSetDevice(h->device));
-  CUDA_TRY(cudaStreamSynchronize(h->stream));
   int rc = stage_work(h, n, descs, true);
   if (rc != LDPC_CUDA_OK) {
     return rc;
@@ -423,6 +468,63 @@ int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const
 }
 
 // ---- batched, host buffers ------------------------------------------------------------------------------------------
+// A chunk = consecutive codeblocks (in launch order) of one (BG, Z) group whose input / output byte ranges are copied and
+// decoded as a unit.
+struct Chunk {
+  uint32_t b, e;            // range in launch order
+  uint64_t in_lo, in_hi;    // host input bytes
+  uint64_t out_lo, out_hi;  // host output bytes
+};
+
+static inline void cb_ranges(const ldpc_cuda_cb_desc& d, bool fused, uint64_t& in_end, uint64_t& out_end)
+{
+  in_end = d.in_offset + (fused ? d.rm_length : d.in_length);
+  out_end = d.out_offset + ((uint64_t)bg_K(d.base_graph) * d.lifting_size + 7) / 8;
+}
+
+// Splits the staged groups into at most MAX_CHUNKS chunks of about equal input size. Chunks are only formed when the
+// caller's layout is monotone in launch order (every codeblock's input and output ranges lie behind its predecessor's),
+// so that the byte ranges of different chunks are disjoint; otherwise each group is one chunk over the whole span.
+static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused,
+                        std::vector<Chunk>& chunks)
+{
+  chunks.clear();
+  bool monotone = true;
+  uint64_t in_prev = 0, out_prev = 0, in_lo = ~0ull, in_hi = 0, out_lo = ~0ull, out_hi = 0;
+  for (uint32_t k = 0; k != n; ++k) {
+    const ldpc_cuda_cb_desc& d = descs[h->order[k]];
+    uint64_t ie, oe;
+    cb_ranges(d, fused, ie, oe);
+    monotone = monotone && (k == 0 || (d.in_offset >= in_prev && d.out_offset >= out_prev));
+    in_prev = ie, out_prev = oe;
+    in_lo = std::min(in_lo, d.in_offset), in_hi = std::max(in_hi, ie);
+    out_lo = std::min(out_lo, d.out_offset), out_hi = std::max(out_hi, oe);
+  }
+  const size_t nof_groups = h->group_begin.size() - 1;
+  const uint64_t total_in = in_hi - in_lo;
+  constexpr uint64_t MIN_CHUNK_BYTES = 8ull << 20;
+  if (!monotone || 2 * nof_groups > MAX_CHUNKS || total_in < 2 * MIN_CHUNK_BYTES) {
+    chunks.push_back({0, n, in_lo, in_hi, out_lo, out_hi});  // one copy in, all launches, one copy out
+    return;
+  }
+  // a chunk closes when it reaches the target size or at the end of its group: at most MAX_CHUNKS chunks
+  const uint64_t by_size = MAX_CHUNKS - nof_groups;
+  const uint64_t target = std::max<uint64_t>(MIN_CHUNK_BYTES, (total_in + by_size - 1) / by_size);
+  for (size_t g = 0; g != nof_groups; ++g) {
+    uint32_t b = h->group_begin[g];
+    const uint32_t ge = h->group_begin[g + 1];
+    while (b != ge) {
+      Chunk c = {b, b, descs[h->order[b]].in_offset, 0, descs[h->order[b]].out_offset, 0};
+      do {
+        cb_ranges(descs[h->order[c.e]], fused, c.in_hi, c.out_hi);
+        ++c.e;
+      } while (c.e != ge && (c.in_hi - c.in_lo < target || chunks.size() + 1 == MAX_CHUNKS));
+      chunks.push_back(c);
+      b = c.e;
+    }
+  }
+}
+
 static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in, uint8_t* out,
                       ldpc_cuda_cb_result* results, bool fused)
 {
@@ -434,26 +536,23 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
     return LDPC_CUDA_OK;
   }
   CUDA_TRY(cudaSetDevice(h->device));
-  CUDA_TRY(cudaStreamSynchronize(h->stream));
   int rc = stage_work(h, n, descs, fused);
   if (rc != LDPC_CUDA_OK) {
     return rc;
   }
-  // One H2D for the span of inputs and one D2H for the span of outputs (callers lay codeblocks out densely).
-  uint64_t in_lo = ~0ull, in_hi = 0, out_lo = ~0ull, out_hi = 0;
-  for (uint32_t i = 0; i != n; ++i) {
-    const ldpc_cuda_cb_desc& d = descs[i];
-    const uint64_t len = fused ? d.rm_length : d.in_length;
-    const uint64_t ob = ((uint64_t)bg_K(d.base_graph) * d.lifting_size + 7) / 8;
-    in_lo = std::min(in_lo, d.in_offset), in_hi = std::max(in_hi, d.in_offset + len);
-    out_lo = std::min(out_lo, d.out_offset), out_hi = std::max(out_hi, d.out_offset + ob);
+  std::vector<Chunk> chunks;
+  plan_chunks(h, n, descs, fused, chunks);
+  if (chunks.empty() || chunks.size() > MAX_CHUNKS) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  const uint64_t in_lo = chunks.front().in_lo, out_lo = chunks.front().out_lo;
+  uint64_t in_hi = 0, out_hi = 0;
+  for (const Chunk& c : chunks) {
+    in_hi = std::max(in_hi, c.in_hi), out_hi = std::max(out_hi, c.out_hi);
   }
   rc = ensure_capacity(h, in_hi - in_lo, out_hi - out_lo);
   if (rc != LDPC_CUDA_OK) {
     return rc;
-  }
-  if (in_hi > in_lo) {
-    CUDA_TRY(cudaMemcpyAsync(h->d_in, in + in_lo, in_hi - in_lo, cudaMemcpyHostToDevice, h->stream));
   }
   // Output bytes / bits a codeblock does not write (skip_decode, all-zero input with a CRC, the bits of the last byte
   // beyond a message that is not a whole number of bytes) must keep the caller's contents.
@@ -462,15 +561,56 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
     preserve = descs[i].skip_decode || descs[i].crc_poly != LDPC_CUDA_CRC_NONE ||
                (bg_K(descs[i].base_graph) * descs[i].lifting_size) % 8 != 0;
   }
-  if (preserve) {
-    CUDA_TRY(cudaMemcpyAsync(h->d_out, out + out_lo, out_hi - out_lo, cudaMemcpyHostToDevice, h->stream));
+  const int8_t* d_in0 = h->d_in - in_lo;   // device address of host input byte 0
+  uint8_t* d_out0 = h->d_out - out_lo;     // device address of host output byte 0
+  // work list upload + result reset on the main stream come first; the copy streams start behind earlier work
+  CUDA_TRY(cudaMemsetAsync(h->d_results, 0, sizeof(CbResult) * n, h->stream));
+  CUDA_TRY(cudaEventRecord(h->ev_misc, h->stream));
+  CUDA_TRY(cudaStreamWaitEvent(h->h2d_stream, h->ev_misc, 0));
+  CUDA_TRY(cudaStreamWaitEvent(h->stream2, h->ev_misc, 0));
+  for (size_t ci = 0; ci != chunks.size(); ++ci) {
+    const Chunk& c = chunks[ci];
+    if (c.in_hi > c.in_lo) {
+      CUDA_TRY(cudaMemcpyAsync(h->d_in + (c.in_lo - in_lo), in + c.in_lo, c.in_hi - c.in_lo, cudaMemcpyHostToDevice,
+                               h->h2d_stream));
+    }
+    if (preserve) {
+      CUDA_TRY(cudaMemcpyAsync(h->d_out + (c.out_lo - out_lo), out + c.out_lo, c.out_hi - c.out_lo,
+                               cudaMemcpyHostToDevice, h->h2d_stream));
+    }
+    CUDA_TRY(cudaEventRecord(h->ev_in[ci], h->h2d_stream));
+    // kernels of consecutive chunks alternate between two streams (and two work counters) so that the blocks of chunk
+    // c + 1 fill the SMs as the last blocks of chunk c retire
+    cudaStream_t ks = (ci & 1) ? h->stream2 : h->stream;
+    CUDA_TRY(cudaStreamWaitEvent(ks, h->ev_in[ci], 0));
+    // a chunk spans several groups only in the single-chunk fallback
+    for (size_t g = 0; g + 1 < h->group_begin.size(); ++g) {
+      const uint32_t b = std::max(c.b, h->group_begin[g]), e = std::min(c.e, h->group_begin[g + 1]);
+      if (b >= e) {
+        continue;
+      }
+      const ldpc_cuda_cb_desc& dg = descs[h->order[b]];
+      if (fused) {
+        rc = launch_dematch_group(h, dg.base_graph, dg.lifting_size, h->d_work + b, e - b, d_in0, ks);
+        if (rc != LDPC_CUDA_OK) {
+          return rc;
+        }
+      }
+      rc = launch_decode_group(h, dg.base_graph, dg.lifting_size, h->d_work + b, e - b, fused ? h->arena : d_in0, d_out0,
+                               h->d_results, ks, h->pair_counter + (ci & 1));
+      if (rc != LDPC_CUDA_OK) {
+        return rc;
+      }
+    }
+    CUDA_TRY(cudaEventRecord(h->ev_done[ci], ks));
+    CUDA_TRY(cudaStreamWaitEvent(h->d2h_stream, h->ev_done[ci], 0));
+    CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo, cudaMemcpyDeviceToHost,
+                             h->d2h_stream));
   }
-  rc = run_groups(h, n, descs, fused, h->d_in - in_lo, h->d_out - out_lo, h->d_results);
-  if (rc != LDPC_CUDA_OK) {
-    return rc;
-  }
-  CUDA_TRY(cudaMemcpyAsync(out + out_lo, h->d_out, out_hi - out_lo, cudaMemcpyDeviceToHost, h->stream));
-  CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->d2h_stream));
+  CUDA_TRY(cudaStreamSynchronize(h->d2h_stream));
+  // everything of this call has finished (the last copy waited for every kernel); later calls may use any stream
+  CUDA_TRY(cudaStreamSynchronize(h->stream2));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   return LDPC_CUDA_OK;
 }
@@ -529,11 +669,11 @@ int ldpc_cuda_rate_dematch(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, i
     return rc;
   }
   d_soft = h->d_in, d_rm = h->d_in + ((N + 63) & ~(size_t)63);
-  CbWork& w = h->h_work[0];
+  CbWork& w = h->h_work[0][0];  // the stream is idle (synchronised above), both slots are free
   std::memset(&w, 0, sizeof(w));
   w.rm_length = desc->rm_length, w.Nref = desc->Nref, w.nof_filler_bits = desc->nof_filler_bits;
   w.rv = desc->rv, w.mod_order = desc->mod_order, w.new_data = desc->new_data;
-  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work, sizeof(CbWork), cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work[0], sizeof(CbWork), cudaMemcpyHostToDevice, h->stream));
   CUDA_TRY(cudaMemcpyAsync(d_soft, soft_inout, N, cudaMemcpyHostToDevice, h->stream));
   if (desc->rm_length) {
     CUDA_TRY(cudaMemcpyAsync(d_rm, in, desc->rm_length, cudaMemcpyHostToDevice, h->stream));
