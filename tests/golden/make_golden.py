@@ -27,7 +27,7 @@ DECODE_CASES = [
 DEMATCH_CASES = [
     (1, 16, 300, 0, 2, 0, 12, 2), (1, 16, 2000, 0, 2, 700, 12, 1), (1, 16, 300, 2, 2, 0, 12, 1), (2, 12, 704, 2, 8, 0, 0, 2),
     (1, 384, 8960, 0, 8, 0, 16, 3), (1, 384, 8992, 3, 8, 0, 16, 1), (1, 384, 30000, 1, 2, 16896, 40, 1),
-    (2, 384, 6000, 0, 6, 0, 0, 3), (1, 56, 1400, 3, 4, 1000, 12, 2), (2, 9, 200, 1, 1, 0, 0, 2),
+    (2, 384, 6000, 0, 6, 0, 0, 3), (1, 56, 1400, 3, 4, 2000, 12, 2), (2, 9, 200, 1, 1, 0, 0, 2),
 ]
 
 
