@@ -147,12 +147,18 @@ GroupParams make_group(const ldpc_cuda_handle* h, int bg, int Z)
   return gp;
 }
 
+int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_rm,
+                         cudaStream_t stream);
+
+// d_rm != nullptr: fused entry - d_llr is the soft-buffer arena and the group is rate-dematched / combined first, inside
+// the decoder's prologue (fast kernel) or by the stand-alone dematch kernel in front of the general decoder.
 int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_llr,
-                        uint8_t* d_out, CbResult* d_res, cudaStream_t stream, unsigned* pair_counter)
+                        const int8_t* d_rm, uint8_t* d_out, CbResult* d_res, cudaStream_t stream, unsigned* pair_counter)
 {
   GroupParams gp = make_group(h, bg, Z);
   if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != TM_SCALE_NONE) {
-    int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_out, d_res, pair_counter, h->sm_count, stream);
+    int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_rm, d_out, d_res, pair_counter, h->sm_count,
+                                stream);
     if (rc == 0) {
       h->launches += 1;
       return LDPC_CUDA_OK;
@@ -161,6 +167,12 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
       return LDPC_CUDA_ERR_CUDA;
     }
     // rc > 0: configuration not covered by the packed kernel -> general kernel below
+  }
+  if (d_rm != nullptr) {
+    int rc = launch_dematch_group(h, bg, Z, d_work, n, d_rm, stream);
+    if (rc != LDPC_CUDA_OK) {
+      return rc;
+    }
   }
   const size_t smem = scalar_kernel_smem_bytes(bg, Z);
   static bool attr_set = false;
@@ -243,18 +255,8 @@ int run_groups(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
   for (size_t g = 0; g + 1 < h->group_begin.size(); ++g) {
     const uint32_t b = h->group_begin[g], e = h->group_begin[g + 1];
     const ldpc_cuda_cb_desc& d0 = descs[h->order[b]];
-    int rc;
-    if (fused) {
-      rc = launch_dematch_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, h->stream);
-      if (rc != LDPC_CUDA_OK) {
-        return rc;
-      }
-      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, h->arena, d_out, d_res, h->stream,
-                               h->pair_counter);
-    } else {
-      rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, d_in, d_out, d_res, h->stream,
-                               h->pair_counter);
-    }
+    const int rc = launch_decode_group(h, d0.base_graph, d0.lifting_size, h->d_work + b, e - b, fused ? h->arena : d_in,
+                                       fused ? d_in : nullptr, d_out, d_res, h->stream, h->pair_counter);
     if (rc != LDPC_CUDA_OK) {
       return rc;
     }
@@ -590,14 +592,8 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
         continue;
       }
       const ldpc_cuda_cb_desc& dg = descs[h->order[b]];
-      if (fused) {
-        rc = launch_dematch_group(h, dg.base_graph, dg.lifting_size, h->d_work + b, e - b, d_in0, ks);
-        if (rc != LDPC_CUDA_OK) {
-          return rc;
-        }
-      }
-      rc = launch_decode_group(h, dg.base_graph, dg.lifting_size, h->d_work + b, e - b, fused ? h->arena : d_in0, d_out0,
-                               h->d_results, ks, h->pair_counter + (ci & 1));
+      rc = launch_decode_group(h, dg.base_graph, dg.lifting_size, h->d_work + b, e - b, fused ? h->arena : d_in0,
+                               fused ? d_in0 : nullptr, d_out0, h->d_results, ks, h->pair_counter + (ci & 1));
       if (rc != LDPC_CUDA_OK) {
         return rc;
       }

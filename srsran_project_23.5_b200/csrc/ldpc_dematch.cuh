@@ -90,13 +90,34 @@ __device__ __forceinline__ int dematch_input(const DematchGeom& g, const int8_t*
   return in[i * g.Qm + j];
 }
 
-// Final content of soft-buffer position p given its previous content.
-__device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8_t* __restrict__ in, unsigned p, int prev)
+// Where soft-buffer position p sits in the walk: its rank r in the stream of de-interleaved input elements (the first
+// element that lands on it; later laps add V each), whether it lies before the start position (first reached in lap 1)
+// and whether the walk reaches it at all.
+struct DematchRank {
+  unsigned r;
+  bool before_start;
+  bool live;  // not a filler and inside the circular buffer
+};
+
+__device__ __forceinline__ DematchRank dematch_rank(const DematchGeom& g, unsigned p)
+{
+  DematchRank d;
+  const bool is_filler = (p >= g.info && p < g.sys);
+  d.live = !is_filler && p < g.Ncb;
+  const unsigned L = dematch_linear(g, p);
+  d.before_start = L < g.Ls0;
+  d.r = d.before_start ? (L + g.V - g.Ls0) : (L - g.Ls0);
+  return d;
+}
+
+// Final content of soft-buffer position p given its previous content and x0 = input element d.r (ignored when d.r >= E).
+// Split from dematch_rank so that a caller can issue the loads of many positions before combining any of them.
+__device__ __forceinline__ int dematch_combine(const DematchGeom& g, const int8_t* __restrict__ in, unsigned p, int prev,
+                                               const DematchRank& d, int x0)
 {
   int v = prev;
-  const bool is_filler = (p >= g.info && p < g.sys);
   if (g.new_data && g.E != 0) {
-    if (is_filler) {
+    if (p >= g.info && p < g.sys) {
       return LLR_INF;
     }
     // zeroing done by the first loop pass before it copies
@@ -104,25 +125,23 @@ __device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8
       v = 0;
     }
   }
-  if (!is_filler && p < g.Ncb) {
-    const unsigned L = dematch_linear(g, p);
-    const bool before_start = L < g.Ls0;
-    unsigned r = before_start ? (L + g.V - g.Ls0) : (L - g.Ls0);
-    bool first = true;
-    for (; r < g.E; r += g.V) {
-      const int x = dematch_input(g, in, r);
-      if (first && g.new_data && !before_start) {
-        v = x;  // copy in the first lap
-      } else {
-        v = llr_add(v, x);
-      }
-      first = false;
+  if (d.live && d.r < g.E) {
+    v = (g.new_data && !d.before_start) ? x0 : llr_add(v, x0);  // copy in the first lap, combine otherwise
+    for (unsigned r = d.r + g.V; r < g.E; r += g.V) {
+      v = llr_add(v, dematch_input(g, in, r));
     }
   }
   if (p >= g.zero_from) {
     v = 0;
   }
   return v;
+}
+
+__device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8_t* __restrict__ in, unsigned p, int prev)
+{
+  const DematchRank d = dematch_rank(g, p);
+  const int x0 = (d.live && d.r < g.E) ? dematch_input(g, in, d.r) : 0;
+  return dematch_combine(g, in, p, prev, d, x0);
 }
 
 // Standalone kernel: one block per codeblock, threads stride over the N positions (coalesced read-modify-write).

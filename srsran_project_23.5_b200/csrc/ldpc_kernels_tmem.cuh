@@ -35,6 +35,7 @@
 #include <cuda_fp16.h>
 
 #include "ldpc_device.cuh"
+#include "ldpc_dematch.cuh"
 
 namespace ldpc_b200 {
 
@@ -50,7 +51,9 @@ struct __align__(8) TmEdge {
 
 struct TmemParams {
   const CbWork* work;
-  const int8_t* llr_base;
+  const int8_t* llr_base;   // decoder input LLRs; fused: the soft-buffer arena (same memory as soft_rw)
+  const int8_t* rm_base;    // fused: rate-matched LLRs of the batch
+  int8_t* soft_rw;          // fused: the soft-buffer arena, updated in place by the prologue
   uint8_t* out_base;
   CbResult* results;
   unsigned* pair_counter;  // dynamic distribution of codeblock pairs over the groups of all blocks
@@ -400,7 +403,10 @@ __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
 }
 constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base address written by tcgen05.alloc
 
-template <int BG, int SCALE>
+// FUSED: the prologue is the rate dematcher (ldpc_rate_dematcher_impl.cpp:43-254): every soft-buffer position is combined
+// with the new transmission in the HBM arena and handed to the decoder in the same pass (no separate kernel, the soft
+// buffer is read once and written once).
+template <int BG, int SCALE, bool FUSED>
 __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
 {
   constexpr int K = (BG == 2) ? 10 : 22, M = (BG == 2) ? LDPC_BG2_M : LDPC_BG1_M, HRR = K + 4;
@@ -462,7 +468,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     const CbWork wA = p.work[2 * pair];
     const CbWork wB = p.work[hasB ? 2 * pair + 1 : 2 * pair];
     const bool useA = !wA.skip_decode, useB = hasB && !wB.skip_decode;
-    if (!useA && !useB) {
+    if (!FUSED && !useA && !useB) {
       tm::group_barrier(bar_id, zpad);
       continue;
     }
@@ -483,30 +489,90 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         return tm::un(__floats2half2_rn(fa, fb));
       };
       soft_w[t] = 0, soft_w[Z + t] = 0;  // punctured columns
-      const unsigned lenA = useA ? wA.in_length : 0u, lenB = useB ? wB.in_length : 0u;
+      if constexpr (!FUSED) {
+        const unsigned lenA = useA ? wA.in_length : 0u, lenB = useB ? wB.in_length : 0u;
 #pragma unroll 1
-      for (int n0 = 2; n0 < K + M; n0 += U) {
-        int a[U], b[U];
+        for (int n0 = 2; n0 < K + M; n0 += U) {
+          int a[U], b[U];
 #pragma unroll
-        for (int k = 0; k < U; ++k) {
-          const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
-          a[k] = (i < lenA) ? (int)__ldg(inA + i) : 0;
-          b[k] = (i < lenB) ? (int)__ldg(inB + i) : 0;
+          for (int k = 0; k < U; ++k) {
+            const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
+            a[k] = (i < lenA) ? (int)__ldg(inA + i) : 0;
+            b[k] = (i < lenB) ? (int)__ldg(inB + i) : 0;
+          }
+#pragma unroll
+          for (int k = 0; k < U; ++k) {
+            const int n = n0 + k;
+            const unsigned i = (unsigned)(n - 2) * Z + t;
+            lastA = a[k] ? i + 1 : lastA;
+            lastB = b[k] ? i + 1 : lastB;
+            const unsigned v = convert(a[k], b[k]);
+            if (n < HRR) {
+              soft_w[n * Z + t] = v;
+            } else {
+              ext_soft_w[(n - HRR) * zpad + t] = v;
+            }
+          }
         }
+      } else {
+        // rate dematching + HARQ combining as the load: position i of each soft buffer = closed form of its previous
+        // content and the input elements that land on it (ldpc_dematch.cuh); codeblocks with skip_decode are combined too
+        const DematchGeom gA = make_dematch_geom(BG, (unsigned)Z, wA.nof_filler_bits, wA.rv, wA.mod_order, wA.Nref,
+                                                 wA.rm_length, wA.new_data);
+        const DematchGeom gB = make_dematch_geom(BG, (unsigned)Z, wB.nof_filler_bits, wB.rv, wB.mod_order, wB.Nref,
+                                                 wB.rm_length, wB.new_data);
+        const int8_t* rmA = p.rm_base + wA.rm_offset;
+        const int8_t* rmB = p.rm_base + wB.rm_offset;
+        int8_t* softA = p.soft_rw + wA.in_offset;
+        int8_t* softB = p.soft_rw + wB.in_offset;
+        constexpr int UF = (BG == 2) ? 5 : 6;
+        static_assert((K + M - 2) % UF == 0, "batches must tile the stored columns");
+#pragma unroll 1
+        for (int n0 = 2; n0 < K + M; n0 += UF) {
+          int pa[UF], pb[UF], xa[UF], xb[UF];
+          DematchRank da[UF], db[UF];
 #pragma unroll
-        for (int k = 0; k < U; ++k) {
-          const int n = n0 + k;
-          const unsigned i = (unsigned)(n - 2) * Z + t;
-          lastA = a[k] ? i + 1 : lastA;
-          lastB = b[k] ? i + 1 : lastB;
-          const unsigned v = convert(a[k], b[k]);
-          if (n < HRR) {
-            soft_w[n * Z + t] = v;
-          } else {
-            ext_soft_w[(n - HRR) * zpad + t] = v;
+          for (int k = 0; k < UF; ++k) {
+            const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
+            da[k] = dematch_rank(gA, i);
+            db[k] = dematch_rank(gB, i);
+            pa[k] = softA[i];
+            pb[k] = hasB ? (int)softB[i] : 0;
+            xa[k] = (da[k].live && da[k].r < gA.E) ? dematch_input(gA, rmA, da[k].r) : 0;
+            xb[k] = (hasB && db[k].live && db[k].r < gB.E) ? dematch_input(gB, rmB, db[k].r) : 0;
+          }
+#pragma unroll
+          for (int k = 0; k < UF; ++k) {
+            const int n = n0 + k;
+            const unsigned i = (unsigned)(n - 2) * Z + t;
+            int a = dematch_combine(gA, rmA, i, pa[k], da[k], xa[k]);
+            if (a != pa[k]) {
+              softA[i] = (int8_t)a;
+            }
+            int b = 0;
+            if (hasB) {
+              b = dematch_combine(gB, rmB, i, pb[k], db[k], xb[k]);
+              if (b != pb[k]) {
+                softB[i] = (int8_t)b;
+              }
+            }
+            a = useA ? a : 0;
+            b = useB ? b : 0;
+            lastA = a ? i + 1 : lastA;
+            lastB = b ? i + 1 : lastB;
+            const unsigned v = convert(a, b);
+            if (n < HRR) {
+              soft_w[n * Z + t] = v;
+            } else {
+              ext_soft_w[(n - HRR) * zpad + t] = v;
+            }
           }
         }
       }
+    }
+    if (FUSED && !useA && !useB) {  // combined only (both CRCs already passed in an earlier transmission)
+      tm::group_barrier(bar_id, zpad);
+      continue;
     }
     for (int n = 0; n < M - 4; ++n) {
       ext_c2v_w[n * zpad + t] = 0;
@@ -732,10 +798,10 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
 constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100
 constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block per SM owns all 512 TMEM columns
 
-template <int BG, int SCALE>
+template <int BG, int SCALE, bool FUSED>
 static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, cudaStream_t stream)
 {
-  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE>;
+  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED>;
   static bool attr_set = false;
   if (!attr_set) {
     const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM_LIMIT);
@@ -754,10 +820,19 @@ static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned g
   return 0;
 }
 
+template <int BG, int SCALE>
+static inline int tm_launch_fused_or_not(bool fused, const TmemParams& p, size_t smem, unsigned grid, cudaStream_t stream)
+{
+  return fused ? tm_launch_variant<BG, SCALE, true>(p, smem, grid, stream)
+               : tm_launch_variant<BG, SCALE, false>(p, smem, grid, stream);
+}
+
 // Returns 0 when launched, > 0 when the configuration is not covered (caller uses the general kernel), < 0 on CUDA error.
+// d_rm != nullptr selects the fused kernel: d_llr is then the soft-buffer arena, combined in place with the rate-matched
+// LLRs at d_rm before decoding.
 static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, const CbWork* d_work, unsigned n,
-                                     const int8_t* d_llr, uint8_t* d_out, CbResult* d_res, unsigned* d_pair_counter,
-                                     int sm_count, cudaStream_t stream)
+                                     const int8_t* d_llr, const int8_t* d_rm, uint8_t* d_out, CbResult* d_res,
+                                     unsigned* d_pair_counter, int sm_count, cudaStream_t stream)
 {
   if (scale_variant == TM_SCALE_NONE || d_pair_counter == nullptr) {
     return 1;
@@ -768,6 +843,8 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
     return 1;
   }
   p.work = d_work, p.llr_base = d_llr, p.out_base = d_out, p.results = d_res, p.pair_counter = d_pair_counter;
+  p.rm_base = d_rm, p.soft_rw = const_cast<int8_t*>(d_llr);
+  const bool fused = d_rm != nullptr;
   p.nof_cbs = n, p.Z = gp.Z, p.Z4 = 4 * gp.Z, p.max_iterations = gp.max_iterations;
   p.zpad = ((gp.Z + 31) / 32) * 32;
   p.groups = TM_THREADS / p.zpad;
@@ -788,11 +865,11 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   }
   const bool gen = scale_variant == TM_SCALE_GENERIC_08;
   if (gp.bg == 1) {
-    return gen ? tm_launch_variant<1, TM_SCALE_GENERIC_08>(p, smem, grid, stream)
-               : tm_launch_variant<1, TM_SCALE_AVX_08>(p, smem, grid, stream);
+    return gen ? tm_launch_fused_or_not<1, TM_SCALE_GENERIC_08>(fused, p, smem, grid, stream)
+               : tm_launch_fused_or_not<1, TM_SCALE_AVX_08>(fused, p, smem, grid, stream);
   }
-  return gen ? tm_launch_variant<2, TM_SCALE_GENERIC_08>(p, smem, grid, stream)
-             : tm_launch_variant<2, TM_SCALE_AVX_08>(p, smem, grid, stream);
+  return gen ? tm_launch_fused_or_not<2, TM_SCALE_GENERIC_08>(fused, p, smem, grid, stream)
+             : tm_launch_fused_or_not<2, TM_SCALE_AVX_08>(fused, p, smem, grid, stream);
 }
 
 }  // namespace ldpc_b200
