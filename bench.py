@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--max-iters", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-pusch-extra", action="store_true")
     return ap.parse_args()
 
 
@@ -109,6 +110,114 @@ def make_workload_gpu(torch, dev, n_cb, esn0_db, seed):
         x = torch.clamp(2.0 * y / sigma2, -20.0, 20.0) / 20.0 * 120.0
         llr[b:e] = (torch.sign(x) * torch.floor(torch.abs(x) + 0.5)).to(torch.int8)
     return llr
+
+
+def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
+    """BASELINE configs 3 + 5 through the FUSED entry (rate dematch + HARQ combine in the HBM arena -> decode -> CRC24B early
+    stop), device-resident: full-slot PUSCH TBs of a 100 MHz cell (273 PRB, 4 layers, 256QAM, R=948/1024: TBS 1 277 992
+    bits, 152 codeblocks BG1 Z=384 F=16, E_r 8960/8992), 16 cells per slot. A step = 8 x (slot A, slot B): slot A carries
+    16 new TBs, 4 of them at an SNR where every codeblock fails; slot B carries 12 new TBs and the rv2 retransmissions of
+    those 4 (new_data = 0: read-combine-write of their soft buffers). 12.5 % of TB transmissions are retransmissions."""
+    import oracles as O
+    tbs, Qm, layers, nsym = 1277992, 8, 4, 42588 * 4
+    descs, _ = pkg.segment(tbs, 1, Qm, layers, nsym)
+    C, F, Zs = len(descs), 16, 384
+    Kb, Nsoft, kb = 22 * Zs, 66 * Zs, 22 * Zs // 8
+    rng = np.random.default_rng(7)
+    E = descs["rm_length"].astype(np.int64)
+    tx = {0: [], 2: []}
+    for r in range(C):
+        msg, cw = O.make_codeword(rng, 1, Zs, F, O.CRC24B)
+        for rv in (0, 2):
+            tx[rv].append(O.port().rate_match(cw, int(E[r]), rv, Qm, 0, F))
+    tb_bytes = int(E.sum())
+    tb_off = np.concatenate([[0], np.cumsum(E)[:-1]])
+    sets, cells, n_bad = 8, 16, 4
+    g = torch.Generator(device=dev)
+    g.manual_seed(99)
+
+    def noisy(bits_list, n_tb, esn0_of_tb):
+        base = torch.from_numpy(np.concatenate(bits_list).astype(np.int8)).to(dev)
+        out = torch.empty((n_tb, tb_bytes), dtype=torch.int8, device=dev)
+        for i in range(n_tb):
+            sigma2 = 10.0 ** (-esn0_of_tb(i) / 10.0) / 2.0
+            y = (1.0 - 2.0 * base.float()) + torch.randn(base.shape, generator=g, device=dev) * (sigma2 ** 0.5)
+            x = torch.clamp(2.0 * y / sigma2, -20.0, 20.0) / 20.0 * 120.0
+            out[i] = (torch.sign(x) * torch.floor(torch.abs(x) + 0.5)).to(torch.int8)
+        return out
+
+    good, bad = 9.0, 4.0
+    n_a = sets * cells
+    rm_a = noisy(tx[0], n_a, lambda i: bad if (i % cells) < n_bad else good)
+    # slot B: per set, TBs 0..3 are the retransmissions (rv 2) of slot A's TBs 0..3, TBs 4..15 are new (rv 0)
+    rm_b_new = noisy(tx[0], sets * (cells - n_bad), lambda i: good)
+    rm_b_rtx = noisy(tx[2], sets * n_bad, lambda i: bad)
+    n_buf = sets * (2 * cells - n_bad)
+    dec.softbuffer_reserve(n_buf * C * Nsoft)
+
+    def build(n_tb, rm_index_of, buf_of, new_data_of, rv_of):
+        d = np.zeros(n_tb * C, pkg.CB_DESC)
+        for i in range(n_tb):
+            s = d[i * C:(i + 1) * C]
+            s[:] = descs
+            s["crc_poly"], s["early_stop"], s["skip_decode"] = pkg.CRC24B, 1, 0
+            s["new_data"], s["rv"] = new_data_of(i), rv_of(i)
+            s["in_offset"] = rm_index_of(i) * tb_bytes + tb_off
+            s["soft_offset"] = (buf_of(i) * C + np.arange(C)) * Nsoft
+            s["out_offset"] = (i * C + np.arange(C)) * kb
+        return d
+
+    per_set = 2 * cells - n_bad
+    d_a = build(n_a, lambda i: i, lambda i: (i // cells) * per_set + (i % cells), lambda i: 1, lambda i: 0)
+    # slot B input buffer = [retransmissions | new]; index into the concatenation
+    rm_b = torch.cat([rm_b_rtx, rm_b_new])
+    n_rtx = sets * n_bad
+
+    def b_rm(i):
+        st, c = divmod(i, cells)
+        return st * n_bad + c if c < n_bad else n_rtx + st * (cells - n_bad) + (c - n_bad)
+
+    def b_buf(i):
+        st, c = divmod(i, cells)
+        return st * per_set + (c if c < n_bad else cells + (c - n_bad))
+
+    d_b = build(n_a, b_rm, b_buf, lambda i: 0 if (i % cells) < n_bad else 1, lambda i: 2 if (i % cells) < n_bad else 0)
+    out_d = torch.zeros(n_a * C * kb, dtype=torch.uint8, device=dev)
+    res_a = torch.zeros(n_a * C, dtype=torch.int32, device=dev)
+    res_b = torch.zeros(n_a * C, dtype=torch.int32, device=dev)
+
+    def step():
+        dec.dematch_decode_batch_device(d_a, rm_a.data_ptr(), out_d.data_ptr(), res_a.data_ptr())
+        dec.dematch_decode_batch_device(d_b, rm_b.data_ptr(), out_d.data_ptr(), res_b.data_ptr())
+
+    for _ in range(3):
+        step()
+    dec.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = dec.launch_count
+    e0.record(stream)
+    for _ in range(steps):
+        step()
+    e1.record(stream)
+    dec.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    ra = res_a.cpu().numpy().view(pkg.CB_RESULT).reshape(n_a, C)
+    rb = res_b.cpu().numpy().view(pkg.CB_RESULT).reshape(n_a, C)
+    bad_a = (np.arange(n_a) % cells) < n_bad
+    n_cb = 2 * n_a * C
+    bits = n_cb * (Kb - F)
+    slots = 2 * sets
+    return {"what": "configs 3+5: fused rate-dematch + HARQ combine (HBM arena) + decode + CRC24B early stop, 16 cells x "
+                    "152-codeblock full-slot TBs (BG1 Z=384 F=16, E 8960/8992, R=0.94), 12.5% retransmissions (rv2)",
+            "value": bits / (ms * 1e-3) / 1e9, "unit": "Gb/s", "ms_per_slot_16_cells": ms / slots,
+            "codeblocks_per_step": n_cb, "rm_llr_bytes_per_step": int(2 * n_a * tb_bytes),
+            "soft_buffer_arena_bytes": int(n_buf * C * Nsoft), "launches_per_step": (dec.launch_count - launches0) // steps,
+            "cells_in_real_time_at_0.5ms_slots": cells * 0.5 / (ms / slots),
+            "crc_pass_rate": {"new_good_snr": float(ra[~bad_a]["crc_ok"].mean()), "new_bad_snr": float(ra[bad_a]["crc_ok"].mean()),
+                              "retransmission": float(rb[bad_a]["crc_ok"].mean())},
+            "mean_iterations": {"new_good_snr": float(ra[~bad_a]["iterations"].mean()),
+                                "new_bad_snr": float(ra[bad_a]["iterations"].mean()),
+                                "retransmission": float(rb[bad_a]["iterations"].mean())}}
 
 
 def make_workload_cpu(n_cb, esn0_db, seed):
@@ -181,7 +290,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     n_cb = args.codeblocks
-    dec = pkg.LdpcCuda(device=local, max_codeblocks=n_cb, max_iterations=args.max_iters)
+    dec = pkg.LdpcCuda(device=local, max_codeblocks=max(n_cb, 19456), max_iterations=args.max_iters)
     stream = torch.cuda.ExternalStream(dec.stream, device=dev)
     llr_d = make_workload_gpu(torch, dev, n_cb, args.esn0, 1000 + rank)
     out_d = torch.zeros((n_cb, OUT_BYTES), dtype=torch.uint8, device=dev)
@@ -281,9 +390,14 @@ def run_ours(args):
             "early_stop": es, "clocks": clocks, "gpu_launches": int(launches)}
     if e2e is not None:
         line["e2e"] = e2e
+    llrs_sample = llr_d[:2048].cpu().numpy() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
+    if rank == 0 and world == 1 and not args.no_pusch_extra:
+        del llr_d, out_d
+        torch.cuda.empty_cache()
+        line["pusch_slot"] = pusch_slot_extra(torch, pkg, dec, dev, stream, args.steps)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sample = 2048
-        llrs = llr_d[:sample].cpu().numpy()
+        llrs = llrs_sample
         gbps, kind, threads, desc = cpu_reference_run(llrs, args.max_iters, 3)
         line["cpu_baseline"] = {"value": gbps, "unit": "Gb/s", "cores": threads, "kind": kind,
                                 "sample": "first %d codeblocks of the same workload, best of 3, %s" % (sample, desc)}

@@ -546,15 +546,11 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
             const int n = n0 + k;
             const unsigned i = (unsigned)(n - 2) * Z + t;
             int a = dematch_combine(gA, rmA, i, pa[k], da[k], xa[k]);
-            if (a != pa[k]) {
-              softA[i] = (int8_t)a;
-            }
+            softA[i] = (int8_t)a;  // written back unconditionally: one coalesced byte per lane
             int b = 0;
             if (hasB) {
               b = dematch_combine(gB, rmB, i, pb[k], db[k], xb[k]);
-              if (b != pb[k]) {
-                softB[i] = (int8_t)b;
-              }
+              softB[i] = (int8_t)b;
             }
             a = useA ? a : 0;
             b = useB ? b : 0;

@@ -200,3 +200,52 @@ def test_host_entry_pipelined_chunks_two_groups(dec):
         o = int(descs["out_offset"][i])
         assert (out[o:o + bits.size] == bits).all(), i
         assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, i
+
+
+def test_fused_prologue_dematch_all_cases_with_stale_priors(dec):
+    """Every rate-dematcher case of test_gpu_parity.RM_CASES through the FUSED entry: the arena is pre-filled with arbitrary
+    prior contents (so the reference's stale-byte / partial-zeroing behaviour is visible), one call carries a new-data and
+    a retransmission codeblock of each case plus a skip_decode twin; soft buffers, bits and results must equal the oracle."""
+    from test_gpu_parity import RM_CASES
+    rng = np.random.default_rng(35)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    cbs = []
+    so = oo = ro = 0
+    for case in RM_CASES:
+        bg, Z, E, rv, Qm, Nref, F = case
+        N, kb = O.BG_N_SHORT[bg] * Z, (O.BG_K[bg] * Z + 7) // 8
+        for new_data, skip in ((1, 0), (0, 0), (0, 1)):
+            prior = rng.integers(-120, 121, N).astype(np.int8)
+            prior[(O.BG_K[bg] - 2) * Z - F:(O.BG_K[bg] - 2) * Z] = 127
+            rm = rng.integers(-120, 121, E).astype(np.int8)
+            cbs.append(dict(case=case, new_data=new_data, skip=skip, prior=prior, rm=rm, so=so, oo=oo, ro=ro, N=N, kb=kb))
+            so += (N + 63) // 64 * 64
+            oo += kb
+            ro += E
+    dec.softbuffer_reserve(so)
+    descs = np.zeros(len(cbs), pkg.CB_DESC)
+    for i, c in enumerate(cbs):
+        bg, Z, E, rv, Qm, Nref, F = c["case"]
+        dec.softbuffer_write(c["so"], c["prior"])
+        d = descs[i]
+        d["base_graph"], d["lifting_size"], d["nof_filler_bits"], d["crc_poly"] = bg, Z, F, O.CRC16
+        d["early_stop"], d["rv"], d["mod_order"], d["Nref"], d["new_data"] = 1, rv, Qm, Nref, c["new_data"]
+        d["rm_length"], d["in_offset"], d["out_offset"], d["soft_offset"] = E, c["ro"], c["oo"], c["so"]
+        d["in_length"], d["skip_decode"] = c["N"], c["skip"]
+    rm_all = np.concatenate([c["rm"] for c in cbs] + [np.zeros(16, np.int8)])
+    out = np.full(oo, 0xa5, np.uint8)
+    out, res = dec.dematch_decode_batch(descs, rm_all, out)
+    for i, c in enumerate(cbs):
+        bg, Z, E, rv, Qm, Nref, F = c["case"]
+        want = c["prior"].copy()
+        O.port().rate_dematch(want, c["rm"], c["new_data"], rv, Qm, Nref, F)
+        got = dec.softbuffer_read(c["so"], c["N"])
+        assert (got == want).all(), (c["case"], c["new_data"], c["skip"], np.nonzero(got != want)[0][:10])
+        o = c["oo"]
+        if c["skip"]:
+            assert (out[o:o + c["kb"]] == 0xa5).all(), i
+            continue
+        bits, it = O.port().decode(bg, Z, want, fillers=F, crc=O.CRC16, out_init=0xa5)
+        assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, (i, c["case"])
+        if want.any():
+            assert (out[o:o + c["kb"]] == bits).all(), (i, c["case"])
