@@ -258,7 +258,7 @@ struct Ctx {
 // One check row: D high-rate edges (rotated accesses to shared soft values, messages in cw[]) plus, when EXT, the row's
 // private extension node. e0 / r / tmw are warp-uniform.
 template <int D, bool EXT, int SCALE>
-__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
+__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw, int bar_id, int zpad)
 {
   constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
   constexpr int W = (D + 1) / 2;         // message words of the row
@@ -271,14 +271,20 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
     const TmEdge ed = p.edge[e0 + k];
     const unsigned a = c.t4 + ed.s4;
     addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
-    u[k] = lds32(addr[k]);
   }
   unsigned xaddr = 0, caddr = 0;
   if constexpr (EXT) {
     const unsigned ro = (unsigned)(r - 4) * c.zpad4;
     xaddr = c.ext_soft + ro;
     caddr = c.ext_c2v + ro;
-    u[D] = hsub(lds32(xaddr), lds32(caddr));
+    u[D] = hsub(lds32(xaddr), lds32(caddr));  // thread-private: no ordering with other threads needed
+  }
+  // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
+  // message load, addresses, extension node) runs while slower warps finish the previous row.
+  group_barrier(bar_id, zpad);
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    u[k] = lds32(addr[k]);
   }
   // previous messages: byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
   tm_wait_ld();
@@ -352,7 +358,7 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
 }
 
 template <int SCALE>
-__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r)
+__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad)
 {
   const int cls = p.rowcls[r];
   const int e0 = p.rowedge[r];
@@ -360,7 +366,7 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r)
   switch (cls) {
 #define LDPC_TM_CASE(D, EXT)                        \
   case 2 * (D) + (EXT):                             \
-    row_body<D, (EXT) != 0, SCALE>(c, p, r, e0, tmw); \
+    row_body<D, (EXT) != 0, SCALE>(c, p, r, e0, tmw, bar_id, zpad); \
     break;
     LDPC_TM_CASE(2, 1)
     LDPC_TM_CASE(3, 1)
@@ -626,9 +632,9 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
       for (int r = 0; r < nof_layers; ++r) {
-        tm::row_dispatch<SCALE>(c, p, r);
-        tm::group_barrier(bar_id, zpad);
+        tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad);  // the barrier that orders row r after row r - 1 is inside
       }
+      tm::group_barrier(bar_id, zpad);
       tm::tm_wait_st();
       ++it;
       const bool last = (it == p.max_iterations);
