@@ -67,6 +67,7 @@ struct TmemParams {
   unsigned char rowcls[LDPC_BG1_M];    // per row: 2 * (number of high-rate edges) + (1 if the row has an extension node)
   unsigned short rowedge[LDPC_BG1_M];  // per row: index of its first entry in edge[]
   unsigned short rowtm[LDPC_BG1_M];    // per row: first TMEM word (relative to the warp's column block)
+  unsigned rowdesc[LDPC_BG1_M + 2];    // per row: rowcls | rowedge << 8 | rowtm << 20 (one uniform load per row)
   unsigned short tm_words;             // TMEM words used per thread
   TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
 };
@@ -115,7 +116,14 @@ __device__ __forceinline__ unsigned lds32(unsigned addr)
 }
 __device__ __forceinline__ void sts32(unsigned addr, unsigned v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 
-__device__ __forceinline__ void group_barrier(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+__device__ __forceinline__ void group_barrier(int id, int nthreads)
+{
+  if (nthreads == 384) {  // one group per block: barrier 1 with immediate operands (no operand register to rebuild per row)
+    asm volatile("bar.sync 1, 384;" ::: "memory");
+  } else {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+  }
+}
 
 // ---- tensor memory as thread-private message storage (shape 32x32b: thread i of the warp <-> TMEM lane base + i) -----
 __device__ __forceinline__ void tm_ld8(unsigned ta, unsigned* r)
@@ -358,11 +366,11 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
 }
 
 template <int SCALE>
-__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad)
+__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad, unsigned rd)
 {
-  const int cls = p.rowcls[r];
-  const int e0 = p.rowedge[r];
-  const unsigned tmw = p.rowtm[r];
+  const int cls = rd & 0xffu;
+  const int e0 = (rd >> 8) & 0xfffu;
+  const unsigned tmw = rd >> 20;
   switch (cls) {
 #define LDPC_TM_CASE(D, EXT)                        \
   case 2 * (D) + (EXT):                             \
@@ -631,8 +639,11 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
 
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
+      unsigned rd = p.rowdesc[0];
       for (int r = 0; r < nof_layers; ++r) {
-        tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad);  // the barrier that orders row r after row r - 1 is inside
+        const unsigned rd_next = p.rowdesc[r + 1];  // fetched a whole row ahead of its use
+        tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad, rd);  // the barrier that orders row r after row r - 1 is inside
+        rd = rd_next;
       }
       tm::group_barrier(bar_id, zpad);
       tm::tm_wait_st();
@@ -791,6 +802,7 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
       return false;
     }
     p.rowcls[r] = (unsigned char)(2 * d + ext);
+    p.rowdesc[r] = (unsigned)p.rowcls[r] | ((unsigned)p.rowedge[r] << 8) | ((unsigned)p.rowtm[r] << 20);
     tmw += (d + 1) / 2;
   }
   p.tm_words = (unsigned short)tmw;
