@@ -254,8 +254,7 @@ __device__ __forceinline__ MinPair reduce_pairs(MinPair* p)
 // Per-thread context of the row loop.
 struct Ctx {
   unsigned soft_base;  // shared address of the group's high-rate soft array (uniform per warp)
-  unsigned ext_soft;   // shared address of this thread's extension soft word of row 4 (row r: + (r - 4) * zpad4)
-  unsigned ext_c2v;    // same for the extension message
+  unsigned ext_soft;   // shared address of this thread's extension-node word of row 4 (row r: + (r - 4) * zpad4)
   unsigned t4;         // 4 * lane
   unsigned Z4;
   unsigned zpad4;
@@ -280,12 +279,14 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
     const unsigned a = c.t4 + ed.s4;
     addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
   }
-  unsigned xaddr = 0, caddr = 0;
+  // The row's extension node has degree one: its variable-to-check message is its channel LLR until the soft value
+  // LLR + c2v is promoted to +-inf (|sum| > 120), and +-inf for ever after (soft - c2v_old = LLR exactly otherwise:
+  // log_likelihood_ratio.cpp:38-85). So the node is ONE thread-private word holding that message - no soft value, no
+  // stored check-to-variable message.
+  unsigned xaddr = 0;
   if constexpr (EXT) {
-    const unsigned ro = (unsigned)(r - 4) * c.zpad4;
-    xaddr = c.ext_soft + ro;
-    caddr = c.ext_c2v + ro;
-    u[D] = hsub(lds32(xaddr), lds32(caddr));  // thread-private: no ordering with other threads needed
+    xaddr = c.ext_soft + (unsigned)(r - 4) * c.zpad4;
+    u[D] = lds32(xaddr);  // thread-private: no ordering with other threads needed
   }
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
@@ -341,17 +342,18 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
     const unsigned s = hadd(v, cn);
     const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
     const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
-    // lanes frozen at +-inf stay there (HSET2.BM + LOP3 on the ALU pipe: the FP16 pipe is the busier one in this pass)
-    const unsigned isinf = __heq2_mask(__habs2(h2(uk)), h2(0x7c007c00u));
-    const unsigned n = (uk & isinf) | (n1 & ~isinf);
     if (k < D) {
+      // lanes frozen at +-inf stay there (HSET2.BM + LOP3 on the ALU pipe: the FP16 pipe is the busier one in this pass)
+      const unsigned isinf = __heq2_mask(__habs2(h2(uk)), h2(0x7c007c00u));
+      const unsigned n = (uk & isinf) | (n1 & ~isinf);
       if (c.active) {
         sts32(addr[k], n);
       }
       tn[k] = hadd(cn, hc(1152.f));
     } else {
-      sts32(xaddr, n);
-      sts32(caddr, cn);
+      // the message becomes +-inf once the soft value is promoted (sign of s = sign of u when u is already infinite)
+      const unsigned prom = __heq2_mask(__habs2(h2(n1)), h2(0x7c007c00u));
+      sts32(xaddr, (n1 & prom) | (uk & ~prom));
     }
   }
   if constexpr (D & 1) {
@@ -398,9 +400,9 @@ __device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, 
 }  // namespace tm
 
 // Shared memory: [crc tables 3 x 256 words][group 0][group 1]...; group = soft[HRR * Z] | ext_soft[(M-4) * zpad] |
-// ext_c2v[(M-4) * zpad] | hard[2][msg_bytes16] | flags[8].
+// hard[2][msg_bytes16] | flags[8]. ext_soft holds one word per extension node (see row_body).
 struct TmLayout {
-  unsigned soft, ext_soft, ext_c2v, hard, flags, total;
+  unsigned soft, ext_soft, hard, flags, total;
 };
 __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
 {
@@ -409,8 +411,7 @@ __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
   TmLayout l;
   l.soft = 0;
   l.ext_soft = l.soft + hrr * Z * 4;
-  l.ext_c2v = l.ext_soft + (M - 4) * zpad * 4;
-  l.hard = l.ext_c2v + (M - 4) * zpad * 4;
+  l.hard = l.ext_soft + (M - 4) * zpad * 4;
   l.flags = l.hard + 2 * msg_bytes16;
   l.total = (l.flags + 8 * 4 + 15) & ~15u;
   return l;
@@ -452,14 +453,12 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   unsigned char* gsm = smem + TM_CRC_TABLE_BYTES + (size_t)grp * p.group_stride;
   unsigned* soft_w = reinterpret_cast<unsigned*>(gsm + lay.soft);
   unsigned* ext_soft_w = reinterpret_cast<unsigned*>(gsm + lay.ext_soft);
-  unsigned* ext_c2v_w = reinterpret_cast<unsigned*>(gsm + lay.ext_c2v);
   unsigned char* hard = gsm + lay.hard;
   volatile unsigned* flags = reinterpret_cast<volatile unsigned*>(gsm + lay.flags);  // 0,1: last non-zero + 1; 2,3: crc ok; 4: pair
 
   tm::Ctx c;
   c.soft_base = (unsigned)__cvta_generic_to_shared(soft_w);
   c.ext_soft = (unsigned)__cvta_generic_to_shared(ext_soft_w + t);
-  c.ext_c2v = (unsigned)__cvta_generic_to_shared(ext_c2v_w + t);
   c.t4 = 4u * (unsigned)t;
   c.Z4 = (unsigned)p.Z4;
   c.zpad4 = 4u * (unsigned)zpad;
@@ -583,9 +582,6 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     if (FUSED && !useA && !useB) {  // combined only (both CRCs already passed in an earlier transmission)
       tm::group_barrier(bar_id, zpad);
       continue;
-    }
-    for (int n = 0; n < M - 4; ++n) {
-      ext_c2v_w[n * zpad + t] = 0;
     }
     {
       unsigned init[8];
