@@ -226,8 +226,8 @@ struct MinPair {
 __device__ __forceinline__ MinPair merge(MinPair a, MinPair b)
 {
   MinPair r;
-  r.m1 = umin2(a.m1, b.m1);
-  r.m2 = umin3(umax2(a.m1, b.m1), a.m2, b.m2);
+  r.m1 = hmin(a.m1, b.m1);  // non-negative halves: fp16 order == integer order; these two go to the FP16 pipe, which
+  r.m2 = umin3(hmax(a.m1, b.m1), a.m2, b.m2);  // is the idler one while the minima are formed
   return r;
 }
 // Tree reduction over N sorted pairs.
