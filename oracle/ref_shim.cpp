@@ -29,9 +29,12 @@
 // variant name "cuda" selects the product's factories (srsran_project_23.5_b200/host/ldpc_cuda_factories.h), so that the
 // reference's UNMODIFIED pusch_decoder_impl / interfaces run on top of the B200 kernels. Used by tests/test_gpu_dropin.py.
 #include "../srsran_project_23.5_b200/host/ldpc_cuda_factories.h"
+#include "../srsran_project_23.5_b200/host/pusch_decoder_cuda.h"
 #endif
 
+#include <algorithm>
 #include <atomic>
+#include <map>
 #include <chrono>
 #include <cstring>
 #include <thread>
@@ -103,9 +106,36 @@ struct decoder_handle {
   std::unique_ptr<crc_calculator> crc[4];
 };
 
+// Plain rx_softbuffer for transport blocks with more codeblocks than the reference pool supports (MAX_NOF_SEGMENTS = 52):
+// CRC flags and decoded message bits only - enough for a pusch_decoder that keeps its soft bits elsewhere.
+class big_softbuffer : public rx_softbuffer
+{
+public:
+  explicit big_softbuffer(unsigned nof_cbs) : crcs(new bool[nof_cbs]()), n(nof_cbs)
+  {
+    for (unsigned i = 0; i != nof_cbs; ++i) {
+      bits.emplace_back(std::make_unique<dynamic_bit_buffer>(22 * 384));
+      bits.back()->zero();
+    }
+  }
+  ~big_softbuffer() override { delete[] crcs; }
+  unsigned   get_nof_codeblocks() const override { return n; }
+  void       reset_codeblocks_crc() override { std::fill(crcs, crcs + n, false); }
+  span<bool> get_codeblocks_crc() override { return span<bool>(crcs, n); }
+  span<log_likelihood_ratio> get_codeblock_soft_bits(unsigned, unsigned) override { return {}; }
+  bit_buffer get_codeblock_data_bits(unsigned cb, unsigned data_size) override { return bits[cb]->first(data_size); }
+
+private:
+  bool*                                            crcs;
+  unsigned                                         n;
+  std::vector<std::unique_ptr<dynamic_bit_buffer>> bits;
+};
+
 struct pusch_handle {
-  std::unique_ptr<pusch_decoder>      dec;
-  std::unique_ptr<rx_softbuffer_pool> pool;
+  std::unique_ptr<pusch_decoder>                     dec;
+  std::unique_ptr<rx_softbuffer_pool>                pool;
+  bool                                               batched = false;
+  std::map<unsigned, std::unique_ptr<big_softbuffer>> big; // key (rnti << 8) | harq, transport blocks above 52 codeblocks
 };
 
 } // namespace
@@ -494,9 +524,32 @@ void* ref_pusch_create(const char* decoder_type,
                        unsigned    max_nof_codeblocks,
                        unsigned    expire_timeout_slots)
 {
+  auto crc_f = create_crc_calculator_factory_sw("auto");
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (std::strcmp(decoder_type, "cuda-batched") == 0) {
+    // the product's pusch_decoder (one fused batched call per transport block) behind the reference interface
+    pusch_decoder_cuda_configuration pc = {};
+    pc.crc_factory                      = crc_f;
+    pc.arena_codeblocks                 = std::max(256u, max_softbuffers * max_nof_codeblocks);
+    auto fac                            = create_pusch_decoder_factory_cuda(pc);
+    auto dec                            = fac ? fac->create() : nullptr;
+    if (!dec) {
+      return nullptr;
+    }
+    auto* h                      = new pusch_handle;
+    h->dec                       = std::move(dec);
+    h->batched                   = true;
+    rx_softbuffer_pool_config rc = {};
+    rc.max_codeblock_size        = ldpc::MAX_CODEBLOCK_SIZE;
+    rc.max_softbuffers           = max_softbuffers;
+    rc.max_nof_codeblocks        = max_nof_codeblocks;
+    rc.expire_timeout_slots      = expire_timeout_slots;
+    h->pool                      = create_rx_softbuffer_pool(rc);
+    return h;
+  }
+#endif
   auto dec_f   = decoder_factory_of(decoder_type);
   auto dem_f   = dematcher_factory_of(dematcher_type);
-  auto crc_f   = create_crc_calculator_factory_sw("auto");
   auto seg_f   = create_ldpc_segmenter_rx_factory_sw();
   auto decoder = dec_f ? dec_f->create() : nullptr;
   auto demat   = dem_f ? dem_f->create() : nullptr;
@@ -547,14 +600,25 @@ int ref_pusch_decode(void*         handle,
 {
   auto*    h       = static_cast<pusch_handle*>(handle);
   unsigned nof_cbs = ldpc::compute_nof_codeblocks(units::bits(tb_bytes * 8), to_bg(bg));
-  if (nof_cbs > MAX_NOF_SEGMENTS) {
-    return -2;
-  }
   slot_point               slot(1, slot_count % (1024 * 20));
   rx_softbuffer_identifier id  = {static_cast<uint16_t>(rnti), static_cast<uint8_t>(harq_id)};
-  unique_rx_softbuffer     buf = h->pool->reserve_softbuffer(slot, id, nof_cbs);
-  if (!buf.is_valid()) {
-    return -1;
+  const bool               big = nof_cbs > MAX_NOF_SEGMENTS;
+  if (big && !h->batched) {
+    return -2; // the reference pusch_decoder_impl and pool stop at 52 codeblocks
+  }
+  unique_rx_softbuffer buf = big ? unique_rx_softbuffer() : h->pool->reserve_softbuffer(slot, id, nof_cbs);
+  rx_softbuffer*       sb  = nullptr;
+  if (big) {
+    auto& slot_sb = h->big[(rnti << 8) | harq_id];
+    if (!slot_sb || slot_sb->get_nof_codeblocks() != nof_cbs) {
+      slot_sb = std::make_unique<big_softbuffer>(nof_cbs);
+    }
+    sb = slot_sb.get();
+  } else {
+    if (!buf.is_valid()) {
+      return -1;
+    }
+    sb = &buf.get();
   }
   pusch_decoder::configuration cfg = {};
   cfg.segmenter_cfg.base_graph     = to_bg(bg);
@@ -570,7 +634,7 @@ int ref_pusch_decode(void*         handle,
   pusch_decoder_result stats = {};
   h->dec->decode(span<uint8_t>(tb_out, tb_bytes),
                  stats,
-                 &buf.get(),
+                 sb,
                  span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs),
                  cfg);
   stats_out[0] = stats.tb_crc_ok ? 1 : 0;
@@ -583,7 +647,7 @@ int ref_pusch_decode(void*         handle,
   } else {
     stats_out[3] = stats_out[4] = stats_out[5] = 0;
   }
-  if (stats.tb_crc_ok && release_on_ok) {
+  if (stats.tb_crc_ok && release_on_ok && buf.is_valid()) {
     buf.release();
   }
   h->pool->run_slot(slot);

@@ -1,0 +1,298 @@
+// See pusch_decoder_cuda.h.
+#include "pusch_decoder_cuda.h"
+
+#include "../../include/ldpc_cuda.h"
+#include "srsran/phy/upper/channel_processors/pusch_decoder.h"
+#include "srsran/ran/modulation_scheme.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <unordered_map>
+#include <vector>
+
+using namespace srsran;
+
+namespace {
+
+constexpr unsigned CB_SLOT_BYTES = 66 * 384; // largest soft buffer of one codeblock (ldpc::MAX_CODEBLOCK_SIZE)
+constexpr unsigned LONG_CRC_BITS = 24;
+
+void check(int status, const char* what)
+{
+  if (status != LDPC_CUDA_OK) {
+    std::fprintf(stderr, "pusch_decoder_cuda fatal: %s: %s\n", what, ldpc_cuda_status_string(status));
+    std::abort();
+  }
+}
+
+void require(bool cond, const char* what)
+{
+  if (!cond) {
+    std::fprintf(stderr, "pusch_decoder_cuda fatal: %s\n", what);
+    std::abort();
+  }
+}
+
+// dst[dst_off, dst_off + nbits) = src[0, nbits), both MSB first (bit i at byte i / 8, position 7 - i % 8).
+void copy_bits(uint8_t* dst, unsigned dst_off, const uint8_t* src, unsigned nbits)
+{
+  unsigned i = 0;
+  if ((dst_off & 7u) == 0) {
+    std::memcpy(dst + dst_off / 8, src, nbits / 8);
+    i = nbits & ~7u;
+  }
+  for (; i != nbits; ++i) {
+    const unsigned bit = (src[i / 8] >> (7 - (i & 7u))) & 1u;
+    const unsigned o   = dst_off + i;
+    dst[o / 8]         = static_cast<uint8_t>((dst[o / 8] & ~(0x80u >> (o & 7u))) | (bit << (7 - (o & 7u))));
+  }
+}
+
+// Device soft-buffer arena in units of one codeblock slot, keyed by the caller's rx_softbuffer object.
+class arena_index
+{
+public:
+  explicit arena_index(unsigned nof_slots) { free_ranges[0] = nof_slots; }
+
+  struct entry {
+    unsigned first = 0, count = 0;
+    uint64_t last_use = 0;
+  };
+
+  // Returns the entry of key; fresh is set when it had to be (re)allocated - its slots then hold foreign data.
+  entry& get(const void* key, unsigned count, bool& fresh)
+  {
+    ++tick;
+    auto it = table.find(key);
+    if (it != table.end() && it->second.count == count) {
+      it->second.last_use = tick;
+      fresh               = false;
+      return it->second;
+    }
+    if (it != table.end()) {
+      release(it->second);
+      table.erase(it);
+    }
+    unsigned first = 0;
+    while (!allocate(count, first)) {
+      // evict the least recently used HARQ process (equivalent to a soft-buffer expiry)
+      auto victim = table.end();
+      for (auto v = table.begin(); v != table.end(); ++v) {
+        if (victim == table.end() || v->second.last_use < victim->second.last_use) {
+          victim = v;
+        }
+      }
+      require(victim != table.end(), "transport block larger than the device soft-buffer arena");
+      release(victim->second);
+      table.erase(victim);
+    }
+    entry& e   = table[key];
+    e.first    = first;
+    e.count    = count;
+    e.last_use = tick;
+    fresh      = true;
+    return e;
+  }
+
+private:
+  bool allocate(unsigned count, unsigned& first)
+  {
+    for (auto it = free_ranges.begin(); it != free_ranges.end(); ++it) {
+      if (it->second >= count) {
+        first              = it->first;
+        const unsigned rem = it->second - count;
+        free_ranges.erase(it);
+        if (rem != 0) {
+          free_ranges[first + count] = rem;
+        }
+        return true;
+      }
+    }
+    return false;
+  }
+
+  void release(const entry& e)
+  {
+    auto it = free_ranges.emplace(e.first, e.count).first;
+    auto nx = std::next(it);
+    if (nx != free_ranges.end() && it->first + it->second == nx->first) {
+      it->second += nx->second;
+      free_ranges.erase(nx);
+    }
+    if (it != free_ranges.begin()) {
+      auto pv = std::prev(it);
+      if (pv->first + pv->second == it->first) {
+        pv->second += it->second;
+        free_ranges.erase(it);
+      }
+    }
+  }
+
+  std::unordered_map<const void*, entry> table;
+  std::map<unsigned, unsigned>           free_ranges; // first slot -> number of slots
+  uint64_t                               tick = 0;
+};
+
+class pusch_decoder_cuda : public pusch_decoder
+{
+public:
+  pusch_decoder_cuda(ldpc_cuda_handle* h_, std::unique_ptr<crc_calculator> crc24A_, unsigned arena_cbs, unsigned max_cbs) :
+    h(h_), crc24A(std::move(crc24A_)), index(arena_cbs), descs(max_cbs), results(max_cbs), crc_bits(max_cbs)
+  {
+  }
+  ~pusch_decoder_cuda() override { ldpc_cuda_destroy(h); }
+
+  // pusch_decoder interface (pusch_decoder.h:66-74); reference implementation pusch_decoder_impl.cpp:121-225.
+  void decode(span<uint8_t>                    transport_block,
+              pusch_decoder_result&            stats,
+              rx_softbuffer*                   soft_codeword,
+              span<const log_likelihood_ratio> llrs,
+              const configuration&             cfg) override
+  {
+    const unsigned tb_size = static_cast<unsigned>(transport_block.size()) * 8;
+    const int      bg      = (cfg.segmenter_cfg.base_graph == ldpc_base_graph_type::BG2) ? 2 : 1;
+    const int      Qm      = static_cast<int>(get_bits_per_symbol(cfg.segmenter_cfg.mod));
+    // ldpc_segmenter_rx::segment geometry (ldpc_segmenter_impl.cpp:226-308), CRC choice of pusch_decoder_impl.cpp:44-56
+    const int C = ldpc_cuda_segment(tb_size,
+                                    bg,
+                                    static_cast<int>(cfg.segmenter_cfg.rv),
+                                    Qm,
+                                    cfg.segmenter_cfg.Nref,
+                                    cfg.segmenter_cfg.nof_layers,
+                                    cfg.segmenter_cfg.nof_ch_symbols,
+                                    descs.data(),
+                                    static_cast<uint32_t>(descs.size()),
+                                    crc_bits.data());
+    require(C > 0 && static_cast<size_t>(C) <= descs.size(), "invalid segmentation or too many codeblocks");
+    const unsigned nof_cbs = static_cast<unsigned>(C);
+    require(nof_cbs == soft_codeword->get_nof_codeblocks(), "wrong number of codeblocks in the soft buffer");
+    require(descs[nof_cbs - 1].in_offset + descs[nof_cbs - 1].rm_length <= llrs.size(), "not enough LLRs");
+
+    span<bool> cb_crcs = soft_codeword->get_codeblocks_crc();
+    if (cfg.new_data) {
+      std::fill(cb_crcs.begin(), cb_crcs.end(), false);
+    }
+
+    const unsigned Z = descs[0].lifting_size, K = (bg == 2 ? 10u : 22u) * Z, kb = (K + 7) / 8;
+    bool           fresh = false;
+    const auto&    slot  = index.get(soft_codeword, nof_cbs, fresh);
+    if (fresh && !cfg.new_data) {
+      // the soft bits of this process were evicted (or never seen): combine into zeros
+      check(ldpc_cuda_softbuffer_zero(h, static_cast<uint64_t>(slot.first) * CB_SLOT_BYTES,
+                                      static_cast<uint64_t>(nof_cbs) * CB_SLOT_BYTES),
+            "ldpc_cuda_softbuffer_zero");
+    }
+    cb_out.resize(static_cast<size_t>(nof_cbs) * kb);
+    for (unsigned r = 0; r != nof_cbs; ++r) {
+      ldpc_cuda_cb_desc& d = descs[r];
+      d.early_stop         = cfg.use_early_stop ? 1 : 0;
+      d.new_data           = cfg.new_data ? 1 : 0;
+      d.skip_decode        = cb_crcs[r] ? 1 : 0; // decoded in an earlier transmission: combine only (:179-184)
+      d.soft_offset        = static_cast<uint64_t>(slot.first + r) * CB_SLOT_BYTES;
+      d.out_offset         = static_cast<uint64_t>(r) * kb;
+      // bits a decode does not write (all-zero input, padding of the last byte) keep the stored message's content
+      bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
+      std::memcpy(&cb_out[d.out_offset], message.get_buffer().data(), kb);
+    }
+    if (cfg.nof_ldpc_iterations != iterations) {
+      ldpc_cuda_algorithm alg = {cfg.nof_ldpc_iterations, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
+      check(ldpc_cuda_set_algorithm(h, &alg), "ldpc_cuda_set_algorithm");
+      iterations = cfg.nof_ldpc_iterations;
+    }
+    check(ldpc_cuda_dematch_decode_batch(h,
+                                         nof_cbs,
+                                         descs.data(),
+                                         reinterpret_cast<const int8_t*>(llrs.data()),
+                                         cb_out.data(),
+                                         results.data()),
+          "ldpc_cuda_dematch_decode_batch");
+
+    // transport block assembly (pusch_decoder_impl.cpp:156-201)
+    const unsigned tb_and_crc_size = tb_size + (nof_cbs > 1 ? LONG_CRC_BITS : 0);
+    tb_tmp.assign((tb_and_crc_size + 7) / 8, 0);
+    unsigned tb_offset         = 0;
+    stats.nof_codeblocks_total = nof_cbs;
+    stats.ldpc_decoder_stats.reset();
+    for (unsigned r = 0; r != nof_cbs; ++r) {
+      bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
+      if (!cb_crcs[r]) {
+        std::memcpy(message.get_buffer().data(), &cb_out[static_cast<size_t>(r) * kb], kb);
+        if (results[r].crc_ok) {
+          cb_crcs[r] = true;
+          stats.ldpc_decoder_stats.update(results[r].iterations);
+        } else {
+          stats.ldpc_decoder_stats.update(cfg.nof_ldpc_iterations);
+        }
+      }
+      const unsigned nof_data_bits = K - crc_bits[r] - descs[r].nof_filler_bits;
+      const unsigned nof_new_bits  = std::min(tb_and_crc_size - tb_offset, nof_data_bits);
+      copy_bits(tb_tmp.data(), tb_offset, message.get_buffer().data(), nof_new_bits);
+      tb_offset += nof_new_bits;
+    }
+    require(tb_offset == tb_and_crc_size, "all TB bits should be filled at this point");
+
+    stats.tb_crc_ok = false;
+    if (nof_cbs == 1) {
+      stats.tb_crc_ok = cb_crcs[0];
+      if (stats.tb_crc_ok) {
+        std::memcpy(transport_block.data(), tb_tmp.data(), transport_block.size());
+      }
+    } else if (std::all_of(cb_crcs.begin(), cb_crcs.end(), [](bool a) { return a; })) {
+      std::memcpy(transport_block.data(), tb_tmp.data(), transport_block.size());
+      if (crc24A->calculate_byte(span<const uint8_t>(tb_tmp.data(), tb_tmp.size())) == 0) {
+        stats.tb_crc_ok = true;
+      } else {
+        soft_codeword->reset_codeblocks_crc(); // at least one codeblock is a false positive
+      }
+    }
+  }
+
+private:
+  ldpc_cuda_handle*                h;
+  std::unique_ptr<crc_calculator>  crc24A;
+  arena_index                      index;
+  std::vector<ldpc_cuda_cb_desc>   descs;
+  std::vector<ldpc_cuda_cb_result> results;
+  std::vector<uint32_t>            crc_bits;
+  std::vector<uint8_t>             cb_out;
+  std::vector<uint8_t>             tb_tmp;
+  unsigned                         iterations = 0;
+};
+
+class pusch_decoder_factory_cuda : public pusch_decoder_factory
+{
+public:
+  explicit pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration& cfg_) : cfg(cfg_) {}
+
+  std::unique_ptr<pusch_decoder> create() override
+  {
+    ldpc_cuda_handle* h = nullptr;
+    if (ldpc_cuda_create(&h, cfg.device, cfg.max_codeblocks_per_tb, 0) != LDPC_CUDA_OK) {
+      return nullptr;
+    }
+    if (ldpc_cuda_softbuffer_reserve(h, static_cast<uint64_t>(cfg.arena_codeblocks) * CB_SLOT_BYTES) != LDPC_CUDA_OK) {
+      ldpc_cuda_destroy(h);
+      return nullptr;
+    }
+    return std::make_unique<pusch_decoder_cuda>(
+        h, cfg.crc_factory->create(crc_generator_poly::CRC24A), cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
+  }
+
+private:
+  pusch_decoder_cuda_configuration cfg;
+};
+
+} // namespace
+
+std::shared_ptr<pusch_decoder_factory>
+srsran::create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration& config)
+{
+  if (!config.crc_factory || ldpc_cuda_device_count() <= config.device || config.device < 0 ||
+      config.arena_codeblocks < config.max_codeblocks_per_tb) {
+    return nullptr;
+  }
+  return std::make_shared<pusch_decoder_factory_cuda>(config);
+}

@@ -1,0 +1,39 @@
+// "cuda" PUSCH decoder: the reference's pusch_decoder interface
+//   (include/srsran/phy/upper/channel_processors/pusch_decoder.h:37-75)
+// implemented with ONE batched, fused call per transport block (ldpc_cuda_dematch_decode_batch: rate dematch + HARQ
+// combine in an HBM-resident soft-buffer arena -> decode -> CRC early stop) instead of the per-codeblock loop of
+//   pusch_decoder_impl::decode (lib/phy/upper/channel_processors/pusch_decoder_impl.cpp:121-225).
+// What that loop does around the per-codeblock calls stays here, on the host, with the same observable behaviour:
+// codeblock CRC flags and decoded messages live in the caller's rx_softbuffer, codeblocks already decoded are combined
+// but not decoded again, the transport block is assembled from the messages, checked with CRC24A when it has several
+// codeblocks, and all codeblock flags are reset when that check fails. Differences by design:
+//   * the soft bits are NOT kept in rx_softbuffer::get_codeblock_soft_bits but in device memory, keyed by the
+//     rx_softbuffer object (25 KB per codeblock never cross PCIe again);
+//   * no 52-codeblock limit (MAX_NOF_SEGMENTS): geometry comes from ldpc_cuda_segment;
+//   * TB assembly copies exactly nof_data_bits per codeblock (the reference's srsvec::copy_offset drops the last
+//     (nof_data_bits % 8) bits of the first codeblock, lib/srsvec/bit.cpp:333-358 - never triggered by 3GPP TB sizes).
+#pragma once
+
+#include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
+#include "srsran/phy/upper/channel_processors/channel_processor_factories.h"
+
+#include <memory>
+
+namespace srsran {
+
+struct pusch_decoder_cuda_configuration {
+  /// CRC calculators for the transport-block CRC24A (any reference CRC factory).
+  std::shared_ptr<crc_calculator_factory> crc_factory;
+  /// CUDA device ordinal (sm_100 only).
+  int device = 0;
+  /// Capacity of the device soft-buffer arena in codeblocks (25 344 bytes each). When it is exhausted the least recently
+  /// used HARQ process loses its soft bits, which is what a soft-buffer pool expiry does.
+  unsigned arena_codeblocks = 4096;
+  /// Largest number of codeblocks of one transport block.
+  unsigned max_codeblocks_per_tb = 256;
+};
+
+/// Returns nullptr when no usable device exists (no CPU fallback), like the reference's factories for an unsupported type.
+std::shared_ptr<pusch_decoder_factory> create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration& config);
+
+} // namespace srsran

@@ -318,3 +318,24 @@ def make_codeword(rng, bg, Z, fillers=0, crc=CRC_NONE):
 
 def msg_to_packed(msg):
     return np.packbits(np.where(msg == 254, 0, msg).astype(np.uint8))
+
+
+def build_transport_block(rng, tbs_bits, bg, Qm, nof_layers, nof_ch_symbols):
+    """TS 38.212 5.2.2 segmentation of a random transport block with several codeblocks, done with the oracle port (the
+    reference's TX segmenter stops at 52 codeblocks): TB + CRC24A split evenly, CRC24B per codeblock, fillers, encode.
+    Returns (tb bytes, list of codewords, meta[C, 6] from segment_rx)."""
+    meta = port().segment_rx(tbs_bits, bg, Qm, nof_layers, nof_ch_symbols)
+    C = len(meta)
+    assert C > 1 and tbs_bits % 8 == 0
+    tb_bits = rng.integers(0, 2, tbs_bits).astype(np.uint8)
+    crc = port().crc(CRC24A, np.packbits(tb_bits), tbs_bits)
+    tb_all = np.concatenate([tb_bits, np.array([(crc >> (23 - k)) & 1 for k in range(24)], np.uint8)])
+    Z, F = int(meta[0, 0]), int(meta[0, 3])
+    K = BG_K[bg] * Z
+    per_cb = K - F - 24
+    assert per_cb * C == tb_all.size, (per_cb, C, tb_all.size)
+    cws = []
+    for r in range(C):
+        msg = np.concatenate([tb_all[r * per_cb:(r + 1) * per_cb], np.zeros(24, np.uint8), np.full(F, 254, np.uint8)])
+        cws.append(port().encode(bg, Z, attach_crc(msg, CRC24B, F)))
+    return np.packbits(tb_bits), cws, meta

@@ -131,3 +131,79 @@ def test_pusch_decoder_harq_through_reference_pusch_decoder_impl(lib, bg, tbs_by
     assert seen_ok
     lib.lib.ref_pusch_destroy(h_sw)
     lib.lib.ref_pusch_destroy(h_cu)
+
+
+@pytest.mark.parametrize("bg,tbs_bytes,Qm,nsym,esn0", [(1, 4001, 4, 12000, -1.0), (2, 300, 2, 2400, -4.5),
+                                                      (1, 20004, 6, 42588, 2.0), (2, 1905, 4, 6000, -3.0)])
+@pytest.mark.parametrize("early_stop", [True, False])
+def test_batched_pusch_decoder_cuda_matches_reference_pusch_decoder(lib, bg, tbs_bytes, Qm, nsym, esn0, early_stop):
+    """The product's pusch_decoder (srsran_project_23.5_b200/host/pusch_decoder_cuda.cpp: ONE fused batched call per TB,
+    soft bits resident on the device, CRC flags and messages in the reference's rx_softbuffer from the reference's pool)
+    against the reference's pusch_decoder_impl on its generic factories, over a HARQ sequence rv {0,2,3,1}."""
+    rng = np.random.default_rng(tbs_bytes + Qm + 1)
+    tb = rng.integers(0, 256, tbs_bytes).astype(np.uint8)
+    segs = lib.segment_tx(tb, bg, Qm, 1, nsym)
+    meta = lib.segment_rx(tbs_bytes * 8, bg, Qm, 1, nsym)
+    h_sw = lib.lib.ref_pusch_create(b"generic", b"generic", 4, 64, 100)
+    h_cu = lib.lib.ref_pusch_create(b"cuda-batched", b"", 4, 64, 100)
+    assert h_sw and h_cu
+    seen_ok = False
+    for i, rv in enumerate([0, 2, 3, 1]):
+        parts = []
+        for c in range(len(segs)):
+            Z, N, E, F = int(meta[c, 0]), int(meta[c, 1]), int(meta[c, 2]), int(meta[c, 3])
+            cw = lib.encode(bg, Z, segs[c, :O.BG_K[bg] * Z])
+            parts.append(lib.rate_match(cw, E, bg, Z, rv, Qm, 0, F))
+        llrs = O.awgn_llrs(rng, np.concatenate(parts), esn0)
+        want_tb, want_st = _pusch(lib, h_sw, 10 + i, tbs_bytes, llrs, bg, rv, Qm, 1, 6, early_stop, i == 0)
+        got_tb, got_st = _pusch(lib, h_cu, 10 + i, tbs_bytes, llrs, bg, rv, Qm, 1, 6, early_stop, i == 0)
+        assert (want_st == got_st).all(), (i, rv, want_st, got_st)
+        if want_st[0]:
+            assert (got_tb == want_tb).all() and (got_tb == tb).all()
+            seen_ok = True
+            break
+    assert seen_ok
+    lib.lib.ref_pusch_destroy(h_sw)
+    lib.lib.ref_pusch_destroy(h_cu)
+
+
+def test_batched_pusch_decoder_cuda_full_slot_tb_152_codeblocks(lib):
+    """BASELINE config 3 through the pusch_decoder interface: TBS 1 277 992 bits = 152 codeblocks, beyond the reference's
+    52-codeblock limit (MAX_NOF_SEGMENTS), so the expectation is the transmitted TB itself. First transmission with a
+    third of the codeblocks below their decoding threshold (TB fails, the good codeblocks are remembered), rv2
+    retransmission: only the failed codeblocks are decoded again, TB CRC24A passes, bytes equal the transmitted TB."""
+    rng = np.random.default_rng(152)
+    tbs, Qm, layers, nsym = 1277992, 8, 4, 42588 * 4
+    tb, cws, meta = O.build_transport_block(rng, tbs, 1, Qm, layers, nsym)
+    C = len(cws)
+    assert C == 152
+    h = lib.lib.ref_pusch_create(b"cuda-batched", b"", 2, 160, 100)
+    assert h
+    # the reference decoder itself cannot take this transport block
+    h_sw = lib.lib.ref_pusch_create(b"generic", b"generic", 2, 52, 100)
+    dummy, st6 = np.zeros(tbs // 8, np.uint8), np.zeros(6, np.uint32)
+    z = np.zeros(nsym * Qm, np.int8)
+    assert lib.lib.ref_pusch_decode(h_sw, 1, 1, 1, dummy.ctypes.data_as(ctypes.c_void_p), tbs // 8,
+                                    z.ctypes.data_as(ctypes.c_void_p), z.size, 1, 0, Qm, 0, layers, 6, 1, 1, 1,
+                                    st6.ctypes.data_as(ctypes.c_void_p)) == -2
+    lib.lib.ref_pusch_destroy(h_sw)
+    bad = np.arange(C) % 3 == 0
+    nfail = None
+    for i, rv in enumerate([0, 2]):
+        parts = []
+        for r in range(C):
+            Z, N, E, F = int(meta[r, 0]), int(meta[r, 1]), int(meta[r, 2]), int(meta[r, 3])
+            tx = O.port().rate_match(cws[r], E, rv, Qm, 0, F)
+            parts.append(O.awgn_llrs(rng, tx, 4.0 if bad[r] else 9.0))
+        llrs = np.concatenate(parts)
+        got_tb, st = _pusch(lib, h, 20 + i, tbs // 8, llrs, 1, rv, Qm, layers, 6, True, i == 0)
+        assert st[1] == C
+        if i == 0:
+            assert st[0] == 0 and st[2] == C, st     # TB fails, every codeblock was decoded
+            assert st[4] == 6                        # the bad ones ran all iterations
+            nfail = int(bad.sum())
+        else:
+            assert st[0] == 1, st
+            assert st[2] == nfail, (st, nfail)      # only the codeblocks that had failed were decoded again
+            assert (got_tb == tb).all()
+    lib.lib.ref_pusch_destroy(h)
