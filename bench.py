@@ -69,6 +69,27 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.stop_flag = index, [], False
 
     def run(self):
+        # NVML first (sub-millisecond per sample, so even a 100 ms timed region gets dozens), nvidia-smi as fallback
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            hdl = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(hdl, pynvml.NVML_CLOCK_SM)
+            bits = ((0x8, 2), (0x40, 3), (0x20, 4), (0x4, 5))  # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
+            while not self.stop_flag:
+                mhz = pynvml.nvmlDeviceGetClockInfo(hdl, pynvml.NVML_CLOCK_SM)
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(hdl)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(hdl)
+                f = [str(mhz), str(mx), "", "", "", ""]
+                for mask, pos in bits:
+                    f[pos] = "Active" if (r & mask) else "Not Active"
+                self.samples.append(f)
+                time.sleep(0.005)
+            return
+        except Exception:
+            pass
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,

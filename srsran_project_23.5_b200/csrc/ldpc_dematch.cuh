@@ -85,9 +85,16 @@ __device__ __forceinline__ int dematch_input(const DematchGeom& g, const int8_t*
   if (g.Qm == 1) {
     return in[x];
   }
+  // x < E <= 295 680 < 2^24 and Kq = E / Qm are exact in float: the truncated quotient estimate is off by at most one
   const unsigned Kq = g.E / g.Qm;
-  const unsigned j = x / Kq, i = x - j * Kq;
-  return in[i * g.Qm + j];
+  unsigned j = (unsigned)(__uint2float_rz(x) * __frcp_rz(__uint2float_rz(Kq)));
+  int i = (int)x - (int)(j * Kq);
+  if (i < 0) {
+    i += (int)Kq, --j;
+  } else if (i >= (int)Kq) {
+    i -= (int)Kq, ++j;
+  }
+  return in[(unsigned)i * g.Qm + j];
 }
 
 // Where soft-buffer position p sits in the walk: its rank r in the stream of de-interleaved input elements (the first
@@ -142,6 +149,64 @@ __device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8
   const DematchRank d = dematch_rank(g, p);
   const int x0 = (d.live && d.r < g.E) ? dematch_input(g, in, d.r) : 0;
   return dematch_combine(g, in, p, prev, d, x0);
+}
+
+// ---- the same dematcher as three data-parallel phases over a staging copy of the soft buffer (fused decoder prologue) ----
+// A: every position takes its previous content with the new-data initialisation applied (the zero / filler ranges the
+//    first loop pass of allot_llrs writes before it copies);
+// B: lap by lap, every de-interleaved input element is copied (first lap of new data) or saturating-added to the position
+//    it lands on - at most one element per position and lap, laps in order, so the result equals the serial walk;
+// C: the trailing zero range (dematch_final), then the value goes back to HBM and on to the decoder.
+__device__ __forceinline__ int dematch_init(const DematchGeom& g, unsigned p, int prev)
+{
+  if (g.new_data && g.E != 0) {
+    if (p >= g.info && p < g.sys) {
+      return LLR_INF;
+    }
+    if (p < g.info && (g.k0 >= g.info || p < g.k0)) {
+      return 0;
+    }
+  }
+  return prev;
+}
+
+__device__ __forceinline__ unsigned dematch_nof_laps(const DematchGeom& g)
+{
+  return g.E ? (g.Ls0 + g.E + g.V - 1) / g.V : 0u;
+}
+
+// Elements of lap `lap` handled by thread t of `stride`; loads are issued BATCH at a time before they are combined.
+__device__ __forceinline__ void dematch_scatter_lap(const DematchGeom& g, const int8_t* __restrict__ in, int8_t* stage,
+                                                    unsigned lap, unsigned t, unsigned stride)
+{
+  constexpr int BATCH = 8;
+  const unsigned first = lap * g.V;  // Ls0 + r runs over [first, first + V) in this lap
+  const unsigned lo = first > g.Ls0 ? first - g.Ls0 : 0u;
+  const unsigned end = first + g.V - g.Ls0;
+  const unsigned hi = end < g.E ? end : g.E;
+  const bool copy = g.new_data && lap == 0;
+  for (unsigned r0 = lo + t; r0 < hi; r0 += BATCH * stride) {
+    int x[BATCH];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const unsigned r = r0 + k * stride;
+      x[k] = (r < hi) ? dematch_input(g, in, r) : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const unsigned r = r0 + k * stride;
+      if (r < hi) {
+        const unsigned L = g.Ls0 + r - first;
+        const unsigned p = L < g.info ? L : L + (g.sys - g.info);
+        stage[p] = (int8_t)(copy ? x[k] : llr_add((int)stage[p], x[k]));
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ int dematch_final(const DematchGeom& g, unsigned p, int v)
+{
+  return p >= g.zero_from ? 0 : v;
 }
 
 // Standalone kernel: one block per codeblock, threads stride over the N positions (coalesced read-modify-write).

@@ -402,9 +402,10 @@ __device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, 
 // Shared memory: [crc tables 3 x 256 words][group 0][group 1]...; group = soft[HRR * Z] | ext_soft[(M-4) * zpad] |
 // hard[2][msg_bytes16] | flags[8]. ext_soft holds one word per extension node (see row_body).
 struct TmLayout {
-  unsigned soft, ext_soft, hard, flags, total;
+  unsigned soft, ext_soft, hard, flags, stage, stage_stride, total;
 };
-__host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
+// fused: + stage[2][N_short * Z] bytes, the int8 soft buffers of the pair while the dematcher prologue combines them
+__host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad, bool fused)
 {
   const unsigned hrr = (bg == 2) ? 14 : 26, M = (bg == 2) ? LDPC_BG2_M : LDPC_BG1_M, K = (bg == 2) ? 10 : 22;
   const unsigned msg_bytes16 = (((unsigned)(K * Z + 7) / 8) + 15) & ~15u;
@@ -413,7 +414,9 @@ __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad)
   l.ext_soft = l.soft + hrr * Z * 4;
   l.hard = l.ext_soft + (M - 4) * zpad * 4;
   l.flags = l.hard + 2 * msg_bytes16;
-  l.total = (l.flags + 8 * 4 + 15) & ~15u;
+  l.stage = (l.flags + 8 * 4 + 15) & ~15u;
+  l.stage_stride = ((((bg == 2) ? 50u : 66u) * Z) + 15) & ~15u;
+  l.total = l.stage + (fused ? 2 * l.stage_stride : 0);
   return l;
 }
 constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base address written by tcgen05.alloc
@@ -434,7 +437,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   const int nwg = zpad >> 5;             // warps per group
   const int bar_id = 1 + grp;
   const unsigned msg_len = (unsigned)(K * Z), msg_bytes = (msg_len + 7) / 8, msg_bytes16 = (msg_bytes + 15) & ~15u;
-  const TmLayout lay = tm_layout(BG, Z, zpad);
+  const TmLayout lay = tm_layout(BG, Z, zpad, FUSED);
 
   // tensor memory: the whole 512 columns (one block per SM), released at the end
   if (warp == 0) {
@@ -490,19 +493,28 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     const int8_t* inA = p.llr_base + wA.in_offset;
     const int8_t* inB = p.llr_base + wB.in_offset;
     unsigned lastA = 0, lastB = 0;
+    auto convert = [](int a, int b) {
+      float fa = (float)a, fb = (float)b;
+      fa = (a > LLR_MAX) ? __int_as_float(0x7f800000) : ((a < -LLR_MAX) ? __int_as_float(0xff800000) : fa);
+      fb = (b > LLR_MAX) ? __int_as_float(0x7f800000) : ((b < -LLR_MAX) ? __int_as_float(0xff800000) : fb);
+      return tm::un(__floats2half2_rn(fa, fb));
+    };
+    auto put = [&](int n, unsigned v) {
+      if (n < HRR) {
+        soft_w[n * Z + t] = v;
+      } else {
+        ext_soft_w[(n - HRR) * zpad + t] = v;
+      }
+    };
+    // Loads are issued in batches of U columns before any of them is consumed: the prologue is pure DRAM latency
+    // (profiles/r01_ncu_tmem_full_summary.txt: one-at-a-time loads were 12 % of all stall samples).
+    constexpr int U = (BG == 2) ? 10 : 11;
+    static_assert((K + M - 2) % U == 0, "batches must tile the stored columns");
     if (c.active) {
-      // Loads are issued in batches of U columns before any of them is consumed: the prologue is pure DRAM latency
-      // (profiles/r01_ncu_tmem_full_summary.txt: one-at-a-time loads were 12 % of all stall samples).
-      constexpr int U = (BG == 2) ? 10 : 11;
-      static_assert((K + M - 2) % U == 0, "batches must tile the stored columns");
-      auto convert = [](int a, int b) {
-        float fa = (float)a, fb = (float)b;
-        fa = (a > LLR_MAX) ? __int_as_float(0x7f800000) : ((a < -LLR_MAX) ? __int_as_float(0xff800000) : fa);
-        fb = (b > LLR_MAX) ? __int_as_float(0x7f800000) : ((b < -LLR_MAX) ? __int_as_float(0xff800000) : fb);
-        return tm::un(__floats2half2_rn(fa, fb));
-      };
       soft_w[t] = 0, soft_w[Z + t] = 0;  // punctured columns
-      if constexpr (!FUSED) {
+    }
+    if constexpr (!FUSED) {
+      if (c.active) {
         const unsigned lenA = useA ? wA.in_length : 0u, lenB = useB ? wB.in_length : 0u;
 #pragma unroll 1
         for (int n0 = 2; n0 < K + M; n0 += U) {
@@ -519,63 +531,68 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
             const unsigned i = (unsigned)(n - 2) * Z + t;
             lastA = a[k] ? i + 1 : lastA;
             lastB = b[k] ? i + 1 : lastB;
-            const unsigned v = convert(a[k], b[k]);
-            if (n < HRR) {
-              soft_w[n * Z + t] = v;
-            } else {
-              ext_soft_w[(n - HRR) * zpad + t] = v;
-            }
+            put(n, convert(a[k], b[k]));
           }
         }
-      } else {
-        // rate dematching + HARQ combining as the load: position i of each soft buffer = closed form of its previous
-        // content and the input elements that land on it (ldpc_dematch.cuh); codeblocks with skip_decode are combined too
-        const DematchGeom gA = make_dematch_geom(BG, (unsigned)Z, wA.nof_filler_bits, wA.rv, wA.mod_order, wA.Nref,
-                                                 wA.rm_length, wA.new_data);
-        const DematchGeom gB = make_dematch_geom(BG, (unsigned)Z, wB.nof_filler_bits, wB.rv, wB.mod_order, wB.Nref,
-                                                 wB.rm_length, wB.new_data);
-        const int8_t* rmA = p.rm_base + wA.rm_offset;
-        const int8_t* rmB = p.rm_base + wB.rm_offset;
-        int8_t* softA = p.soft_rw + wA.in_offset;
-        int8_t* softB = p.soft_rw + wB.in_offset;
-        constexpr int UF = (BG == 2) ? 5 : 6;
-        static_assert((K + M - 2) % UF == 0, "batches must tile the stored columns");
+      }
+    } else {
+      // Rate dematching + HARQ combining as the load (ldpc_dematch.cuh, phases A-C), on a shared-memory copy of the two
+      // soft buffers; codeblocks with skip_decode are combined too. One pass over the arena: read once, written once.
+      const DematchGeom gA = make_dematch_geom(BG, (unsigned)Z, wA.nof_filler_bits, wA.rv, wA.mod_order, wA.Nref,
+                                               wA.rm_length, wA.new_data);
+      const DematchGeom gB = make_dematch_geom(BG, (unsigned)Z, wB.nof_filler_bits, wB.rv, wB.mod_order, wB.Nref,
+                                               wB.rm_length, wB.new_data);
+      const int8_t* rmA = p.rm_base + wA.rm_offset;
+      const int8_t* rmB = p.rm_base + wB.rm_offset;
+      int8_t* softA = p.soft_rw + wA.in_offset;
+      int8_t* softB = p.soft_rw + wB.in_offset;
+      int8_t* stA = reinterpret_cast<int8_t*>(gsm + lay.stage);
+      int8_t* stB = stA + lay.stage_stride;
+      if (c.active) {  // phase A
 #pragma unroll 1
-        for (int n0 = 2; n0 < K + M; n0 += UF) {
-          int pa[UF], pb[UF], xa[UF], xb[UF];
-          DematchRank da[UF], db[UF];
+        for (int n0 = 2; n0 < K + M; n0 += U) {
+          int a[U], b[U];
 #pragma unroll
-          for (int k = 0; k < UF; ++k) {
+          for (int k = 0; k < U; ++k) {
             const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
-            da[k] = dematch_rank(gA, i);
-            db[k] = dematch_rank(gB, i);
-            pa[k] = softA[i];
-            pb[k] = hasB ? (int)softB[i] : 0;
-            xa[k] = (da[k].live && da[k].r < gA.E) ? dematch_input(gA, rmA, da[k].r) : 0;
-            xb[k] = (hasB && db[k].live && db[k].r < gB.E) ? dematch_input(gB, rmB, db[k].r) : 0;
+            a[k] = softA[i];
+            b[k] = hasB ? (int)softB[i] : 0;
           }
 #pragma unroll
-          for (int k = 0; k < UF; ++k) {
-            const int n = n0 + k;
-            const unsigned i = (unsigned)(n - 2) * Z + t;
-            int a = dematch_combine(gA, rmA, i, pa[k], da[k], xa[k]);
-            softA[i] = (int8_t)a;  // written back unconditionally: one coalesced byte per lane
-            int b = 0;
-            if (hasB) {
-              b = dematch_combine(gB, rmB, i, pb[k], db[k], xb[k]);
-              softB[i] = (int8_t)b;
-            }
-            a = useA ? a : 0;
-            b = useB ? b : 0;
-            lastA = a ? i + 1 : lastA;
-            lastB = b ? i + 1 : lastB;
-            const unsigned v = convert(a, b);
-            if (n < HRR) {
-              soft_w[n * Z + t] = v;
-            } else {
-              ext_soft_w[(n - HRR) * zpad + t] = v;
-            }
+          for (int k = 0; k < U; ++k) {
+            const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
+            stA[i] = (int8_t)dematch_init(gA, i, a[k]);
+            stB[i] = (int8_t)dematch_init(gB, i, b[k]);
           }
+        }
+      }
+      tm::group_barrier(bar_id, zpad);
+      const unsigned lapsA = dematch_nof_laps(gA), lapsB = hasB ? dematch_nof_laps(gB) : 0u;  // phase B
+      for (unsigned lap = 0; lap < max(lapsA, lapsB); ++lap) {
+        if (lap < lapsA) {
+          dematch_scatter_lap(gA, rmA, stA, lap, (unsigned)t, (unsigned)zpad);
+        }
+        if (lap < lapsB) {
+          dematch_scatter_lap(gB, rmB, stB, lap, (unsigned)t, (unsigned)zpad);
+        }
+        tm::group_barrier(bar_id, zpad);
+      }
+      if (c.active) {  // phase C
+#pragma unroll 4
+        for (int n = 2; n < K + M; ++n) {
+          const unsigned i = (unsigned)(n - 2) * Z + t;
+          int a = dematch_final(gA, i, stA[i]);
+          softA[i] = (int8_t)a;
+          int b = 0;
+          if (hasB) {
+            b = dematch_final(gB, i, stB[i]);
+            softB[i] = (int8_t)b;
+          }
+          a = useA ? a : 0;
+          b = useB ? b : 0;
+          lastA = a ? i + 1 : lastA;
+          lastB = b ? i + 1 : lastB;
+          put(n, convert(a, b));
         }
       }
     }
@@ -858,7 +875,7 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   p.nof_cbs = n, p.Z = gp.Z, p.Z4 = 4 * gp.Z, p.max_iterations = gp.max_iterations;
   p.zpad = ((gp.Z + 31) / 32) * 32;
   p.groups = TM_THREADS / p.zpad;
-  const TmLayout lay = tm_layout(gp.bg, gp.Z, p.zpad);
+  const TmLayout lay = tm_layout(gp.bg, gp.Z, p.zpad, fused);
   p.group_stride = lay.total;
   const unsigned n_pairs = (n + 1) / 2;
   if ((unsigned)p.groups > n_pairs) {
