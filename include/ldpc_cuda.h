@@ -192,6 +192,15 @@ int ldpc_cuda_softbuffer_write(ldpc_cuda_handle* handle, uint64_t offset, const 
 /* Device address of the arena (NULL before reserve). */
 void* ldpc_cuda_softbuffer_ptr(ldpc_cuda_handle* handle);
 
+/* A soft-buffer arena that outlives / is shared by several handles of one device (= the memory of one
+ * rx_softbuffer_pool, lib/phy/upper/rx_softbuffer_codeblock_pool.h:35-117, which all PUSCH decoder threads share).
+ * arena_create allocates nof_bytes of device memory, zero-initialised; softbuffer_attach makes a handle use it (not owned:
+ * destroying the handle or reserving a private arena leaves it alone). Handles working on the same arena must use
+ * disjoint soft_offset ranges at any one time, as the reference's decoders use disjoint codeblock entries. */
+int ldpc_cuda_arena_create(int device, uint64_t nof_bytes, void** arena_d);
+int ldpc_cuda_arena_destroy(int device, void* arena_d);
+int ldpc_cuda_softbuffer_attach(ldpc_cuda_handle* handle, void* arena_d, uint64_t nof_bytes);
+
 /* ---------------------------------------------------------------------------------------------------------------------
  * Host-side geometry helpers (no GPU needed).
  */

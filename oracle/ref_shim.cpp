@@ -30,6 +30,7 @@
 // reference's UNMODIFIED pusch_decoder_impl / interfaces run on top of the B200 kernels. Used by tests/test_gpu_dropin.py.
 #include "../srsran_project_23.5_b200/host/ldpc_cuda_factories.h"
 #include "../srsran_project_23.5_b200/host/pusch_decoder_cuda.h"
+#include "../srsran_project_23.5_b200/host/rx_softbuffer_pool_cuda.h"
 #endif
 
 #include <algorithm>
@@ -134,7 +135,8 @@ private:
 struct pusch_handle {
   std::unique_ptr<pusch_decoder>                     dec;
   std::unique_ptr<rx_softbuffer_pool>                pool;
-  bool                                               batched = false;
+  bool                                               batched  = false;
+  bool                                               big_pool = false; // the pool itself takes > 52 codeblocks
   std::map<unsigned, std::unique_ptr<big_softbuffer>> big; // key (rnti << 8) | harq, transport blocks above 52 codeblocks
 };
 
@@ -539,6 +541,20 @@ void* ref_pusch_create(const char* decoder_type,
     auto* h                      = new pusch_handle;
     h->dec                       = std::move(dec);
     h->batched                   = true;
+    if (std::strcmp(dematcher_type, "cuda-pool") == 0) {
+      // device-resident HARQ pool (soft bits in one HBM arena shared by the decoders, reference FSM on the host)
+      rx_softbuffer_pool_cuda_config cc = {};
+      cc.max_softbuffers                = max_softbuffers;
+      cc.max_nof_codeblocks             = max_nof_codeblocks;
+      cc.expire_timeout_slots           = expire_timeout_slots;
+      h->pool                           = create_rx_softbuffer_pool_cuda(cc);
+      h->big_pool                       = true;
+      if (!h->pool) {
+        delete h;
+        return nullptr;
+      }
+      return h;
+    }
     rx_softbuffer_pool_config rc = {};
     rc.max_codeblock_size        = ldpc::MAX_CODEBLOCK_SIZE;
     rc.max_softbuffers           = max_softbuffers;
@@ -602,7 +618,7 @@ int ref_pusch_decode(void*         handle,
   unsigned nof_cbs = ldpc::compute_nof_codeblocks(units::bits(tb_bytes * 8), to_bg(bg));
   slot_point               slot(1, slot_count % (1024 * 20));
   rx_softbuffer_identifier id  = {static_cast<uint16_t>(rnti), static_cast<uint8_t>(harq_id)};
-  const bool               big = nof_cbs > MAX_NOF_SEGMENTS;
+  const bool               big = nof_cbs > MAX_NOF_SEGMENTS && !h->big_pool;
   if (big && !h->batched) {
     return -2; // the reference pusch_decoder_impl and pool stop at 52 codeblocks
   }
@@ -652,6 +668,109 @@ int ref_pusch_decode(void*         handle,
   }
   h->pool->run_slot(slot);
   return 0;
+}
+
+// ---- soft-buffer pool state machine, reference ("sw") or the product's device pool without device memory ("cuda-host") -----
+struct pool_handle {
+  std::unique_ptr<rx_softbuffer_pool>                pool;
+  std::vector<std::unique_ptr<unique_rx_softbuffer>> held;
+};
+
+void* ref_pool_create(const char* type, unsigned max_softbuffers, unsigned max_nof_codeblocks, unsigned expire_timeout_slots)
+{
+  auto* h = new pool_handle;
+  if (std::strcmp(type, "sw") == 0) {
+    rx_softbuffer_pool_config rc = {};
+    rc.max_codeblock_size        = ldpc::MAX_CODEBLOCK_SIZE;
+    rc.max_softbuffers           = max_softbuffers;
+    rc.max_nof_codeblocks        = max_nof_codeblocks;
+    rc.expire_timeout_slots      = expire_timeout_slots;
+    h->pool                      = create_rx_softbuffer_pool(rc);
+  }
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (std::strcmp(type, "cuda-host") == 0 || std::strcmp(type, "cuda") == 0) {
+    rx_softbuffer_pool_cuda_config cc = {};
+    cc.max_softbuffers                = max_softbuffers;
+    cc.max_nof_codeblocks             = max_nof_codeblocks;
+    cc.expire_timeout_slots           = expire_timeout_slots;
+    cc.device                         = std::strcmp(type, "cuda") == 0 ? 0 : -1;
+    h->pool                           = create_rx_softbuffer_pool_cuda(cc);
+  }
+#endif
+  if (!h->pool) {
+    delete h;
+    return nullptr;
+  }
+  return h;
+}
+
+void ref_pool_destroy(void* handle)
+{
+  auto* h = static_cast<pool_handle*>(handle);
+  h->held.clear();
+  delete h;
+}
+
+// Returns a token (>= 0) for a valid, locked soft buffer, -1 for an invalid reservation.
+int ref_pool_reserve(void* handle, unsigned slot_count, unsigned rnti, unsigned harq_id, unsigned nof_codeblocks)
+{
+  auto*                    h = static_cast<pool_handle*>(handle);
+  slot_point               slot(1, slot_count % (1024 * 20));
+  rx_softbuffer_identifier id = {static_cast<uint16_t>(rnti), static_cast<uint8_t>(harq_id)};
+  auto buf = std::make_unique<unique_rx_softbuffer>(h->pool->reserve_softbuffer(slot, id, nof_codeblocks));
+  if (!buf->is_valid()) {
+    return -1;
+  }
+  for (size_t i = 0; i != h->held.size(); ++i) {
+    if (!h->held[i]) {
+      h->held[i] = std::move(buf);
+      return static_cast<int>(i);
+    }
+  }
+  h->held.push_back(std::move(buf));
+  return static_cast<int>(h->held.size() - 1);
+}
+
+int ref_pool_nof_codeblocks(void* handle, int token)
+{
+  return static_cast<int>(static_cast<pool_handle*>(handle)->held[token]->get().get_nof_codeblocks());
+}
+
+// value < 0: read the CRC flag of codeblock cb; otherwise set it. Returns the (new) flag.
+int ref_pool_crc(void* handle, int token, unsigned cb, int value)
+{
+  span<bool> crc = static_cast<pool_handle*>(handle)->held[token]->get().get_codeblocks_crc();
+  if (value >= 0) {
+    crc[cb] = value != 0;
+  }
+  return crc[cb] ? 1 : 0;
+}
+
+// First byte of the stored message of codeblock cb (value < 0: read, else write): data bits persist with the entry.
+int ref_pool_data_byte(void* handle, int token, unsigned cb, int value)
+{
+  bit_buffer bits = static_cast<pool_handle*>(handle)->held[token]->get().get_codeblock_data_bits(cb, 64);
+  if (value >= 0) {
+    bits.get_buffer()[0] = static_cast<uint8_t>(value);
+  }
+  return bits.get_buffer()[0];
+}
+
+void ref_pool_unlock(void* handle, int token)
+{
+  static_cast<pool_handle*>(handle)->held[token].reset();
+}
+
+void ref_pool_release(void* handle, int token)
+{
+  auto* h = static_cast<pool_handle*>(handle);
+  h->held[token]->release();
+  h->held[token].reset();
+}
+
+void ref_pool_run_slot(void* handle, unsigned slot_count)
+{
+  static_cast<pool_handle*>(handle)->pool->run_slot(slot_point(1, slot_count % (1024 * 20)));
 }
 
 } // extern "C"

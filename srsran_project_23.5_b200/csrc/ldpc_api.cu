@@ -48,6 +48,7 @@ struct ldpc_cuda_handle {
   size_t d_out_cap = 0;
   int8_t* arena = nullptr;
   size_t arena_bytes = 0;
+  bool arena_owned = false;  // false: attached, belongs to a pool shared between handles
   unsigned* pair_counter = nullptr;  // packed kernel: dynamic work distribution
   uint64_t launches = 0;
   std::vector<uint32_t> order;
@@ -387,7 +388,9 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
   cudaFree(h->d_results);
   cudaFree(h->d_in);
   cudaFree(h->d_out);
-  cudaFree(h->arena);
+  if (h->arena_owned) {
+    cudaFree(h->arena);
+  }
   cudaFree(h->pair_counter);
   if (h->stream) {
     cudaStreamDestroy(h->stream);
@@ -690,12 +693,13 @@ int ldpc_cuda_softbuffer_reserve(ldpc_cuda_handle* h, uint64_t nof_bytes)
   }
   CUDA_TRY(cudaSetDevice(h->device));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
-  if (h->arena) {
+  if (h->arena && h->arena_owned) {
     CUDA_TRY(cudaFree(h->arena));
-    h->arena = nullptr, h->arena_bytes = 0;
   }
+  h->arena = nullptr, h->arena_bytes = 0, h->arena_owned = false;
   CUDA_TRY(cudaMalloc(&h->arena, nof_bytes));
   h->arena_bytes = nof_bytes;
+  h->arena_owned = true;
   // zero-initialised once, like the reference pool (rx_softbuffer_codeblock_pool.h)
   CUDA_TRY(cudaMemsetAsync(h->arena, 0, nof_bytes, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -735,5 +739,52 @@ int ldpc_cuda_softbuffer_write(ldpc_cuda_handle* h, uint64_t offset, const int8_
 }
 
 void* ldpc_cuda_softbuffer_ptr(ldpc_cuda_handle* h) { return h ? h->arena : nullptr; }
+
+int ldpc_cuda_arena_create(int device, uint64_t nof_bytes, void** arena_d)
+{
+  if (arena_d == nullptr || nof_bytes == 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  *arena_d = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n || !usable_device(device)) {
+    cudaGetLastError();
+    return LDPC_CUDA_ERR_CUDA;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  void* ptr = nullptr;
+  CUDA_TRY(cudaMalloc(&ptr, nof_bytes));
+  // zero-initialised once, like the reference pool (rx_softbuffer_codeblock_pool.h)
+  CUDA_TRY(cudaMemset(ptr, 0, nof_bytes));
+  *arena_d = ptr;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_arena_destroy(int device, void* arena_d)
+{
+  if (arena_d == nullptr) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaFree(arena_d));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_softbuffer_attach(ldpc_cuda_handle* h, void* arena_d, uint64_t nof_bytes)
+{
+  if (h == nullptr || arena_d == nullptr || nof_bytes == 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (h->arena && h->arena_owned) {
+    CUDA_TRY(cudaFree(h->arena));
+  }
+  h->arena = static_cast<int8_t*>(arena_d);
+  h->arena_bytes = nof_bytes;
+  h->arena_owned = false;
+  return LDPC_CUDA_OK;
+}
 
 }  // extern "C"

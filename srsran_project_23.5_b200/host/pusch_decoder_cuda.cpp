@@ -2,6 +2,7 @@
 #include "pusch_decoder_cuda.h"
 
 #include "../../include/ldpc_cuda.h"
+#include "rx_softbuffer_pool_cuda.h"
 #include "srsran/phy/upper/channel_processors/pusch_decoder.h"
 #include "srsran/ran/modulation_scheme.h"
 
@@ -139,8 +140,9 @@ private:
 class pusch_decoder_cuda : public pusch_decoder
 {
 public:
-  pusch_decoder_cuda(ldpc_cuda_handle* h_, std::unique_ptr<crc_calculator> crc24A_, unsigned arena_cbs, unsigned max_cbs) :
-    h(h_), crc24A(std::move(crc24A_)), index(arena_cbs), descs(max_cbs), results(max_cbs), crc_bits(max_cbs)
+  pusch_decoder_cuda(ldpc_cuda_handle* h_, std::unique_ptr<crc_calculator> crc24A_, unsigned arena_cbs_, unsigned max_cbs) :
+    h(h_), crc24A(std::move(crc24A_)), arena_cbs(arena_cbs_), index(arena_cbs_), descs(max_cbs), results(max_cbs),
+    crc_bits(max_cbs)
   {
   }
   ~pusch_decoder_cuda() override { ldpc_cuda_destroy(h); }
@@ -177,13 +179,35 @@ public:
     }
 
     const unsigned Z = descs[0].lifting_size, K = (bg == 2 ? 10u : 22u) * Z, kb = (K + 7) / 8;
-    bool           fresh = false;
-    const auto&    slot  = index.get(soft_codeword, nof_cbs, fresh);
-    if (fresh && !cfg.new_data) {
-      // the soft bits of this process were evicted (or never seen): combine into zeros
-      check(ldpc_cuda_softbuffer_zero(h, static_cast<uint64_t>(slot.first) * CB_SLOT_BYTES,
-                                      static_cast<uint64_t>(nof_cbs) * CB_SLOT_BYTES),
-            "ldpc_cuda_softbuffer_zero");
+    // Where the soft bits of this HARQ process live: in the device arena of a rx_softbuffer_pool_cuda (shared by every
+    // decoder of the device, reservation / expiry handled by the pool), or - with the reference's host pool - in this
+    // decoder's private arena, indexed by the rx_softbuffer object with least-recently-used eviction.
+    const auto* dev_sb = dynamic_cast<const rx_softbuffer_device*>(soft_codeword);
+    unsigned    first_slot = 0;
+    if (dev_sb != nullptr && dev_sb->arena() != nullptr) {
+      if (attached != dev_sb->arena()) {
+        check(ldpc_cuda_softbuffer_attach(h, dev_sb->arena(), dev_sb->arena_bytes()), "ldpc_cuda_softbuffer_attach");
+        attached      = dev_sb->arena();
+        private_arena = false; // attaching released the decoder's own arena
+      }
+    } else {
+      if (attached != nullptr || !private_arena) {
+        check(ldpc_cuda_softbuffer_reserve(h, static_cast<uint64_t>(arena_cbs) * CB_SLOT_BYTES),
+              "ldpc_cuda_softbuffer_reserve");
+        attached      = nullptr;
+        private_arena = true;
+        index         = arena_index(arena_cbs);
+      }
+      dev_sb            = nullptr;
+      bool        fresh = false;
+      const auto& slot  = index.get(soft_codeword, nof_cbs, fresh);
+      first_slot        = slot.first;
+      if (fresh && !cfg.new_data) {
+        // the soft bits of this process were evicted (or never seen): combine into zeros
+        check(ldpc_cuda_softbuffer_zero(h, static_cast<uint64_t>(slot.first) * CB_SLOT_BYTES,
+                                        static_cast<uint64_t>(nof_cbs) * CB_SLOT_BYTES),
+              "ldpc_cuda_softbuffer_zero");
+      }
     }
     cb_out.resize(static_cast<size_t>(nof_cbs) * kb);
     for (unsigned r = 0; r != nof_cbs; ++r) {
@@ -191,7 +215,7 @@ public:
       d.early_stop         = cfg.use_early_stop ? 1 : 0;
       d.new_data           = cfg.new_data ? 1 : 0;
       d.skip_decode        = cb_crcs[r] ? 1 : 0; // decoded in an earlier transmission: combine only (:179-184)
-      d.soft_offset        = static_cast<uint64_t>(slot.first + r) * CB_SLOT_BYTES;
+      d.soft_offset        = dev_sb ? dev_sb->soft_offset(r) : static_cast<uint64_t>(first_slot + r) * CB_SLOT_BYTES;
       d.out_offset         = static_cast<uint64_t>(r) * kb;
       // bits a decode does not write (all-zero input, padding of the last byte) keep the stored message's content
       bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
@@ -253,7 +277,10 @@ public:
 private:
   ldpc_cuda_handle*                h;
   std::unique_ptr<crc_calculator>  crc24A;
+  unsigned                         arena_cbs;
   arena_index                      index;
+  const void*                      attached      = nullptr; // arena of a rx_softbuffer_pool_cuda in use
+  bool                             private_arena = false;   // the decoder's own arena exists (allocated on first use)
   std::vector<ldpc_cuda_cb_desc>   descs;
   std::vector<ldpc_cuda_cb_result> results;
   std::vector<uint32_t>            crc_bits;
@@ -271,10 +298,6 @@ public:
   {
     ldpc_cuda_handle* h = nullptr;
     if (ldpc_cuda_create(&h, cfg.device, cfg.max_codeblocks_per_tb, 0) != LDPC_CUDA_OK) {
-      return nullptr;
-    }
-    if (ldpc_cuda_softbuffer_reserve(h, static_cast<uint64_t>(cfg.arena_codeblocks) * CB_SLOT_BYTES) != LDPC_CUDA_OK) {
-      ldpc_cuda_destroy(h);
       return nullptr;
     }
     return std::make_unique<pusch_decoder_cuda>(

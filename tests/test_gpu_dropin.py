@@ -136,16 +136,19 @@ def test_pusch_decoder_harq_through_reference_pusch_decoder_impl(lib, bg, tbs_by
 @pytest.mark.parametrize("bg,tbs_bytes,Qm,nsym,esn0", [(1, 4001, 4, 12000, -1.0), (2, 300, 2, 2400, -4.5),
                                                       (1, 20004, 6, 42588, 2.0), (2, 1905, 4, 6000, -3.0)])
 @pytest.mark.parametrize("early_stop", [True, False])
-def test_batched_pusch_decoder_cuda_matches_reference_pusch_decoder(lib, bg, tbs_bytes, Qm, nsym, esn0, early_stop):
+@pytest.mark.parametrize("pool", [b"", b"cuda-pool"], ids=["ref-pool", "device-pool"])
+def test_batched_pusch_decoder_cuda_matches_reference_pusch_decoder(lib, bg, tbs_bytes, Qm, nsym, esn0, early_stop, pool):
     """The product's pusch_decoder (srsran_project_23.5_b200/host/pusch_decoder_cuda.cpp: ONE fused batched call per TB,
-    soft bits resident on the device, CRC flags and messages in the reference's rx_softbuffer from the reference's pool)
-    against the reference's pusch_decoder_impl on its generic factories, over a HARQ sequence rv {0,2,3,1}."""
+    soft bits resident on the device, CRC flags and messages in the rx_softbuffer) against the reference's
+    pusch_decoder_impl on its generic factories, over a HARQ sequence rv {0,2,3,1}. Soft buffers come either from the
+    reference's own pool (the decoder then keeps the soft bits in a private device arena keyed by the buffer object) or
+    from the product's device-resident pool (host/rx_softbuffer_pool_cuda.cpp: one HBM arena, reference FSM)."""
     rng = np.random.default_rng(tbs_bytes + Qm + 1)
     tb = rng.integers(0, 256, tbs_bytes).astype(np.uint8)
     segs = lib.segment_tx(tb, bg, Qm, 1, nsym)
     meta = lib.segment_rx(tbs_bytes * 8, bg, Qm, 1, nsym)
     h_sw = lib.lib.ref_pusch_create(b"generic", b"generic", 4, 64, 100)
-    h_cu = lib.lib.ref_pusch_create(b"cuda-batched", b"", 4, 64, 100)
+    h_cu = lib.lib.ref_pusch_create(b"cuda-batched", pool, 4, 64, 100)
     assert h_sw and h_cu
     seen_ok = False
     for i, rv in enumerate([0, 2, 3, 1]):
@@ -167,7 +170,8 @@ def test_batched_pusch_decoder_cuda_matches_reference_pusch_decoder(lib, bg, tbs
     lib.lib.ref_pusch_destroy(h_cu)
 
 
-def test_batched_pusch_decoder_cuda_full_slot_tb_152_codeblocks(lib):
+@pytest.mark.parametrize("pool", [b"", b"cuda-pool"], ids=["shim-softbuffer", "device-pool"])
+def test_batched_pusch_decoder_cuda_full_slot_tb_152_codeblocks(lib, pool):
     """BASELINE config 3 through the pusch_decoder interface: TBS 1 277 992 bits = 152 codeblocks, beyond the reference's
     52-codeblock limit (MAX_NOF_SEGMENTS), so the expectation is the transmitted TB itself. First transmission with a
     third of the codeblocks below their decoding threshold (TB fails, the good codeblocks are remembered), rv2
@@ -177,7 +181,7 @@ def test_batched_pusch_decoder_cuda_full_slot_tb_152_codeblocks(lib):
     tb, cws, meta = O.build_transport_block(rng, tbs, 1, Qm, layers, nsym)
     C = len(cws)
     assert C == 152
-    h = lib.lib.ref_pusch_create(b"cuda-batched", b"", 2, 160, 100)
+    h = lib.lib.ref_pusch_create(b"cuda-batched", pool, 2, 160, 100)
     assert h
     # the reference decoder itself cannot take this transport block
     h_sw = lib.lib.ref_pusch_create(b"generic", b"generic", 2, 52, 100)
