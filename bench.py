@@ -113,14 +113,45 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.samples)}
 
 
-def make_workload_gpu(torch, dev, n_cb, esn0_db, seed):
+def crc_attach(bits, poly, order):
+    """bits: uint8 [n, L] of 0/1. Returns [n, L + order] with the CRC of every row appended (MSB first, zero initial
+    value, no final XOR - TS 38.212 5.1). Plain numpy, vectorised over the rows; input generation only."""
+    n, L = bits.shape
+    reg = np.zeros(n, np.uint32)
+    top, mask = np.uint32(1 << (order - 1)), np.uint32((1 << order) - 1)
+    for i in range(L):
+        fb = ((reg & top) != 0).astype(np.uint32) ^ bits[:, i]
+        reg = ((reg << np.uint32(1)) & mask) ^ (fb * np.uint32(poly & ((1 << order) - 1)))
+    crc = np.stack([(reg >> np.uint32(order - 1 - k)) & np.uint32(1) for k in range(order)], axis=1).astype(np.uint8)
+    return np.concatenate([bits, crc], axis=1)
+
+
+CRC24B_POLY = 0x1800063
+
+
+def make_codewords_gpu(torch, pkg, dec, dev, rng, n, bg, Z, fillers):
+    """n random messages with a valid CRC24B (and `fillers` filler bits), encoded by the PRODUCT's own device encoder
+    (ldpc_cuda_encode_batch_device; parity-tested against the reference encoder in tests/test_gpu_tx.py). Returns the
+    device tensors (messages [n, K], codeblocks [n, N]) as unpacked bits, fillers = 254."""
+    K, N = (22 if bg == 1 else 10) * Z, (66 if bg == 1 else 50) * Z
+    payload = rng.integers(0, 2, (n, K - fillers - 24)).astype(np.uint8)
+    msg = np.concatenate([crc_attach(payload, CRC24B_POLY, 24), np.full((n, fillers), 254, np.uint8)], axis=1)
+    msg_d = torch.from_numpy(np.ascontiguousarray(msg)).to(dev)
+    cw_d = torch.empty((n, N), dtype=torch.uint8, device=dev)
+    descs = pkg.make_descs(n, bg, Z, nof_filler_bits=fillers, in_stride=K, out_stride=N)
+    torch.cuda.synchronize()
+    dec.encode_batch_device(descs, msg_d.data_ptr(), cw_d.data_ptr())
+    dec.synchronize()
+    return msg_d, cw_d
+
+
+def make_workload_gpu(torch, pkg, dec, dev, n_cb, esn0_db, seed):
     """n_cb AWGN-corrupted BG1 Z=384 codewords as int8 LLRs on the GPU (256 distinct codewords carrying a CRC24B,
     independent noise per codeblock), quantised as log_likelihood_ratio::quantize(2y/sigma^2, 20)."""
-    import oracles as O
     rng = np.random.default_rng(seed)
     n_distinct = 256
-    cws = np.stack([O.make_codeword(rng, BG, Z, 0, O.CRC24B)[1] for _ in range(n_distinct)])
-    cw_d = torch.from_numpy(cws.astype(np.int8)).to(dev)
+    _, cw_d = make_codewords_gpu(torch, pkg, dec, dev, rng, n_distinct, BG, Z, 0)
+    cw_d = cw_d.to(torch.int8)
     sigma2 = 10.0 ** (-esn0_db / 10.0) / 2.0
     g = torch.Generator(device=dev)
     g.manual_seed(seed)
@@ -142,26 +173,31 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
     bits, 152 codeblocks BG1 Z=384 F=16, E_r 8960/8992), 16 cells per slot. A step = 8 x (slot A, slot B): slot A carries
     16 new TBs, 4 of them at an SNR where every codeblock fails; slot B carries 12 new TBs and the rv2 retransmissions of
     those 4 (new_data = 0: read-combine-write of their soft buffers). 12.5 % of TB transmissions are retransmissions."""
-    import oracles as O
     tbs, Qm, layers, nsym = 1277992, 8, 4, 42588 * 4
     descs, _ = pkg.segment(tbs, 1, Qm, layers, nsym)
     C, F, Zs = len(descs), 16, 384
     Kb, Nsoft, kb = 22 * Zs, 66 * Zs, 22 * Zs // 8
     rng = np.random.default_rng(7)
     E = descs["rm_length"].astype(np.int64)
-    tx = {0: [], 2: []}
-    for r in range(C):
-        msg, cw = O.make_codeword(rng, 1, Zs, F, O.CRC24B)
-        for rv in (0, 2):
-            tx[rv].append(O.port().rate_match(cw, int(E[r]), rv, Qm, 0, F))
+    # one transport block's worth of codeblocks, encoded and rate-matched (rv 0 and rv 2) by the product's device kernels
+    _, cw_d = make_codewords_gpu(torch, pkg, dec, dev, rng, C, 1, Zs, F)
+    tx = {}
+    for rv in (0, 2):
+        d = descs.copy()
+        d["rv"] = rv
+        d["in_offset"] = np.arange(C, dtype=np.uint64) * np.uint64(Nsoft)
+        d["out_offset"] = np.concatenate([[0], np.cumsum(E)[:-1]]).astype(np.uint64)
+        out = torch.empty(int(E.sum()), dtype=torch.uint8, device=dev)
+        dec.rate_match_batch_device(d, cw_d.data_ptr(), out.data_ptr())
+        dec.synchronize()
+        tx[rv] = out.to(torch.int8)
     tb_bytes = int(E.sum())
     tb_off = np.concatenate([[0], np.cumsum(E)[:-1]])
     sets, cells, n_bad = 8, 16, 4
     g = torch.Generator(device=dev)
     g.manual_seed(99)
 
-    def noisy(bits_list, n_tb, esn0_of_tb):
-        base = torch.from_numpy(np.concatenate(bits_list).astype(np.int8)).to(dev)
+    def noisy(base, n_tb, esn0_of_tb):
         out = torch.empty((n_tb, tb_bytes), dtype=torch.int8, device=dev)
         for i in range(n_tb):
             sigma2 = 10.0 ** (-esn0_of_tb(i) / 10.0) / 2.0
@@ -316,7 +352,7 @@ def run_ours(args):
     n_cb = args.codeblocks
     dec = pkg.LdpcCuda(device=local, max_codeblocks=max(n_cb, 19456), max_iterations=args.max_iters)
     stream = torch.cuda.ExternalStream(dec.stream, device=dev)
-    llr_d = make_workload_gpu(torch, dev, n_cb, args.esn0, 1000 + rank)
+    llr_d = make_workload_gpu(torch, pkg, dec, dev, n_cb, args.esn0, 1000 + rank)
     out_d = torch.zeros((n_cb, OUT_BYTES), dtype=torch.uint8, device=dev)
     res_d = torch.zeros((n_cb,), dtype=torch.int32, device=dev)
     torch.cuda.synchronize()

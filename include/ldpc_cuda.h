@@ -202,6 +202,31 @@ int ldpc_cuda_arena_destroy(int device, void* arena_d);
 int ldpc_cuda_softbuffer_attach(ldpc_cuda_handle* handle, void* arena_d, uint64_t nof_bytes);
 
 /* ---------------------------------------------------------------------------------------------------------------------
+ * Transmit side (also how bench.py builds its synthetic codewords without leaving the device).
+ * Bits are unpacked, one per byte, as in the reference's encoder chain; filler bits are 254
+ * (include/srsran/phy/upper/channel_coding/ldpc/ldpc.h:113).
+ *   encode     = ldpc_encoder::encode (ldpc_encoder.h:41-46, ldpc_encoder_impl.cpp:33-150): bg_K*Z message bits at
+ *                in_offset -> N_short*Z codeblock bits at out_offset (the 2Z punctured bits are not part of it).
+ *   rate_match = ldpc_rate_matcher::rate_match (ldpc_rate_matcher.h:41-45, ldpc_rate_matcher_impl.cpp:43-200):
+ *                N_short*Z codeblock bits at in_offset -> rm_length bits at out_offset (rv, mod_order, Nref, fillers).
+ */
+int ldpc_cuda_encode_batch_device(ldpc_cuda_handle*        handle,
+                                  uint32_t                 nof_codeblocks,
+                                  const ldpc_cuda_cb_desc* descs,
+                                  const uint8_t*           msg_bits_d,
+                                  uint8_t*                 codeblocks_d);
+int ldpc_cuda_rate_match_batch_device(ldpc_cuda_handle*        handle,
+                                      uint32_t                 nof_codeblocks,
+                                      const ldpc_cuda_cb_desc* descs,
+                                      const uint8_t*           codeblocks_d,
+                                      uint8_t*                 out_bits_d);
+int ldpc_cuda_encode(ldpc_cuda_handle* handle, const ldpc_cuda_cb_desc* desc, const uint8_t* msg_bits, uint8_t* codeblock);
+int ldpc_cuda_rate_match(ldpc_cuda_handle*        handle,
+                         const ldpc_cuda_cb_desc* desc,
+                         const uint8_t*           codeblock,
+                         uint8_t*                 out_bits);
+
+/* ---------------------------------------------------------------------------------------------------------------------
  * Host-side geometry helpers (no GPU needed).
  */
 

@@ -10,6 +10,7 @@
 #include "ldpc_kernels_scalar.cuh"
 #include "ldpc_dematch.cuh"
 #include "ldpc_kernels_tmem.cuh"  // needs c_crc / crc_warp from the scalar header
+#include "ldpc_encode.cuh"
 
 using namespace ldpc_b200;
 
@@ -262,6 +263,50 @@ int run_groups(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
       return rc;
     }
   }
+  return LDPC_CUDA_OK;
+}
+
+// Work records of the transmit-side kernels (ldpc_encode.cuh): crc_poly carries the base graph, in_length the lifting
+// size, reserved the lifting set. rate_match: geometry fields as for the dematcher.
+int stage_tx_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool rate_match)
+{
+  if (n > h->max_cbs) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  for (uint32_t i = 0; i != n; ++i) {
+    const ldpc_cuda_cb_desc& d = descs[i];
+    if ((d.base_graph != 1 && d.base_graph != 2) || lifting_set_of(d.lifting_size) < 0 ||
+        d.nof_filler_bits >= (bg_K(d.base_graph) - 2) * d.lifting_size) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    if (rate_match) {
+      const int rc = validate_dematch_desc(d);
+      if (rc != LDPC_CUDA_OK) {
+        return rc;
+      }
+    }
+  }
+  const unsigned slot = (h->work_slot++) & 1u;
+  CUDA_TRY(cudaEventSynchronize(h->ev_work[slot]));
+  CbWork* h_work = h->h_work[slot];
+  for (uint32_t i = 0; i != n; ++i) {
+    const ldpc_cuda_cb_desc& d = descs[i];
+    CbWork& w = h_work[i];
+    std::memset(&w, 0, sizeof(w));
+    w.in_offset = d.in_offset;
+    w.out_offset = d.out_offset;
+    w.in_length = d.lifting_size;
+    w.crc_poly = d.base_graph;
+    w.reserved = (unsigned)lifting_set_of(d.lifting_size);
+    w.nof_filler_bits = d.nof_filler_bits;
+    w.rm_length = d.rm_length;
+    w.Nref = d.Nref;
+    w.rv = d.rv;
+    w.mod_order = d.mod_order;
+    w.result_index = i;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h_work, sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaEventRecord(h->ev_work[slot], h->stream));
   return LDPC_CUDA_OK;
 }
 
@@ -785,6 +830,91 @@ int ldpc_cuda_softbuffer_attach(ldpc_cuda_handle* h, void* arena_d, uint64_t nof
   h->arena_bytes = nof_bytes;
   h->arena_owned = false;
   return LDPC_CUDA_OK;
+}
+
+// ---- transmit side (LDPC encoder + rate matcher), device buffers ------------------------------------------------------
+int ldpc_cuda_encode_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const uint8_t* msg_bits_d,
+                                  uint8_t* codeblocks_d)
+{
+  if (h == nullptr || descs == nullptr || msg_bits_d == nullptr || codeblocks_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  const int rc = stage_tx_work(h, n, descs, false);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  const size_t smem = (size_t)(LDPC_BG1_N_FULL + 4) * MAX_Z;
+  const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 4u);
+  ldpc_encode_kernel<<<grid, ENC_THREADS, smem, h->stream>>>(h->d_work, n, msg_bits_d, codeblocks_d);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_rate_match_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs,
+                                      const uint8_t* codeblocks_d, uint8_t* out_bits_d)
+{
+  if (h == nullptr || descs == nullptr || codeblocks_d == nullptr || out_bits_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  const int rc = stage_tx_work(h, n, descs, true);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 16u);
+  ldpc_rate_match_kernel<<<grid, 256, 0, h->stream>>>(h->d_work, n, codeblocks_d, out_bits_d);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+// ---- transmit side, one codeblock, host buffers (mirrors of ldpc_encoder::encode / ldpc_rate_matcher::rate_match) -------
+static int tx_single(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, const uint8_t* in, uint8_t* out, bool rate_match)
+{
+  if (h == nullptr || desc == nullptr || in == nullptr || out == nullptr ||
+      (desc->base_graph != 1 && desc->base_graph != 2) || lifting_set_of(desc->lifting_size) < 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  const size_t Z = desc->lifting_size, N = bg_N_short(desc->base_graph) * Z, K = bg_K(desc->base_graph) * Z;
+  const size_t in_bytes = rate_match ? N : K, out_bytes = rate_match ? desc->rm_length : N;
+  if (out_bytes == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  int rc = ensure_capacity(h, in_bytes, out_bytes);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  ldpc_cuda_cb_desc d = *desc;
+  d.in_offset = 0, d.out_offset = 0;
+  CUDA_TRY(cudaMemcpyAsync(h->d_in, in, in_bytes, cudaMemcpyHostToDevice, h->stream));
+  rc = rate_match ? ldpc_cuda_rate_match_batch_device(h, 1, &d, reinterpret_cast<const uint8_t*>(h->d_in), h->d_out)
+                  : ldpc_cuda_encode_batch_device(h, 1, &d, reinterpret_cast<const uint8_t*>(h->d_in), h->d_out);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_encode(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, const uint8_t* msg_bits, uint8_t* codeblock)
+{
+  return tx_single(h, desc, msg_bits, codeblock, false);
+}
+
+int ldpc_cuda_rate_match(ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* desc, const uint8_t* codeblock, uint8_t* out_bits)
+{
+  return tx_single(h, desc, codeblock, out_bits, true);
 }
 
 }  // extern "C"

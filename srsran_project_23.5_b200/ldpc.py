@@ -77,6 +77,13 @@ def library():
         L.ldpc_cuda_softbuffer_write.argtypes = [vp, u64, vp, u64]
         L.ldpc_cuda_softbuffer_ptr.argtypes = [vp]
         L.ldpc_cuda_softbuffer_ptr.restype = vp
+        L.ldpc_cuda_arena_create.argtypes = [i32, u64, ctypes.POINTER(vp)]
+        L.ldpc_cuda_arena_destroy.argtypes = [i32, vp]
+        L.ldpc_cuda_softbuffer_attach.argtypes = [vp, vp, u64]
+        for name in ("ldpc_cuda_encode_batch_device", "ldpc_cuda_rate_match_batch_device"):
+            getattr(L, name).argtypes = [vp, u32, vp, vp, vp]
+        for name in ("ldpc_cuda_encode", "ldpc_cuda_rate_match"):
+            getattr(L, name).argtypes = [vp, vp, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
         L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
         _lib = L
@@ -224,6 +231,35 @@ class LdpcCuda:
         descs = np.ascontiguousarray(descs, CB_DESC)
         self._check(self._L.ldpc_cuda_dematch_decode_batch_device(self._h, descs.size, _ptr(descs), rm_ptr, out_ptr,
                                                                   results_ptr), "ldpc_cuda_dematch_decode_batch_device")
+
+    # -- transmit side (encoder + rate matcher) ------------------------------------------------------------------------
+    def encode(self, bg, Z, msg_bits):
+        """ldpc_encoder::encode: bg_K*Z unpacked bits (fillers = 254) -> N_short*Z codeblock bits."""
+        msg_bits = np.ascontiguousarray(msg_bits, np.uint8)
+        assert msg_bits.size == BG_K[bg] * Z
+        d = make_descs(1, bg, Z)
+        out = np.zeros(BG_N_SHORT[bg] * Z, np.uint8)
+        self._check(self._L.ldpc_cuda_encode(self._h, _ptr(d), _ptr(msg_bits), _ptr(out)), "ldpc_cuda_encode")
+        return out
+
+    def rate_match(self, codeblock, E, bg, Z, rv=0, mod_order=1, Nref=0, fillers=0):
+        """ldpc_rate_matcher::rate_match: N_short*Z codeblock bits -> E rate-matched, interleaved bits."""
+        codeblock = np.ascontiguousarray(codeblock, np.uint8)
+        assert codeblock.size == BG_N_SHORT[bg] * Z
+        d = make_descs(1, bg, Z, rm_length=E, rv=rv, mod_order=mod_order, Nref=Nref, nof_filler_bits=fillers)
+        out = np.zeros(max(E, 1), np.uint8)
+        self._check(self._L.ldpc_cuda_rate_match(self._h, _ptr(d), _ptr(codeblock), _ptr(out)), "ldpc_cuda_rate_match")
+        return out[:E]
+
+    def encode_batch_device(self, descs, msg_ptr, out_ptr):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_encode_batch_device(self._h, descs.size, _ptr(descs), msg_ptr, out_ptr),
+                    "ldpc_cuda_encode_batch_device")
+
+    def rate_match_batch_device(self, descs, cw_ptr, out_ptr):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_rate_match_batch_device(self._h, descs.size, _ptr(descs), cw_ptr, out_ptr),
+                    "ldpc_cuda_rate_match_batch_device")
 
     # -- soft-buffer arena ---------------------------------------------------------------------------------------------
     def softbuffer_reserve(self, nbytes):
