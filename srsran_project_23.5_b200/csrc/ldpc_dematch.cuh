@@ -152,13 +152,20 @@ __device__ __forceinline__ int dematch_position(const DematchGeom& g, const int8
 }
 
 // ---- the same dematcher as three data-parallel phases over a staging copy of the soft buffer (fused decoder prologue) ----
-// A: every position takes its previous content with the new-data initialisation applied (the zero / filler ranges the
-//    first loop pass of allot_llrs writes before it copies);
-// B: lap by lap, every de-interleaved input element is copied (first lap of new data) or saturating-added to the position
-//    it lands on - at most one element per position and lap, laps in order, so the result equals the serial walk;
-// C: the trailing zero range (dematch_final), then the value goes back to HBM and on to the decoder.
+// A (dematch_stage_in): every position takes its previous content with the new-data initialisation applied (the zero /
+//    filler ranges the first loop pass of allot_llrs writes before it copies) and the trailing zero range - the walk
+//    never reaches that range when it exists, so zeroing it first is the same as zeroing it last;
+// B: every de-interleaved input element is copied (first lap of new data) or saturating-added to the position it lands
+//    on. E <= V (dematch_scatter_once): a position receives at most one element, so the elements are taken in INPUT
+//    order - coalesced loads, symbol index i and bit index j known without a division - and no ordering is needed.
+//    Otherwise (dematch_scatter_lap) lap by lap: at most one element per position and lap, laps in order, so the result
+//    equals the serial walk;
+// C (dematch_stage_out): the combined soft buffer goes back to the HBM arena.
 __device__ __forceinline__ int dematch_init(const DematchGeom& g, unsigned p, int prev)
 {
+  if (p >= g.zero_from) {
+    return 0;
+  }
   if (g.new_data && g.E != 0) {
     if (p >= g.info && p < g.sys) {
       return LLR_INF;
@@ -170,13 +177,202 @@ __device__ __forceinline__ int dematch_init(const DematchGeom& g, unsigned p, in
   return prev;
 }
 
+// New data from the start of the buffer that covers the whole message and ends inside the first lap (the usual first
+// transmission): [0, info) and [sys, end) are copied, fillers are +127, [end, N) is zeroed - nothing of the previous
+// content survives, so the arena is not read at all.
+__device__ __forceinline__ bool dematch_is_fresh(const DematchGeom& g)
+{
+  return g.new_data && g.k0 == 0 && g.Ncb == g.N && g.E >= g.info && g.E < g.V;
+}
+
+// stage[lo, hi) = value by the threads of one group; 16-byte stores on the aligned interior (stage is 16-byte aligned).
+__device__ __forceinline__ void dematch_fill(int8_t* stage, unsigned lo, unsigned hi, int value, unsigned t, unsigned stride)
+{
+  if (lo >= hi) {
+    return;
+  }
+  unsigned a = (lo + 15u) & ~15u;
+  a = a < hi ? a : hi;
+  unsigned b = hi & ~15u;
+  b = b > a ? b : a;
+  for (unsigned p = lo + t; p < a; p += stride) {
+    stage[p] = (int8_t)value;
+  }
+  const unsigned w = (unsigned)(value & 0xff) * 0x01010101u;
+  const uint4 v = make_uint4(w, w, w, w);
+  for (unsigned p = a + 16u * t; p < b; p += 16u * stride) {
+    *reinterpret_cast<uint4*>(stage + p) = v;
+  }
+  for (unsigned p = b + t; p < hi; p += stride) {
+    stage[p] = (int8_t)value;
+  }
+}
+
+// Phase A for one codeblock.
+__device__ __noinline__ void dematch_stage_in(const DematchGeom& g, const int8_t* __restrict__ soft, int8_t* stage,
+                                                 unsigned t, unsigned stride)
+{
+  if (dematch_is_fresh(g)) {
+    dematch_fill(stage, g.info, g.sys, LLR_INF, t, stride);
+    dematch_fill(stage, g.zero_from, g.N, 0, t, stride);
+    return;
+  }
+  const bool plain = !(g.new_data && g.E != 0) && g.zero_from >= g.N;  // dematch_init is the identity
+  if (plain && (reinterpret_cast<uintptr_t>(soft) & 15u) == 0) {
+    constexpr int VB = 5;  // 66 * 384 / 16 / 384 = 4.1 vectors per thread
+    const unsigned nvec = g.N / 16u;
+    for (unsigned v0 = t; v0 < nvec; v0 += VB * stride) {
+      uint4 x[VB];
+#pragma unroll
+      for (int k = 0; k < VB; ++k) {
+        const unsigned v = v0 + k * stride;
+        if (v < nvec) {
+          x[k] = __ldg(reinterpret_cast<const uint4*>(soft) + v);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < VB; ++k) {
+        const unsigned v = v0 + k * stride;
+        if (v < nvec) {
+          reinterpret_cast<uint4*>(stage)[v] = x[k];
+        }
+      }
+    }
+    for (unsigned p = nvec * 16u + t; p < g.N; p += stride) {
+      stage[p] = soft[p];
+    }
+    return;
+  }
+  constexpr int UB = 11;
+  for (unsigned p0 = t; p0 < g.N; p0 += UB * stride) {
+    int x[UB];
+#pragma unroll
+    for (int k = 0; k < UB; ++k) {
+      const unsigned p = p0 + k * stride;
+      x[k] = (p < g.N) ? (int)soft[p] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < UB; ++k) {
+      const unsigned p = p0 + k * stride;
+      if (p < g.N) {
+        stage[p] = (int8_t)dematch_init(g, p, x[k]);
+      }
+    }
+  }
+}
+
+// Phase C for one codeblock (the conversion to the decoder's format reads the same staging copy).
+__device__ __noinline__ void dematch_stage_out(const DematchGeom& g, const int8_t* stage, int8_t* __restrict__ soft,
+                                                  unsigned t, unsigned stride)
+{
+  unsigned done = 0;
+  if ((reinterpret_cast<uintptr_t>(soft) & 15u) == 0) {
+    const unsigned nvec = g.N / 16u;
+    for (unsigned v = t; v < nvec; v += stride) {
+      reinterpret_cast<uint4*>(soft)[v] = reinterpret_cast<const uint4*>(stage)[v];
+    }
+    done = nvec * 16u;
+  }
+  for (unsigned p = done + t; p < g.N; p += stride) {
+    soft[p] = stage[p];
+  }
+}
+
 __device__ __forceinline__ unsigned dematch_nof_laps(const DematchGeom& g)
 {
   return g.E ? (g.Ls0 + g.E + g.V - 1) / g.V : 0u;
 }
 
+// E <= V and Qm in {1, 2, 4, 6, 8}: handled by dematch_scatter_once.
+__device__ __forceinline__ bool dematch_single_pass(const DematchGeom& g)
+{
+  const bool qm_ok = g.Qm == 1 || g.Qm == 2 || g.Qm == 4 || g.Qm == 6 || g.Qm == 8;
+  return g.E != 0 && g.E <= g.V && qm_ok && (g.E % g.Qm) == 0;
+}
+
+// Symbol i carries the elements e = j * (E / Qm) + i, j < Qm, of the de-interleaved stream (deinterleave_llrs :200-210).
+template <int QM>
+__device__ __forceinline__ void dematch_scatter_once_q(const DematchGeom& g, const int8_t* __restrict__ in, int8_t* stage,
+                                                       unsigned t, unsigned stride)
+{
+  constexpr int BI = (QM >= 4) ? 2 : ((QM == 2) ? 4 : 8);  // symbols per batch: 8 .. 16 LLRs in flight per thread
+  const unsigned Kq = g.E / QM;
+  const unsigned gap = g.sys - g.info;
+  const unsigned wrap = g.V - g.Ls0;  // elements from here on are in the second lap (positions before the start)
+  const bool vec = (QM == 2 || QM == 4 || QM == 8) && (reinterpret_cast<uintptr_t>(in) % QM) == 0;
+  for (unsigned i0 = t; i0 < Kq; i0 += BI * stride) {
+    int x[BI][QM];
+#pragma unroll
+    for (int b = 0; b < BI; ++b) {
+      const unsigned i = i0 + b * stride;
+      if (i < Kq) {
+        if (vec) {
+          unsigned lo = 0, hi = 0;
+          if (QM == 2) {
+            lo = __ldg(reinterpret_cast<const unsigned short*>(in) + i);
+          } else if (QM == 4) {
+            lo = __ldg(reinterpret_cast<const unsigned*>(in) + i);
+          } else {
+            const uint2 w = __ldg(reinterpret_cast<const uint2*>(in) + i);
+            lo = w.x, hi = w.y;
+          }
+#pragma unroll
+          for (int j = 0; j < QM; ++j) {
+            x[b][j] = (int)(int8_t)(((j < 4) ? lo : hi) >> (8 * (j & 3)));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < QM; ++j) {
+            x[b][j] = in[i * QM + j];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < BI; ++b) {
+      const unsigned i = i0 + b * stride;
+      if (i < Kq) {
+#pragma unroll
+        for (int j = 0; j < QM; ++j) {
+          const unsigned e = (unsigned)j * Kq + i;
+          const bool first = e < wrap;
+          const unsigned L = first ? g.Ls0 + e : e - wrap;
+          const unsigned p = L < g.info ? L : L + gap;
+          if (g.new_data && first) {
+            stage[p] = (int8_t)x[b][j];
+          } else {
+            stage[p] = (int8_t)llr_add((int)stage[p], x[b][j]);
+          }
+        }
+      }
+    }
+  }
+}
+
+__device__ __noinline__ void dematch_scatter_once(const DematchGeom& g, const int8_t* __restrict__ in, int8_t* stage,
+                                                     unsigned t, unsigned stride)
+{
+  switch (g.Qm) {
+    case 1:
+      dematch_scatter_once_q<1>(g, in, stage, t, stride);
+      break;
+    case 2:
+      dematch_scatter_once_q<2>(g, in, stage, t, stride);
+      break;
+    case 4:
+      dematch_scatter_once_q<4>(g, in, stage, t, stride);
+      break;
+    case 6:
+      dematch_scatter_once_q<6>(g, in, stage, t, stride);
+      break;
+    default:
+      dematch_scatter_once_q<8>(g, in, stage, t, stride);
+      break;
+  }
+}
+
 // Elements of lap `lap` handled by thread t of `stride`; loads are issued BATCH at a time before they are combined.
-__device__ __forceinline__ void dematch_scatter_lap(const DematchGeom& g, const int8_t* __restrict__ in, int8_t* stage,
+__device__ __noinline__ void dematch_scatter_lap(const DematchGeom& g, const int8_t* __restrict__ in, int8_t* stage,
                                                     unsigned lap, unsigned t, unsigned stride)
 {
   constexpr int BATCH = 8;
@@ -202,11 +398,6 @@ __device__ __forceinline__ void dematch_scatter_lap(const DematchGeom& g, const 
       }
     }
   }
-}
-
-__device__ __forceinline__ int dematch_final(const DematchGeom& g, unsigned p, int v)
-{
-  return p >= g.zero_from ? 0 : v;
 }
 
 // Standalone kernel: one block per codeblock, threads stride over the N positions (coalesced read-modify-write).

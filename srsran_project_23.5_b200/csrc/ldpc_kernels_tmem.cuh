@@ -548,26 +548,21 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       int8_t* softB = p.soft_rw + wB.in_offset;
       int8_t* stA = reinterpret_cast<int8_t*>(gsm + lay.stage);
       int8_t* stB = stA + lay.stage_stride;
-      if (c.active) {  // phase A
-#pragma unroll 1
-        for (int n0 = 2; n0 < K + M; n0 += U) {
-          int a[U], b[U];
-#pragma unroll
-          for (int k = 0; k < U; ++k) {
-            const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
-            a[k] = softA[i];
-            b[k] = hasB ? (int)softB[i] : 0;
-          }
-#pragma unroll
-          for (int k = 0; k < U; ++k) {
-            const unsigned i = (unsigned)(n0 - 2 + k) * Z + t;
-            stA[i] = (int8_t)dematch_init(gA, i, a[k]);
-            stB[i] = (int8_t)dematch_init(gB, i, b[k]);
-          }
-        }
+      // phase A: staging copy of the previous content (not read at all for a fresh first transmission)
+      dematch_stage_in(gA, softA, stA, (unsigned)t, (unsigned)zpad);
+      if (hasB) {
+        dematch_stage_in(gB, softB, stB, (unsigned)t, (unsigned)zpad);
       }
       tm::group_barrier(bar_id, zpad);
-      const unsigned lapsA = dematch_nof_laps(gA), lapsB = hasB ? dematch_nof_laps(gB) : 0u;  // phase B
+      // phase B: one pass in input order when no position is hit twice, else lap by lap
+      const bool onceA = dematch_single_pass(gA), onceB = hasB && dematch_single_pass(gB);
+      if (onceA) {
+        dematch_scatter_once(gA, rmA, stA, (unsigned)t, (unsigned)zpad);
+      }
+      if (onceB) {
+        dematch_scatter_once(gB, rmB, stB, (unsigned)t, (unsigned)zpad);
+      }
+      const unsigned lapsA = onceA ? 0u : dematch_nof_laps(gA), lapsB = (!hasB || onceB) ? 0u : dematch_nof_laps(gB);
       for (unsigned lap = 0; lap < max(lapsA, lapsB); ++lap) {
         if (lap < lapsA) {
           dematch_scatter_lap(gA, rmA, stA, lap, (unsigned)t, (unsigned)zpad);
@@ -575,21 +570,22 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         if (lap < lapsB) {
           dematch_scatter_lap(gB, rmB, stB, lap, (unsigned)t, (unsigned)zpad);
         }
-        tm::group_barrier(bar_id, zpad);
+        if (lap + 1 < max(lapsA, lapsB)) {
+          tm::group_barrier(bar_id, zpad);
+        }
       }
-      if (c.active) {  // phase C
-#pragma unroll 4
+      tm::group_barrier(bar_id, zpad);
+      // phase C: back to the arena, and on to the decoder
+      dematch_stage_out(gA, stA, softA, (unsigned)t, (unsigned)zpad);
+      if (hasB) {
+        dematch_stage_out(gB, stB, softB, (unsigned)t, (unsigned)zpad);
+      }
+      if (c.active) {
+#pragma unroll 6
         for (int n = 2; n < K + M; ++n) {
           const unsigned i = (unsigned)(n - 2) * Z + t;
-          int a = dematch_final(gA, i, stA[i]);
-          softA[i] = (int8_t)a;
-          int b = 0;
-          if (hasB) {
-            b = dematch_final(gB, i, stB[i]);
-            softB[i] = (int8_t)b;
-          }
-          a = useA ? a : 0;
-          b = useB ? b : 0;
+          const int a = useA ? (int)stA[i] : 0;
+          const int b = useB ? (int)stB[i] : 0;
           lastA = a ? i + 1 : lastA;
           lastB = b ? i + 1 : lastB;
           put(n, convert(a, b));

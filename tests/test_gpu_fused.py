@@ -202,15 +202,18 @@ def test_host_entry_pipelined_chunks_two_groups(dec):
         assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, i
 
 
-def test_fused_prologue_dematch_all_cases_with_stale_priors(dec):
+@pytest.mark.parametrize("misaligned", [False, True])
+def test_fused_prologue_dematch_all_cases_with_stale_priors(dec, misaligned):
     """Every rate-dematcher case of test_gpu_parity.RM_CASES through the FUSED entry: the arena is pre-filled with arbitrary
     prior contents (so the reference's stale-byte / partial-zeroing behaviour is visible), one call carries a new-data and
-    a retransmission codeblock of each case plus a skip_decode twin; soft buffers, bits and results must equal the oracle."""
+    a retransmission codeblock of each case plus a skip_decode twin; soft buffers, bits and results must equal the oracle.
+    misaligned: soft buffers and rate-matched inputs at odd byte offsets (the kernel's 16-byte / Qm-byte vector accesses
+    must fall back to byte accesses)."""
     from test_gpu_parity import RM_CASES
     rng = np.random.default_rng(35)
     dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
     cbs = []
-    so = oo = ro = 0
+    so, oo, ro = (5, 0, 3) if misaligned else (0, 0, 0)
     for case in RM_CASES:
         bg, Z, E, rv, Qm, Nref, F = case
         N, kb = O.BG_N_SHORT[bg] * Z, (O.BG_K[bg] * Z + 7) // 8
@@ -219,9 +222,9 @@ def test_fused_prologue_dematch_all_cases_with_stale_priors(dec):
             prior[(O.BG_K[bg] - 2) * Z - F:(O.BG_K[bg] - 2) * Z] = 127
             rm = rng.integers(-120, 121, E).astype(np.int8)
             cbs.append(dict(case=case, new_data=new_data, skip=skip, prior=prior, rm=rm, so=so, oo=oo, ro=ro, N=N, kb=kb))
-            so += (N + 63) // 64 * 64
+            so += N + 3 if misaligned else (N + 63) // 64 * 64
             oo += kb
-            ro += E
+            ro += E + (1 if misaligned else 0)
     dec.softbuffer_reserve(so)
     descs = np.zeros(len(cbs), pkg.CB_DESC)
     for i, c in enumerate(cbs):
@@ -232,7 +235,9 @@ def test_fused_prologue_dematch_all_cases_with_stale_priors(dec):
         d["early_stop"], d["rv"], d["mod_order"], d["Nref"], d["new_data"] = 1, rv, Qm, Nref, c["new_data"]
         d["rm_length"], d["in_offset"], d["out_offset"], d["soft_offset"] = E, c["ro"], c["oo"], c["so"]
         d["in_length"], d["skip_decode"] = c["N"], c["skip"]
-    rm_all = np.concatenate([c["rm"] for c in cbs] + [np.zeros(16, np.int8)])
+    rm_all = np.zeros(ro + 16, np.int8)
+    for c in cbs:
+        rm_all[c["ro"]:c["ro"] + c["rm"].size] = c["rm"]
     out = np.full(oo, 0xa5, np.uint8)
     out, res = dec.dematch_decode_batch(descs, rm_all, out)
     for i, c in enumerate(cbs):
