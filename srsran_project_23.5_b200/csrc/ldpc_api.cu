@@ -87,6 +87,21 @@ int upload_constants()
     crc_params(code, ct.poly[code], ct.order[code]);
   }
   CUDA_TRY(cudaMemcpyToSymbol(c_crc, &ct, sizeof(ct)));
+  // x^e mod P per polynomial (parallel CRC check of the TMEM decoder kernel)
+  static std::vector<unsigned> pw;
+  pw.assign(3 * TM_CRC_POW_LEN, 0);
+  for (int code = 1; code <= 3; ++code) {
+    const unsigned top = 1U << ct.order[code];
+    unsigned       r   = 1;
+    for (unsigned e = 0; e != TM_CRC_POW_LEN; ++e) {
+      pw[(code - 1) * TM_CRC_POW_LEN + e] = r;
+      r <<= 1;
+      if (r & top) {
+        r ^= ct.poly[code];
+      }
+    }
+  }
+  CUDA_TRY(cudaMemcpyToSymbol(g_crc_pow, pw.data(), pw.size() * sizeof(unsigned)));
   return LDPC_CUDA_OK;
 }
 

@@ -49,6 +49,11 @@ struct __align__(8) TmEdge {
   unsigned cb;  // byte offset of the column's soft values inside the group's soft array: col * 4 * Z
 };
 
+constexpr unsigned TM_CRC_POW_LEN = 22 * 384;  // longest message in bits
+// x^e mod P for CRC16 / CRC24A / CRC24B (poly codes 1..3), e < TM_CRC_POW_LEN: the parallel CRC check of the decoder.
+// Filled once per device by upload_constants (ldpc_api.cu).
+__device__ unsigned g_crc_pow[3][TM_CRC_POW_LEN];
+
 struct TmemParams {
   const CbWork* work;
   const int8_t* llr_base;   // decoder input LLRs; fused: the soft-buffer arena (same memory as soft_rw)
@@ -400,7 +405,7 @@ __device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, 
 }  // namespace tm
 
 // Shared memory: [crc tables 3 x 256 words][group 0][group 1]...; group = soft[HRR * Z] | ext_soft[(M-4) * zpad] |
-// hard[2][msg_bytes16] | flags[8]. ext_soft holds one word per extension node (see row_body).
+// hard[2][msg_bytes16] | flags[16]. ext_soft holds one word per extension node (see row_body).
 struct TmLayout {
   unsigned soft, ext_soft, hard, flags, stage, stage_stride, total;
 };
@@ -414,7 +419,7 @@ __host__ __device__ inline TmLayout tm_layout(int bg, int Z, int zpad, bool fuse
   l.ext_soft = l.soft + hrr * Z * 4;
   l.hard = l.ext_soft + (M - 4) * zpad * 4;
   l.flags = l.hard + 2 * msg_bytes16;
-  l.stage = (l.flags + 8 * 4 + 15) & ~15u;
+  l.stage = (l.flags + 16 * 4 + 15) & ~15u;
   l.stage_stride = ((((bg == 2) ? 50u : 66u) * Z) + 15) & ~15u;
   l.total = l.stage + (fused ? 2 * l.stage_stride : 0);
   return l;
@@ -445,10 +450,6 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  unsigned* s_crc = reinterpret_cast<unsigned*>(smem);
-  for (int i = tid; i < 3 * 256; i += blockDim.x) {
-    s_crc[i] = c_crc.table[1 + i / 256][i & 255];
-  }
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;");
@@ -457,7 +458,8 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   unsigned* soft_w = reinterpret_cast<unsigned*>(gsm + lay.soft);
   unsigned* ext_soft_w = reinterpret_cast<unsigned*>(gsm + lay.ext_soft);
   unsigned char* hard = gsm + lay.hard;
-  volatile unsigned* flags = reinterpret_cast<volatile unsigned*>(gsm + lay.flags);  // 0,1: last non-zero + 1; 2,3: crc ok; 4: pair
+  // 0,1: last non-zero + 1; 4: pair; 8..11: CRC remainder accumulators of (A, B) for even / odd iterations
+  volatile unsigned* flags = reinterpret_cast<volatile unsigned*>(gsm + lay.flags);
 
   tm::Ctx c;
   c.soft_base = (unsigned)__cvta_generic_to_shared(soft_w);
@@ -473,7 +475,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     // next pair of codeblocks for this group
     if (t == 0) {
       flags[4] = atomicAdd(p.pair_counter, 1u);
-      flags[0] = 0, flags[1] = 0, flags[2] = 0, flags[3] = 0;
+      flags[0] = 0, flags[1] = 0, flags[8] = 0, flags[9] = 0, flags[10] = 0, flags[11] = 0;
     }
     tm::group_barrier(bar_id, zpad);
     const unsigned pair = (unsigned)tm::uniform((int)flags[4]);
@@ -661,40 +663,80 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       const bool chkA = !doneA && ((wA.crc_poly && wA.early_stop) || last);
       const bool chkB = !doneB && ((wB.crc_poly && wB.early_stop) || last);
       if (chkA || chkB) {
-        // get_hard_bits (ldpc_decoder_generic.cpp:132-138): bit = soft <= 0, MSB first, both halves at once
-        for (unsigned i = t; i < msg_bytes; i += zpad) {
-          unsigned ba = 0, bb = 0;
+        // CRC of the hard decisions (ldpc_decoder_impl.cpp:125-133) without serialising on one warp: the remainder of
+        // the message polynomial is linear in its bits, so every thread XORs x^(n-1-i) mod P (table crc_pow) for the set
+        // bits it owns and the group XOR-reduces the partial remainders. remainder == 0 <=> crc->calculate(...) == 0
+        // (x is invertible modulo the generator polynomials, all of which have a constant term).
+        const bool crcA = chkA && wA.crc_poly, crcB = chkB && wB.crc_poly;
+        const unsigned acc_a = 8 + 2 * (it & 1), acc_b = acc_a + 1;
+        if (crcA || crcB) {
+          const unsigned nbA = msg_len - wA.nof_filler_bits, nbB = msg_len - wB.nof_filler_bits;
+          const unsigned* tabA = g_crc_pow[crcA ? wA.crc_poly - 1 : 0];
+          const unsigned* tabB = g_crc_pow[crcB ? wB.crc_poly - 1 : 0];
+          unsigned ra = 0, rb = 0;
+          if (c.active) {
+            // all table loads are issued before the first is consumed (no branch on the bit: the entry is masked)
+            constexpr int CU = (K == 22) ? 11 : 10;
+#pragma unroll 1
+            for (int n0 = 0; n0 < K; n0 += CU) {
+              unsigned v[CU], ea[CU], eb[CU];
 #pragma unroll
-          for (unsigned k = 0; k < 8; ++k) {
-            const unsigned b = 8 * i + k;
-            if (b < msg_len) {
-              const unsigned v = soft_w[b];
-              ba |= (((v & 0x7fffu) == 0 || (v & 0x8000u)) ? 0x80u : 0u) >> k;
-              bb |= (((v & 0x7fff0000u) == 0 || (v & 0x80000000u)) ? 0x80u : 0u) >> k;
+              for (int u = 0; u < CU; ++u) {
+                v[u] = soft_w[(unsigned)(n0 + u) * Z + t];
+              }
+#pragma unroll
+              for (int u = 0; u < CU; ++u) {
+                const unsigned i = (unsigned)(n0 + u) * Z + t;
+                ea[u] = __ldg(tabA + (i < nbA ? nbA - 1 - i : 0));
+                eb[u] = __ldg(tabB + (i < nbB ? nbB - 1 - i : 0));
+              }
+#pragma unroll
+              for (int u = 0; u < CU; ++u) {
+                const unsigned i = (unsigned)(n0 + u) * Z + t;
+                // get_hard_bits (ldpc_decoder_generic.cpp:132-138): bit = soft <= 0
+                const bool ba = (v[u] & 0x7fffu) == 0 || (v[u] & 0x8000u);
+                const bool bb = (v[u] & 0x7fff0000u) == 0 || (v[u] & 0x80000000u);
+                ra ^= (crcA && ba && i < nbA) ? ea[u] : 0u;
+                rb ^= (crcB && bb && i < nbB) ? eb[u] : 0u;
+              }
             }
           }
-          if (chkA) {
-            hard[i] = (unsigned char)ba;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            ra ^= __shfl_xor_sync(0xffffffffu, ra, o);
+            rb ^= __shfl_xor_sync(0xffffffffu, rb, o);
           }
-          if (chkB) {
+          if ((t & 31) == 0) {
+            if (ra) {
+              atomicXor(const_cast<unsigned*>(&flags[acc_a]), ra);
+            }
+            if (rb) {
+              atomicXor(const_cast<unsigned*>(&flags[acc_b]), rb);
+            }
+          }
+          if (t == 0) {  // the accumulators of the next iteration (nobody touches them before the barriers below)
+            flags[acc_a ^ 2] = 0, flags[acc_b ^ 2] = 0;
+          }
+        }
+        tm::group_barrier(bar_id, zpad);
+        const bool okA = crcA && flags[acc_a] == 0, okB = crcB && flags[acc_b] == 0;
+        // the message bytes are only formed for a codeblock that finishes now
+        if ((chkA && (okA || last)) || (chkB && (okB || last))) {
+          for (unsigned i = t; i < msg_bytes; i += zpad) {
+            unsigned ba = 0, bb = 0;
+#pragma unroll
+            for (unsigned k = 0; k < 8; ++k) {
+              const unsigned b = 8 * i + k;
+              if (b < msg_len) {
+                const unsigned v = soft_w[b];
+                ba |= (((v & 0x7fffu) == 0 || (v & 0x8000u)) ? 0x80u : 0u) >> k;
+                bb |= (((v & 0x7fff0000u) == 0 || (v & 0x80000000u)) ? 0x80u : 0u) >> k;
+              }
+            }
+            hard[i] = (unsigned char)ba;
             hard[msg_bytes16 + i] = (unsigned char)bb;
           }
         }
-        tm::group_barrier(bar_id, zpad);
-        if (wig == 0 && chkA && wA.crc_poly) {
-          const unsigned rr = crc_warp(hard, msg_len - wA.nof_filler_bits, wA.crc_poly, s_crc + 256 * (wA.crc_poly - 1));
-          if ((t & 31) == 0) {
-            flags[2] = (rr == 0);
-          }
-        }
-        if (wig == (nwg > 1 ? 1 : 0) && chkB && wB.crc_poly) {
-          const unsigned rr =
-              crc_warp(hard + msg_bytes16, msg_len - wB.nof_filler_bits, wB.crc_poly, s_crc + 256 * (wB.crc_poly - 1));
-          if ((t & 31) == 0) {
-            flags[3] = (rr == 0);
-          }
-        }
-        tm::group_barrier(bar_id, zpad);
         auto finish = [&](const CbWork& w, CbResult& res, bool& done, const unsigned char* bits, bool ok) {
           if (ok || last) {
             uint8_t* out = p.out_base + w.out_offset;
@@ -716,10 +758,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
           }
         };
         if (chkA) {
-          finish(wA, resA, doneA, hard, wA.crc_poly && flags[2]);
+          finish(wA, resA, doneA, hard, okA);
         }
         if (chkB) {
-          finish(wB, resB, doneB, hard + msg_bytes16, wB.crc_poly && flags[3]);
+          finish(wB, resB, doneB, hard + msg_bytes16, okB);
         }
         tm::group_barrier(bar_id, zpad);
       }
