@@ -18,6 +18,9 @@
  *                                   (rate_dematch :182, decode_cblk :94-118/:186, CRC flags :188-195) - new batched entry
  *   ldpc_cuda_softbuffer_*     <->  rx_softbuffer::get_codeblock_soft_bits / get_codeblocks_crc storage
  *                                   include/srsran/phy/upper/rx_softbuffer.h:42-72 (HBM-resident equivalent)
+ *   ldpc_cuda_tb_assemble*     <->  transport-block assembly + TB CRC24A + verdict of pusch_decoder_impl::decode
+ *                                   lib/phy/upper/channel_processors/pusch_decoder_impl.cpp:156-222 (:196-200 bit copy,
+ *                                   :205-222 CRC check) - on the device, so a slot's transport blocks never leave HBM
  *   ldpc_cuda_segment          <->  ldpc_segmenter_rx::segment geometry
  *                                   lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_impl.cpp:226-308 (no 52-CB cap)
  *
@@ -180,6 +183,57 @@ int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle*        handle,
                                           const int8_t*            rm_llrs_d,
                                           uint8_t*                 out_bits_d,
                                           ldpc_cuda_cb_result*     results_d);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Transport-block assembly + TB CRC on the device (what pusch_decoder_impl::decode does after its codeblock loop,
+ * pusch_decoder_impl.cpp:156-222).
+ */
+
+/* One transport block = a run of consecutive descriptors of the same call (ldpc_cuda_segment order). */
+typedef struct {
+  uint32_t first_codeblock; /* index of its first codeblock in descs / results */
+  uint32_t nof_codeblocks;  /* C >= 1 */
+  uint32_t tbs_bits;        /* transport block size in bits, a multiple of 8 (transport_block is a byte span) */
+  uint32_t nof_cb_crc_bits; /* cb_specific.nof_crc_bits of its codeblocks: 24 when C > 1, else 16 or 24 (ldpc_cuda_segment) */
+  uint64_t tb_offset;       /* byte offset of the assembled block inside the transport-block output buffer; the kernel
+                               writes tbs_bits/8 bytes, plus the 3 bytes of the TB CRC24A when C > 1 */
+} ldpc_cuda_tb_desc;
+
+/* pusch_decoder_result::tb_crc_ok and what it was derived from. */
+typedef struct {
+  uint32_t crc_remainder;  /* CRC24A remainder over the assembled bytes (meaningful when C > 1; 0 = check passed) */
+  uint16_t nof_cb_failed;  /* codeblocks whose CRC flag is not set (neither by this call nor by skip_decode) */
+  uint8_t  tb_crc_ok;      /* C == 1: the codeblock's CRC flag; C > 1: no failed codeblock and crc_remainder == 0 */
+  uint8_t  reserved;
+} ldpc_cuda_tb_result;
+
+/* DEVICE buffers, asynchronous on the handle's stream (enqueue it behind the decode call that produced out_bits_d and
+ * results_d). descs / tbs are host memory, copied at enqueue; descs are the descriptors of that decode call
+ * (out_offset, skip_decode, base_graph, lifting_size, nof_filler_bits are read). Unlike the reference, which leaves the
+ * caller's transport_block untouched unless every codeblock passed, the assembled bits are always written: consumers
+ * look at tb_crc_ok. */
+int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle*          handle,
+                                 uint32_t                   nof_tbs,
+                                 const ldpc_cuda_tb_desc*   tbs,
+                                 uint32_t                   nof_codeblocks,
+                                 const ldpc_cuda_cb_desc*   descs,
+                                 const uint8_t*             out_bits_d,
+                                 const ldpc_cuda_cb_result* results_d,
+                                 uint8_t*                   tb_out_d,
+                                 ldpc_cuda_tb_result*       tb_results_d);
+
+/* ldpc_cuda_dematch_decode_batch followed by the assembly of its transport blocks in the same call, HOST buffers:
+ * out_bits / results as in ldpc_cuda_dematch_decode_batch; tb_out / tb_results receive the assembled blocks. */
+int ldpc_cuda_dematch_decode_tb_batch(ldpc_cuda_handle*        handle,
+                                      uint32_t                 nof_codeblocks,
+                                      const ldpc_cuda_cb_desc* descs,
+                                      const int8_t*            rm_llrs,
+                                      uint8_t*                 out_bits,
+                                      ldpc_cuda_cb_result*     results,
+                                      uint32_t                 nof_tbs,
+                                      const ldpc_cuda_tb_desc* tbs,
+                                      uint8_t*                 tb_out,
+                                      ldpc_cuda_tb_result*     tb_results);
 
 /* ---------------------------------------------------------------------------------------------------------------------
  * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,

@@ -11,6 +11,7 @@
 #include "ldpc_dematch.cuh"
 #include "ldpc_kernels_tmem.cuh"  // needs c_crc / crc_warp from the scalar header
 #include "ldpc_encode.cuh"
+#include "ldpc_tb.cuh"
 
 using namespace ldpc_b200;
 
@@ -25,6 +26,7 @@ using namespace ldpc_b200;
   } while (0)
 
 constexpr unsigned MAX_CHUNKS = 16;
+static_assert(sizeof(TbResult) == sizeof(ldpc_cuda_tb_result) && sizeof(ldpc_cuda_tb_result) == 8, "TbResult mirrors the ABI struct");
 
 struct ldpc_cuda_handle {
   int device = 0;
@@ -52,6 +54,12 @@ struct ldpc_cuda_handle {
   bool arena_owned = false;  // false: attached, belongs to a pool shared between handles
   unsigned* pair_counter = nullptr;  // packed kernel: dynamic work distribution
   uint64_t launches = 0;
+  // transport-block assembly: work records + accumulators, and the output staging of the host entry
+  uint8_t* d_tbwork = nullptr;
+  size_t d_tbwork_cap = 0;
+  uint8_t* d_tb_out = nullptr;
+  size_t d_tb_out_cap = 0;
+  std::vector<uint8_t> tb_stage;
   std::vector<uint32_t> order;
   std::vector<uint32_t> group_begin;
 };
@@ -325,6 +333,81 @@ int stage_tx_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* desc
   return LDPC_CUDA_OK;
 }
 
+// Transport-block assembly (ldpc_tb.cuh): validates the geometry, uploads the work records and launches the kernel on
+// `stream`. d_tb_results receives one TbResult per transport block.
+int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs,
+                        uint32_t n, const ldpc_cuda_cb_desc* descs, const uint8_t* d_msgs, const CbResult* d_results,
+                        uint8_t* d_tb_out, TbResult* d_tb_results)
+{
+  const size_t off_cb = sizeof(TbWork) * nof_tbs, off_scratch = off_cb + sizeof(TbCb) * n;
+  const size_t bytes = off_scratch + 2 * sizeof(unsigned) * nof_tbs;
+  h->tb_stage.assign(bytes, 0);
+  TbWork* tw = reinterpret_cast<TbWork*>(h->tb_stage.data());
+  TbCb* tc = reinterpret_cast<TbCb*>(h->tb_stage.data() + off_cb);
+  unsigned max_chunks = 0;
+  for (uint32_t t = 0; t != nof_tbs; ++t) {
+    const ldpc_cuda_tb_desc& tb = tbs[t];
+    if (tb.nof_codeblocks == 0 || tb.first_codeblock > n || tb.nof_codeblocks > n - tb.first_codeblock ||
+        tb.tbs_bits == 0 || tb.tbs_bits % 8 != 0 || (tb.nof_cb_crc_bits != 16 && tb.nof_cb_crc_bits != 24) ||
+        (tb.nof_codeblocks > 1 && tb.nof_cb_crc_bits != 24)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const ldpc_cuda_cb_desc& d0 = descs[tb.first_codeblock];
+    if ((d0.base_graph != 1 && d0.base_graph != 2) || lifting_set_of(d0.lifting_size) < 0) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const unsigned K = bg_K(d0.base_graph) * d0.lifting_size;
+    if (K <= tb.nof_cb_crc_bits + d0.nof_filler_bits) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const unsigned data_bits = K - tb.nof_cb_crc_bits - d0.nof_filler_bits;
+    const uint64_t total = (uint64_t)tb.tbs_bits + (tb.nof_codeblocks > 1 ? 24u : 0u);
+    // "All TB bits should be filled at this point" (pusch_decoder_impl.cpp:203)
+    if ((uint64_t)data_bits * tb.nof_codeblocks < total || total / 8 > 0x7fffffffu) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    for (uint32_t r = 0; r != tb.nof_codeblocks; ++r) {
+      const ldpc_cuda_cb_desc& d = descs[tb.first_codeblock + r];
+      if (d.base_graph != d0.base_graph || d.lifting_size != d0.lifting_size || d.nof_filler_bits != d0.nof_filler_bits) {
+        return LDPC_CUDA_ERR_ARG;
+      }
+      TbCb& c = tc[tb.first_codeblock + r];
+      c.src_offset = d.out_offset;
+      c.already_ok = d.skip_decode ? 1u : 0u;
+      c.result_index = tb.first_codeblock + r;
+    }
+    tw[t].tb_offset = tb.tb_offset;
+    tw[t].first_cb = tb.first_codeblock;
+    tw[t].nof_cbs = tb.nof_codeblocks;
+    tw[t].data_bits = data_bits;
+    tw[t].nbytes = (unsigned)(total / 8);
+    max_chunks = std::max(max_chunks, (tw[t].nbytes + TB_THREADS - 1) / TB_THREADS);
+  }
+  if (nof_tbs > 65535u) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  if (bytes > h->d_tbwork_cap) {
+    // the previous buffer may still be read by an earlier launch: wait for the handle's work before releasing it
+    if (h->d_tbwork) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      CUDA_TRY(cudaFree(h->d_tbwork));
+      h->d_tbwork = nullptr, h->d_tbwork_cap = 0;
+    }
+    const size_t cap = bytes + (bytes >> 2) + 4096;
+    CUDA_TRY(cudaMalloc(&h->d_tbwork, cap));
+    h->d_tbwork_cap = cap;
+  }
+  // pageable source: the copy is staged before the call returns, tb_stage may be reused by the next call
+  CUDA_TRY(cudaMemcpyAsync(h->d_tbwork, h->tb_stage.data(), bytes, cudaMemcpyHostToDevice, stream));
+  const dim3 grid(max_chunks, nof_tbs);
+  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, stream>>>(
+      reinterpret_cast<const TbWork*>(h->d_tbwork), reinterpret_cast<const TbCb*>(h->d_tbwork + off_cb), d_msgs, d_results,
+      d_tb_out, d_tb_results, reinterpret_cast<unsigned*>(h->d_tbwork + off_scratch));
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -452,6 +535,8 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
     cudaFree(h->arena);
   }
   cudaFree(h->pair_counter);
+  cudaFree(h->d_tbwork);
+  cudaFree(h->d_tb_out);
   if (h->stream) {
     cudaStreamDestroy(h->stream);
   }
@@ -591,8 +676,12 @@ static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc
 }
 
 static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in, uint8_t* out,
-                      ldpc_cuda_cb_result* results, bool fused)
+                      ldpc_cuda_cb_result* results, bool fused, uint32_t nof_tbs = 0, const ldpc_cuda_tb_desc* tbs = nullptr,
+                      uint8_t* tb_out = nullptr, ldpc_cuda_tb_result* tb_results = nullptr)
 {
+  if (nof_tbs != 0 && (tbs == nullptr || tb_out == nullptr || tb_results == nullptr)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
   if (h == nullptr || descs == nullptr || in == nullptr || out == nullptr || results == nullptr ||
       (fused && h->arena == nullptr)) {
     return LDPC_CUDA_ERR_ARG;
@@ -666,6 +755,35 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
     CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo, cudaMemcpyDeviceToHost,
                              h->d2h_stream));
   }
+  if (nof_tbs != 0) {
+    // transport blocks are assembled from the messages in device memory once every chunk has been decoded (the copy-out
+    // stream already waits for all of them) and leave as whole blocks
+    uint64_t tb_lo = ~0ull, tb_hi = 0;
+    for (uint32_t t = 0; t != nof_tbs; ++t) {
+      tb_lo = std::min<uint64_t>(tb_lo, tbs[t].tb_offset);
+      tb_hi = std::max<uint64_t>(tb_hi, tbs[t].tb_offset + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0));
+    }
+    const size_t need = (size_t)(tb_hi - tb_lo) + sizeof(TbResult) * nof_tbs + 16;
+    if (need > h->d_tb_out_cap) {
+      if (h->d_tb_out) {
+        CUDA_TRY(cudaFree(h->d_tb_out));
+        h->d_tb_out = nullptr, h->d_tb_out_cap = 0;
+      }
+      CUDA_TRY(cudaMalloc(&h->d_tb_out, need + (need >> 2)));
+      h->d_tb_out_cap = need + (need >> 2);
+    }
+    TbResult* d_tb_res = reinterpret_cast<TbResult*>(h->d_tb_out);  // results first (aligned), blocks behind them
+    uint8_t* d_tb_bytes = h->d_tb_out + ((sizeof(TbResult) * nof_tbs + 15) & ~(size_t)15);
+    rc = enqueue_tb_assemble(h, h->d2h_stream, nof_tbs, tbs, n, descs, d_out0, h->d_results, d_tb_bytes - tb_lo, d_tb_res);
+    if (rc != LDPC_CUDA_OK) {
+      cudaStreamSynchronize(h->d2h_stream);
+      cudaStreamSynchronize(h->stream2);
+      cudaStreamSynchronize(h->stream);
+      return rc;
+    }
+    CUDA_TRY(cudaMemcpyAsync(tb_out + tb_lo, d_tb_bytes, tb_hi - tb_lo, cudaMemcpyDeviceToHost, h->d2h_stream));
+    CUDA_TRY(cudaMemcpyAsync(tb_results, d_tb_res, sizeof(TbResult) * nof_tbs, cudaMemcpyDeviceToHost, h->d2h_stream));
+  }
   CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->d2h_stream));
   CUDA_TRY(cudaStreamSynchronize(h->d2h_stream));
   // everything of this call has finished (the last copy waited for every kernel); later calls may use any stream
@@ -684,6 +802,33 @@ int ldpc_cuda_dematch_decode_batch(ldpc_cuda_handle* h, uint32_t n, const ldpc_c
                                    uint8_t* out_bits, ldpc_cuda_cb_result* results)
 {
   return batch_host(h, n, descs, rm_llrs, out_bits, results, true);
+}
+
+// ---- transport-block assembly + TB CRC24A on the device (pusch_decoder_impl.cpp:156-222) --------------------------------
+int ldpc_cuda_dematch_decode_tb_batch(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* rm_llrs,
+                                      uint8_t* out_bits, ldpc_cuda_cb_result* results, uint32_t nof_tbs,
+                                      const ldpc_cuda_tb_desc* tbs, uint8_t* tb_out, ldpc_cuda_tb_result* tb_results)
+{
+  if (nof_tbs == 0 || n == 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  return batch_host(h, n, descs, rm_llrs, out_bits, results, true, nof_tbs, tbs, tb_out, tb_results);
+}
+
+int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle* h, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs, uint32_t n,
+                                 const ldpc_cuda_cb_desc* descs, const uint8_t* out_bits_d,
+                                 const ldpc_cuda_cb_result* results_d, uint8_t* tb_out_d, ldpc_cuda_tb_result* tb_results_d)
+{
+  if (h == nullptr || tbs == nullptr || descs == nullptr || out_bits_d == nullptr || results_d == nullptr ||
+      tb_out_d == nullptr || tb_results_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_tbs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  return enqueue_tb_assemble(h, h->stream, nof_tbs, tbs, n, descs, out_bits_d, reinterpret_cast<const CbResult*>(results_d),
+                             tb_out_d, reinterpret_cast<TbResult*>(tb_results_d));
 }
 
 // ---- drop-in single codeblock ---------------------------------------------------------------------------------------

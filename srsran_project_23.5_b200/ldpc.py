@@ -22,6 +22,12 @@ CB_DESC = np.dtype([("base_graph", "u1"), ("crc_poly", "u1"), ("rv", "u1"), ("mo
                    align=True)
 CB_RESULT = np.dtype([("iterations", "<u2"), ("crc_ok", "u1"), ("flags", "u1")], align=True)
 assert CB_DESC.itemsize == 48 and CB_RESULT.itemsize == 4
+# ldpc_cuda_tb_desc (24 bytes) and ldpc_cuda_tb_result (8 bytes)
+TB_DESC = np.dtype([("first_codeblock", "<u4"), ("nof_codeblocks", "<u4"), ("tbs_bits", "<u4"),
+                    ("nof_cb_crc_bits", "<u4"), ("tb_offset", "<u8")], align=True)
+TB_RESULT = np.dtype([("crc_remainder", "<u4"), ("nof_cb_failed", "<u2"), ("tb_crc_ok", "u1"), ("reserved", "u1")],
+                     align=True)
+assert TB_DESC.itemsize == 24 and TB_RESULT.itemsize == 8
 
 
 class LdpcCudaError(RuntimeError):
@@ -84,6 +90,8 @@ def library():
             getattr(L, name).argtypes = [vp, u32, vp, vp, vp]
         for name in ("ldpc_cuda_encode", "ldpc_cuda_rate_match"):
             getattr(L, name).argtypes = [vp, vp, vp, vp]
+        L.ldpc_cuda_tb_assemble_device.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, vp]
+        L.ldpc_cuda_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
         L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
         _lib = L
@@ -231,6 +239,27 @@ class LdpcCuda:
         descs = np.ascontiguousarray(descs, CB_DESC)
         self._check(self._L.ldpc_cuda_dematch_decode_batch_device(self._h, descs.size, _ptr(descs), rm_ptr, out_ptr,
                                                                   results_ptr), "ldpc_cuda_dematch_decode_batch_device")
+
+    # -- transport-block assembly + TB CRC24A on the device (pusch_decoder_impl.cpp:156-222) ----------------------------
+    def tb_assemble_device(self, tbs, descs, out_ptr, results_ptr, tb_out_ptr, tb_results_ptr):
+        tbs = np.ascontiguousarray(tbs, TB_DESC)
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_tb_assemble_device(self._h, tbs.size, _ptr(tbs), descs.size, _ptr(descs), out_ptr,
+                                                         results_ptr, tb_out_ptr, tb_results_ptr),
+                    "ldpc_cuda_tb_assemble_device")
+
+    def dematch_decode_tb_batch(self, descs, rm_llrs, out, tbs, tb_out, results=None, tb_results=None):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        tbs = np.ascontiguousarray(tbs, TB_DESC)
+        rm_llrs = np.ascontiguousarray(rm_llrs, np.int8)
+        if results is None:
+            results = np.zeros(descs.size, CB_RESULT)
+        if tb_results is None:
+            tb_results = np.zeros(tbs.size, TB_RESULT)
+        self._check(self._L.ldpc_cuda_dematch_decode_tb_batch(self._h, descs.size, _ptr(descs), _ptr(rm_llrs), _ptr(out),
+                                                              _ptr(results), tbs.size, _ptr(tbs), _ptr(tb_out),
+                                                              _ptr(tb_results)), "ldpc_cuda_dematch_decode_tb_batch")
+        return out, results, tb_out, tb_results
 
     # -- transmit side (encoder + rate matcher) ------------------------------------------------------------------------
     def encode(self, bg, Z, msg_bits):
