@@ -37,21 +37,6 @@ void require(bool cond, const char* what)
   }
 }
 
-// dst[dst_off, dst_off + nbits) = src[0, nbits), both MSB first (bit i at byte i / 8, position 7 - i % 8).
-void copy_bits(uint8_t* dst, unsigned dst_off, const uint8_t* src, unsigned nbits)
-{
-  unsigned i = 0;
-  if ((dst_off & 7u) == 0) {
-    std::memcpy(dst + dst_off / 8, src, nbits / 8);
-    i = nbits & ~7u;
-  }
-  for (; i != nbits; ++i) {
-    const unsigned bit = (src[i / 8] >> (7 - (i & 7u))) & 1u;
-    const unsigned o   = dst_off + i;
-    dst[o / 8]         = static_cast<uint8_t>((dst[o / 8] & ~(0x80u >> (o & 7u))) | (bit << (7 - (o & 7u))));
-  }
-}
-
 // Device soft-buffer arena in units of one codeblock slot, keyed by the caller's rx_softbuffer object.
 class arena_index
 {
@@ -140,8 +125,8 @@ private:
 class pusch_decoder_cuda : public pusch_decoder
 {
 public:
-  pusch_decoder_cuda(ldpc_cuda_handle* h_, std::unique_ptr<crc_calculator> crc24A_, unsigned arena_cbs_, unsigned max_cbs) :
-    h(h_), crc24A(std::move(crc24A_)), arena_cbs(arena_cbs_), index(arena_cbs_), descs(max_cbs), results(max_cbs),
+  pusch_decoder_cuda(ldpc_cuda_handle* h_, unsigned arena_cbs_, unsigned max_cbs) :
+    h(h_), arena_cbs(arena_cbs_), index(arena_cbs_), descs(max_cbs), results(max_cbs),
     crc_bits(max_cbs)
   {
   }
@@ -226,23 +211,30 @@ public:
       check(ldpc_cuda_set_algorithm(h, &alg), "ldpc_cuda_set_algorithm");
       iterations = cfg.nof_ldpc_iterations;
     }
-    check(ldpc_cuda_dematch_decode_batch(h,
-                                         nof_cbs,
-                                         descs.data(),
-                                         reinterpret_cast<const int8_t*>(llrs.data()),
-                                         cb_out.data(),
-                                         results.data()),
-          "ldpc_cuda_dematch_decode_batch");
-
-    // transport block assembly (pusch_decoder_impl.cpp:156-201)
+    // One call: rate dematch + combine + decode + codeblock CRCs, then - still on the device - the transport block
+    // assembly, its CRC24A and the verdict (pusch_decoder_impl.cpp:156-222).
     const unsigned tb_and_crc_size = tb_size + (nof_cbs > 1 ? LONG_CRC_BITS : 0);
+    ldpc_cuda_tb_desc tbd = {0, nof_cbs, tb_size, crc_bits[0], 0};
+    ldpc_cuda_tb_result tbr = {};
     tb_tmp.assign((tb_and_crc_size + 7) / 8, 0);
-    unsigned tb_offset         = 0;
+    check(ldpc_cuda_dematch_decode_tb_batch(h,
+                                            nof_cbs,
+                                            descs.data(),
+                                            reinterpret_cast<const int8_t*>(llrs.data()),
+                                            cb_out.data(),
+                                            results.data(),
+                                            1,
+                                            &tbd,
+                                            tb_tmp.data(),
+                                            &tbr),
+          "ldpc_cuda_dematch_decode_tb_batch");
+
+    // codeblock bookkeeping of the soft buffer (pusch_decoder_impl.cpp:179-195): messages and CRC flags
     stats.nof_codeblocks_total = nof_cbs;
     stats.ldpc_decoder_stats.reset();
     for (unsigned r = 0; r != nof_cbs; ++r) {
-      bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
       if (!cb_crcs[r]) {
+        bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
         std::memcpy(message.get_buffer().data(), &cb_out[static_cast<size_t>(r) * kb], kb);
         if (results[r].crc_ok) {
           cb_crcs[r] = true;
@@ -251,12 +243,9 @@ public:
           stats.ldpc_decoder_stats.update(cfg.nof_ldpc_iterations);
         }
       }
-      const unsigned nof_data_bits = K - crc_bits[r] - descs[r].nof_filler_bits;
-      const unsigned nof_new_bits  = std::min(tb_and_crc_size - tb_offset, nof_data_bits);
-      copy_bits(tb_tmp.data(), tb_offset, message.get_buffer().data(), nof_new_bits);
-      tb_offset += nof_new_bits;
     }
-    require(tb_offset == tb_and_crc_size, "all TB bits should be filled at this point");
+    const bool all_cbs_ok = std::all_of(cb_crcs.begin(), cb_crcs.end(), [](bool a) { return a; });
+    require(all_cbs_ok == (tbr.nof_cb_failed == 0), "device and host codeblock CRC flags disagree");
 
     stats.tb_crc_ok = false;
     if (nof_cbs == 1) {
@@ -264,9 +253,9 @@ public:
       if (stats.tb_crc_ok) {
         std::memcpy(transport_block.data(), tb_tmp.data(), transport_block.size());
       }
-    } else if (std::all_of(cb_crcs.begin(), cb_crcs.end(), [](bool a) { return a; })) {
+    } else if (all_cbs_ok) {
       std::memcpy(transport_block.data(), tb_tmp.data(), transport_block.size());
-      if (crc24A->calculate_byte(span<const uint8_t>(tb_tmp.data(), tb_tmp.size())) == 0) {
+      if (tbr.tb_crc_ok) {
         stats.tb_crc_ok = true;
       } else {
         soft_codeword->reset_codeblocks_crc(); // at least one codeblock is a false positive
@@ -276,7 +265,6 @@ public:
 
 private:
   ldpc_cuda_handle*                h;
-  std::unique_ptr<crc_calculator>  crc24A;
   unsigned                         arena_cbs;
   arena_index                      index;
   const void*                      attached      = nullptr; // arena of a rx_softbuffer_pool_cuda in use
@@ -300,8 +288,8 @@ public:
     if (ldpc_cuda_create(&h, cfg.device, cfg.max_codeblocks_per_tb, 0) != LDPC_CUDA_OK) {
       return nullptr;
     }
-    return std::make_unique<pusch_decoder_cuda>(
-        h, cfg.crc_factory->create(crc_generator_poly::CRC24A), cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
+    // the transport block CRC24A is computed on the device: cfg.crc_factory is not used by this decoder
+    return std::make_unique<pusch_decoder_cuda>(h, cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
   }
 
 private:
