@@ -129,12 +129,27 @@ def crc_attach(bits, poly, order):
 CRC24B_POLY = 0x1800063
 
 
-def make_codewords_gpu(torch, pkg, dec, dev, rng, n, bg, Z, fillers):
+def crc24a_bytes(data):
+    """CRC24A (0x1864CFB, zero initial value, no final XOR) of a byte string; table driven, input generation only."""
+    table = []
+    for b in range(256):
+        r = b << 16
+        for _ in range(8):
+            r = ((r << 1) ^ 0x1864CFB) if (r & 0x800000) else (r << 1)
+        table.append(r & 0xFFFFFF)
+    reg = 0
+    for b in bytes(data):
+        reg = ((reg << 8) & 0xFFFFFF) ^ table[((reg >> 16) ^ b) & 0xFF]
+    return reg
+
+
+def make_codewords_gpu(torch, pkg, dec, dev, rng, n, bg, Z, fillers, payload=None):
     """n random messages with a valid CRC24B (and `fillers` filler bits), encoded by the PRODUCT's own device encoder
     (ldpc_cuda_encode_batch_device; parity-tested against the reference encoder in tests/test_gpu_tx.py). Returns the
     device tensors (messages [n, K], codeblocks [n, N]) as unpacked bits, fillers = 254."""
     K, N = (22 if bg == 1 else 10) * Z, (66 if bg == 1 else 50) * Z
-    payload = rng.integers(0, 2, (n, K - fillers - 24)).astype(np.uint8)
+    if payload is None:
+        payload = rng.integers(0, 2, (n, K - fillers - 24)).astype(np.uint8)
     msg = np.concatenate([crc_attach(payload, CRC24B_POLY, 24), np.full((n, fillers), 254, np.uint8)], axis=1)
     msg_d = torch.from_numpy(np.ascontiguousarray(msg)).to(dev)
     cw_d = torch.empty((n, N), dtype=torch.uint8, device=dev)
@@ -179,8 +194,14 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
     Kb, Nsoft, kb = 22 * Zs, 66 * Zs, 22 * Zs // 8
     rng = np.random.default_rng(7)
     E = descs["rm_length"].astype(np.int64)
-    # one transport block's worth of codeblocks, encoded and rate-matched (rv 0 and rv 2) by the product's device kernels
-    _, cw_d = make_codewords_gpu(torch, pkg, dec, dev, rng, C, 1, Zs, F)
+    # one real transport block (random bits + CRC24A, TS 38.212 5.2.2 segmentation: 152 x 8408 bits), its codeblocks
+    # CRC24B-protected, encoded and rate-matched (rv 0 and rv 2) by the product's device kernels
+    tb_bytes_host = rng.integers(0, 256, tbs // 8).astype(np.uint8)
+    tb_crc = crc24a_bytes(tb_bytes_host)
+    tb_all = np.concatenate([np.unpackbits(tb_bytes_host),
+                             np.array([(tb_crc >> (23 - k)) & 1 for k in range(24)], np.uint8)])
+    assert tb_all.size == C * (Kb - F - 24)
+    _, cw_d = make_codewords_gpu(torch, pkg, dec, dev, rng, C, 1, Zs, F, payload=tb_all.reshape(C, Kb - F - 24))
     tx = {}
     for rv in (0, 2):
         d = descs.copy()
@@ -245,10 +266,20 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
     out_d = torch.zeros(n_a * C * kb, dtype=torch.uint8, device=dev)
     res_a = torch.zeros(n_a * C, dtype=torch.int32, device=dev)
     res_b = torch.zeros(n_a * C, dtype=torch.int32, device=dev)
+    # transport-block assembly + TB CRC24A on the device behind every slot (pusch_decoder_impl.cpp:156-222)
+    tb_stride = (tbs // 8 + 3 + 15) // 16 * 16
+    tbd = np.zeros(n_a, pkg.TB_DESC)
+    tbd["first_codeblock"], tbd["nof_codeblocks"], tbd["tbs_bits"] = np.arange(n_a) * C, C, tbs
+    tbd["nof_cb_crc_bits"], tbd["tb_offset"] = 24, np.arange(n_a, dtype=np.uint64) * np.uint64(tb_stride)
+    tb_out_d = torch.zeros(n_a * tb_stride, dtype=torch.uint8, device=dev)
+    tbres_a = torch.zeros(2 * n_a, dtype=torch.int32, device=dev)
+    tbres_b = torch.zeros(2 * n_a, dtype=torch.int32, device=dev)
 
     def step():
         dec.dematch_decode_batch_device(d_a, rm_a.data_ptr(), out_d.data_ptr(), res_a.data_ptr())
+        dec.tb_assemble_device(tbd, d_a, out_d.data_ptr(), res_a.data_ptr(), tb_out_d.data_ptr(), tbres_a.data_ptr())
         dec.dematch_decode_batch_device(d_b, rm_b.data_ptr(), out_d.data_ptr(), res_b.data_ptr())
+        dec.tb_assemble_device(tbd, d_b, out_d.data_ptr(), res_b.data_ptr(), tb_out_d.data_ptr(), tbres_b.data_ptr())
 
     for _ in range(3):
         step()
@@ -264,17 +295,26 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
     ra = res_a.cpu().numpy().view(pkg.CB_RESULT).reshape(n_a, C)
     rb = res_b.cpu().numpy().view(pkg.CB_RESULT).reshape(n_a, C)
     bad_a = (np.arange(n_a) % cells) < n_bad
+    ta = tbres_a.cpu().numpy().view(pkg.TB_RESULT)
+    tbb = tbres_b.cpu().numpy().view(pkg.TB_RESULT)
+    tb_back = tb_out_d.view(n_a, tb_stride)[:, :tbs // 8].cpu().numpy()  # slot B's blocks: all of them pass
+    tb_identical = bool((tb_back == tb_bytes_host[None, :]).all())
     n_cb = 2 * n_a * C
     bits = n_cb * (Kb - F)
     slots = 2 * sets
-    return {"what": "configs 3+5: fused rate-dematch + HARQ combine (HBM arena) + decode + CRC24B early stop, 16 cells x "
-                    "152-codeblock full-slot TBs (BG1 Z=384 F=16, E 8960/8992, R=0.94), 12.5% retransmissions (rv2)",
+    return {"what": "configs 3+5: fused rate-dematch + HARQ combine (HBM arena) + decode + CRC24B early stop + TB assembly and "
+                    "TB CRC24A on the device, 16 cells x 152-codeblock full-slot TBs (BG1 Z=384 F=16, E 8960/8992, "
+                    "R=0.94), 12.5% retransmissions (rv2)",
             "value": bits / (ms * 1e-3) / 1e9, "unit": "Gb/s", "ms_per_slot_16_cells": ms / slots,
             "codeblocks_per_step": n_cb, "rm_llr_bytes_per_step": int(2 * n_a * tb_bytes),
             "soft_buffer_arena_bytes": int(n_buf * C * Nsoft), "launches_per_step": (dec.launch_count - launches0) // steps,
             "cells_in_real_time_at_0.5ms_slots": cells * 0.5 / (ms / slots),
             "crc_pass_rate": {"new_good_snr": float(ra[~bad_a]["crc_ok"].mean()), "new_bad_snr": float(ra[bad_a]["crc_ok"].mean()),
                               "retransmission": float(rb[bad_a]["crc_ok"].mean())},
+            "tb_crc_ok_rate": {"new_good_snr": float(ta[~bad_a]["tb_crc_ok"].mean()),
+                               "new_bad_snr": float(ta[bad_a]["tb_crc_ok"].mean()),
+                               "slot_b_incl_retransmissions": float(tbb["tb_crc_ok"].mean()),
+                               "assembled_blocks_identical_to_sent": tb_identical},
             "mean_iterations": {"new_good_snr": float(ra[~bad_a]["iterations"].mean()),
                                 "new_bad_snr": float(ra[bad_a]["iterations"].mean()),
                                 "retransmission": float(rb[bad_a]["iterations"].mean())}}

@@ -59,7 +59,10 @@ struct ldpc_cuda_handle {
   size_t d_tbwork_cap = 0;
   uint8_t* d_tb_out = nullptr;
   size_t d_tb_out_cap = 0;
-  std::vector<uint8_t> tb_stage;
+  uint8_t* h_tbwork[2] = {nullptr, nullptr};  // pinned, double-buffered like h_work: enqueueing never waits for the GPU
+  size_t h_tbwork_cap[2] = {0, 0};
+  cudaEvent_t ev_tbwork[2] = {nullptr, nullptr};
+  unsigned tbwork_slot = 0;
   std::vector<uint32_t> order;
   std::vector<uint32_t> group_begin;
 };
@@ -110,6 +113,23 @@ int upload_constants()
     }
   }
   CUDA_TRY(cudaMemcpyToSymbol(g_crc_pow, pw.data(), pw.size() * sizeof(unsigned)));
+  // x^(8 TB_CHUNK k) mod P_24A (transport-block CRC: weight of a whole chunk, ldpc_tb.cuh)
+  {
+    static std::vector<unsigned> cp;
+    cp.assign(TB_POW_CHUNKS, 0);
+    const unsigned top = 1U << 24;
+    unsigned r = 1;
+    for (unsigned k = 0; k != TB_POW_CHUNKS; ++k) {
+      cp[k] = r;
+      for (unsigned e = 0; e != 8u * TB_CHUNK; ++e) {
+        r <<= 1;
+        if (r & top) {
+          r ^= TB_CRC24A_POLY;
+        }
+      }
+    }
+    CUDA_TRY(cudaMemcpyToSymbol(g_tb_chunk_pow, cp.data(), cp.size() * sizeof(unsigned)));
+  }
   return LDPC_CUDA_OK;
 }
 
@@ -339,12 +359,36 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
                         uint32_t n, const ldpc_cuda_cb_desc* descs, const uint8_t* d_msgs, const CbResult* d_results,
                         uint8_t* d_tb_out, TbResult* d_tb_results)
 {
-  const size_t off_cb = sizeof(TbWork) * nof_tbs, off_scratch = off_cb + sizeof(TbCb) * n;
-  const size_t bytes = off_scratch + 2 * sizeof(unsigned) * nof_tbs;
-  h->tb_stage.assign(bytes, 0);
-  TbWork* tw = reinterpret_cast<TbWork*>(h->tb_stage.data());
-  TbCb* tc = reinterpret_cast<TbCb*>(h->tb_stage.data() + off_cb);
-  unsigned max_chunks = 0;
+  if (nof_tbs > 65535u) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  // device buffer: work records (uploaded) | one partial remainder per chunk of every transport block (device only)
+  const size_t off_cb = sizeof(TbWork) * nof_tbs, bytes = off_cb + sizeof(TbCb) * n;
+  uint64_t total_chunks = 0;
+  for (uint32_t t = 0; t != nof_tbs; ++t) {
+    total_chunks += ((uint64_t)tbs[t].tbs_bits / 8 + 3 + TB_CHUNK - 1) / TB_CHUNK;
+  }
+  const size_t off_partial = (bytes + 15) & ~(size_t)15, dev_bytes = off_partial + sizeof(unsigned) * total_chunks;
+  const unsigned slot = (h->tbwork_slot++) & 1u;
+  if (h->ev_tbwork[slot] == nullptr) {
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_tbwork[slot], cudaEventDisableTiming));
+  } else {
+    CUDA_TRY(cudaEventSynchronize(h->ev_tbwork[slot]));  // the copy that last read this staging buffer has finished
+  }
+  if (bytes > h->h_tbwork_cap[slot]) {
+    if (h->h_tbwork[slot]) {
+      CUDA_TRY(cudaFreeHost(h->h_tbwork[slot]));
+      h->h_tbwork[slot] = nullptr, h->h_tbwork_cap[slot] = 0;
+    }
+    const size_t cap = bytes + (bytes >> 2) + 4096;
+    CUDA_TRY(cudaHostAlloc(&h->h_tbwork[slot], cap, cudaHostAllocDefault));
+    h->h_tbwork_cap[slot] = cap;
+  }
+  uint8_t* stage = h->h_tbwork[slot];
+  std::memset(stage, 0, bytes);
+  TbWork* tw = reinterpret_cast<TbWork*>(stage);
+  TbCb* tc = reinterpret_cast<TbCb*>(stage + off_cb);
+  unsigned max_chunks = 0, chunk_base = 0;
   for (uint32_t t = 0; t != nof_tbs; ++t) {
     const ldpc_cuda_tb_desc& tb = tbs[t];
     if (tb.nof_codeblocks == 0 || tb.first_codeblock > n || tb.nof_codeblocks > n - tb.first_codeblock ||
@@ -381,29 +425,33 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
     tw[t].nof_cbs = tb.nof_codeblocks;
     tw[t].data_bits = data_bits;
     tw[t].nbytes = (unsigned)(total / 8);
-    max_chunks = std::max(max_chunks, (tw[t].nbytes + TB_THREADS - 1) / TB_THREADS);
+    tw[t].chunk_base = chunk_base;
+    const unsigned chunks = (tw[t].nbytes + TB_CHUNK - 1) / TB_CHUNK;
+    chunk_base += chunks;
+    max_chunks = std::max(max_chunks, chunks);
   }
-  if (nof_tbs > 65535u) {
-    return LDPC_CUDA_ERR_CAPACITY;
-  }
-  if (bytes > h->d_tbwork_cap) {
+  if (dev_bytes > h->d_tbwork_cap) {
     // the previous buffer may still be read by an earlier launch: wait for the handle's work before releasing it
     if (h->d_tbwork) {
       CUDA_TRY(cudaDeviceSynchronize());
       CUDA_TRY(cudaFree(h->d_tbwork));
       h->d_tbwork = nullptr, h->d_tbwork_cap = 0;
     }
-    const size_t cap = bytes + (bytes >> 2) + 4096;
+    const size_t cap = dev_bytes + (dev_bytes >> 2) + 4096;
     CUDA_TRY(cudaMalloc(&h->d_tbwork, cap));
     h->d_tbwork_cap = cap;
   }
-  // pageable source: the copy is staged before the call returns, tb_stage may be reused by the next call
-  CUDA_TRY(cudaMemcpyAsync(h->d_tbwork, h->tb_stage.data(), bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaMemcpyAsync(h->d_tbwork, stage, bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaEventRecord(h->ev_tbwork[slot], stream));
+  const TbWork* d_tw = reinterpret_cast<const TbWork*>(h->d_tbwork);
+  const TbCb* d_tc = reinterpret_cast<const TbCb*>(h->d_tbwork + off_cb);
+  unsigned* d_partial = reinterpret_cast<unsigned*>(h->d_tbwork + off_partial);
   const dim3 grid(max_chunks, nof_tbs);
-  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, stream>>>(
-      reinterpret_cast<const TbWork*>(h->d_tbwork), reinterpret_cast<const TbCb*>(h->d_tbwork + off_cb), d_msgs, d_results,
-      d_tb_out, d_tb_results, reinterpret_cast<unsigned*>(h->d_tbwork + off_scratch));
+  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, stream>>>(d_tw, d_tc, d_msgs, d_tb_out, d_partial);
   CUDA_TRY(cudaGetLastError());
+  ldpc_tb_finish_kernel<<<nof_tbs, 128, 0, stream>>>(d_tw, d_tc, d_results, d_partial, d_tb_results);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
   h->launches += 1;
   return LDPC_CUDA_OK;
 }
@@ -536,6 +584,12 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
   }
   cudaFree(h->pair_counter);
   cudaFree(h->d_tbwork);
+  for (int i = 0; i != 2; ++i) {
+    cudaFreeHost(h->h_tbwork[i]);
+    if (h->ev_tbwork[i]) {
+      cudaEventDestroy(h->ev_tbwork[i]);
+    }
+  }
   cudaFree(h->d_tb_out);
   if (h->stream) {
     cudaStreamDestroy(h->stream);

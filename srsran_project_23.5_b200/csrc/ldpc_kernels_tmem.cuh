@@ -52,7 +52,7 @@ struct __align__(8) TmEdge {
 constexpr unsigned TM_CRC_POW_LEN = 22 * 384;  // longest message in bits
 // x^e mod P for CRC16 / CRC24A / CRC24B (poly codes 1..3), e < TM_CRC_POW_LEN: the parallel CRC check of the decoder.
 // Filled once per device by upload_constants (ldpc_api.cu).
-__device__ unsigned g_crc_pow[3][TM_CRC_POW_LEN];
+__device__ __align__(32) unsigned g_crc_pow[3][TM_CRC_POW_LEN];
 
 struct TmemParams {
   const CbWork* work;

@@ -7,11 +7,13 @@
 // whole bytes, init 0, no final xor) and tb_crc_ok is set as :205-222 does: one codeblock -> its own CRC flag; several
 // -> every codeblock flag set AND remainder == 0.
 //
-// Work split: one thread per OUTPUT byte (gather: conflict-free coalesced stores; a byte takes its bits from at most two
-// codeblocks). The CRC is linear in the message bits: a thread XORs x^e mod P for the set bits of its byte (table
-// g_crc_pow of the decoder kernel), a block reduces its 256 bytes, multiplies the partial remainder by
-// x^(bits behind the block) mod P and XORs it into the transport block's accumulator; the last block of a transport
-// block to finish counts the failed codeblocks and writes the public result. HBM traffic = the bits themselves, once.
+// Work split: one thread per 4 OUTPUT bytes (gather: conflict-free stores; a byte takes its bits from at most two
+// codeblocks). The CRC is linear in the message bits: a thread XORs x^e mod P for the set bits of its bytes (table
+// g_crc_pow of the decoder kernel), a block reduces its 1024 bytes, multiplies the partial remainder by
+// x^(bits behind the block) mod P - two table look-ups and two 24-bit carry-less multiplications - and stores it; a
+// second small kernel (one block per transport block) XORs the partial remainders, counts the failed codeblocks and
+// writes the public result. No atomics, no fences (a first version that accumulated with same-address atomics and a
+// last-block-done counter took 612 us for 128 full-slot blocks; see profiles/). HBM traffic = the bits themselves, once.
 #pragma once
 
 #include "ldpc_device.cuh"
@@ -24,6 +26,8 @@ struct TbWork {
   unsigned nof_cbs;              // C
   unsigned data_bits;            // bits taken from each codeblock message: K - nof_crc_bits - nof_filler_bits
   unsigned nbytes;               // bytes written: (tbs + (C > 1 ? 24 : 0)) / 8
+  unsigned chunk_base;           // index of its first per-chunk partial remainder
+  unsigned reserved;
 };
 
 struct TbCb {
@@ -40,6 +44,11 @@ struct TbResult {  // == ldpc_cuda_tb_result
 };
 
 constexpr int TB_THREADS = 256;
+constexpr int TB_BYTES_PER_THREAD = 4;
+constexpr int TB_CHUNK = TB_THREADS * TB_BYTES_PER_THREAD;  // output bytes per block; 8 * TB_CHUNK <= TM_CRC_POW_LEN
+constexpr unsigned TB_POW_CHUNKS = 1024;                   // x^(8 TB_CHUNK k) mod P for k < 1024: blocks up to 1 MB
+__device__ unsigned g_tb_chunk_pow[TB_POW_CHUNKS];
+static_assert(8 * TB_CHUNK + 24 <= (int)TM_CRC_POW_LEN, "in-chunk exponents come from g_crc_pow");
 constexpr unsigned TB_CRC24A_POLY = 0x1864CFBu;  // crc_calculator.h:33-39
 constexpr unsigned TB_CRC24A_CODE = 2;           // ldpc_cuda_crc / g_crc_pow row TB_CRC24A_CODE - 1
 
@@ -70,48 +79,56 @@ __device__ __forceinline__ unsigned tb_xpow24(unsigned e)
   return result;
 }
 
-// grid (chunks of 256 output bytes, transport blocks). scratch: {remainder accumulator, finished-chunk counter} per
-// transport block, zero on entry.
+// grid (chunks of TB_CHUNK output bytes, transport blocks). partial: one weighted remainder per chunk.
 __global__ void __launch_bounds__(TB_THREADS) ldpc_tb_assemble_kernel(const TbWork* __restrict__ tbs,
                                                                       const TbCb* __restrict__ cbs,
                                                                       const uint8_t* __restrict__ msgs,
-                                                                      const CbResult* __restrict__ results,
                                                                       uint8_t* __restrict__ tb_out,
-                                                                      TbResult* __restrict__ tb_results,
-                                                                      unsigned* scratch)
+                                                                      unsigned* __restrict__ partial)
 {
   const unsigned tb = blockIdx.y;
   const TbWork w = tbs[tb];
-  const unsigned j0 = blockIdx.x * TB_THREADS;
+  const unsigned j0 = blockIdx.x * TB_CHUNK;
   if (j0 >= w.nbytes) {
     return;
   }
-  const unsigned L = min((unsigned)TB_THREADS, w.nbytes - j0);
+  const unsigned L = min((unsigned)TB_CHUNK, w.nbytes - j0);
   const unsigned i = threadIdx.x;
   __shared__ unsigned red[TB_THREADS / 32];
-  __shared__ unsigned last_flag;
   unsigned r = 0;
-  if (i < L) {
-    const unsigned p = 8u * (j0 + i);    // first transport-block bit of this byte
-    const unsigned cb = p / w.data_bits;  // codeblock it starts in
-    const unsigned o = p - cb * w.data_bits;
-    const uint8_t* s = msgs + cbs[w.first_cb + cb].src_offset;
-    const unsigned two = ((unsigned)s[o >> 3] << 8) | (unsigned)s[(o >> 3) + 1];  // message has >= 16 bits behind the data
-    unsigned v = (two >> (8 - (o & 7u))) & 0xffu;
-    const unsigned avail = w.data_bits - o;
-    if (avail < 8) {  // the byte straddles two codeblocks
-      v &= 0xff00u >> avail;
-      if (cb + 1 < w.nof_cbs) {
-        v |= (unsigned)msgs[cbs[w.first_cb + cb + 1].src_offset] >> avail;
+  // codeblock and bit offset of this thread's first byte; its next bytes lie 8 TB_THREADS bits further each (one division
+  // per thread, then a step that wraps at most once for codeblocks of 2048 data bits or more)
+  unsigned cb = (8u * (j0 + i)) / w.data_bits;
+  unsigned o = 8u * (j0 + i) - cb * w.data_bits;
+#pragma unroll
+  for (int q = 0; q < TB_BYTES_PER_THREAD; ++q) {
+    const unsigned ib = q * TB_THREADS + i;  // byte of the chunk: consecutive lanes, consecutive bytes
+    if (q != 0) {
+      o += 8u * TB_THREADS;
+      while (o >= w.data_bits) {
+        o -= w.data_bits;
+        ++cb;
       }
     }
-    tb_out[w.tb_offset + j0 + i] = (uint8_t)v;
-    // bit b of the byte (LSB = 0) carries x^(8 (L - 1 - i) + b) inside the chunk
-    const unsigned* pw = g_crc_pow[TB_CRC24A_CODE - 1] + 8u * (L - 1 - i);
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const unsigned e = __ldg(pw + b);
-      r ^= ((v >> b) & 1u) ? e : 0u;
+    if (ib < L) {
+      const uint8_t* s = msgs + cbs[w.first_cb + cb].src_offset;
+      const unsigned two = ((unsigned)s[o >> 3] << 8) | (unsigned)s[(o >> 3) + 1];  // >= 16 message bits follow the data
+      unsigned v = (two >> (8 - (o & 7u))) & 0xffu;
+      const unsigned avail = w.data_bits - o;
+      if (avail < 8) {  // the byte straddles two codeblocks
+        v &= 0xff00u >> avail;
+        if (cb + 1 < w.nof_cbs) {
+          v |= (unsigned)msgs[cbs[w.first_cb + cb + 1].src_offset] >> avail;
+        }
+      }
+      tb_out[w.tb_offset + j0 + ib] = (uint8_t)v;
+      // bit b of the byte (LSB = 0) carries x^(8 (L - 1 - ib) + b) inside the chunk: 8 consecutive table entries, two
+      // 16-byte loads (the first version issued 8 scalar loads per byte with 128-byte lane strides and was bound by the
+      // L1 data pipe at 97 %: profiles/r01_ncu_tb_assemble_summary.txt)
+      const uint4* pw = reinterpret_cast<const uint4*>(g_crc_pow[TB_CRC24A_CODE - 1] + 8u * (L - 1 - ib));
+      const uint4 e0 = __ldg(pw), e1 = __ldg(pw + 1);
+      r ^= ((v & 1u) ? e0.x : 0u) ^ ((v & 2u) ? e0.y : 0u) ^ ((v & 4u) ? e0.z : 0u) ^ ((v & 8u) ? e0.w : 0u);
+      r ^= ((v & 16u) ? e1.x : 0u) ^ ((v & 32u) ? e1.y : 0u) ^ ((v & 64u) ? e1.z : 0u) ^ ((v & 128u) ? e1.w : 0u);
     }
   }
 #pragma unroll
@@ -122,49 +139,66 @@ __global__ void __launch_bounds__(TB_THREADS) ldpc_tb_assemble_kernel(const TbWo
     red[i >> 5] = r;
   }
   __syncthreads();
-  const unsigned nof_chunks = (w.nbytes + TB_THREADS - 1) / TB_THREADS;
+  const unsigned nof_chunks = (w.nbytes + TB_CHUNK - 1) / TB_CHUNK;
   if (i == 0) {
     unsigned acc = 0;
 #pragma unroll
     for (int k = 0; k < TB_THREADS / 32; ++k) {
       acc ^= red[k];
     }
-    // transport-block bits behind this chunk, + 24: crc_calculator's checksum is the remainder of m(x) x^24, so that
-    // crc_remainder equals crc_calculator::calculate_byte of the assembled bytes and not only its zero test
-    const unsigned behind = 8u * (w.nbytes - j0 - L) + 24u;
+    // x^(transport-block bits behind this chunk + 24): crc_calculator's checksum is the remainder of m(x) x^24, so that
+    // crc_remainder equals crc_calculator::calculate_byte of the assembled bytes and not only its zero test. The last
+    // chunk has 24 bits behind it; chunk c < last has 8 TB_CHUNK (last - c - 1) + 8 (bytes of the last chunk) + 24.
     if (acc != 0) {
-      acc = tb_mulmod24(acc, tb_xpow24(behind));
-      atomicXor(&scratch[2 * tb], acc);
+      const unsigned last = nof_chunks - 1, c = blockIdx.x;
+      const unsigned* pw1 = g_crc_pow[TB_CRC24A_CODE - 1];
+      if (c == last) {
+        acc = tb_mulmod24(acc, pw1[24]);
+      } else {
+        const unsigned tail = 8u * (w.nbytes - last * TB_CHUNK) + 24u, k = last - c - 1;
+        acc = tb_mulmod24(acc, pw1[tail]);
+        acc = tb_mulmod24(acc, k < TB_POW_CHUNKS ? g_tb_chunk_pow[k] : tb_xpow24(8u * TB_CHUNK * k));
+      }
     }
-    __threadfence();
-    last_flag = (atomicAdd(&scratch[2 * tb + 1], 1u) == nof_chunks - 1) ? 1u : 0u;
+    partial[w.chunk_base + blockIdx.x] = acc;
   }
-  __syncthreads();
-  if (!last_flag) {
-    return;
+}
+
+// One block per transport block: remainder = XOR of its chunks' weighted remainders; codeblock flags
+// (pusch_decoder_impl.cpp:188-195) and the verdict (:205-222).
+__global__ void __launch_bounds__(128) ldpc_tb_finish_kernel(const TbWork* __restrict__ tbs, const TbCb* __restrict__ cbs,
+                                                             const CbResult* __restrict__ results,
+                                                             const unsigned* __restrict__ partial,
+                                                             TbResult* __restrict__ tb_results)
+{
+  const unsigned tb = blockIdx.x, i = threadIdx.x;
+  const TbWork w = tbs[tb];
+  const unsigned nof_chunks = (w.nbytes + TB_CHUNK - 1) / TB_CHUNK;
+  unsigned rem = 0, bad = 0;
+  for (unsigned k = i; k < nof_chunks; k += 128) {
+    rem ^= partial[w.chunk_base + k];
   }
-  // last chunk of the transport block to finish: codeblock flags (pusch_decoder_impl.cpp:188-195) and the verdict
-  __threadfence();
-  __shared__ unsigned failed;
-  if (i == 0) {
-    failed = 0;
-  }
-  __syncthreads();
-  unsigned mine = 0;
-  for (unsigned k = i; k < w.nof_cbs; k += TB_THREADS) {
+  for (unsigned k = i; k < w.nof_cbs; k += 128) {
     const TbCb c = cbs[w.first_cb + k];
-    mine += (c.already_ok || results[c.result_index].crc_ok) ? 0u : 1u;
+    bad += (c.already_ok || results[c.result_index].crc_ok) ? 0u : 1u;
   }
-  if (mine) {
-    atomicAdd(&failed, mine);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    rem ^= __shfl_xor_sync(0xffffffffu, rem, o);
+    bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  }
+  __shared__ unsigned s_rem[4], s_bad[4];
+  if ((i & 31u) == 0) {
+    s_rem[i >> 5] = rem, s_bad[i >> 5] = bad;
   }
   __syncthreads();
   if (i == 0) {
-    const unsigned rem = atomicXor(&scratch[2 * tb], 0u);
+    rem = s_rem[0] ^ s_rem[1] ^ s_rem[2] ^ s_rem[3];
+    bad = s_bad[0] + s_bad[1] + s_bad[2] + s_bad[3];
     TbResult out;
     out.crc_remainder = rem;
-    out.nof_cb_failed = (unsigned short)min(failed, 0xffffu);
-    out.tb_crc_ok = (failed == 0 && (w.nof_cbs == 1 || rem == 0)) ? 1 : 0;
+    out.nof_cb_failed = (unsigned short)min(bad, 0xffffu);
+    out.tb_crc_ok = (bad == 0 && (w.nof_cbs == 1 || rem == 0)) ? 1 : 0;
     out.reserved = 0;
     tb_results[tb] = out;
   }
