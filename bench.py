@@ -30,8 +30,8 @@ EDGES_BG1 = 316
 ALG_BYTES_PER_CB = N_LLR + OUT_BYTES  # 25344 B in + 1056 B out = 26400 B / codeblock
 INT_OPS_PER_EMU = 20                  # SURVEY.md 8(d) canonical cost of one edge-message update
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the decode kernel over 65536 codeblocks, from the
-# `ncu --set full` capture summarised in profiles/r01_ncu_tmem_full_summary.txt (1.6737 GB + 0.0714 GB)
-NCU_TRAFFIC_BYTES_PER_CB = 1.7451e9 / 65536
+# `ncu --set full` capture summarised in profiles/r01_ncu_tmem_head_summary.txt (1.6712 GB + 0.0717 GB)
+NCU_TRAFFIC_BYTES_PER_CB = 1.7429e9 / 65536
 METRIC = "LDPC decoded info Gb/s (BG1 Z=384, 6 iters)"
 
 
@@ -482,7 +482,7 @@ def run_ours(args):
                        "l2": "inputs (%.2f GB) larger than L2" % (n_cb * N_LLR / 1e9)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES_PER_CB * n_cb,
-                         "traffic_unit": "bytes per launch (ncu dram read+write, profiles/r01_ncu_tmem_full_summary.txt)",
+                         "traffic_unit": "bytes per launch (ncu dram read+write, profiles/r01_ncu_tmem_head_summary.txt)",
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "kernel": "decode kernel of the (BG1, Z=384) group, %d launch(es) per step" % (launches // args.steps),
                          "note": "the path is integer-ALU-issue bound, not HBM bound: see roofline_alu"},
