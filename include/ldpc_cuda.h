@@ -21,6 +21,12 @@
  *   ldpc_cuda_tb_assemble*     <->  transport-block assembly + TB CRC24A + verdict of pusch_decoder_impl::decode
  *                                   lib/phy/upper/channel_processors/pusch_decoder_impl.cpp:156-222 (:196-200 bit copy,
  *                                   :205-222 CRC check) - on the device, so a slot's transport blocks never leave HBM
+ *   ldpc_cuda_demodulate*      <->  demodulation_mapper::demodulate_soft
+ *                                   include/srsran/phy/upper/channel_modulation/demodulation_mapper.h
+ *                                   (lib/phy/upper/channel_modulation/demodulation_mapper_impl.cpp:36-106) followed by
+ *                                   pusch_demodulator_impl::descramble
+ *                                   lib/phy/upper/channel_processors/pusch_demodulator_impl.cpp:100-152 - the producer of
+ *                                   the LLRs, so that they are born in device memory
  *   ldpc_cuda_segment          <->  ldpc_segmenter_rx::segment geometry
  *                                   lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_impl.cpp:226-308 (no 52-CB cap)
  *
@@ -234,6 +240,49 @@ int ldpc_cuda_dematch_decode_tb_batch(ldpc_cuda_handle*        handle,
                                       const ldpc_cuda_tb_desc* tbs,
                                       uint8_t*                 tb_out,
                                       ldpc_cuda_tb_result*     tb_results);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Upstream producer of the LLRs: soft demodulation of equalised symbols + descrambling, on the device
+ * (pusch_demodulator_impl::demodulate after the equaliser, pusch_demodulator_impl.cpp:88-98: demodulate_soft, descramble).
+ * Results are bit-exact with the reference's generic per-symbol code (its AVX2 kernels differ from that by one LLR step on
+ * a few values per million).
+ */
+
+/* One job = one codeword (one PUSCH transmission). Symbols are complex floats (re, im interleaved = cf_t), one noise
+ * variance per symbol; noise_var <= 0 or NaN gives LLR 0 as in the reference. */
+typedef struct {
+  uint8_t  mod_order;     /* bits per symbol: 1 (BPSK), 2, 4, 6, 8; 0 = the input already is int8 LLRs (descramble only) */
+  uint8_t  pi2_bpsk;      /* with mod_order 1: pi/2-BPSK (modulation_scheme::PI_2_BPSK) */
+  uint8_t  descramble;    /* 1: apply the scrambling sequence of c_init (LLR sign flips), 0: demodulate only */
+  uint8_t  reserved;
+  uint32_t nof_symbols;   /* symbols of the job; LLRs written = nof_symbols * mod_order (mod_order 0: number of LLRs) */
+  uint32_t c_init;        /* rnti * 2^15 + n_id (pusch_demodulator_impl.cpp:105) */
+  uint32_t reserved2;
+  uint64_t symbol_offset; /* index of its first symbol / noise variance in the input arrays (mod_order 0: first input LLR) */
+  uint64_t llr_offset;    /* byte offset of its first LLR in the output buffer */
+} ldpc_cuda_demod_desc;
+
+/* DEVICE buffers, asynchronous on the handle's stream. in_llrs_d may be NULL unless a job has mod_order 0. The output
+ * can be handed to ldpc_cuda_dematch_decode_batch_device as rm_llrs_d without leaving the device. */
+int ldpc_cuda_demodulate_batch_device(ldpc_cuda_handle*           handle,
+                                      uint32_t                    nof_jobs,
+                                      const ldpc_cuda_demod_desc* jobs,
+                                      const float*                symbols_d,
+                                      const float*                noise_vars_d,
+                                      const int8_t*               in_llrs_d,
+                                      int8_t*                     llrs_d);
+
+/* demodulation_mapper::demodulate_soft, HOST buffers, synchronous. llrs: nof_symbols * mod_order int8. */
+int ldpc_cuda_demodulate_soft(ldpc_cuda_handle* handle,
+                              int               mod_order,
+                              int               pi2_bpsk,
+                              uint32_t          nof_symbols,
+                              const float*      symbols,
+                              const float*      noise_vars,
+                              int8_t*           llrs);
+
+/* pusch_demodulator_impl::descramble without repetition placeholders, HOST buffers, synchronous (in may equal out). */
+int ldpc_cuda_descramble(ldpc_cuda_handle* handle, uint32_t c_init, uint32_t nof_llrs, const int8_t* in, int8_t* out);
 
 /* ---------------------------------------------------------------------------------------------------------------------
  * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,

@@ -33,6 +33,8 @@
 #include "../srsran_project_23.5_b200/host/rx_softbuffer_pool_cuda.h"
 #endif
 
+#include "phy/upper/channel_modulation/demodulation_mapper_impl.h"
+#include "phy/upper/sequence_generators/pseudo_random_generator_impl.h"
 #include <algorithm>
 #include <atomic>
 #include <map>
@@ -771,6 +773,47 @@ void ref_pool_release(void* handle, int token)
 void ref_pool_run_slot(void* handle, unsigned slot_count)
 {
   static_cast<pool_handle*>(handle)->pool->run_slot(slot_point(1, slot_count % (1024 * 20)));
+}
+
+
+// ---- upstream producer of the LLRs: soft demodulator + descrambler ---------------------------------
+// demodulation_mapper_impl::demodulate_soft (lib/phy/upper/channel_modulation/demodulation_mapper_impl.cpp:74-106).
+// mod_order 1 = BPSK, 1 + pi2 = pi/2-BPSK, 2/4/6/8 = QPSK/16/64/256QAM. batch > 0 feeds the mapper `batch` symbols at a
+// time: below the width of its AVX2 kernels (16/8/16/4 symbols) only the generic per-symbol code runs.
+int ref_demodulate_soft(int mod_order, int pi2, unsigned nof_symbols, const float* symbols, const float* noise_vars,
+                        int8_t* llrs, unsigned batch)
+{
+  modulation_scheme mod;
+  switch (mod_order) {
+    case 1: mod = pi2 ? modulation_scheme::PI_2_BPSK : modulation_scheme::BPSK; break;
+    case 2: mod = modulation_scheme::QPSK; break;
+    case 4: mod = modulation_scheme::QAM16; break;
+    case 6: mod = modulation_scheme::QAM64; break;
+    case 8: mod = modulation_scheme::QAM256; break;
+    default: return -1;
+  }
+  demodulation_mapper_impl demod;
+  const cf_t* sym = reinterpret_cast<const cf_t*>(symbols);
+  log_likelihood_ratio* out = reinterpret_cast<log_likelihood_ratio*>(llrs);
+  if (batch == 0) {
+    batch = nof_symbols;
+  }
+  for (unsigned b = 0; b < nof_symbols; b += batch) {
+    const unsigned n = std::min(batch, nof_symbols - b);
+    demod.demodulate_soft(span<log_likelihood_ratio>(out + (size_t)b * mod_order, (size_t)n * mod_order),
+                          span<const cf_t>(sym + b, n), span<const float>(noise_vars + b, n), mod);
+  }
+  return 0;
+}
+
+// pusch_demodulator_impl::descramble without placeholders (pusch_demodulator_impl.cpp:100-152):
+// pseudo_random_generator::init(c_init) + apply_xor(span<llr>, span<const llr>).
+void ref_descramble(unsigned c_init, unsigned n, const int8_t* in, int8_t* out)
+{
+  pseudo_random_generator_impl prg;
+  prg.init(c_init);
+  prg.apply_xor(span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(out), n),
+                span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), n));
 }
 
 } // extern "C"

@@ -12,6 +12,8 @@
 #include "ldpc_kernels_tmem.cuh"  // needs c_crc / crc_warp from the scalar header
 #include "ldpc_encode.cuh"
 #include "ldpc_tb.cuh"
+#include "ldpc_demod.cuh"
+#include <cmath>
 
 using namespace ldpc_b200;
 
@@ -26,6 +28,7 @@ using namespace ldpc_b200;
   } while (0)
 
 constexpr unsigned MAX_CHUNKS = 16;
+static_assert(sizeof(DemodJob) == sizeof(ldpc_cuda_demod_desc) && sizeof(DemodJob) == 32, "DemodJob mirrors the ABI struct");
 static_assert(sizeof(TbResult) == sizeof(ldpc_cuda_tb_result) && sizeof(ldpc_cuda_tb_result) == 8, "TbResult mirrors the ABI struct");
 
 struct ldpc_cuda_handle {
@@ -63,6 +66,13 @@ struct ldpc_cuda_handle {
   size_t h_tbwork_cap[2] = {0, 0};
   cudaEvent_t ev_tbwork[2] = {nullptr, nullptr};
   unsigned tbwork_slot = 0;
+  // demodulator jobs (same double-buffered pinned staging) and the device staging of its host entries
+  uint8_t* d_demod = nullptr;
+  size_t d_demod_cap = 0;
+  uint8_t* h_demod[2] = {nullptr, nullptr};
+  size_t h_demod_cap[2] = {0, 0};
+  cudaEvent_t ev_demod[2] = {nullptr, nullptr};
+  unsigned demod_slot = 0;
   std::vector<uint32_t> order;
   std::vector<uint32_t> group_begin;
 };
@@ -113,6 +123,70 @@ int upload_constants()
     }
   }
   CUDA_TRY(cudaMemcpyToSymbol(g_crc_pow, pw.data(), pw.size() * sizeof(unsigned)));
+  // demodulator: interval tables of 64QAM / 256QAM from the TS 38.211 5.1.5 / 5.1.6 bit mapping, scrambler jump matrices
+  {
+    static DemodTables dt;
+    std::memset(&dt, 0, sizeof(dt));
+    for (int m = 0; m != 2; ++m) {
+      const int L = m ? 16 : 8, nb = m ? 4 : 3;
+      const float d = 1.0f / std::sqrt(m ? 170.0f : 42.0f), den = m ? 85.0f : 21.0f;
+      // PAM level of every axis bit pattern: Re = (1 - 2 b0) [L/2 - (1 - 2 b1) [L/4 - ...]] (odd integers, unit 1/sqrt(norm))
+      int level[16];
+      for (int code = 0; code != L; ++code) {
+        int v = 2 - (1 - 2 * ((code >> (nb - 1)) & 1)), step = 2;
+        for (int k = nb - 2; k >= 1; --k) {
+          step *= 2;
+          v = step - (1 - 2 * ((code >> k) & 1)) * v;
+        }
+        level[code] = (1 - 2 * (code & 1)) * v;
+      }
+      for (int k = 0; k != nb; ++k) {
+        const bool fine = (k == nb - 1);  // the finest bit uses half as many intervals, twice as wide (as the reference)
+        const int n = fine ? L / 2 : L;
+        dt.nof_intervals[m][k] = n;
+        dt.width[m][k] = (float)(fine ? 4 : 2) * d;
+        for (int i = 0; i != n; ++i) {
+          // nearest level with bit k = 0 / 1 from the middle of interval i (distances doubled to stay integer)
+          const int mid2 = fine ? 2 * (4 * (i - L / 4) + 2) : 2 * (2 * (i - L / 2) + 1);
+          int best[2] = {0, 0}, dist[2] = {1 << 30, 1 << 30};
+          for (int code = 0; code != L; ++code) {
+            const int bit = (code >> k) & 1, dd = std::abs(2 * level[code] - mid2);
+            if (dd < dist[bit]) {
+              dist[bit] = dd, best[bit] = level[code];
+            }
+          }
+          // max-log LLR on the interval: ((x - a1)^2 - (x - a0)^2) / norm = slope * x + intercept
+          dt.slope[m][k][i] = (float)(2 * (best[0] - best[1])) * d;
+          dt.intercept[m][k][i] = (float)((best[1] * best[1] - best[0] * best[0]) / 2) / den;
+        }
+      }
+    }
+    const float s10 = 1.0f / std::sqrt(10.0f);
+    dt.qam16_gain = 4 * s10;
+    dt.qam16_threshold = 2 * s10;
+    CUDA_TRY(cudaMemcpyToSymbol(c_demod, &dt, sizeof(dt)));
+    // A^(2^j) of the two shift registers (state bit i = x(n + i); row i = state bits whose XOR is the new bit i)
+    static unsigned pw[2][32][32];
+    std::memset(pw, 0, sizeof(pw));
+    for (int q = 0; q != 2; ++q) {
+      for (int i = 0; i != 30; ++i) {
+        pw[q][0][i] = 1u << (i + 1);
+      }
+      pw[q][0][30] = q ? 0xFu : 0x9u;  // x2(n+31) = x2(n+3)^x2(n+2)^x2(n+1)^x2(n); x1(n+31) = x1(n+3)^x1(n)
+      for (int j = 1; j != 32; ++j) {
+        for (int i = 0; i != 31; ++i) {
+          unsigned row = 0;
+          for (int k = 0; k != 31; ++k) {
+            if ((pw[q][j - 1][i] >> k) & 1u) {
+              row ^= pw[q][j - 1][k];
+            }
+          }
+          pw[q][j][i] = row;
+        }
+      }
+    }
+    CUDA_TRY(cudaMemcpyToSymbol(g_prg_pow, pw, sizeof(pw)));
+  }
   // x^(8 TB_CHUNK k) mod P_24A (transport-block CRC: weight of a whole chunk, ldpc_tb.cuh)
   {
     static std::vector<unsigned> cp;
@@ -456,6 +530,76 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
   return LDPC_CUDA_OK;
 }
 
+// Demodulator / descrambler jobs (ldpc_demod.cuh): validation, upload through pinned double-buffered staging, launch.
+int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, const ldpc_cuda_demod_desc* jobs,
+                  const float* d_symbols, const float* d_noise, const int8_t* d_in_llrs, int8_t* d_out)
+{
+  if (nof_jobs > 65535u) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  unsigned max_chunks = 0;
+  for (uint32_t i = 0; i != nof_jobs; ++i) {
+    const ldpc_cuda_demod_desc& j = jobs[i];
+    const bool mod_ok = j.mod_order == 0 || j.mod_order == 1 || j.mod_order == 2 || j.mod_order == 4 || j.mod_order == 6 ||
+                        j.mod_order == 8;
+    const uint64_t nllr = (uint64_t)j.nof_symbols * (j.mod_order ? j.mod_order : 1u);
+    if (!mod_ok || (j.pi2_bpsk && j.mod_order != 1) || nllr > 0x7fffffffu || (j.mod_order == 0 && d_in_llrs == nullptr) ||
+        (j.mod_order != 0 && (d_symbols == nullptr || d_noise == nullptr))) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    max_chunks = std::max(max_chunks, (unsigned)((nllr + DEMOD_CHUNK - 1) / DEMOD_CHUNK));
+  }
+  if (max_chunks == 0) {
+    return LDPC_CUDA_OK;
+  }
+  const size_t bytes = sizeof(DemodJob) * nof_jobs;
+  const unsigned slot = (h->demod_slot++) & 1u;
+  if (h->ev_demod[slot] == nullptr) {
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_demod[slot], cudaEventDisableTiming));
+  } else {
+    CUDA_TRY(cudaEventSynchronize(h->ev_demod[slot]));
+  }
+  if (bytes > h->h_demod_cap[slot]) {
+    if (h->h_demod[slot]) {
+      CUDA_TRY(cudaFreeHost(h->h_demod[slot]));
+      h->h_demod[slot] = nullptr, h->h_demod_cap[slot] = 0;
+    }
+    CUDA_TRY(cudaHostAlloc(&h->h_demod[slot], 2 * bytes + 4096, cudaHostAllocDefault));
+    h->h_demod_cap[slot] = 2 * bytes + 4096;
+  }
+  if (bytes > h->d_demod_cap) {
+    if (h->d_demod) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      CUDA_TRY(cudaFree(h->d_demod));
+      h->d_demod = nullptr, h->d_demod_cap = 0;
+    }
+    CUDA_TRY(cudaMalloc(&h->d_demod, 2 * bytes + 4096));
+    h->d_demod_cap = 2 * bytes + 4096;
+  }
+  DemodJob* hj = reinterpret_cast<DemodJob*>(h->h_demod[slot]);
+  for (uint32_t i = 0; i != nof_jobs; ++i) {
+    const ldpc_cuda_demod_desc& j = jobs[i];
+    DemodJob& w = hj[i];
+    std::memset(&w, 0, sizeof(w));
+    w.sym_offset = j.symbol_offset;
+    w.llr_offset = j.llr_offset;
+    w.nof_llrs = j.nof_symbols * (j.mod_order ? j.mod_order : 1u);
+    w.c_init = j.c_init;
+    w.mod_order = j.mod_order;
+    w.pi2 = j.pi2_bpsk ? 1 : 0;
+    w.descramble = j.descramble ? 1 : 0;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_demod, hj, bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaEventRecord(h->ev_demod[slot], stream));
+  const dim3 grid(max_chunks, nof_jobs);
+  ldpc_demod_kernel<<<grid, DEMOD_THREADS, 0, stream>>>(reinterpret_cast<const DemodJob*>(h->d_demod),
+                                                         reinterpret_cast<const float2*>(d_symbols), d_noise, d_in_llrs,
+                                                         d_out);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -584,6 +728,13 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
   }
   cudaFree(h->pair_counter);
   cudaFree(h->d_tbwork);
+  cudaFree(h->d_demod);
+  for (int i = 0; i != 2; ++i) {
+    cudaFreeHost(h->h_demod[i]);
+    if (h->ev_demod[i]) {
+      cudaEventDestroy(h->ev_demod[i]);
+    }
+  }
   for (int i = 0; i != 2; ++i) {
     cudaFreeHost(h->h_tbwork[i]);
     if (h->ev_tbwork[i]) {
@@ -883,6 +1034,73 @@ int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle* h, uint32_t nof_tbs, const ld
   CUDA_TRY(cudaSetDevice(h->device));
   return enqueue_tb_assemble(h, h->stream, nof_tbs, tbs, n, descs, out_bits_d, reinterpret_cast<const CbResult*>(results_d),
                              tb_out_d, reinterpret_cast<TbResult*>(tb_results_d));
+}
+
+// ---- soft demodulator + descrambler (demodulation_mapper::demodulate_soft, pusch_demodulator_impl::descramble) -----------
+int ldpc_cuda_demodulate_batch_device(ldpc_cuda_handle* h, uint32_t nof_jobs, const ldpc_cuda_demod_desc* jobs,
+                                      const float* symbols_d, const float* noise_vars_d, const int8_t* in_llrs_d,
+                                      int8_t* llrs_d)
+{
+  if (h == nullptr || jobs == nullptr || llrs_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_jobs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  return enqueue_demod(h, h->stream, nof_jobs, jobs, symbols_d, noise_vars_d, in_llrs_d, llrs_d);
+}
+
+// Host-buffer mirrors: inputs through the handle's input staging, LLRs through its output staging.
+static int demod_host(ldpc_cuda_handle* h, const ldpc_cuda_demod_desc& job, const void* in0, size_t in0_bytes,
+                      const void* in1, size_t in1_bytes, int8_t* out, size_t out_bytes)
+{
+  CUDA_TRY(cudaSetDevice(h->device));
+  const size_t off1 = (in0_bytes + 255) & ~(size_t)255;
+  int rc = ensure_capacity(h, off1 + in1_bytes, out_bytes);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_in, in0, in0_bytes, cudaMemcpyHostToDevice, h->stream));
+  if (in1_bytes) {
+    CUDA_TRY(cudaMemcpyAsync(h->d_in + off1, in1, in1_bytes, cudaMemcpyHostToDevice, h->stream));
+  }
+  rc = enqueue_demod(h, h->stream, 1, &job, reinterpret_cast<const float*>(h->d_in),
+                     reinterpret_cast<const float*>(h->d_in + off1), h->d_in, reinterpret_cast<int8_t*>(h->d_out));
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_demodulate_soft(ldpc_cuda_handle* h, int mod_order, int pi2_bpsk, uint32_t nof_symbols, const float* symbols,
+                              const float* noise_vars, int8_t* llrs)
+{
+  if (h == nullptr || symbols == nullptr || noise_vars == nullptr || llrs == nullptr || mod_order < 1 || mod_order > 8) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_symbols == 0) {
+    return LDPC_CUDA_OK;
+  }
+  ldpc_cuda_demod_desc job = {};
+  job.mod_order = (uint8_t)mod_order, job.pi2_bpsk = pi2_bpsk ? 1 : 0, job.nof_symbols = nof_symbols;
+  return demod_host(h, job, symbols, sizeof(float) * 2 * (size_t)nof_symbols, noise_vars, sizeof(float) * (size_t)nof_symbols,
+                    llrs, (size_t)nof_symbols * mod_order);
+}
+
+int ldpc_cuda_descramble(ldpc_cuda_handle* h, uint32_t c_init, uint32_t nof_llrs, const int8_t* in, int8_t* out)
+{
+  if (h == nullptr || in == nullptr || out == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_llrs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  ldpc_cuda_demod_desc job = {};
+  job.mod_order = 0, job.descramble = 1, job.nof_symbols = nof_llrs, job.c_init = c_init;
+  return demod_host(h, job, in, nof_llrs, nullptr, 0, out, nof_llrs);
 }
 
 // ---- drop-in single codeblock ---------------------------------------------------------------------------------------

@@ -28,6 +28,11 @@ TB_DESC = np.dtype([("first_codeblock", "<u4"), ("nof_codeblocks", "<u4"), ("tbs
 TB_RESULT = np.dtype([("crc_remainder", "<u4"), ("nof_cb_failed", "<u2"), ("tb_crc_ok", "u1"), ("reserved", "u1")],
                      align=True)
 assert TB_DESC.itemsize == 24 and TB_RESULT.itemsize == 8
+# ldpc_cuda_demod_desc (32 bytes)
+DEMOD_DESC = np.dtype([("mod_order", "u1"), ("pi2_bpsk", "u1"), ("descramble", "u1"), ("reserved", "u1"),
+                       ("nof_symbols", "<u4"), ("c_init", "<u4"), ("reserved2", "<u4"), ("symbol_offset", "<u8"),
+                       ("llr_offset", "<u8")], align=True)
+assert DEMOD_DESC.itemsize == 32
 
 
 class LdpcCudaError(RuntimeError):
@@ -92,6 +97,9 @@ def library():
             getattr(L, name).argtypes = [vp, vp, vp, vp]
         L.ldpc_cuda_tb_assemble_device.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, vp]
         L.ldpc_cuda_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp]
+        L.ldpc_cuda_demodulate_batch_device.argtypes = [vp, u32, vp, vp, vp, vp, vp]
+        L.ldpc_cuda_demodulate_soft.argtypes = [vp, i32, i32, u32, vp, vp, vp]
+        L.ldpc_cuda_descramble.argtypes = [vp, u32, u32, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
         L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
         _lib = L
@@ -260,6 +268,27 @@ class LdpcCuda:
                                                               _ptr(results), tbs.size, _ptr(tbs), _ptr(tb_out),
                                                               _ptr(tb_results)), "ldpc_cuda_dematch_decode_tb_batch")
         return out, results, tb_out, tb_results
+
+    # -- soft demodulator + descrambler (demodulation_mapper::demodulate_soft, pusch_demodulator_impl::descramble) ------
+    def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False):
+        """symbols: complex64 [n], noise_vars: float32 [n] -> int8 [n * mod_order]."""
+        symbols = np.ascontiguousarray(symbols, np.complex64)
+        noise_vars = np.ascontiguousarray(noise_vars, np.float32)
+        out = np.zeros(symbols.size * mod_order, np.int8)
+        self._check(self._L.ldpc_cuda_demodulate_soft(self._h, mod_order, int(pi2), symbols.size, _ptr(symbols),
+                                                      _ptr(noise_vars), _ptr(out)), "ldpc_cuda_demodulate_soft")
+        return out
+
+    def descramble(self, c_init, llrs):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.zeros_like(llrs)
+        self._check(self._L.ldpc_cuda_descramble(self._h, c_init, llrs.size, _ptr(llrs), _ptr(out)), "ldpc_cuda_descramble")
+        return out
+
+    def demodulate_batch_device(self, jobs, symbols_ptr, noise_ptr, in_llrs_ptr, llrs_ptr):
+        jobs = np.ascontiguousarray(jobs, DEMOD_DESC)
+        self._check(self._L.ldpc_cuda_demodulate_batch_device(self._h, jobs.size, _ptr(jobs), symbols_ptr, noise_ptr,
+                                                              in_llrs_ptr, llrs_ptr), "ldpc_cuda_demodulate_batch_device")
 
     # -- transmit side (encoder + rate matcher) ------------------------------------------------------------------------
     def encode(self, bg, Z, msg_bits):

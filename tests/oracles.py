@@ -52,6 +52,28 @@ class PortOracle:
         L.oracle_encode.argtypes = [c_int, c_int, c_void_p, c_void_p, c_uint]
         L.oracle_rate_match.argtypes = [c_void_p, c_uint, c_void_p, c_uint, c_int, c_int, c_uint, c_uint]
         L.oracle_hard_decision.argtypes = [c_void_p, c_uint, c_void_p]
+        L.oracle_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p]
+        L.oracle_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
+        L.oracle_gold_sequence.argtypes = [c_uint, c_uint, c_void_p]
+
+    def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False):
+        """symbols: complex64 [n]; noise_vars: float32 [n]. Returns int8 [n * mod_order]."""
+        symbols = np.ascontiguousarray(symbols, np.complex64)
+        noise_vars = np.ascontiguousarray(noise_vars, np.float32)
+        out = np.zeros(symbols.size * mod_order, np.int8)
+        self.lib.oracle_demodulate_soft(mod_order, int(pi2), symbols.size, _ptr(symbols), _ptr(noise_vars), _ptr(out))
+        return out
+
+    def descramble(self, c_init, llrs):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.zeros_like(llrs)
+        self.lib.oracle_descramble(c_init, llrs.size, _ptr(llrs), _ptr(out))
+        return out
+
+    def gold_sequence(self, c_init, n):
+        c = np.zeros(n, np.uint8)
+        self.lib.oracle_gold_sequence(c_init, n, _ptr(c))
+        return c
 
     def llr_add(self, a, b):
         return self.lib.oracle_llr_add(int(a), int(b))
@@ -147,8 +169,27 @@ class RefOracle:
         L.ref_pusch_destroy.argtypes = [c_void_p]
         L.ref_pusch_decode.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_int,
                                        c_int, c_int, c_uint, c_uint, c_uint, c_int, c_int, c_int, c_void_p]
+        L.ref_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p, c_uint]
+        L.ref_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
         self._decoders = {}
         self._dematchers = {}
+
+    def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False, batch=0):
+        """demodulation_mapper_impl::demodulate_soft; batch > 0 feeds `batch` symbols per call (below the AVX2 width: the
+        reference's generic per-symbol code only)."""
+        symbols = np.ascontiguousarray(symbols, np.complex64)
+        noise_vars = np.ascontiguousarray(noise_vars, np.float32)
+        out = np.zeros(symbols.size * mod_order, np.int8)
+        rc = self.lib.ref_demodulate_soft(mod_order, int(pi2), symbols.size, _ptr(symbols), _ptr(noise_vars), _ptr(out),
+                                          batch)
+        assert rc == 0
+        return out
+
+    def descramble(self, c_init, llrs):
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.zeros_like(llrs)
+        self.lib.ref_descramble(c_init, llrs.size, _ptr(llrs), _ptr(out))
+        return out
 
     def supports(self, kind):
         return bool(self.lib.ref_cpu_supports(kind.encode()))
@@ -314,6 +355,26 @@ def make_codeword(rng, bg, Z, fillers=0, crc=CRC_NONE):
         attach_crc(msg, crc, fillers)
     cw = port().encode(bg, Z, msg)
     return msg, cw
+
+
+MOD_NORM = {1: 2.0, 2: 2.0, 4: 10.0, 6: 42.0, 8: 170.0}
+
+
+def random_symbols(rng, mod_order, n, noise_var=0.01, spread=1.3):
+    """Equalised symbols for demodulator tests: constellation points (not bit-mapped: any grid point) + complex noise, a
+    few outliers far outside the constellation, and per-symbol noise variances over three decades (plus some <= 0, for
+    which the reference emits 0)."""
+    levels = {1: 1, 2: 1, 4: 3, 6: 7, 8: 15}[mod_order]
+    pts = np.arange(-levels, levels + 1, 2)
+    d = 1.0 / np.sqrt(MOD_NORM[mod_order])
+    re, im = rng.choice(pts, n) * d, rng.choice(pts, n) * d
+    sym = (re + 1j * im + (rng.normal(0, 1, n) + 1j * rng.normal(0, 1, n)) * np.sqrt(noise_var / 2)).astype(np.complex64)
+    far = rng.random(n) < 0.01
+    sym[far] *= np.float32(spread * 2)
+    nv = (noise_var * 10.0 ** rng.uniform(-1.5, 1.5, n)).astype(np.float32)
+    nv[rng.random(n) < 0.005] = 0.0
+    nv[rng.random(n) < 0.002] = -1.0
+    return sym, nv
 
 
 def msg_to_packed(msg):
