@@ -43,6 +43,7 @@ struct DemodJob {
 // from the TS 38.211 5.1 bit mapping (build_demod_tables in ldpc_api.cu) with the reference's float expressions.
 struct DemodTables {
   float width[2][4];
+  float rcp_width[2][4];  // RN(1 / width)
   int nof_intervals[2][4];
   float slope[2][4][16];
   float intercept[2][4][16];
@@ -58,27 +59,72 @@ constexpr int DEMOD_THREADS = 256;
 constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block
 constexpr float DEMOD_2SQRT2 = 2.0f * 1.41421356237309504880f;
 
-__device__ __forceinline__ int demod_quantize(float value, float range_limit)
+// a / b correctly rounded with rb = RN(1 / b) (Markstein: q0 = RN(a rb), r = a - b q0 exactly, q = RN(q0 + r rb)), without
+// the reciprocal approximation and range checks of a general division. Falls back to the IEEE division when the
+// intermediate leaves the range in which the residual is exact.
+__device__ __forceinline__ float demod_div(float a, float b, float rb)
 {
+  const float q0 = __fmul_rn(a, rb);
+  const float r = __fmaf_rn(-b, q0, a);
+  const float q = __fmaf_rn(r, rb, q0);
+  return (fabsf(q0) < 1e30f && fabsf(rb) > 1e-30f) ? q : __fdiv_rn(a, b);
+}
+
+// Same for a constant divisor and a bounded dividend (interval width, quantiser range): no fallback needed.
+__device__ __forceinline__ float demod_div_const(float a, float b, float rb)
+{
+  const float q0 = __fmul_rn(a, rb);
+  return __fmaf_rn(__fmaf_rn(-b, q0, a), rb, q0);
+}
+
+// log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip, / range * 120, std::round (half away from zero).
+// RCP = RN(1 / RANGE). Rounding: nearest-even through the 1.5 * 2^23 magic constant (the integer falls out of the
+// mantissa), ties corrected to "away".
+template <int RANGE>
+__device__ __forceinline__ int demod_quantize(float value)
+{
+  constexpr float range_limit = (float)RANGE, rcp = 1.0f / (float)RANGE;
   float clipped = value;
   if (fabsf(value) > range_limit) {
     clipped = copysignf(range_limit, value);
   }
-  return (int)roundf(__fmul_rn(__fdiv_rn(clipped, range_limit), 120.0f));
+  const float x = __fmul_rn(demod_div_const(clipped, range_limit, rcp), 120.0f);
+  const float magic = 12582912.0f;
+  float t = __fadd_rn(x, magic);
+  const float diff = __fsub_rn(x, __fsub_rn(t, magic));
+  if (fabsf(diff) == 0.5f) {
+    t = __fadd_rn(__fadd_rn(x, copysignf(0.5f, x)), magic);
+  }
+  const int i = __float_as_int(t) - 0x4B400000;
+  return (x == x) ? i : 0;  // NaN -> 0, as the conversion of the reference's platform
 }
 
-__device__ __forceinline__ float demod_interval(float value, float rcp_noise, int m, int k)
+// Per-block copy of the job's interval tables (divergent indices: shared memory instead of the constant cache).
+struct DemodSmem {
+  float slope[4][16];
+  float intercept[4][16];
+};
+
+// (symbols beyond +-1e30 would overflow the quotient; the reference's float -> int conversion is undefined there too)
+__device__ __forceinline__ float demod_interval(const DemodSmem& tab, float value, float rcp_noise, int m, int k)
 {
   const int n = c_demod.nof_intervals[m][k];
-  int idx = (int)floorf(__fdiv_rn(value, c_demod.width[m][k])) + n / 2;
+  int idx = __float2int_rd(demod_div_const(value, c_demod.width[m][k], c_demod.rcp_width[m][k])) + n / 2;
   idx = max(0, min(n - 1, idx));
-  const float l = __fmaf_rn(c_demod.slope[m][k][idx], value, c_demod.intercept[m][k][idx]);
+  const float l = __fmaf_rn(tab.slope[k][idx], value, tab.intercept[k][idx]);
   return __fmul_rn(l, rcp_noise);
 }
 
+// Per-symbol state shared by the LLRs of a symbol.
+struct DemodSym {
+  unsigned index;
+  float2 z;
+  float nv, rcp;  // rcp = RN(1 / nv) when nv > 0, else 0
+};
+
 // LLR j of a job (before descrambling).
-__device__ __forceinline__ int demod_llr(const DemodJob& job, unsigned j, const float2* __restrict__ sym,
-                                         const float* __restrict__ noise)
+__device__ __forceinline__ int demod_llr(const DemodJob& job, const DemodSmem& tab, unsigned j, DemodSym& cur,
+                                         const float2* __restrict__ sym, const float* __restrict__ noise)
 {
   const unsigned q = job.mod_order;
   unsigned s, b;
@@ -89,42 +135,111 @@ __device__ __forceinline__ int demod_llr(const DemodJob& job, unsigned j, const 
     case 6: s = j / 6u, b = j - 6u * s; break;
     default: s = j >> 3, b = j & 7u; break;
   }
-  const float2 z = __ldg(sym + s);
-  const float nv = __ldg(noise + s);
+  if (s != cur.index) {
+    cur.index = s;
+    cur.z = __ldg(sym + s);
+    cur.nv = __ldg(noise + s);
+    cur.rcp = (cur.nv > 0) ? __fdiv_rn(1.0f, cur.nv) : 0.0f;
+  }
+  const float2 z = cur.z;
+  const float nv = cur.nv;
   const float x = (b & 1u) ? z.y : z.x;
+  if (q >= 6) {
+    return demod_quantize<20>(demod_interval(tab, x, cur.rcp, q == 8 ? 1 : 0, (int)(b >> 1)));
+  }
+  if (!(nv > 0)) {  // also false for NaN
+    return 0;
+  }
   if (q == 1) {
-    if (!(nv > 0)) {
-      return 0;
-    }
     const float sum = (job.pi2 && (j & 1u)) ? __fadd_rn(z.y, -z.x) : __fadd_rn(z.x, z.y);
-    return demod_quantize(__fdiv_rn(__fmul_rn(DEMOD_2SQRT2, sum), nv), 24.0f);
+    return demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, sum), nv, cur.rcp));
   }
   if (q == 2) {
-    if (!(nv > 0)) {
-      return 0;
-    }
-    return demod_quantize(__fdiv_rn(__fmul_rn(DEMOD_2SQRT2, x), nv), 24.0f);
+    return demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, x), nv, cur.rcp));
   }
-  if (q == 4) {
-    if (!(nv > 0)) {
-      return 0;
+  float l;
+  if (b < 2) {
+    l = __fmul_rn(c_demod.qam16_gain, x);
+    if (fabsf(x) > c_demod.qam16_threshold) {
+      l = __fsub_rn(__fmul_rn(2.0f, l), copysignf(0.8f, x));
     }
-    float l;
-    if (b < 2) {
-      l = __fmul_rn(c_demod.qam16_gain, x);
-      if (fabsf(x) > c_demod.qam16_threshold) {
-        l = __fsub_rn(__fmul_rn(2.0f, l), copysignf(0.8f, x));
+  } else {
+    l = __fmaf_rn(-c_demod.qam16_gain, fabsf(x), 0.8f);
+  }
+  return demod_quantize<20>(demod_div(l, nv, cur.rcp));
+}
+
+// Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q, before descrambling, one per byte.
+// valid = number of LLRs that exist (1..4). Straight-line per modulation: the symbol, its noise variance and the
+// reciprocal are fetched once.
+template <int Q>
+__device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodSmem& tab, unsigned j, unsigned valid,
+                                               const float2* __restrict__ sym, const float* __restrict__ noise)
+{
+  int v[4] = {0, 0, 0, 0};
+  if (Q == 8 || Q == 4) {
+    const unsigned s = (Q == 8) ? (j >> 3) : (j >> 2);
+    const float2 z = __ldg(sym + s);
+    const float nv = __ldg(noise + s);
+    const bool ok = nv > 0;  // false for NaN
+    const float rcp = ok ? __fdiv_rn(1.0f, nv) : 0.0f;
+    if (Q == 8) {
+      const int k0 = (int)((j >> 1) & 2u);  // axis-bit level of LLRs 0,1; LLRs 2,3 are one level finer
+      v[0] = demod_quantize<20>(demod_interval(tab, z.x, rcp, 1, k0));
+      v[1] = demod_quantize<20>(demod_interval(tab, z.y, rcp, 1, k0));
+      v[2] = demod_quantize<20>(demod_interval(tab, z.x, rcp, 1, k0 + 1));
+      v[3] = demod_quantize<20>(demod_interval(tab, z.y, rcp, 1, k0 + 1));
+    } else if (ok) {
+      const float g = c_demod.qam16_gain, th = c_demod.qam16_threshold;
+      float l0 = __fmul_rn(g, z.x), l1 = __fmul_rn(g, z.y);
+      if (fabsf(z.x) > th) {
+        l0 = __fsub_rn(__fmul_rn(2.0f, l0), copysignf(0.8f, z.x));
       }
-    } else {
-      l = __fmaf_rn(-c_demod.qam16_gain, fabsf(x), 0.8f);
+      if (fabsf(z.y) > th) {
+        l1 = __fsub_rn(__fmul_rn(2.0f, l1), copysignf(0.8f, z.y));
+      }
+      v[0] = demod_quantize<20>(demod_div(l0, nv, rcp));
+      v[1] = demod_quantize<20>(demod_div(l1, nv, rcp));
+      v[2] = demod_quantize<20>(demod_div(__fmaf_rn(-g, fabsf(z.x), 0.8f), nv, rcp));
+      v[3] = demod_quantize<20>(demod_div(__fmaf_rn(-g, fabsf(z.y), 0.8f), nv, rcp));
     }
-    return demod_quantize(__fdiv_rn(l, nv), 20.0f);
+  } else if (Q == 2) {
+#pragma unroll
+    for (unsigned h = 0; h < 2; ++h) {
+      if (2 * h < valid) {
+        const float2 z = __ldg(sym + (j >> 1) + h);
+        const float nv = __ldg(noise + (j >> 1) + h);
+        if (nv > 0) {
+          const float rcp = __fdiv_rn(1.0f, nv);
+          v[2 * h] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, z.x), nv, rcp));
+          v[2 * h + 1] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, z.y), nv, rcp));
+        }
+      }
+    }
+  } else if (Q == 1) {
+#pragma unroll
+    for (unsigned u = 0; u < 4; ++u) {
+      if (u < valid) {
+        const float2 z = __ldg(sym + j + u);
+        const float nv = __ldg(noise + j + u);
+        if (nv > 0) {
+          const float sum = (job.pi2 && (u & 1u)) ? __fadd_rn(z.y, -z.x) : __fadd_rn(z.x, z.y);
+          v[u] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, sum), nv, __fdiv_rn(1.0f, nv)));
+        }
+      }
+    }
+  } else {  // 64QAM: the four LLRs straddle symbols
+    DemodSym cur;
+    cur.index = 0xffffffffu;
+#pragma unroll
+    for (unsigned u = 0; u < 4; ++u) {
+      if (u < valid) {
+        v[u] = demod_llr(job, tab, j + u, cur, sym, noise);
+      }
+    }
   }
-  float rcp = 0.0f;
-  if (nv > 0) {
-    rcp = __fdiv_rn(1.0f, nv);
-  }
-  return demod_quantize(demod_interval(x, rcp, q == 8 ? 1 : 0, (int)(b >> 1)), 20.0f);
+  return ((unsigned)v[0] & 0xffu) | (((unsigned)v[1] & 0xffu) << 8) | (((unsigned)v[2] & 0xffu) << 16) |
+         (((unsigned)v[3] & 0xffu) << 24);
 }
 
 // x1 / x2 advanced by k <= 28 chips: the 28 new bits x(n+31..n+58) follow from the state in one step.
@@ -149,6 +264,12 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   }
   const unsigned t = threadIdx.x, lane = t & 31u;
   __shared__ unsigned chips[DEMOD_THREADS];
+  __shared__ DemodSmem tab;
+  if (job.mod_order >= 6 && t < 64) {
+    const int m = job.mod_order == 8 ? 1 : 0;
+    tab.slope[t >> 4][t & 15] = c_demod.slope[m][t >> 4][t & 15];
+    tab.intercept[t >> 4][t & 15] = c_demod.intercept[m][t >> 4][t & 15];
+  }
   if (job.descramble) {
     // state of both registers at chip 1600 + first chip of the warp (Nc = 1600, TS 38.211 5.2.1)
     const unsigned n = 1600u + j0 + (t & ~31u) * 32u;
@@ -161,13 +282,14 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
       }
     }
     // this lane's word starts 32 * lane chips further
-    unsigned left = 32u * lane;
-    while (left) {
-      const unsigned k = min(left, 28u);
-      s1 = prg_advance(s1, k, false);
-      s2 = prg_advance(s2, k, true);
-      left -= k;
+    // (full steps of 28 chips with constant shifts, then one partial step)
+    const unsigned full = (32u * lane) / 28u, rest = 32u * lane - 28u * full;
+    for (unsigned i = 0; i < full; ++i) {
+      s1 = ((s1 >> 28) | (((s1 >> 3) ^ s1) << 3)) & 0x7fffffffu;
+      s2 = ((s2 >> 28) | (((s2 >> 3) ^ (s2 >> 2) ^ (s2 >> 1) ^ s2) << 3)) & 0x7fffffffu;
     }
+    s1 = prg_advance(s1, rest, false);
+    s2 = prg_advance(s2, rest, true);
     const unsigned b1 = ((s1 >> 3) ^ s1) & 1u, b2 = ((s2 >> 3) ^ (s2 >> 2) ^ (s2 >> 1) ^ s2) & 1u;
     chips[t] = (s1 ^ s2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
   }
@@ -185,16 +307,25 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
       break;
     }
     const unsigned cw = job.descramble ? (chips[local >> 5] >> (local & 31u)) : 0u;
-    unsigned packed = 0;
-#pragma unroll
-    for (unsigned u = 0; u < 4; ++u) {
-      int v = 0;
-      if (j + u < job.nof_llrs) {
-        v = job.mod_order ? demod_llr(job, j + u, sym, noise) : (int)in[j + u];
-        v = ((cw >> u) & 1u) ? -v : v;
-      }
-      packed |= ((unsigned)v & 0xffu) << (8u * u);
+    const unsigned valid = min(4u, job.nof_llrs - j);
+    unsigned packed;
+    switch (job.mod_order) {  // uniform over the block
+      case 8: packed = demod_four<8>(job, tab, j, valid, sym, noise); break;
+      case 6: packed = demod_four<6>(job, tab, j, valid, sym, noise); break;
+      case 4: packed = demod_four<4>(job, tab, j, valid, sym, noise); break;
+      case 2: packed = demod_four<2>(job, tab, j, valid, sym, noise); break;
+      case 1: packed = demod_four<1>(job, tab, j, valid, sym, noise); break;
+      default:
+        packed = 0;
+        for (unsigned u = 0; u < valid; ++u) {
+          packed |= ((unsigned)in[j + u] & 0xffu) << (8u * u);
+        }
     }
+    // descrambling: two's complement negation of the bytes whose chip is 1 (per byte: (v ^ 0xff) + 1)
+    const unsigned m = (cw & 1u) * 0xffu | ((cw >> 1) & 1u) * 0xff00u | ((cw >> 2) & 1u) * 0xff0000u |
+                       ((cw >> 3) & 1u) * 0xff000000u;
+    const unsigned x = packed ^ m, one = m & 0x01010101u;
+    packed = ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);  // byte-wise x + one without carries across bytes
     if (aligned && j + 3 < job.nof_llrs) {
       *reinterpret_cast<unsigned*>(dst + j) = packed;
     } else {
