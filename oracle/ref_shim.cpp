@@ -31,6 +31,7 @@
 #include "../srsran_project_23.5_b200/host/ldpc_cuda_factories.h"
 #include "../srsran_project_23.5_b200/host/pusch_decoder_cuda.h"
 #include "../srsran_project_23.5_b200/host/rx_softbuffer_pool_cuda.h"
+#include "../srsran_project_23.5_b200/host/demodulation_mapper_cuda.h"
 #endif
 
 #include "phy/upper/channel_modulation/demodulation_mapper_impl.h"
@@ -792,7 +793,21 @@ int ref_demodulate_soft(int mod_order, int pi2, unsigned nof_symbols, const floa
     case 8: mod = modulation_scheme::QAM256; break;
     default: return -1;
   }
-  demodulation_mapper_impl demod;
+  // batch == 0xffffffff (drop-in library only): the product's "cuda" mapper behind the same reference interface
+  std::unique_ptr<demodulation_mapper> demod_ptr;
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (batch == 0xffffffffu) {
+    demod_ptr = create_demodulation_mapper_cuda(0);
+    if (!demod_ptr) {
+      return -2;
+    }
+    batch = 0;
+  }
+#endif
+  if (!demod_ptr) {
+    demod_ptr = std::make_unique<demodulation_mapper_impl>();
+  }
+  demodulation_mapper& demod = *demod_ptr;
   const cf_t* sym = reinterpret_cast<const cf_t*>(symbols);
   log_likelihood_ratio* out = reinterpret_cast<log_likelihood_ratio*>(llrs);
   if (batch == 0) {

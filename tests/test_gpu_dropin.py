@@ -211,3 +211,18 @@ def test_batched_pusch_decoder_cuda_full_slot_tb_152_codeblocks(lib, pool):
             assert st[2] == nfail, (st, nfail)      # only the codeblocks that had failed were decoded again
             assert (got_tb == tb).all()
     lib.lib.ref_pusch_destroy(h)
+
+
+@pytest.mark.parametrize("mod_order,pi2,batch", [(1, False, 0), (1, True, 0), (2, False, 15), (4, False, 7), (6, False, 15),
+                                                 (8, False, 3)])
+def test_demodulation_mapper_interface(lib, mod_order, pi2, batch):
+    """create_demodulation_mapper_cuda() behind the reference's demodulation_mapper interface against
+    demodulation_mapper_impl on the same symbols: identical LLRs to the reference's generic per-symbol code, within one
+    step of its AVX2 kernels."""
+    rng = np.random.default_rng(40 + mod_order)
+    sym, nv = O.random_symbols(rng, mod_order, 50003, 0.02)
+    got = lib.demodulate_soft(mod_order, sym, nv, pi2, 0xffffffff)
+    want = lib.demodulate_soft(mod_order, sym, nv, pi2, batch)
+    assert (got == want).all()
+    simd = lib.demodulate_soft(mod_order, sym, nv, pi2, 0)
+    assert np.abs(simd.astype(np.int16) - got).max() <= 1
