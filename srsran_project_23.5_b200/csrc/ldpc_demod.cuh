@@ -18,8 +18,8 @@
 //
 // Work split: a block of 256 threads produces 8192 consecutive LLRs of one job. Phase 1 (descrambling only): each warp
 // jumps the two 31-bit LFSRs of TS 38.211 5.2.1 to its first chip with GF(2) matrix powers A^(2^j) applied
-// co-operatively (one row per lane, ballot), each lane then advances by 32 * lane chips 28 at a time and writes its 32-chip
-// word to shared memory. Phase 2: a thread computes 4 consecutive LLRs per step (one packed 32-bit store, coalesced),
+// co-operatively (one row per lane, ballot), groups of 4 lanes are reached with A^128 the same way, each lane then advances
+// by at most 96 chips, 28 at a time, and writes its 32-chip word to shared memory. Phase 2: a thread computes 4 consecutive LLRs per step (one packed 32-bit store, coalesced),
 // 8 steps. HBM-bound by design: 1 byte out + 12 / Qm bytes in per LLR.
 #pragma once
 
@@ -281,9 +281,24 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
         s2 = __ballot_sync(0xffffffffu, __popc(r2 & s2) & 1);
       }
     }
-    // this lane's word starts 32 * lane chips further
-    // (full steps of 28 chips with constant shifts, then one partial step)
-    const unsigned full = (32u * lane) / 28u, rest = 32u * lane - 28u * full;
+    // Lane L needs the state 32 L chips further. Groups of 4 lanes: the start of group g follows from the start of group
+    // g - 1 by one more co-operative product with A^128 (its rows stay in registers); inside a group a lane advances by
+    // 0, 32, 64 or 96 chips in steps of 28. (Advancing every lane on its own from the warp's start took up to 36 steps
+    // and was a third of the kernel's instructions: profiles/r01_ncu_demod_summary.txt.)
+    {
+      const unsigned q1 = g_prg_pow[0][7][lane], q2 = g_prg_pow[1][7][lane];
+      unsigned m1 = s1, m2 = s2;
+#pragma unroll
+      for (unsigned g = 1; g < 8; ++g) {
+        s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
+        s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
+        if ((lane >> 2) == g) {
+          m1 = s1, m2 = s2;
+        }
+      }
+      s1 = m1, s2 = m2;
+    }
+    const unsigned ahead = 32u * (lane & 3u), full = ahead / 28u, rest = ahead - 28u * full;
     for (unsigned i = 0; i < full; ++i) {
       s1 = ((s1 >> 28) | (((s1 >> 3) ^ s1) << 3)) & 0x7fffffffu;
       s2 = ((s2 >> 28) | (((s2 >> 3) ^ (s2 >> 2) ^ (s2 >> 1) ^ s2) << 3)) & 0x7fffffffu;

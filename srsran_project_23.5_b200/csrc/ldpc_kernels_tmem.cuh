@@ -205,11 +205,6 @@ __device__ __forceinline__ void tm_store(unsigned ta, const unsigned* r)
 
 constexpr unsigned SIGN2 = 0x80008000u;
 
-// Development switch for A/B builds (tools/build_variant.sh ... -DTM_VARIANT=n); the shipped value is the measured best.
-// bit 0: clamp by HMNMX2.XORSIGN, bit 1: soft update in the magnitude domain, bit 2: cap (120,120) applied after the tree
-#ifndef TM_VARIANT
-#define TM_VARIANT 1
-#endif
 // sign(a) * min(|a|, |b|) for b > 0 (one HMNMX2.XORSIGN)
 __device__ __forceinline__ unsigned hmin_xorsign_abs(unsigned a, unsigned b)
 {
@@ -321,8 +316,7 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
     u[k] = hadd(hsub(u[k], tb), hc(1152.f));  // variable-to-check message (compute_var_to_check_msgs)
   }
   // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
-  constexpr bool CAP_LAST = (TM_VARIANT & 4) && !(NV & 1);  // even rows: two min ops after the tree instead of a merge
-  constexpr int NP = CAP_LAST ? NV / 2 : (NV + 2) / 2;        // sorted pairs, including the cap (120, 120)
+  constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
   MinPair pr[NP];
   const unsigned c120 = hc(120.f);
 #pragma unroll
@@ -333,15 +327,11 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
   if constexpr (NV & 1) {
     pr[NP - 1].m1 = hmin_abs(u[NV - 1], c120);
     pr[NP - 1].m2 = c120;
-  } else if constexpr (!CAP_LAST) {
+  } else {
     pr[NP - 1].m1 = c120;
     pr[NP - 1].m2 = c120;
   }
-  MinPair mm = reduce_pairs<NP>(pr);
-  if constexpr (CAP_LAST) {
-    mm.m1 = umin2(mm.m1, c120);
-    mm.m2 = umin2(mm.m2, c120);
-  }
+  const MinPair mm = reduce_pairs<NP>(pr);
   unsigned S = 0;
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
@@ -360,22 +350,9 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
     const unsigned uk = u[k];
     const unsigned indp = hadd_sat_abs(uk, nM1);  // 0 where |u| == min1, 1 elsewhere
     const unsigned cm = hfma(indp, nD, Q2s);
-    if constexpr ((TM_VARIANT & 2) && true) {
-      if (k < D) {
-        // magnitude domain: soft = sign(u) * promote(min(|u|, 120) + T-signed message); |u| = inf adds inf and stays
-        const unsigned a = hadd(hmin_abs(uk, c120), hfma_relu_abs(uk, hc(1.f), hc(-216.f)));
-        const unsigned b = hadd(a, cm);
-        const unsigned rp = hfma_relu_abs(b, hc(544.f), hc(-65280.f));
-        const unsigned n1 = hfma(rp, b, b);
-        if (c.active) {
-          sts32(addr[k], n1 ^ (uk & SIGN2));
-        }
-        tn[k] = hfma(cm, (uk & SIGN2) | 0x3c003c00u, hc(1152.f));
-        continue;
-      }
-    }
     const unsigned cn = cm ^ (uk & SIGN2);
-    const unsigned v = (TM_VARIANT & 1) ? hmin_xorsign_abs(uk, c120) : hmax(hmin(uk, c120), hc(-120.f));
+    // clamp to +-120 in one HMNMX2.XORSIGN (the two-instruction min/max form was 1.3 % slower: profiles/r01_icache_microbench.md)
+    const unsigned v = hmin_xorsign_abs(uk, c120);
     const unsigned s = hadd(v, cn);
     const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
     const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
@@ -471,7 +448,6 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   const int grp = tm::uniform(tid / zpad);
   const int t = tid - grp * zpad;
   const int wig = tm::uniform(t >> 5);   // warp index inside the group
-  const int nwg = zpad >> 5;             // warps per group
   const int bar_id = 1 + grp;
   const unsigned msg_len = (unsigned)(K * Z), msg_bytes = (msg_len + 7) / 8, msg_bytes16 = (msg_bytes + 15) & ~15u;
   const TmLayout lay = tm_layout(BG, Z, zpad, FUSED);
