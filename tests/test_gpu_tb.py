@@ -187,3 +187,44 @@ def test_dematch_decode_tb_batch_end_to_end(dec, tbs, Qm, layers, nsym):
     D = (tbs + 24) // C
     good = tb_out[tbs // 8 + 3:][:(C // 2) * D // 8]
     assert (good == tb_want[1][:good.size]).all()
+
+
+def test_dematch_decode_tb_batch_pipelined_in_chunks(dec):
+    """16 full-slot transport blocks (2432 codeblocks, 21.8 MB of LLRs) in one call: the host entry splits the call into
+    overlapping copy / decode chunks, the assembly runs behind the last of them. One block is sent below threshold."""
+    rng = np.random.default_rng(16)
+    tbs, Qm, layers, nsym, n_tb = 1277992, 8, 4, 42588 * 4, 16
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    tb, cws, meta = O.build_transport_block(rng, tbs, 1, Qm, layers, nsym)
+    descs1, crc_bits = pkg.segment(tbs, 1, Qm, layers, nsym)
+    C = descs1.size
+    tx = [O.port().rate_match(cws[r], int(meta[r, 2]), 0, Qm, 0, int(meta[r, 3])) for r in range(C)]
+    tx_all = np.concatenate(tx)
+    E = descs1["rm_length"].astype(np.int64)
+    cb_off = np.concatenate([[0], np.cumsum(E)[:-1]])
+    kb = 22 * 384 // 8
+    descs = np.zeros(n_tb * C, pkg.CB_DESC)
+    rms = []
+    tbs_arr = np.zeros(n_tb, pkg.TB_DESC)
+    stride = tbs // 8 + 3
+    for b in range(n_tb):
+        s = descs[b * C:(b + 1) * C]
+        s[:] = descs1
+        s["early_stop"], s["new_data"], s["in_length"] = 1, 1, 66 * 384
+        s["in_offset"] = b * tx_all.size + cb_off
+        s["soft_offset"] = (b * C + np.arange(C)) * 66 * 384
+        s["out_offset"] = (b * C + np.arange(C)) * kb
+        rms.append(O.awgn_llrs(rng, tx_all, 3.0 if b == 5 else 9.0))
+        tbs_arr[b]["first_codeblock"], tbs_arr[b]["nof_codeblocks"], tbs_arr[b]["tbs_bits"] = b * C, C, tbs
+        tbs_arr[b]["nof_cb_crc_bits"], tbs_arr[b]["tb_offset"] = 24, b * stride
+    dec.softbuffer_reserve(n_tb * C * 66 * 384)
+    out = np.zeros(n_tb * C * kb, np.uint8)
+    tb_out = np.zeros(n_tb * stride, np.uint8)
+    _, res, tb_out, tbres = dec.dematch_decode_tb_batch(descs, np.concatenate(rms), out, tbs_arr, tb_out)
+    for b in range(n_tb):
+        if b == 5:
+            assert int(tbres[b]["tb_crc_ok"]) == 0 and int(tbres[b]["nof_cb_failed"]) > 0
+        else:
+            assert int(tbres[b]["tb_crc_ok"]) == 1, b
+            assert (tb_out[b * stride:b * stride + tbs // 8] == tb).all(), b
+            assert int(tbres[b]["crc_remainder"]) == 0
