@@ -27,7 +27,10 @@ using namespace ldpc_b200;
     }                                                                                                        \
   } while (0)
 
-constexpr unsigned MAX_CHUNKS = 16;
+#ifndef LDPC_MAX_CHUNKS
+#define LDPC_MAX_CHUNKS 32  // e2e 15.4-15.5 (16 chunks) -> 15.9 Gb/s (32) -> 15.6 (48): tools/ab_e2e.sh
+#endif
+constexpr unsigned MAX_CHUNKS = LDPC_MAX_CHUNKS;
 static_assert(sizeof(DemodJob) == sizeof(ldpc_cuda_demod_desc) && sizeof(DemodJob) == 32, "DemodJob mirrors the ABI struct");
 static_assert(sizeof(TbResult) == sizeof(ldpc_cuda_tb_result) && sizeof(ldpc_cuda_tb_result) == 8, "TbResult mirrors the ABI struct");
 
