@@ -519,11 +519,13 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     const int8_t* inA = p.llr_base + wA.in_offset;
     const int8_t* inB = p.llr_base + wB.in_offset;
     unsigned lastA = 0, lastB = 0;
+    // int8 pair -> half2 without conversion instructions: byte ^ 0x80 under a 0x64 high byte is the fp16 number
+    // 1024 + (value + 128); |value| > 120 (the "infinite" LLR +-127, log_likelihood_ratio.h:239) becomes +-inf.
     auto convert = [](int a, int b) {
-      float fa = (float)a, fb = (float)b;
-      fa = (a > LLR_MAX) ? __int_as_float(0x7f800000) : ((a < -LLR_MAX) ? __int_as_float(0xff800000) : fa);
-      fb = (b > LLR_MAX) ? __int_as_float(0x7f800000) : ((b < -LLR_MAX) ? __int_as_float(0xff800000) : fb);
-      return tm::un(__floats2half2_rn(fa, fb));
+      const unsigned w = (__byte_perm((unsigned)a, (unsigned)b, 0x0400) & 0x00ff00ffu) ^ 0x64806480u;
+      const unsigned v = tm::hadd(w, tm::hc(-1152.f));
+      const unsigned m = __hgt2_mask(__habs2(tm::h2(v)), tm::h2(tm::hc(120.f)));
+      return (v & (~m | tm::SIGN2)) | (m & 0x7c007c00u);
     };
     auto put = [&](int n, unsigned v) {
       if (n < HRR) {
