@@ -77,42 +77,101 @@ __device__ __forceinline__ float demod_div_const(float a, float b, float rb)
   return __fmaf_rn(__fmaf_rn(-b, q0, a), rb, q0);
 }
 
-// log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip, / range * 120, std::round (half away from zero).
-// RCP = RN(1 / RANGE). Rounding: nearest-even through the 1.5 * 2^23 magic constant (the integer falls out of the
-// mantissa), ties corrected to "away".
+// log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip to +-RANGE, / RANGE * 120, std::round (half away
+// from zero), int8. Every step is odd in the value, so magnitude and sign are carried apart: the magnitude of 4 LLRs is
+// formed here, the sign bits join the scrambling chips in one byte mask (demod_quantize4).
+//   y  = min(|value|, RANGE)                     (= |clipped|; NaN -> 0 like the conversion of the reference's platform)
+//   a  = RN(y / RANGE)                           (Markstein with RCP = RN(1 / RANGE))
+//   b  = RN(a * 120) * 65536 = RN(a * 7864320)   (scaling by a power of two commutes with the rounding)
+//   |q| = floor(b / 65536 + 0.5) = bits 16-22 of RZ(b + 32768 + 2^23): one round-toward-zero addition leaves
+//         floor(b + 32768) in the mantissa (b + 32768 < 2^23, unit in the last place = 1)
+// Returns the bit pattern whose byte 2 is |q| (0..120).
 template <int RANGE>
-__device__ __forceinline__ int demod_quantize(float value)
+__device__ __forceinline__ unsigned demod_qmag(float value)
 {
   constexpr float range_limit = (float)RANGE, rcp = 1.0f / (float)RANGE;
-  float clipped = value;
-  if (fabsf(value) > range_limit) {
-    clipped = copysignf(range_limit, value);
-  }
-  const float x = __fmul_rn(demod_div_const(clipped, range_limit, rcp), 120.0f);
-  const float magic = 12582912.0f;
-  float t = __fadd_rn(x, magic);
-  const float diff = __fsub_rn(x, __fsub_rn(t, magic));
-  if (fabsf(diff) == 0.5f) {
-    t = __fadd_rn(__fadd_rn(x, copysignf(0.5f, x)), magic);
-  }
-  const int i = __float_as_int(t) - 0x4B400000;
-  return (x == x) ? i : 0;  // NaN -> 0, as the conversion of the reference's platform
+  const float y = fminf(fmaxf(fabsf(value), 0.0f), range_limit);  // fmaxf drops a NaN
+  const float b = __fmul_rn(demod_div_const(y, range_limit, rcp), 7864320.0f);
+  return __float_as_uint(__fadd_rz(b, 8421376.0f));
 }
 
-// Per-block copy of the job's interval tables (divergent indices: shared memory instead of the constant cache).
+// byte 0 = 0xff if a < 0 else 0, byte 1 the same for b: prmt with the selector's replicate-sign bit (bit 3 of a nibble),
+// which __byte_perm does not document.
+__device__ __forceinline__ unsigned demod_sign_bytes(float a, float b)
+{
+  unsigned r;
+  asm("prmt.b32 %0, %1, %2, 0x00fb;" : "=r"(r) : "r"(__float_as_uint(a)), "r"(__float_as_uint(b)));
+  return r;
+}
+
+// Four LLR values -> four int8 (byte u = LLR u), descrambled with chip u = bit u of chips4. The bytes whose value is
+// negative XOR whose chip is 1 are negated in two's complement ((v ^ 0xff) + 1 per byte, no carries across bytes; zero
+// stays zero, so the sign of a zero or NaN value does not matter).
+template <int RANGE>
+__device__ __forceinline__ unsigned demod_quantize4(float l0, float l1, float l2, float l3, unsigned chips4)
+{
+  const unsigned u0 = demod_qmag<RANGE>(l0), u1 = demod_qmag<RANGE>(l1), u2 = demod_qmag<RANGE>(l2),
+                 u3 = demod_qmag<RANGE>(l3);
+  // byte 2 of each magnitude word; sign bit of each value replicated over a byte (PRMT selector bit 3)
+  const unsigned mag = __byte_perm(__byte_perm(u0, u1, 0x0062), __byte_perm(u2, u3, 0x0062), 0x5410);
+  const unsigned sgn = __byte_perm(demod_sign_bytes(l0, l1), demod_sign_bytes(l2, l3), 0x5410);
+  const unsigned chip_lsb = ((chips4 & 0xfu) * 0x00204081u) & 0x01010101u;  // bit u -> bit 8 u
+  const unsigned m = sgn ^ (chip_lsb * 0xffu);
+  const unsigned x = mag ^ m, one = m & 0x01010101u;
+  return ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);
+}
+
+// Descrambling of four int8 LLRs that already exist (mod_order 0): same negation, no quantiser.
+__device__ __forceinline__ unsigned demod_negate4(unsigned packed, unsigned chips4)
+{
+  const unsigned one = ((chips4 & 0xfu) * 0x00204081u) & 0x01010101u;
+  const unsigned x = packed ^ (one * 0xffu);
+  return ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);
+}
+
+// Per-block copy of the job's interval tables (divergent indices: shared memory instead of the constant cache);
+// (slope, intercept) pairs: one 8-byte load per LLR, conflict-free (16 entries = 32 banks, equal indices broadcast).
 struct DemodSmem {
-  float slope[4][16];
-  float intercept[4][16];
+  float2 line[4][16];
 };
 
-// (symbols beyond +-1e30 would overflow the quotient; the reference's float -> int conversion is undefined there too)
+// interval_function (demodulation_mapper_intervals.h:36-64) of one axis value for all NB axis bits of 64QAM (NB = 3) /
+// 256QAM (NB = 4): out[2 k] = LLR of axis bit k before quantisation. The NB - 1 coarse bits share interval width and
+// count, so one quotient serves them; the finest bit uses intervals twice as wide (width exactly doubled, so its quotient
+// is half the coarse one and floor(q / 2) = floor(q) >> 1) and half as many.
+// (int)floorf(value / width) + n / 2 of the reference for a width with reciprocal rw, wrapping like its platform: quotients
+// beyond the int range convert to INT_MIN there (interval 0 for every bit). Here the conversion saturates, INT_MAX + n / 2
+// wraps to a negative number and the clamp gives interval 0 as well; an infinite or NaN value leaves the Markstein
+// sequence as NaN, which is sent to INT_MIN explicitly.
+__device__ __forceinline__ int demod_interval_base(float value, float w, float rw, int half)
+{
+  const float q = demod_div_const(value, w, rw);
+  const int i = (q == q) ? __float2int_rd(q) : (int)0x80000000;
+  return (int)((unsigned)i + (unsigned)half);
+}
+
+template <int NB>
+__device__ __forceinline__ void demod_axis(const DemodSmem& tab, float x, float rcp_noise, float* out)
+{
+  constexpr int L = 1 << NB, m = NB - 3;
+  const int ib = demod_interval_base(x, c_demod.width[m][0], c_demod.rcp_width[m][0], L / 2);
+  const int ic = max(0, min(L - 1, ib));
+  const int ifine = max(0, min(L / 2 - 1, ib >> 1));
+#pragma unroll
+  for (int k = 0; k < NB; ++k) {
+    const float2 t = tab.line[k][k == NB - 1 ? ifine : ic];
+    out[2 * k] = __fmul_rn(__fmaf_rn(t.x, x, t.y), rcp_noise);
+  }
+}
+
+// One axis bit (64QAM four-LLR groups, which straddle symbols).
 __device__ __forceinline__ float demod_interval(const DemodSmem& tab, float value, float rcp_noise, int m, int k)
 {
   const int n = c_demod.nof_intervals[m][k];
-  int idx = __float2int_rd(demod_div_const(value, c_demod.width[m][k], c_demod.rcp_width[m][k])) + n / 2;
+  int idx = demod_interval_base(value, c_demod.width[m][k], c_demod.rcp_width[m][k], n / 2);
   idx = max(0, min(n - 1, idx));
-  const float l = __fmaf_rn(tab.slope[k][idx], value, tab.intercept[k][idx]);
-  return __fmul_rn(l, rcp_noise);
+  const float2 t = tab.line[k][idx];
+  return __fmul_rn(__fmaf_rn(t.x, value, t.y), rcp_noise);
 }
 
 // Per-symbol state shared by the LLRs of a symbol.
@@ -122,74 +181,35 @@ struct DemodSym {
   float nv, rcp;  // rcp = RN(1 / nv) when nv > 0, else 0
 };
 
-// LLR j of a job (before descrambling).
-__device__ __forceinline__ int demod_llr(const DemodJob& job, const DemodSmem& tab, unsigned j, DemodSym& cur,
-                                         const float2* __restrict__ sym, const float* __restrict__ noise)
+// LLR j of a 64QAM job before quantisation (the four LLRs of a thread straddle symbols).
+__device__ __forceinline__ float demod_llr_qam64(const DemodSmem& tab, unsigned j, DemodSym& cur,
+                                                 const float2* __restrict__ sym, const float* __restrict__ noise)
 {
-  const unsigned q = job.mod_order;
-  unsigned s, b;
-  switch (q) {
-    case 1: s = j, b = 0; break;
-    case 2: s = j >> 1, b = j & 1u; break;
-    case 4: s = j >> 2, b = j & 3u; break;
-    case 6: s = j / 6u, b = j - 6u * s; break;
-    default: s = j >> 3, b = j & 7u; break;
-  }
+  const unsigned s = j / 6u, b = j - 6u * s;
   if (s != cur.index) {
     cur.index = s;
     cur.z = __ldg(sym + s);
     cur.nv = __ldg(noise + s);
     cur.rcp = (cur.nv > 0) ? __fdiv_rn(1.0f, cur.nv) : 0.0f;
   }
-  const float2 z = cur.z;
-  const float nv = cur.nv;
-  const float x = (b & 1u) ? z.y : z.x;
-  if (q >= 6) {
-    return demod_quantize<20>(demod_interval(tab, x, cur.rcp, q == 8 ? 1 : 0, (int)(b >> 1)));
-  }
-  if (!(nv > 0)) {  // also false for NaN
-    return 0;
-  }
-  if (q == 1) {
-    const float sum = (job.pi2 && (j & 1u)) ? __fadd_rn(z.y, -z.x) : __fadd_rn(z.x, z.y);
-    return demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, sum), nv, cur.rcp));
-  }
-  if (q == 2) {
-    return demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, x), nv, cur.rcp));
-  }
-  float l;
-  if (b < 2) {
-    l = __fmul_rn(c_demod.qam16_gain, x);
-    if (fabsf(x) > c_demod.qam16_threshold) {
-      l = __fsub_rn(__fmul_rn(2.0f, l), copysignf(0.8f, x));
-    }
-  } else {
-    l = __fmaf_rn(-c_demod.qam16_gain, fabsf(x), 0.8f);
-  }
-  return demod_quantize<20>(demod_div(l, nv, cur.rcp));
+  return demod_interval(tab, (b & 1u) ? cur.z.y : cur.z.x, cur.rcp, 0, (int)(b >> 1));
 }
 
-// Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q, before descrambling, one per byte.
-// valid = number of LLRs that exist (1..4). Straight-line per modulation: the symbol, its noise variance and the
-// reciprocal are fetched once.
+// Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q <= 6, descrambled with the low four
+// bits of chips4, one per byte. valid = number of LLRs that exist (1..4); the others come out as 0. Straight-line per
+// modulation: the symbol, its noise variance and the reciprocal are fetched once.
 template <int Q>
 __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodSmem& tab, unsigned j, unsigned valid,
-                                               const float2* __restrict__ sym, const float* __restrict__ noise)
+                                               unsigned chips4, const float2* __restrict__ sym,
+                                               const float* __restrict__ noise)
 {
-  int v[4] = {0, 0, 0, 0};
-  if (Q == 8 || Q == 4) {
-    const unsigned s = (Q == 8) ? (j >> 3) : (j >> 2);
+  float l[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  if (Q == 4) {
+    const unsigned s = j >> 2;
     const float2 z = __ldg(sym + s);
     const float nv = __ldg(noise + s);
-    const bool ok = nv > 0;  // false for NaN
-    const float rcp = ok ? __fdiv_rn(1.0f, nv) : 0.0f;
-    if (Q == 8) {
-      const int k0 = (int)((j >> 1) & 2u);  // axis-bit level of LLRs 0,1; LLRs 2,3 are one level finer
-      v[0] = demod_quantize<20>(demod_interval(tab, z.x, rcp, 1, k0));
-      v[1] = demod_quantize<20>(demod_interval(tab, z.y, rcp, 1, k0));
-      v[2] = demod_quantize<20>(demod_interval(tab, z.x, rcp, 1, k0 + 1));
-      v[3] = demod_quantize<20>(demod_interval(tab, z.y, rcp, 1, k0 + 1));
-    } else if (ok) {
+    if (nv > 0) {  // false for NaN
+      const float rcp = __fdiv_rn(1.0f, nv);
       const float g = c_demod.qam16_gain, th = c_demod.qam16_threshold;
       float l0 = __fmul_rn(g, z.x), l1 = __fmul_rn(g, z.y);
       if (fabsf(z.x) > th) {
@@ -198,12 +218,14 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
       if (fabsf(z.y) > th) {
         l1 = __fsub_rn(__fmul_rn(2.0f, l1), copysignf(0.8f, z.y));
       }
-      v[0] = demod_quantize<20>(demod_div(l0, nv, rcp));
-      v[1] = demod_quantize<20>(demod_div(l1, nv, rcp));
-      v[2] = demod_quantize<20>(demod_div(__fmaf_rn(-g, fabsf(z.x), 0.8f), nv, rcp));
-      v[3] = demod_quantize<20>(demod_div(__fmaf_rn(-g, fabsf(z.y), 0.8f), nv, rcp));
+      l[0] = demod_div(l0, nv, rcp);
+      l[1] = demod_div(l1, nv, rcp);
+      l[2] = demod_div(__fmaf_rn(-g, fabsf(z.x), 0.8f), nv, rcp);
+      l[3] = demod_div(__fmaf_rn(-g, fabsf(z.y), 0.8f), nv, rcp);
     }
-  } else if (Q == 2) {
+    return demod_quantize4<20>(l[0], l[1], l[2], l[3], chips4);
+  }
+  if (Q == 2) {
 #pragma unroll
     for (unsigned h = 0; h < 2; ++h) {
       if (2 * h < valid) {
@@ -211,12 +233,14 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
         const float nv = __ldg(noise + (j >> 1) + h);
         if (nv > 0) {
           const float rcp = __fdiv_rn(1.0f, nv);
-          v[2 * h] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, z.x), nv, rcp));
-          v[2 * h + 1] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, z.y), nv, rcp));
+          l[2 * h] = demod_div(__fmul_rn(DEMOD_2SQRT2, z.x), nv, rcp);
+          l[2 * h + 1] = demod_div(__fmul_rn(DEMOD_2SQRT2, z.y), nv, rcp);
         }
       }
     }
-  } else if (Q == 1) {
+    return demod_quantize4<24>(l[0], l[1], l[2], l[3], chips4);
+  }
+  if (Q == 1) {
 #pragma unroll
     for (unsigned u = 0; u < 4; ++u) {
       if (u < valid) {
@@ -224,22 +248,39 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
         const float nv = __ldg(noise + j + u);
         if (nv > 0) {
           const float sum = (job.pi2 && (u & 1u)) ? __fadd_rn(z.y, -z.x) : __fadd_rn(z.x, z.y);
-          v[u] = demod_quantize<24>(demod_div(__fmul_rn(DEMOD_2SQRT2, sum), nv, __fdiv_rn(1.0f, nv)));
+          l[u] = demod_div(__fmul_rn(DEMOD_2SQRT2, sum), nv, __fdiv_rn(1.0f, nv));
         }
       }
     }
-  } else {  // 64QAM: the four LLRs straddle symbols
-    DemodSym cur;
-    cur.index = 0xffffffffu;
+    return demod_quantize4<24>(l[0], l[1], l[2], l[3], chips4);
+  }
+  // 64QAM
+  DemodSym cur;
+  cur.index = 0xffffffffu;
 #pragma unroll
-    for (unsigned u = 0; u < 4; ++u) {
-      if (u < valid) {
-        v[u] = demod_llr(job, tab, j + u, cur, sym, noise);
-      }
+  for (unsigned u = 0; u < 4; ++u) {
+    if (u < valid) {
+      l[u] = demod_llr_qam64(tab, j + u, cur, sym, noise);
     }
   }
-  return ((unsigned)v[0] & 0xffu) | (((unsigned)v[1] & 0xffu) << 8) | (((unsigned)v[2] & 0xffu) << 16) |
-         (((unsigned)v[3] & 0xffu) << 24);
+  return demod_quantize4<20>(l[0], l[1], l[2], l[3], chips4);
+}
+
+// The eight LLRs of 256QAM symbol s (demodulation_mapper_qam256.cpp:279-350: LLR 2 k = axis bit k of the real part,
+// LLR 2 k + 1 of the imaginary part), descrambled with the low eight bits of chips8.
+__device__ __forceinline__ uint2 demod_symbol_qam256(const DemodSmem& tab, unsigned s, unsigned chips8,
+                                                     const float2* __restrict__ sym, const float* __restrict__ noise)
+{
+  const float2 z = __ldg(sym + s);
+  const float nv = __ldg(noise + s);
+  const float rcp = (nv > 0) ? __fdiv_rn(1.0f, nv) : 0.0f;  // not > 0 covers NaN
+  float l[8];
+  demod_axis<4>(tab, z.x, rcp, l);
+  demod_axis<4>(tab, z.y, rcp, l + 1);
+  uint2 r;
+  r.x = demod_quantize4<20>(l[0], l[1], l[2], l[3], chips8);
+  r.y = demod_quantize4<20>(l[4], l[5], l[6], l[7], chips8 >> 4);
+  return r;
 }
 
 // x1 / x2 advanced by k <= 28 chips: the 28 new bits x(n+31..n+58) follow from the state in one step.
@@ -267,8 +308,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   __shared__ DemodSmem tab;
   if (job.mod_order >= 6 && t < 64) {
     const int m = job.mod_order == 8 ? 1 : 0;
-    tab.slope[t >> 4][t & 15] = c_demod.slope[m][t >> 4][t & 15];
-    tab.intercept[t >> 4][t & 15] = c_demod.intercept[m][t >> 4][t & 15];
+    tab.line[t >> 4][t & 15] = make_float2(c_demod.slope[m][t >> 4][t & 15], c_demod.intercept[m][t >> 4][t & 15]);
   }
   if (job.descramble) {
     // state of both registers at chip 1600 + first chip of the warp (Nc = 1600, TS 38.211 5.2.1)
@@ -313,7 +353,34 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   const float* noise = noise_vars + job.sym_offset;
   const int8_t* in = in_llrs + job.sym_offset;
   int8_t* dst = out + job.llr_offset;
-  const bool aligned = ((reinterpret_cast<unsigned long long>(dst) & 3ull) == 0);
+  const unsigned long long dst_bits = reinterpret_cast<unsigned long long>(dst);
+  if (job.mod_order == 8) {
+    // one symbol = 8 LLRs = one 8-byte store per thread and step (nof_llrs is a multiple of 8)
+#pragma unroll 1
+    for (unsigned it = 0; it < 32u / 8u; ++it) {
+      const unsigned local = 8u * (it * DEMOD_THREADS + t);
+      const unsigned j = j0 + local;
+      if (j >= job.nof_llrs) {
+        break;
+      }
+      const unsigned cw = job.descramble ? (chips[local >> 5] >> (local & 31u)) : 0u;
+      const uint2 w = demod_symbol_qam256(tab, j >> 3, cw, sym, noise);
+      if ((dst_bits & 7ull) == 0) {
+        *reinterpret_cast<uint2*>(dst + j) = w;
+      } else if ((dst_bits & 3ull) == 0) {
+        reinterpret_cast<unsigned*>(dst + j)[0] = w.x;
+        reinterpret_cast<unsigned*>(dst + j)[1] = w.y;
+      } else {
+        for (unsigned u = 0; u < 4; ++u) {
+          dst[j + u] = (int8_t)(w.x >> (8u * u));
+          dst[j + 4 + u] = (int8_t)(w.y >> (8u * u));
+        }
+      }
+    }
+    return;
+  }
+  const bool aligned = ((dst_bits & 3ull) == 0);
+  const bool in_aligned = ((reinterpret_cast<unsigned long long>(in) & 3ull) == 0);
 #pragma unroll 1
   for (unsigned it = 0; it < 32u / 4u; ++it) {
     const unsigned local = 4u * (it * DEMOD_THREADS + t);  // first of this thread's 4 LLRs inside the chunk
@@ -325,26 +392,25 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
     const unsigned valid = min(4u, job.nof_llrs - j);
     unsigned packed;
     switch (job.mod_order) {  // uniform over the block
-      case 8: packed = demod_four<8>(job, tab, j, valid, sym, noise); break;
-      case 6: packed = demod_four<6>(job, tab, j, valid, sym, noise); break;
-      case 4: packed = demod_four<4>(job, tab, j, valid, sym, noise); break;
-      case 2: packed = demod_four<2>(job, tab, j, valid, sym, noise); break;
-      case 1: packed = demod_four<1>(job, tab, j, valid, sym, noise); break;
+      case 6: packed = demod_four<6>(job, tab, j, valid, cw, sym, noise); break;
+      case 4: packed = demod_four<4>(job, tab, j, valid, cw, sym, noise); break;
+      case 2: packed = demod_four<2>(job, tab, j, valid, cw, sym, noise); break;
+      case 1: packed = demod_four<1>(job, tab, j, valid, cw, sym, noise); break;
       default:
         packed = 0;
-        for (unsigned u = 0; u < valid; ++u) {
-          packed |= ((unsigned)in[j + u] & 0xffu) << (8u * u);
+        if (in_aligned && valid == 4) {
+          packed = *reinterpret_cast<const unsigned*>(in + j);
+        } else {
+          for (unsigned u = 0; u < valid; ++u) {
+            packed |= ((unsigned)in[j + u] & 0xffu) << (8u * u);
+          }
         }
+        packed = demod_negate4(packed, cw);
     }
-    // descrambling: two's complement negation of the bytes whose chip is 1 (per byte: (v ^ 0xff) + 1)
-    const unsigned m = (cw & 1u) * 0xffu | ((cw >> 1) & 1u) * 0xff00u | ((cw >> 2) & 1u) * 0xff0000u |
-                       ((cw >> 3) & 1u) * 0xff000000u;
-    const unsigned x = packed ^ m, one = m & 0x01010101u;
-    packed = ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);  // byte-wise x + one without carries across bytes
-    if (aligned && j + 3 < job.nof_llrs) {
+    if (aligned && valid == 4) {
       *reinterpret_cast<unsigned*>(dst + j) = packed;
     } else {
-      for (unsigned u = 0; u < 4 && j + u < job.nof_llrs; ++u) {
+      for (unsigned u = 0; u < valid; ++u) {
         dst[j + u] = (int8_t)(packed >> (8u * u));
       }
     }

@@ -36,6 +36,44 @@ def test_demodulate_soft_bit_exact(dec, mod_order, pi2):
             assert diff.max() <= 1 and (diff != 0).mean() < 1e-3
 
 
+def _tie_inputs(rng, count=64):
+    """QPSK axis values x (noise variance 1) whose quantiser input RN(RN(l / 24) * 120), l = RN(2 sqrt2 x), lands exactly on
+    k + 0.5: std::round goes away from zero there, round-to-nearest-even does not."""
+    c = np.float32(2.0) * np.float32(1.41421356237309504880)
+    found = []
+    while sum(f.size for f in found) < count:
+        x = rng.uniform(-9.0, 9.0, 4_000_000).astype(np.float32)
+        b = (c * x / np.float32(24.0)) * np.float32(120.0)
+        assert b.dtype == np.float32
+        found.append(x[(np.abs(b) < 120) & (np.abs(b) * 2 % 2 == 1)])
+    return np.concatenate(found)[:count]
+
+
+@pytest.mark.parametrize("mod_order", [1, 2, 4, 6, 8])
+def test_demodulate_soft_special_values(dec, mod_order):
+    """Rounding ties, signed zeros, subnormals, far outliers, infinities and NaN in the symbols; zero, negative,
+    subnormal, huge, infinite and NaN noise variances (log_likelihood_ratio.cpp:87-96 clip + round, the nv <= 0 branches
+    of demodulation_mapper_*.cpp). Bit-exact with the oracle port on the same platform."""
+    rng = np.random.default_rng(900 + mod_order)
+    ties = _tie_inputs(rng)
+    vals = np.concatenate([ties, -ties, np.float32([0.0, -0.0, 1e-45, -1e-45, 1e-39, -3e-39, 1e-30, 0.5, -0.5, 1.0, 3.25,
+                                                    -77.0, 1e4, -1e4, 1e7, -1e7, np.inf, -np.inf, np.nan]),
+                           (rng.integers(-16, 17, 200) / np.sqrt(O.MOD_NORM[mod_order])).astype(np.float32),  # boundaries
+                           rng.normal(0, 1, 300).astype(np.float32)])
+    nvs = np.float32([1.0, 0.0, -0.0, -1.0, 1e-45, 1e-39, 1e-20, 0.01, 3.0, 1e20, 3e38, np.inf, np.nan])
+    re = np.repeat(vals, nvs.size)
+    nv = np.tile(nvs, vals.size)
+    im = rng.permutation(re)
+    for a, b in ((re, im), (im, re), (re, np.zeros_like(re))):
+        sym = np.empty(a.size, np.complex64)
+        sym.real, sym.imag = a, b
+        with np.errstate(all="ignore"):
+            want = O.port().demodulate_soft(mod_order, sym, nv)
+        got = dec.demodulate_soft(mod_order, sym, nv)
+        bad = np.flatnonzero(got != want)
+        assert bad.size == 0, (bad[:8], got[bad[:8]], want[bad[:8]])
+
+
 @pytest.mark.parametrize("c_init,n", [(0, 1), (1, 31), (0x7fffffff, 33), ((0x4601 << 15) + 935, 100001),
                                       (0x12345678, 8192), (77, 8193), ((0xffff << 15) + 1023, 1362816)])
 def test_descramble_bit_exact(dec, c_init, n):
