@@ -542,6 +542,7 @@ int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, c
     return LDPC_CUDA_ERR_CAPACITY;
   }
   unsigned max_chunks = 0;
+  uint64_t total_chunks = 0;
   for (uint32_t i = 0; i != nof_jobs; ++i) {
     const ldpc_cuda_demod_desc& j = jobs[i];
     const bool mod_ok = j.mod_order == 0 || j.mod_order == 1 || j.mod_order == 2 || j.mod_order == 4 || j.mod_order == 6 ||
@@ -552,10 +553,18 @@ int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, c
       return LDPC_CUDA_ERR_ARG;
     }
     max_chunks = std::max(max_chunks, (unsigned)((nllr + DEMOD_CHUNK - 1) / DEMOD_CHUNK));
+    total_chunks += (nllr + DEMOD_CHUNK - 1) / DEMOD_CHUNK;
   }
   if (max_chunks == 0) {
     return LDPC_CUDA_OK;
   }
+  // Spans of 8192 LLRs per block: more of them amortise the scrambler's jump-ahead, fewer keep a small launch spread over
+  // the SMs (8 resident blocks each).
+  unsigned spans = DEMOD_MAX_SPANS;
+  while (spans > 1 && total_chunks / spans < 8u * (unsigned)h->sm_count) {
+    spans /= 2;
+  }
+  max_chunks = (max_chunks + spans - 1) / spans;
   const size_t bytes = sizeof(DemodJob) * nof_jobs;
   const unsigned slot = (h->demod_slot++) & 1u;
   if (h->ev_demod[slot] == nullptr) {
@@ -598,7 +607,7 @@ int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, c
   const dim3 grid(max_chunks, nof_jobs);
   ldpc_demod_kernel<<<grid, DEMOD_THREADS, 0, stream>>>(reinterpret_cast<const DemodJob*>(h->d_demod),
                                                          reinterpret_cast<const float2*>(d_symbols), d_noise, d_in_llrs,
-                                                         d_out);
+                                                         d_out, spans);
   CUDA_TRY(cudaGetLastError());
   h->launches += 1;
   return LDPC_CUDA_OK;

@@ -56,7 +56,8 @@ __constant__ DemodTables c_demod;
 __device__ unsigned g_prg_pow[2][32][32];
 
 constexpr int DEMOD_THREADS = 256;
-constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block
+constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
+constexpr int DEMOD_MAX_SPANS = 4;               // spans per block: the launch picks 1, 2 or 4 from the amount of work
 constexpr float DEMOD_2SQRT2 = 2.0f * 1.41421356237309504880f;
 
 // a / b correctly rounded with rb = RN(1 / b) (Markstein: q0 = RN(a rb), r = a - b q0 exactly, q = RN(q0 + r rb)), without
@@ -296,23 +297,26 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
                                                                    const float2* __restrict__ symbols,
                                                                    const float* __restrict__ noise_vars,
                                                                    const int8_t* __restrict__ in_llrs,
-                                                                   int8_t* __restrict__ out)
+                                                                   int8_t* __restrict__ out, unsigned spans)
 {
   const DemodJob job = jobs[blockIdx.y];
-  const unsigned j0 = blockIdx.x * DEMOD_CHUNK;
+  const unsigned chunk = DEMOD_CHUNK * spans;  // LLRs of this block: spans (1..DEMOD_MAX_SPANS) x 1024 per warp
+  const unsigned j0 = blockIdx.x * chunk;
   if (j0 >= job.nof_llrs) {
     return;
   }
   const unsigned t = threadIdx.x, lane = t & 31u;
-  __shared__ unsigned chips[DEMOD_THREADS];
+  __shared__ unsigned chips[DEMOD_THREADS * DEMOD_MAX_SPANS];
   __shared__ DemodSmem tab;
   if (job.mod_order >= 6 && t < 64) {
     const int m = job.mod_order == 8 ? 1 : 0;
     tab.line[t >> 4][t & 15] = make_float2(c_demod.slope[m][t >> 4][t & 15], c_demod.intercept[m][t >> 4][t & 15]);
   }
   if (job.descramble) {
-    // state of both registers at chip 1600 + first chip of the warp (Nc = 1600, TS 38.211 5.2.1)
-    const unsigned n = 1600u + j0 + (t & ~31u) * 32u;
+    // A warp owns spans x 1024 consecutive chips. State of both registers at chip 1600 + first chip of the warp
+    // (Nc = 1600, TS 38.211 5.2.1):
+    const unsigned first = (t >> 5) * 1024u * spans;
+    const unsigned n = 1600u + j0 + first;
     unsigned s1 = 1u, s2 = job.c_init & 0x7fffffffu;
     for (unsigned jb = 0; jb < 32; ++jb) {
       if ((n >> jb) & 1u) {
@@ -324,29 +328,29 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
     // Lane L needs the state 32 L chips further. Groups of 4 lanes: the start of group g follows from the start of group
     // g - 1 by one more co-operative product with A^128 (its rows stay in registers); inside a group a lane advances by
     // 0, 32, 64 or 96 chips in steps of 28. (Advancing every lane on its own from the warp's start took up to 36 steps
-    // and was a third of the kernel's instructions: profiles/r01_ncu_demod_summary.txt.)
-    {
-      const unsigned q1 = g_prg_pow[0][7][lane], q2 = g_prg_pow[1][7][lane];
+    // and was a third of the kernel's instructions: profiles/r01_ncu_demod_summary.txt.) The eighth product is the start
+    // of the warp's next span of 1024 chips, so the jump above is paid once per spans x 1024 chips.
+    const unsigned q1 = g_prg_pow[0][7][lane], q2 = g_prg_pow[1][7][lane];
+    const unsigned ahead = 32u * (lane & 3u), full = ahead / 28u, rest = ahead - 28u * full;
+    for (unsigned c = 0; c < spans && j0 + first + 1024u * c < job.nof_llrs; ++c) {
       unsigned m1 = s1, m2 = s2;
 #pragma unroll
-      for (unsigned g = 1; g < 8; ++g) {
+      for (unsigned g = 1; g <= 8; ++g) {
         s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
         s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
         if ((lane >> 2) == g) {
           m1 = s1, m2 = s2;
         }
       }
-      s1 = m1, s2 = m2;
+      for (unsigned i = 0; i < full; ++i) {
+        m1 = ((m1 >> 28) | (((m1 >> 3) ^ m1) << 3)) & 0x7fffffffu;
+        m2 = ((m2 >> 28) | (((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) << 3)) & 0x7fffffffu;
+      }
+      m1 = prg_advance(m1, rest, false);
+      m2 = prg_advance(m2, rest, true);
+      const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
+      chips[(t >> 5) * 32u * spans + 32u * c + lane] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
     }
-    const unsigned ahead = 32u * (lane & 3u), full = ahead / 28u, rest = ahead - 28u * full;
-    for (unsigned i = 0; i < full; ++i) {
-      s1 = ((s1 >> 28) | (((s1 >> 3) ^ s1) << 3)) & 0x7fffffffu;
-      s2 = ((s2 >> 28) | (((s2 >> 3) ^ (s2 >> 2) ^ (s2 >> 1) ^ s2) << 3)) & 0x7fffffffu;
-    }
-    s1 = prg_advance(s1, rest, false);
-    s2 = prg_advance(s2, rest, true);
-    const unsigned b1 = ((s1 >> 3) ^ s1) & 1u, b2 = ((s2 >> 3) ^ (s2 >> 2) ^ (s2 >> 1) ^ s2) & 1u;
-    chips[t] = (s1 ^ s2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
   }
   __syncthreads();
   const float2* sym = symbols + job.sym_offset;
@@ -357,7 +361,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   if (job.mod_order == 8) {
     // one symbol = 8 LLRs = one 8-byte store per thread and step (nof_llrs is a multiple of 8)
 #pragma unroll 1
-    for (unsigned it = 0; it < 32u / 8u; ++it) {
+    for (unsigned it = 0; it < spans * (32u / 8u); ++it) {
       const unsigned local = 8u * (it * DEMOD_THREADS + t);
       const unsigned j = j0 + local;
       if (j >= job.nof_llrs) {
@@ -382,7 +386,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   const bool aligned = ((dst_bits & 3ull) == 0);
   const bool in_aligned = ((reinterpret_cast<unsigned long long>(in) & 3ull) == 0);
 #pragma unroll 1
-  for (unsigned it = 0; it < 32u / 4u; ++it) {
+  for (unsigned it = 0; it < spans * (32u / 4u); ++it) {
     const unsigned local = 4u * (it * DEMOD_THREADS + t);  // first of this thread's 4 LLRs inside the chunk
     const unsigned j = j0 + local;
     if (j >= job.nof_llrs) {

@@ -128,6 +128,49 @@ def test_demodulate_batch_device_heterogeneous_jobs(dec):
     assert (out[end:] == 0x55).all()
 
 
+@pytest.mark.parametrize("nof_jobs", [40, 80])
+def test_demodulate_batch_device_many_jobs(dec, nof_jobs):
+    """Launches large enough for 2 and 4 spans of 8192 LLRs per block (the scrambler's jump-ahead is then paid once per
+    warp and 2048 / 4096 chips): ragged lengths, every modulation, a different c_init per job."""
+    import torch
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(40 + nof_jobs)
+    nsym = 110003
+    base = {}
+    for q in (1, 2, 4, 6, 8):
+        sym, nv = O.random_symbols(rng, q, nsym, 0.02)
+        base[q] = (sym, nv, O.port().demodulate_soft(q, sym, nv))
+    in_llrs = rng.integers(-127, 128, nsym).astype(np.int8)
+    order = [8, 8, 8, 6, 8, 4, 8, 2, 8, 1, 8, 0]
+    sym_all = np.concatenate([base[q][0] for q in (1, 2, 4, 6, 8)])
+    nv_all = np.concatenate([base[q][1] for q in (1, 2, 4, 6, 8)])
+    sym_off = {q: i * nsym for i, q in enumerate((1, 2, 4, 6, 8))}
+    jobs = np.zeros(nof_jobs, pkg.DEMOD_DESC)
+    want, lo = [], 0
+    for i in range(nof_jobs):
+        q = order[i % len(order)]
+        n = nsym - 97 * (i % 5)  # ragged: the last block of a job ends inside a span
+        j = jobs[i]
+        j["mod_order"], j["descramble"], j["nof_symbols"], j["c_init"] = q, 1, n, (0x1357 * (i + 1)) & 0x7fffffff
+        j["symbol_offset"] = sym_off[q] if q else 0
+        j["llr_offset"] = lo
+        w = base[q][2][:n * q] if q else in_llrs[:n]
+        want.append((lo, O.port().descramble(int(j["c_init"]), w)))
+        lo += (w.size + 15) // 8 * 8
+    sym_d = torch.from_numpy(sym_all.view(np.float32)).to(dev)
+    nv_d = torch.from_numpy(nv_all).to(dev)
+    in_d = torch.from_numpy(in_llrs).to(dev)
+    out_d = torch.full((lo,), 0x55, dtype=torch.int8, device=dev)
+    torch.cuda.synchronize()
+    dec.demodulate_batch_device(jobs, sym_d.data_ptr(), nv_d.data_ptr(), in_d.data_ptr(), out_d.data_ptr())
+    dec.synchronize()
+    out = out_d.cpu().numpy()
+    for i, (off, w) in enumerate(want):
+        bad = np.flatnonzero(out[off:off + w.size] != w)
+        assert bad.size == 0, (i, int(jobs[i]["mod_order"]), bad[:8])
+        assert (out[off + w.size:(off + w.size + 15) // 8 * 8] == 0x55).all()
+
+
 QAM_BITS = {2: 1, 4: 2, 6: 3, 8: 4}
 
 
