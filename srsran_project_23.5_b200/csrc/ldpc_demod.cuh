@@ -57,6 +57,7 @@ __device__ unsigned g_prg_pow[2][32][32];
 
 constexpr int DEMOD_THREADS = 256;
 constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
+constexpr unsigned DEMOD_QAM256_BATCH = 2;        // divides 32 / 8 steps per span
 constexpr int DEMOD_MAX_SPANS = 4;               // spans per block: the launch picks 1, 2 or 4 from the amount of work
 constexpr float DEMOD_2SQRT2 = 2.0f * 1.41421356237309504880f;
 
@@ -81,19 +82,22 @@ __device__ __forceinline__ float demod_div_const(float a, float b, float rb)
 // log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip to +-RANGE, / RANGE * 120, std::round (half away
 // from zero), int8. Every step is odd in the value, so magnitude and sign are carried apart: the magnitude of 4 LLRs is
 // formed here, the sign bits join the scrambling chips in one byte mask (demod_quantize4).
-//   y  = min(|value|, RANGE)                     (= |clipped|; NaN -> 0 like the conversion of the reference's platform)
-//   a  = RN(y / RANGE)                           (Markstein with RCP = RN(1 / RANGE))
-//   b  = RN(a * 120) * 65536 = RN(a * 7864320)   (scaling by a power of two commutes with the rounding)
-//   |q| = floor(b / 65536 + 0.5) = bits 16-22 of RZ(b + 32768 + 2^23): one round-toward-zero addition leaves
-//         floor(b + 32768) in the mantissa (b + 32768 < 2^23, unit in the last place = 1)
-// Returns the bit pattern whose byte 2 is |q| (0..120).
-template <int RANGE>
+//   y  = min(|value|, RANGE)                      (= |clipped|)
+//   a  = RN(y / RANGE)                            (Markstein with RCP = RN(1 / RANGE))
+//   b  = RN(a * 120) * 2^17 = RN(a * 15728640)    (scaling by a power of two commutes with the rounding)
+//   |q| = floor(b / 2^17 + 0.5) = bits 16-22 of RZ(b + 2^16 + 2^24): the sum lies in [2^24, 2^25), unit in the last place
+//         2, so one round-toward-zero addition leaves floor((b + 2^16) / 2) in the mantissa
+// Returns the bit pattern whose byte 2 is 0x80 | |q| (|q| = 0..120; bit 7 is the odd exponent's last bit and serves as a
+// guard bit for the byte-wise negation below).
+// NANSAFE: a NaN value gives |q| = 0 like the float -> int conversion of the reference's platform (fmaxf drops the NaN);
+// without it a NaN would come out as 120, so the caller must know the value is not NaN.
+template <int RANGE, bool NANSAFE>
 __device__ __forceinline__ unsigned demod_qmag(float value)
 {
   constexpr float range_limit = (float)RANGE, rcp = 1.0f / (float)RANGE;
-  const float y = fminf(fmaxf(fabsf(value), 0.0f), range_limit);  // fmaxf drops a NaN
-  const float b = __fmul_rn(demod_div_const(y, range_limit, rcp), 7864320.0f);
-  return __float_as_uint(__fadd_rz(b, 8421376.0f));
+  const float y = NANSAFE ? fminf(fmaxf(fabsf(value), 0.0f), range_limit) : fminf(fabsf(value), range_limit);
+  const float b = __fmul_rn(demod_div_const(y, range_limit, rcp), 15728640.0f);
+  return __float_as_uint(__fadd_rz(b, 16842752.0f));
 }
 
 // byte 0 = 0xff if a < 0 else 0, byte 1 the same for b: prmt with the selector's replicate-sign bit (bit 3 of a nibble),
@@ -105,73 +109,76 @@ __device__ __forceinline__ unsigned demod_sign_bytes(float a, float b)
   return r;
 }
 
+// bit u of chips4 -> bit 8 u (u = 0..3)
+__device__ __forceinline__ unsigned demod_chip_lsb(unsigned chips4) { return ((chips4 & 0xfu) * 0x00204081u) & 0x01010101u; }
+
 // Four LLR values -> four int8 (byte u = LLR u), descrambled with chip u = bit u of chips4. The bytes whose value is
-// negative XOR whose chip is 1 are negated in two's complement ((v ^ 0xff) + 1 per byte, no carries across bytes; zero
-// stays zero, so the sign of a zero or NaN value does not matter).
-template <int RANGE>
+// negative XOR whose chip is 1 are negated in two's complement; zero stays zero, so the sign of a zero or NaN value does
+// not matter. Per byte, with g = 0x80 | |q| and n = 1 where the byte is negated: g - n never borrows from the next byte
+// (g >= 0x80); XOR with 0x7f where negated (0x80 + |q| - 1 -> 0x100 - |q|, and 0x7f -> 0 for |q| = 0), with 0x80 where kept.
+template <int RANGE, bool NANSAFE>
 __device__ __forceinline__ unsigned demod_quantize4(float l0, float l1, float l2, float l3, unsigned chips4)
 {
-  const unsigned u0 = demod_qmag<RANGE>(l0), u1 = demod_qmag<RANGE>(l1), u2 = demod_qmag<RANGE>(l2),
-                 u3 = demod_qmag<RANGE>(l3);
+  const unsigned u0 = demod_qmag<RANGE, NANSAFE>(l0), u1 = demod_qmag<RANGE, NANSAFE>(l1),
+                 u2 = demod_qmag<RANGE, NANSAFE>(l2), u3 = demod_qmag<RANGE, NANSAFE>(l3);
   // byte 2 of each magnitude word; sign bit of each value replicated over a byte (PRMT selector bit 3)
   const unsigned mag = __byte_perm(__byte_perm(u0, u1, 0x0062), __byte_perm(u2, u3, 0x0062), 0x5410);
   const unsigned sgn = __byte_perm(demod_sign_bytes(l0, l1), demod_sign_bytes(l2, l3), 0x5410);
-  const unsigned chip_lsb = ((chips4 & 0xfu) * 0x00204081u) & 0x01010101u;  // bit u -> bit 8 u
+  const unsigned chip_lsb = demod_chip_lsb(chips4);
   const unsigned m = sgn ^ (chip_lsb * 0xffu);
-  const unsigned x = mag ^ m, one = m & 0x01010101u;
-  return ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);
+  const unsigned one = (sgn & 0x01010101u) ^ chip_lsb;
+  return (mag - one) ^ m ^ 0x80808080u;
 }
 
-// Descrambling of four int8 LLRs that already exist (mod_order 0): same negation, no quantiser.
+// Descrambling of four int8 LLRs that already exist (mod_order 0; any byte value): (v ^ 0xff) + 1 per byte without
+// carries across bytes.
 __device__ __forceinline__ unsigned demod_negate4(unsigned packed, unsigned chips4)
 {
-  const unsigned one = ((chips4 & 0xfu) * 0x00204081u) & 0x01010101u;
+  const unsigned one = demod_chip_lsb(chips4);
   const unsigned x = packed ^ (one * 0xffu);
   return ((x & 0x7f7f7f7fu) + one) ^ (x & 0x80808080u);
 }
 
 // Per-block copy of the job's interval tables (divergent indices: shared memory instead of the constant cache);
 // (slope, intercept) pairs: one 8-byte load per LLR, conflict-free (16 entries = 32 banks, equal indices broadcast).
+// Every axis bit is indexed with the interval of the COARSE bits: the finest bit of the reference uses intervals exactly
+// twice as wide and half as many (quotient halved exactly, floor(q / 2) = floor(q) >> 1, clamp(i, 0, L - 1) >> 1 =
+// clamp(i >> 1, 0, L / 2 - 1)), so its line holds every entry twice.
 struct DemodSmem {
   float2 line[4][16];
 };
 
-// interval_function (demodulation_mapper_intervals.h:36-64) of one axis value for all NB axis bits of 64QAM (NB = 3) /
-// 256QAM (NB = 4): out[2 k] = LLR of axis bit k before quantisation. The NB - 1 coarse bits share interval width and
-// count, so one quotient serves them; the finest bit uses intervals twice as wide (width exactly doubled, so its quotient
-// is half the coarse one and floor(q / 2) = floor(q) >> 1) and half as many.
-// (int)floorf(value / width) + n / 2 of the reference for a width with reciprocal rw, wrapping like its platform: quotients
-// beyond the int range convert to INT_MIN there (interval 0 for every bit). Here the conversion saturates, INT_MAX + n / 2
-// wraps to a negative number and the clamp gives interval 0 as well; an infinite or NaN value leaves the Markstein
-// sequence as NaN, which is sent to INT_MIN explicitly.
-__device__ __forceinline__ int demod_interval_base(float value, float w, float rw, int half)
-{
-  const float q = demod_div_const(value, w, rw);
-  const int i = (q == q) ? __float2int_rd(q) : (int)0x80000000;
-  return (int)((unsigned)i + (unsigned)half);
-}
-
-template <int NB>
-__device__ __forceinline__ void demod_axis(const DemodSmem& tab, float x, float rcp_noise, float* out)
+// (int)floorf(value / width) + L / 2 of the reference (demodulation_mapper_intervals.h:36-64) for the coarse width,
+// clamped to 0 .. L - 1, wrapping like the reference's platform: quotients beyond the int range convert to INT_MIN there
+// (interval 0 for every bit). Here the conversion saturates, INT_MAX + L / 2 wraps to a negative number and the clamp
+// gives interval 0 as well; an infinite or NaN value leaves the Markstein sequence as NaN, which is sent to INT_MIN
+// explicitly unless the caller knows the value is finite (FINITE).
+template <int NB, bool FINITE>
+__device__ __forceinline__ int demod_interval_index(float value)
 {
   constexpr int L = 1 << NB, m = NB - 3;
-  const int ib = demod_interval_base(x, c_demod.width[m][0], c_demod.rcp_width[m][0], L / 2);
-  const int ic = max(0, min(L - 1, ib));
-  const int ifine = max(0, min(L / 2 - 1, ib >> 1));
+  const float q = demod_div_const(value, c_demod.width[m][0], c_demod.rcp_width[m][0]);
+  const int i = (FINITE || q == q) ? __float2int_rd(q) : (int)0x80000000;
+  return max(0, min(L - 1, (int)((unsigned)i + (unsigned)(L / 2))));
+}
+
+// interval_function of one axis value for all NB axis bits of 64QAM (NB = 3) / 256QAM (NB = 4): out[2 k] = LLR of axis
+// bit k before quantisation.
+template <int NB, bool FINITE>
+__device__ __forceinline__ void demod_axis(const DemodSmem& tab, float x, float rcp_noise, float* out)
+{
+  const int ic = demod_interval_index<NB, FINITE>(x);
 #pragma unroll
   for (int k = 0; k < NB; ++k) {
-    const float2 t = tab.line[k][k == NB - 1 ? ifine : ic];
+    const float2 t = tab.line[k][ic];
     out[2 * k] = __fmul_rn(__fmaf_rn(t.x, x, t.y), rcp_noise);
   }
 }
 
-// One axis bit (64QAM four-LLR groups, which straddle symbols).
-__device__ __forceinline__ float demod_interval(const DemodSmem& tab, float value, float rcp_noise, int m, int k)
+// One axis bit of 64QAM (its four-LLR groups straddle symbols).
+__device__ __forceinline__ float demod_interval_qam64(const DemodSmem& tab, float value, float rcp_noise, int k)
 {
-  const int n = c_demod.nof_intervals[m][k];
-  int idx = demod_interval_base(value, c_demod.width[m][k], c_demod.rcp_width[m][k], n / 2);
-  idx = max(0, min(n - 1, idx));
-  const float2 t = tab.line[k][idx];
+  const float2 t = tab.line[k][demod_interval_index<3, false>(value)];
   return __fmul_rn(__fmaf_rn(t.x, value, t.y), rcp_noise);
 }
 
@@ -193,7 +200,7 @@ __device__ __forceinline__ float demod_llr_qam64(const DemodSmem& tab, unsigned 
     cur.nv = __ldg(noise + s);
     cur.rcp = (cur.nv > 0) ? __fdiv_rn(1.0f, cur.nv) : 0.0f;
   }
-  return demod_interval(tab, (b & 1u) ? cur.z.y : cur.z.x, cur.rcp, 0, (int)(b >> 1));
+  return demod_interval_qam64(tab, (b & 1u) ? cur.z.y : cur.z.x, cur.rcp, (int)(b >> 1));
 }
 
 // Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q <= 6, descrambled with the low four
@@ -224,7 +231,7 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
       l[2] = demod_div(__fmaf_rn(-g, fabsf(z.x), 0.8f), nv, rcp);
       l[3] = demod_div(__fmaf_rn(-g, fabsf(z.y), 0.8f), nv, rcp);
     }
-    return demod_quantize4<20>(l[0], l[1], l[2], l[3], chips4);
+    return demod_quantize4<20, true>(l[0], l[1], l[2], l[3], chips4);
   }
   if (Q == 2) {
 #pragma unroll
@@ -239,7 +246,7 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
         }
       }
     }
-    return demod_quantize4<24>(l[0], l[1], l[2], l[3], chips4);
+    return demod_quantize4<24, true>(l[0], l[1], l[2], l[3], chips4);
   }
   if (Q == 1) {
 #pragma unroll
@@ -253,7 +260,7 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
         }
       }
     }
-    return demod_quantize4<24>(l[0], l[1], l[2], l[3], chips4);
+    return demod_quantize4<24, true>(l[0], l[1], l[2], l[3], chips4);
   }
   // 64QAM
   DemodSym cur;
@@ -264,23 +271,22 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
       l[u] = demod_llr_qam64(tab, j + u, cur, sym, noise);
     }
   }
-  return demod_quantize4<20>(l[0], l[1], l[2], l[3], chips4);
+  return demod_quantize4<20, true>(l[0], l[1], l[2], l[3], chips4);
 }
 
-// The eight LLRs of 256QAM symbol s (demodulation_mapper_qam256.cpp:279-350: LLR 2 k = axis bit k of the real part,
-// LLR 2 k + 1 of the imaginary part), descrambled with the low eight bits of chips8.
-__device__ __forceinline__ uint2 demod_symbol_qam256(const DemodSmem& tab, unsigned s, unsigned chips8,
-                                                     const float2* __restrict__ sym, const float* __restrict__ noise)
+// The eight LLRs of a 256QAM symbol (demodulation_mapper_qam256.cpp:279-350: LLR 2 k = axis bit k of the real part,
+// LLR 2 k + 1 of the imaginary part), descrambled with the low eight bits of chips8. rcp = RN(1 / noise variance) or 0.
+// TAME: both parts and rcp are below 1e30 in magnitude, so no NaN can arise (|slope x + intercept| stays finite, finite or
+// infinite times rcp >= 0 is not 0 x inf) and the NaN guards of the interval index and the quantiser are left out.
+template <bool TAME>
+__device__ __forceinline__ uint2 demod_symbol_qam256(const DemodSmem& tab, float2 z, float rcp, unsigned chips8)
 {
-  const float2 z = __ldg(sym + s);
-  const float nv = __ldg(noise + s);
-  const float rcp = (nv > 0) ? __fdiv_rn(1.0f, nv) : 0.0f;  // not > 0 covers NaN
   float l[8];
-  demod_axis<4>(tab, z.x, rcp, l);
-  demod_axis<4>(tab, z.y, rcp, l + 1);
+  demod_axis<4, TAME>(tab, z.x, rcp, l);
+  demod_axis<4, TAME>(tab, z.y, rcp, l + 1);
   uint2 r;
-  r.x = demod_quantize4<20>(l[0], l[1], l[2], l[3], chips8);
-  r.y = demod_quantize4<20>(l[4], l[5], l[6], l[7], chips8 >> 4);
+  r.x = demod_quantize4<20, !TAME>(l[0], l[1], l[2], l[3], chips8);
+  r.y = demod_quantize4<20, !TAME>(l[4], l[5], l[6], l[7], chips8 >> 4);
   return r;
 }
 
@@ -310,7 +316,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   __shared__ DemodSmem tab;
   if (job.mod_order >= 6 && t < 64) {
     const int m = job.mod_order == 8 ? 1 : 0;
-    tab.line[t >> 4][t & 15] = make_float2(c_demod.slope[m][t >> 4][t & 15], c_demod.intercept[m][t >> 4][t & 15]);
+    const unsigned k = t >> 4, i = (k == (m ? 3u : 2u)) ? ((t & 15u) >> 1) : (t & 15u);  // finest bit: every entry twice
+    tab.line[k][t & 15] = make_float2(c_demod.slope[m][k][i], c_demod.intercept[m][k][i]);
   }
   if (job.descramble) {
     // A warp owns spans x 1024 consecutive chips. State of both registers at chip 1600 + first chip of the warp
@@ -360,24 +367,43 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
   const unsigned long long dst_bits = reinterpret_cast<unsigned long long>(dst);
   if (job.mod_order == 8) {
     // one symbol = 8 LLRs = one 8-byte store per thread and step (nof_llrs is a multiple of 8)
+    // and span: DEMOD_QAM256_BATCH symbols in flight per thread (loads first, one address computation)
 #pragma unroll 1
-    for (unsigned it = 0; it < spans * (32u / 8u); ++it) {
+    for (unsigned it = 0; it < spans * (32u / 8u); it += DEMOD_QAM256_BATCH) {
       const unsigned local = 8u * (it * DEMOD_THREADS + t);
       const unsigned j = j0 + local;
       if (j >= job.nof_llrs) {
         break;
       }
-      const unsigned cw = job.descramble ? (chips[local >> 5] >> (local & 31u)) : 0u;
-      const uint2 w = demod_symbol_qam256(tab, j >> 3, cw, sym, noise);
-      if ((dst_bits & 7ull) == 0) {
-        *reinterpret_cast<uint2*>(dst + j) = w;
-      } else if ((dst_bits & 3ull) == 0) {
-        reinterpret_cast<unsigned*>(dst + j)[0] = w.x;
-        reinterpret_cast<unsigned*>(dst + j)[1] = w.y;
-      } else {
-        for (unsigned u = 0; u < 4; ++u) {
-          dst[j + u] = (int8_t)(w.x >> (8u * u));
-          dst[j + 4 + u] = (int8_t)(w.y >> (8u * u));
+      const float2* ps = sym + (j >> 3);
+      const float* pn = noise + (j >> 3);
+      float2 z[DEMOD_QAM256_BATCH];
+      float nv[DEMOD_QAM256_BATCH];
+#pragma unroll
+      for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
+        const bool ok = j + 8u * DEMOD_THREADS * i < job.nof_llrs;
+        z[i] = ok ? __ldg(ps + DEMOD_THREADS * i) : make_float2(0.0f, 0.0f);
+        nv[i] = ok ? __ldg(pn + DEMOD_THREADS * i) : 0.0f;
+      }
+#pragma unroll
+      for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
+        const unsigned li = local + 8u * DEMOD_THREADS * i, ji = j + 8u * DEMOD_THREADS * i;
+        if (ji < job.nof_llrs) {
+          const unsigned cw = job.descramble ? (chips[li >> 5] >> (li & 31u)) : 0u;
+          const float rcp = (nv[i] > 0) ? __fdiv_rn(1.0f, nv[i]) : 0.0f;  // not > 0 covers NaN
+          const bool tame = fabsf(z[i].x) < 1e30f && fabsf(z[i].y) < 1e30f && rcp < 1e30f;
+          const uint2 w = tame ? demod_symbol_qam256<true>(tab, z[i], rcp, cw) : demod_symbol_qam256<false>(tab, z[i], rcp, cw);
+          if ((dst_bits & 7ull) == 0) {
+            *reinterpret_cast<uint2*>(dst + ji) = w;
+          } else if ((dst_bits & 3ull) == 0) {
+            reinterpret_cast<unsigned*>(dst + ji)[0] = w.x;
+            reinterpret_cast<unsigned*>(dst + ji)[1] = w.y;
+          } else {
+            for (unsigned u = 0; u < 4; ++u) {
+              dst[ji + u] = (int8_t)(w.x >> (8u * u));
+              dst[ji + 4 + u] = (int8_t)(w.y >> (8u * u));
+            }
+          }
         }
       }
     }
