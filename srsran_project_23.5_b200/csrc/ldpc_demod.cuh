@@ -312,7 +312,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
     return;
   }
   const unsigned t = threadIdx.x, lane = t & 31u;
-  __shared__ unsigned chips[DEMOD_THREADS * DEMOD_MAX_SPANS];
+  __shared__ __align__(16) unsigned chips[DEMOD_THREADS * DEMOD_MAX_SPANS];
   __shared__ DemodSmem tab;
   if (job.mod_order >= 6 && t < 64) {
     const int m = job.mod_order == 8 ? 1 : 0;
@@ -332,31 +332,34 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
         s2 = __ballot_sync(0xffffffffu, __popc(r2 & s2) & 1);
       }
     }
-    // Lane L needs the state 32 L chips further. Groups of 4 lanes: the start of group g follows from the start of group
-    // g - 1 by one more co-operative product with A^128 (its rows stay in registers); inside a group a lane advances by
-    // 0, 32, 64 or 96 chips in steps of 28. (Advancing every lane on its own from the warp's start took up to 36 steps
-    // and was a third of the kernel's instructions: profiles/r01_ncu_demod_summary.txt.) The eighth product is the start
-    // of the warp's next span of 1024 chips, so the jump above is paid once per spans x 1024 chips.
+    // The warp's chips form groups of 128 (8 per span, at most 32): lane L owns group L. Its start state is reached by L
+    // co-operative products with A^128 (the rows stay in registers, every lane keeps the state of its own step); from
+    // there the lane produces its four 32-chip words alone, advancing by 28 + 4 chips in between. (Earlier versions:
+    // every lane stepping from the warp's start, up to 36 steps, was a third of the kernel's instructions; groups of 4
+    // lanes per span with 8 products per span still a quarter: profiles/r01_ncu_demod_summary.txt.)
+    const unsigned left = (j0 + first < job.nof_llrs) ? job.nof_llrs - (j0 + first) : 0u;
+    const unsigned groups = min(8u * spans, (left + 127u) / 128u);
     const unsigned q1 = g_prg_pow[0][7][lane], q2 = g_prg_pow[1][7][lane];
-    const unsigned ahead = 32u * (lane & 3u), full = ahead / 28u, rest = ahead - 28u * full;
-    for (unsigned c = 0; c < spans && j0 + first + 1024u * c < job.nof_llrs; ++c) {
-      unsigned m1 = s1, m2 = s2;
+    unsigned m1 = s1, m2 = s2;
+    for (unsigned g = 1; g < groups; ++g) {
+      s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
+      s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
+      if (lane == g) {
+        m1 = s1, m2 = s2;
+      }
+    }
+    if (lane < groups) {
+      unsigned w[4];
 #pragma unroll
-      for (unsigned g = 1; g <= 8; ++g) {
-        s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
-        s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
-        if ((lane >> 2) == g) {
-          m1 = s1, m2 = s2;
+      for (int k = 0; k < 4; ++k) {
+        const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
+        w[k] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
+        if (k < 3) {
+          m1 = prg_advance(prg_advance(m1, 28u, false), 4u, false);
+          m2 = prg_advance(prg_advance(m2, 28u, true), 4u, true);
         }
       }
-      for (unsigned i = 0; i < full; ++i) {
-        m1 = ((m1 >> 28) | (((m1 >> 3) ^ m1) << 3)) & 0x7fffffffu;
-        m2 = ((m2 >> 28) | (((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) << 3)) & 0x7fffffffu;
-      }
-      m1 = prg_advance(m1, rest, false);
-      m2 = prg_advance(m2, rest, true);
-      const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
-      chips[(t >> 5) * 32u * spans + 32u * c + lane] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
+      *reinterpret_cast<uint4*>(&chips[(t >> 5) * 32u * spans + 4u * lane]) = make_uint4(w[0], w[1], w[2], w[3]);
     }
   }
   __syncthreads();
