@@ -57,8 +57,11 @@ __device__ unsigned g_prg_pow[2][32][32];
 
 constexpr int DEMOD_THREADS = 256;
 constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
-constexpr unsigned DEMOD_QAM256_BATCH = 2;        // divides 32 / 8 steps per span
-constexpr int DEMOD_MAX_SPANS = 4;               // spans per block: the launch picks 1, 2 or 4 from the amount of work
+#ifndef DEMOD_BATCH
+#define DEMOD_BATCH 2
+#endif
+constexpr unsigned DEMOD_QAM256_BATCH = DEMOD_BATCH;  // symbols in flight per thread; divides 32 / 8 steps per span
+constexpr int DEMOD_MAX_SPANS = 8;               // spans per block: the launch picks 1, 2, 4 or 8 from the amount of work
 constexpr float DEMOD_2SQRT2 = 2.0f * 1.41421356237309504880f;
 
 // a / b correctly rounded with rb = RN(1 / b) (Markstein: q0 = RN(a rb), r = a - b q0 exactly, q = RN(q0 + r rb)), without
@@ -332,14 +335,14 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
         s2 = __ballot_sync(0xffffffffu, __popc(r2 & s2) & 1);
       }
     }
-    // The warp's chips form groups of 128 (8 per span, at most 32): lane L owns group L. Its start state is reached by L
-    // co-operative products with A^128 (the rows stay in registers, every lane keeps the state of its own step); from
-    // there the lane produces its four 32-chip words alone, advancing by 28 + 4 chips in between. (Earlier versions:
+    // The warp's chips form groups of 256 (4 per span, at most 32): lane L owns group L. Its start state is reached by L
+    // co-operative products with A^256 (the rows stay in registers, every lane keeps the state of its own step); from
+    // there the lane produces its eight 32-chip words alone, advancing by 28 + 4 chips in between. (Earlier versions:
     // every lane stepping from the warp's start, up to 36 steps, was a third of the kernel's instructions; groups of 4
     // lanes per span with 8 products per span still a quarter: profiles/r01_ncu_demod_summary.txt.)
     const unsigned left = (j0 + first < job.nof_llrs) ? job.nof_llrs - (j0 + first) : 0u;
-    const unsigned groups = min(8u * spans, (left + 127u) / 128u);
-    const unsigned q1 = g_prg_pow[0][7][lane], q2 = g_prg_pow[1][7][lane];
+    const unsigned groups = min(4u * spans, (left + 255u) / 256u);
+    const unsigned q1 = g_prg_pow[0][8][lane], q2 = g_prg_pow[1][8][lane];
     unsigned m1 = s1, m2 = s2;
     for (unsigned g = 1; g < groups; ++g) {
       s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
@@ -349,17 +352,21 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
       }
     }
     if (lane < groups) {
-      unsigned w[4];
+      uint4* dst_words = reinterpret_cast<uint4*>(&chips[(t >> 5) * 32u * spans + 8u * lane]);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
-        w[k] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
-        if (k < 3) {
-          m1 = prg_advance(prg_advance(m1, 28u, false), 4u, false);
-          m2 = prg_advance(prg_advance(m2, 28u, true), 4u, true);
+      for (int h = 0; h < 2; ++h) {
+        unsigned w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
+          w[k] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
+          if (h == 0 || k < 3) {
+            m1 = prg_advance(prg_advance(m1, 28u, false), 4u, false);
+            m2 = prg_advance(prg_advance(m2, 28u, true), 4u, true);
+          }
         }
+        dst_words[h] = make_uint4(w[0], w[1], w[2], w[3]);
       }
-      *reinterpret_cast<uint4*>(&chips[(t >> 5) * 32u * spans + 4u * lane]) = make_uint4(w[0], w[1], w[2], w[3]);
     }
   }
   __syncthreads();

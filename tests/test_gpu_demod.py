@@ -128,10 +128,10 @@ def test_demodulate_batch_device_heterogeneous_jobs(dec):
     assert (out[end:] == 0x55).all()
 
 
-@pytest.mark.parametrize("nof_jobs", [40, 80])
+@pytest.mark.parametrize("nof_jobs", [40, 80, 160])
 def test_demodulate_batch_device_many_jobs(dec, nof_jobs):
-    """Launches large enough for 2 and 4 spans of 8192 LLRs per block (the scrambler's jump-ahead is then paid once per
-    warp and 2048 / 4096 chips): ragged lengths, every modulation, a different c_init per job."""
+    """Launches large enough for 2, 4 and 8 spans of 8192 LLRs per block (the scrambler's jump-ahead is then paid once per
+    warp and 2048 / 4096 / 8192 chips): ragged lengths, every modulation, a different c_init per job."""
     import torch
     dev = torch.device("cuda", 0)
     rng = np.random.default_rng(40 + nof_jobs)
