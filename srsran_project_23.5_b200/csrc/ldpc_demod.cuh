@@ -57,6 +57,9 @@ __device__ unsigned g_prg_pow[2][32][32];
 
 constexpr int DEMOD_THREADS = 256;
 constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
+#ifndef DEMOD_MIN_BLOCKS
+#define DEMOD_MIN_BLOCKS 8
+#endif
 #ifndef DEMOD_BATCH
 #define DEMOD_BATCH 2
 #endif
@@ -302,7 +305,7 @@ __device__ __forceinline__ unsigned prg_advance(unsigned s, unsigned k, bool is_
 }
 
 // grid (chunks, jobs). in_llrs: input of descramble-only jobs.
-__global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJob* __restrict__ jobs,
+__global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_kernel(const DemodJob* __restrict__ jobs,
                                                                    const float2* __restrict__ symbols,
                                                                    const float* __restrict__ noise_vars,
                                                                    const int8_t* __restrict__ in_llrs,
@@ -368,6 +371,10 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
         dst_words[h] = make_uint4(w[0], w[1], w[2], w[3]);
       }
     }
+  } else {
+    for (unsigned k = t; k < DEMOD_THREADS * spans; k += DEMOD_THREADS) {
+      chips[k] = 0u;  // no descrambling: every chip 0
+    }
   }
   __syncthreads();
   const float2* sym = symbols + job.sym_offset;
@@ -395,23 +402,41 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
         z[i] = ok ? __ldg(ps + DEMOD_THREADS * i) : make_float2(0.0f, 0.0f);
         nv[i] = ok ? __ldg(pn + DEMOD_THREADS * i) : 0.0f;
       }
+      // rcp = RN(1 / noise variance) or 0 (not > 0 covers NaN); symbols outside the batch count as (0, 0) / 0
+      float rcp[DEMOD_QAM256_BATCH];
+      bool tame = true;
 #pragma unroll
       for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
-        const unsigned li = local + 8u * DEMOD_THREADS * i, ji = j + 8u * DEMOD_THREADS * i;
+        rcp[i] = (nv[i] > 0) ? __frcp_rn(nv[i]) : 0.0f;
+        tame = tame && fabsf(z[i].x) < 1e30f && fabsf(z[i].y) < 1e30f && rcp[i] < 1e30f;
+      }
+      uint2 w[DEMOD_QAM256_BATCH];
+      if (tame) {
+#pragma unroll
+        for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
+          const unsigned li = local + 8u * DEMOD_THREADS * i;
+          w[i] = demod_symbol_qam256<true>(tab, z[i], rcp[i], chips[li >> 5] >> (li & 31u));
+        }
+      } else {
+#pragma unroll
+        for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
+          const unsigned li = local + 8u * DEMOD_THREADS * i;
+          w[i] = demod_symbol_qam256<false>(tab, z[i], rcp[i], chips[li >> 5] >> (li & 31u));
+        }
+      }
+#pragma unroll
+      for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
+        const unsigned ji = j + 8u * DEMOD_THREADS * i;
         if (ji < job.nof_llrs) {
-          const unsigned cw = job.descramble ? (chips[li >> 5] >> (li & 31u)) : 0u;
-          const float rcp = (nv[i] > 0) ? __fdiv_rn(1.0f, nv[i]) : 0.0f;  // not > 0 covers NaN
-          const bool tame = fabsf(z[i].x) < 1e30f && fabsf(z[i].y) < 1e30f && rcp < 1e30f;
-          const uint2 w = tame ? demod_symbol_qam256<true>(tab, z[i], rcp, cw) : demod_symbol_qam256<false>(tab, z[i], rcp, cw);
           if ((dst_bits & 7ull) == 0) {
-            *reinterpret_cast<uint2*>(dst + ji) = w;
+            *reinterpret_cast<uint2*>(dst + ji) = w[i];
           } else if ((dst_bits & 3ull) == 0) {
-            reinterpret_cast<unsigned*>(dst + ji)[0] = w.x;
-            reinterpret_cast<unsigned*>(dst + ji)[1] = w.y;
+            reinterpret_cast<unsigned*>(dst + ji)[0] = w[i].x;
+            reinterpret_cast<unsigned*>(dst + ji)[1] = w[i].y;
           } else {
             for (unsigned u = 0; u < 4; ++u) {
-              dst[ji + u] = (int8_t)(w.x >> (8u * u));
-              dst[ji + 4 + u] = (int8_t)(w.y >> (8u * u));
+              dst[ji + u] = (int8_t)(w[i].x >> (8u * u));
+              dst[ji + 4 + u] = (int8_t)(w[i].y >> (8u * u));
             }
           }
         }
@@ -428,7 +453,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS) ldpc_demod_kernel(const DemodJo
     if (j >= job.nof_llrs) {
       break;
     }
-    const unsigned cw = job.descramble ? (chips[local >> 5] >> (local & 31u)) : 0u;
+    const unsigned cw = chips[local >> 5] >> (local & 31u);
     const unsigned valid = min(4u, job.nof_llrs - j);
     unsigned packed;
     switch (job.mod_order) {  // uniform over the block
