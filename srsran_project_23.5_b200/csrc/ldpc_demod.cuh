@@ -95,14 +95,23 @@ __device__ __forceinline__ float demod_div_const(float a, float b, float rb)
 //         2, so one round-toward-zero addition leaves floor((b + 2^16) / 2) in the mantissa
 // Returns the bit pattern whose byte 2 is 0x80 | |q| (|q| = 0..120; bit 7 is the odd exponent's last bit and serves as a
 // guard bit for the byte-wise negation below).
-// NANSAFE: a NaN value gives |q| = 0 like the float -> int conversion of the reference's platform (fmaxf drops the NaN);
-// without it a NaN would come out as 120, so the caller must know the value is not NaN.
+// NANSAFE: any value; a NaN gives |q| = 0 like the float -> int conversion of the reference's platform. Otherwise the
+// caller guarantees |value| < 1e30 (no NaN, no infinity) and the clip costs no instruction.
 template <int RANGE, bool NANSAFE>
 __device__ __forceinline__ unsigned demod_qmag(float value)
 {
   constexpr float range_limit = (float)RANGE, rcp = 1.0f / (float)RANGE;
-  const float y = NANSAFE ? fminf(fmaxf(fabsf(value), 0.0f), range_limit) : fminf(fabsf(value), range_limit);
-  const float b = __fmul_rn(demod_div_const(y, range_limit, rcp), 15728640.0f);
+  float a;
+  if (NANSAFE) {
+    const float y = fminf(fmaxf(fabsf(value), 0.0f), range_limit);  // fmaxf drops a NaN
+    a = demod_div_const(y, range_limit, rcp);
+  } else {
+    // min(RN(|value| / RANGE), 1) = RN(min(|value|, RANGE) / RANGE) (rounding is monotone): the clip rides on the last
+    // multiply-add of the division as its saturation modifier. Needs |value| * rcp finite (|value| < 1e30).
+    const float y = fabsf(value), q0 = __fmul_rn(y, rcp);
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(a) : "f"(__fmaf_rn(-range_limit, q0, y)), "f"(rcp), "f"(q0));
+  }
+  const float b = __fmul_rn(a, 15728640.0f);
   return __float_as_uint(__fadd_rz(b, 16842752.0f));
 }
 
@@ -282,8 +291,8 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
 
 // The eight LLRs of a 256QAM symbol (demodulation_mapper_qam256.cpp:279-350: LLR 2 k = axis bit k of the real part,
 // LLR 2 k + 1 of the imaginary part), descrambled with the low eight bits of chips8. rcp = RN(1 / noise variance) or 0.
-// TAME: both parts and rcp are below 1e30 in magnitude, so no NaN can arise (|slope x + intercept| stays finite, finite or
-// infinite times rcp >= 0 is not 0 x inf) and the NaN guards of the interval index and the quantiser are left out.
+// TAME: both parts and rcp are below 1e14 in magnitude, so every LLR value stays below 1e30 (|slope| < 3, |intercept| < 8)
+// and neither NaN nor infinity can arise: the NaN guards of the interval index and the quantiser are left out.
 template <bool TAME>
 __device__ __forceinline__ uint2 demod_symbol_qam256(const DemodSmem& tab, float2 z, float rcp, unsigned chips8)
 {
@@ -408,7 +417,7 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
 #pragma unroll
       for (unsigned i = 0; i < DEMOD_QAM256_BATCH; ++i) {
         rcp[i] = (nv[i] > 0) ? __frcp_rn(nv[i]) : 0.0f;
-        tame = tame && fabsf(z[i].x) < 1e30f && fabsf(z[i].y) < 1e30f && rcp[i] < 1e30f;
+        tame = tame && fabsf(z[i].x) < 1e14f && fabsf(z[i].y) < 1e14f && rcp[i] < 1e14f;
       }
       uint2 w[DEMOD_QAM256_BATCH];
       if (tame) {
