@@ -61,7 +61,7 @@ constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
 #define DEMOD_MIN_BLOCKS 8
 #endif
 #ifndef DEMOD_BATCH
-#define DEMOD_BATCH 2
+#define DEMOD_BATCH 4
 #endif
 constexpr unsigned DEMOD_QAM256_BATCH = DEMOD_BATCH;  // symbols in flight per thread; divides 32 / 8 steps per span
 constexpr int DEMOD_MAX_SPANS = 8;               // spans per block: the launch picks 1, 2, 4 or 8 from the amount of work
