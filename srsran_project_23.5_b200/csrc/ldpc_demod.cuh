@@ -313,6 +313,48 @@ __device__ __forceinline__ unsigned prg_advance(unsigned s, unsigned k, bool is_
   return (unsigned)(w >> k) & 0x7fffffffu;
 }
 
+// Phase 2 of a block for every modulation but 256QAM: 4 consecutive LLRs (one packed store) per thread and step.
+template <int Q>
+__device__ __forceinline__ void demod_loop4(const DemodJob& job, const DemodSmem& tab, const unsigned* chips, unsigned j0,
+                                            unsigned spans, const float2* __restrict__ sym,
+                                            const float* __restrict__ noise, const int8_t* in, int8_t* dst)
+{
+  const unsigned t = threadIdx.x;
+  const bool aligned = ((reinterpret_cast<unsigned long long>(dst) & 3ull) == 0);
+  const bool in_aligned = ((reinterpret_cast<unsigned long long>(in) & 3ull) == 0);
+#pragma unroll 2
+  for (unsigned it = 0; it < spans * (32u / 4u); ++it) {
+    const unsigned local = 4u * (it * DEMOD_THREADS + t);  // first of this thread's 4 LLRs inside the chunk
+    const unsigned j = j0 + local;
+    if (j >= job.nof_llrs) {
+      break;
+    }
+    const unsigned cw = chips[local >> 5] >> (local & 31u);
+    const unsigned valid = min(4u, job.nof_llrs - j);
+    unsigned packed;
+    if (Q != 0) {
+      packed = demod_four<Q>(job, tab, j, valid, cw, sym, noise);
+    } else {
+      packed = 0;
+      if (in_aligned && valid == 4) {
+        packed = *reinterpret_cast<const unsigned*>(in + j);
+      } else {
+        for (unsigned u = 0; u < valid; ++u) {
+          packed |= ((unsigned)in[j + u] & 0xffu) << (8u * u);
+        }
+      }
+      packed = demod_negate4(packed, cw);
+    }
+    if (aligned && valid == 4) {
+      *reinterpret_cast<unsigned*>(dst + j) = packed;
+    } else {
+      for (unsigned u = 0; u < valid; ++u) {
+        dst[j + u] = (int8_t)(packed >> (8u * u));
+      }
+    }
+  }
+}
+
 // grid (chunks, jobs). in_llrs: input of descramble-only jobs.
 __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_kernel(const DemodJob* __restrict__ jobs,
                                                                    const float2* __restrict__ symbols,
@@ -453,39 +495,39 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
     }
     return;
   }
-  const bool aligned = ((dst_bits & 3ull) == 0);
-  const bool in_aligned = ((reinterpret_cast<unsigned long long>(in) & 3ull) == 0);
-#pragma unroll 1
-  for (unsigned it = 0; it < spans * (32u / 4u); ++it) {
-    const unsigned local = 4u * (it * DEMOD_THREADS + t);  // first of this thread's 4 LLRs inside the chunk
-    const unsigned j = j0 + local;
-    if (j >= job.nof_llrs) {
-      break;
-    }
-    const unsigned cw = chips[local >> 5] >> (local & 31u);
-    const unsigned valid = min(4u, job.nof_llrs - j);
-    unsigned packed;
-    switch (job.mod_order) {  // uniform over the block
-      case 6: packed = demod_four<6>(job, tab, j, valid, cw, sym, noise); break;
-      case 4: packed = demod_four<4>(job, tab, j, valid, cw, sym, noise); break;
-      case 2: packed = demod_four<2>(job, tab, j, valid, cw, sym, noise); break;
-      case 1: packed = demod_four<1>(job, tab, j, valid, cw, sym, noise); break;
-      default:
-        packed = 0;
-        if (in_aligned && valid == 4) {
-          packed = *reinterpret_cast<const unsigned*>(in + j);
-        } else {
-          for (unsigned u = 0; u < valid; ++u) {
-            packed |= ((unsigned)in[j + u] & 0xffu) << (8u * u);
+  switch (job.mod_order) {  // uniform over the block
+    case 6: demod_loop4<6>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
+    case 4: demod_loop4<4>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
+    case 2: demod_loop4<2>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
+    case 1: demod_loop4<1>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
+    default: {
+      // descrambling of existing LLRs: 16 per thread and step when both buffers allow 16-byte accesses
+      const unsigned long long in_bits = reinterpret_cast<unsigned long long>(in);
+      if (((dst_bits | in_bits) & 15ull) == 0) {
+        const unsigned t = threadIdx.x;
+#pragma unroll 2
+        for (unsigned it = 0; it < spans * (32u / 16u); ++it) {
+          const unsigned local = 16u * (it * DEMOD_THREADS + t);
+          const unsigned j = j0 + local;
+          if (j + 16u > job.nof_llrs) {
+            // ragged end: at most one such thread per job
+            for (unsigned u = 0; j + u < job.nof_llrs; ++u) {
+              const int8_t v = in[j + u];
+              dst[j + u] = ((chips[(local + u) >> 5] >> ((local + u) & 31u)) & 1u) ? (int8_t)(-v) : v;
+            }
+            break;
           }
+          const uint4 v = *reinterpret_cast<const uint4*>(in + j);
+          const unsigned cw = chips[local >> 5] >> (local & 31u);
+          uint4 r;
+          r.x = demod_negate4(v.x, cw);
+          r.y = demod_negate4(v.y, cw >> 4);
+          r.z = demod_negate4(v.z, cw >> 8);
+          r.w = demod_negate4(v.w, cw >> 12);
+          *reinterpret_cast<uint4*>(dst + j) = r;
         }
-        packed = demod_negate4(packed, cw);
-    }
-    if (aligned && valid == 4) {
-      *reinterpret_cast<unsigned*>(dst + j) = packed;
-    } else {
-      for (unsigned u = 0; u < valid; ++u) {
-        dst[j + u] = (int8_t)(packed >> (8u * u));
+      } else {
+        demod_loop4<0>(job, tab, chips, j0, spans, sym, noise, in, dst);
       }
     }
   }
