@@ -16,11 +16,13 @@
 // bit-exact with the reference's generic path (and within one LLR step of its AVX2 kernels, which differ from its own
 // generic code): tests/test_gpu_demod.py.
 //
-// Work split: a block of 256 threads produces 8192 consecutive LLRs of one job. Phase 1 (descrambling only): each warp
-// jumps the two 31-bit LFSRs of TS 38.211 5.2.1 to its first chip with GF(2) matrix powers A^(2^j) applied
-// co-operatively (one row per lane, ballot), groups of 4 lanes are reached with A^128 the same way, each lane then advances
-// by at most 96 chips, 28 at a time, and writes its 32-chip word to shared memory. Phase 2: a thread computes 4 consecutive LLRs per step (one packed 32-bit store, coalesced),
-// 8 steps. HBM-bound by design: 1 byte out + 12 / Qm bytes in per LLR.
+// Work split: a block of 256 threads produces 1, 2, 4 or 8 spans of 8192 consecutive LLRs of one job (the launch picks the
+// span count from the amount of work). Phase 1 (descrambling only): each warp jumps the two 31-bit LFSRs of TS 38.211
+// 5.2.1 to its first chip with GF(2) matrix powers A^(2^j) applied co-operatively (one row per lane, ballot); lane L takes
+// the state after L more products with A^256 and produces its eight 32-chip words alone, into shared memory. Phase 2, per
+// modulation: 256QAM one symbol (8 LLRs, 8-byte store) per thread and step, four in flight; 64QAM one symbol (6 LLRs);
+// 16QAM / QPSK 8 LLRs; BPSK 4 LLRs; existing LLRs (descramble only) 16 per thread and step. HBM-bound by design: 1 byte
+// out + 12 / Qm bytes in per LLR; measured figures in profiles/r01_ncu_demod_summary.txt and profiles/r01_sweep_demod.md.
 #pragma once
 
 #include "ldpc_device.cuh"
@@ -190,35 +192,7 @@ __device__ __forceinline__ void demod_axis(const DemodSmem& tab, float x, float 
   }
 }
 
-// One axis bit of 64QAM (its four-LLR groups straddle symbols).
-__device__ __forceinline__ float demod_interval_qam64(const DemodSmem& tab, float value, float rcp_noise, int k)
-{
-  const float2 t = tab.line[k][demod_interval_index<3, false>(value)];
-  return __fmul_rn(__fmaf_rn(t.x, value, t.y), rcp_noise);
-}
-
-// Per-symbol state shared by the LLRs of a symbol.
-struct DemodSym {
-  unsigned index;
-  float2 z;
-  float nv, rcp;  // rcp = RN(1 / nv) when nv > 0, else 0
-};
-
-// LLR j of a 64QAM job before quantisation (the four LLRs of a thread straddle symbols).
-__device__ __forceinline__ float demod_llr_qam64(const DemodSmem& tab, unsigned j, DemodSym& cur,
-                                                 const float2* __restrict__ sym, const float* __restrict__ noise)
-{
-  const unsigned s = j / 6u, b = j - 6u * s;
-  if (s != cur.index) {
-    cur.index = s;
-    cur.z = __ldg(sym + s);
-    cur.nv = __ldg(noise + s);
-    cur.rcp = (cur.nv > 0) ? __fdiv_rn(1.0f, cur.nv) : 0.0f;
-  }
-  return demod_interval_qam64(tab, (b & 1u) ? cur.z.y : cur.z.x, cur.rcp, (int)(b >> 1));
-}
-
-// Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q <= 6, descrambled with the low four
+// Four consecutive LLRs j .. j + 3 (j a multiple of 4) of a job of modulation order Q <= 4, descrambled with the low four
 // bits of chips4, one per byte. valid = number of LLRs that exist (1..4); the others come out as 0. Straight-line per
 // modulation: the symbol, its noise variance and the reciprocal are fetched once.
 template <int Q>
@@ -277,16 +251,7 @@ __device__ __forceinline__ unsigned demod_four(const DemodJob& job, const DemodS
     }
     return demod_quantize4<24, true>(l[0], l[1], l[2], l[3], chips4);
   }
-  // 64QAM
-  DemodSym cur;
-  cur.index = 0xffffffffu;
-#pragma unroll
-  for (unsigned u = 0; u < 4; ++u) {
-    if (u < valid) {
-      l[u] = demod_llr_qam64(tab, j + u, cur, sym, noise);
-    }
-  }
-  return demod_quantize4<20, true>(l[0], l[1], l[2], l[3], chips4);
+  return 0u;
 }
 
 // The eight LLRs of a 256QAM symbol (demodulation_mapper_qam256.cpp:279-350: LLR 2 k = axis bit k of the real part,
@@ -355,6 +320,139 @@ __device__ __forceinline__ void demod_loop4(const DemodJob& job, const DemodSmem
   }
 }
 
+// Phase 2 for QPSK / 16QAM: 8 consecutive LLRs (4 or 2 symbols, one 8-byte store) per thread and step. When all
+// of them are "tame" (|re|, |im|, |noise variance| and its reciprocal below 1e14: nothing can overflow, no NaN) the
+// divisions by the noise variance are plain Markstein sequences and the quantiser clips for free; a noise variance <= 0
+// gives rcp = 0, hence q0 = 0 and LLR 0 as in the reference. Anything else, and the ragged end of a job, goes through
+// demod_four.
+template <int Q>
+__device__ __forceinline__ void demod_loop8(const DemodJob& job, const DemodSmem& tab, const unsigned* chips, unsigned j0,
+                                            unsigned spans, const float2* __restrict__ sym,
+                                            const float* __restrict__ noise, int8_t* dst)
+{
+  constexpr unsigned NS = 8u / Q;  // symbols per step
+  const unsigned t = threadIdx.x;
+  const unsigned long long dst_bits = reinterpret_cast<unsigned long long>(dst);
+#pragma unroll 2
+  for (unsigned it = 0; it < spans * (32u / 8u); ++it) {
+    const unsigned local = 8u * (it * DEMOD_THREADS + t);
+    const unsigned j = j0 + local;
+    if (j >= job.nof_llrs) {
+      break;
+    }
+    const unsigned cw = chips[local >> 5] >> (local & 31u);
+    const bool full = j + 8u <= job.nof_llrs;
+    float2 z[NS];
+    float nv[NS], rcp[NS];
+    bool tame = full;
+    if (full) {
+#pragma unroll
+      for (unsigned i = 0; i < NS; ++i) {
+        z[i] = __ldg(sym + j / Q + i);
+        nv[i] = __ldg(noise + j / Q + i);
+      }
+#pragma unroll
+      for (unsigned i = 0; i < NS; ++i) {
+        rcp[i] = (nv[i] > 0) ? __frcp_rn(nv[i]) : 0.0f;
+        tame = tame && fabsf(z[i].x) < 1e14f && fabsf(z[i].y) < 1e14f && fabsf(nv[i]) < 1e14f && rcp[i] < 1e14f;
+      }
+    }
+    uint2 w;
+    if (tame) {
+      float l[8];
+#pragma unroll
+      for (unsigned i = 0; i < NS; ++i) {
+        if (Q == 4) {
+          const float g = c_demod.qam16_gain, th = c_demod.qam16_threshold;
+          float l0 = __fmul_rn(g, z[i].x), l1 = __fmul_rn(g, z[i].y);
+          if (fabsf(z[i].x) > th) {
+            l0 = __fsub_rn(__fmul_rn(2.0f, l0), copysignf(0.8f, z[i].x));
+          }
+          if (fabsf(z[i].y) > th) {
+            l1 = __fsub_rn(__fmul_rn(2.0f, l1), copysignf(0.8f, z[i].y));
+          }
+          l[4 * i] = demod_div_const(l0, nv[i], rcp[i]);
+          l[4 * i + 1] = demod_div_const(l1, nv[i], rcp[i]);
+          l[4 * i + 2] = demod_div_const(__fmaf_rn(-g, fabsf(z[i].x), 0.8f), nv[i], rcp[i]);
+          l[4 * i + 3] = demod_div_const(__fmaf_rn(-g, fabsf(z[i].y), 0.8f), nv[i], rcp[i]);
+        } else if (Q == 2) {
+          l[2 * i] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, z[i].x), nv[i], rcp[i]);
+          l[2 * i + 1] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, z[i].y), nv[i], rcp[i]);
+        } else {
+          const float sum = (job.pi2 && (i & 1u)) ? __fadd_rn(z[i].y, -z[i].x) : __fadd_rn(z[i].x, z[i].y);
+          l[i] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, sum), nv[i], rcp[i]);
+        }
+      }
+      constexpr int RANGE = (Q == 4) ? 20 : 24;
+      w.x = demod_quantize4<RANGE, false>(l[0], l[1], l[2], l[3], cw);
+      w.y = demod_quantize4<RANGE, false>(l[4], l[5], l[6], l[7], cw >> 4);
+    } else {
+      const unsigned left = job.nof_llrs - j;
+      w.x = demod_four<Q>(job, tab, j, min(4u, left), cw, sym, noise);
+      w.y = (left > 4u) ? demod_four<Q>(job, tab, j + 4u, min(4u, left - 4u), cw >> 4, sym, noise) : 0u;
+    }
+    if (full && (dst_bits & 7ull) == 0) {
+      *reinterpret_cast<uint2*>(dst + j) = w;
+    } else if (full && (dst_bits & 3ull) == 0) {
+      reinterpret_cast<unsigned*>(dst + j)[0] = w.x;
+      reinterpret_cast<unsigned*>(dst + j)[1] = w.y;
+    } else {
+      for (unsigned u = 0; u < 8u && j + u < job.nof_llrs; ++u) {
+        dst[j + u] = (int8_t)((u < 4u ? w.x : w.y) >> (8u * (u & 3u)));
+      }
+    }
+  }
+}
+
+// Phase 2 for 64QAM: one symbol = 6 LLRs per thread and step. The block's LLR range [j0, end) is not a multiple of 6, so
+// the symbols that straddle its two ends are computed by both neighbouring blocks and each writes its own bytes (pairs of
+// LLRs never straddle: every bound is even). chips[-1] and chips[256 spans] exist as padding (their content only reaches
+// bytes that are not written).
+__device__ __forceinline__ void demod_loop_qam64(const DemodJob& job, const DemodSmem& tab, const unsigned* chips,
+                                                 unsigned j0, unsigned spans, const float2* __restrict__ sym,
+                                                 const float* __restrict__ noise, int8_t* dst)
+{
+  const unsigned end = min(j0 + DEMOD_CHUNK * spans, job.nof_llrs);
+  const unsigned s_last = (end - 1u) / 6u;
+  const bool even = ((reinterpret_cast<unsigned long long>(dst) & 1ull) == 0);
+#pragma unroll 2
+  for (unsigned s = j0 / 6u + threadIdx.x; s <= s_last; s += DEMOD_THREADS) {
+    const float2 z = __ldg(sym + s);
+    const float nv = __ldg(noise + s);
+    const float rcp = (nv > 0) ? __frcp_rn(nv) : 0.0f;  // not > 0 covers NaN
+    const int local = (int)(6u * s) - (int)j0;          // >= -5
+    const unsigned wi = (unsigned)(local + 32) >> 5, sh = (unsigned)(local + 32) & 31u;
+    const unsigned cw = __funnelshift_r(chips[(int)wi - 1], chips[wi], sh);
+    float l[8];
+    l[6] = l[7] = 0.0f;
+    unsigned w0, w1;
+    if (fabsf(z.x) < 1e14f && fabsf(z.y) < 1e14f && rcp < 1e14f) {
+      demod_axis<3, true>(tab, z.x, rcp, l);
+      demod_axis<3, true>(tab, z.y, rcp, l + 1);
+      w0 = demod_quantize4<20, false>(l[0], l[1], l[2], l[3], cw);
+      w1 = demod_quantize4<20, false>(l[4], l[5], l[6], l[7], cw >> 4);
+    } else {
+      demod_axis<3, false>(tab, z.x, rcp, l);
+      demod_axis<3, false>(tab, z.y, rcp, l + 1);
+      w0 = demod_quantize4<20, true>(l[0], l[1], l[2], l[3], cw);
+      w1 = demod_quantize4<20, true>(l[4], l[5], l[6], l[7], cw >> 4);
+    }
+#pragma unroll
+    for (unsigned u = 0; u < 6u; u += 2u) {
+      const unsigned j = 6u * s + u;
+      if (j >= j0 && j < end) {
+        const unsigned pair = ((u < 4u ? w0 : w1) >> (8u * (u & 3u))) & 0xffffu;
+        if (even) {
+          *reinterpret_cast<unsigned short*>(dst + j) = (unsigned short)pair;
+        } else {
+          dst[j] = (int8_t)pair;
+          dst[j + 1] = (int8_t)(pair >> 8);
+        }
+      }
+    }
+  }
+}
+
 // grid (chunks, jobs). in_llrs: input of descramble-only jobs.
 __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_kernel(const DemodJob* __restrict__ jobs,
                                                                    const float2* __restrict__ symbols,
@@ -369,7 +467,8 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
     return;
   }
   const unsigned t = threadIdx.x, lane = t & 31u;
-  __shared__ __align__(16) unsigned chips[DEMOD_THREADS * DEMOD_MAX_SPANS];
+  __shared__ __align__(16) unsigned chips_padded[DEMOD_THREADS * DEMOD_MAX_SPANS + 8];
+  unsigned* const chips = chips_padded + 4;  // one word of padding on either side for the 64QAM loop, 16-byte alignment kept
   __shared__ DemodSmem tab;
   if (job.mod_order >= 6 && t < 64) {
     const int m = job.mod_order == 8 ? 1 : 0;
@@ -496,10 +595,10 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
     return;
   }
   switch (job.mod_order) {  // uniform over the block
-    case 6: demod_loop4<6>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
-    case 4: demod_loop4<4>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
-    case 2: demod_loop4<2>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
-    case 1: demod_loop4<1>(job, tab, chips, j0, spans, sym, noise, in, dst); break;
+    case 6: demod_loop_qam64(job, tab, chips, j0, spans, sym, noise, dst); break;
+    case 4: demod_loop8<4>(job, tab, chips, j0, spans, sym, noise, dst); break;
+    case 2: demod_loop8<2>(job, tab, chips, j0, spans, sym, noise, dst); break;
+    case 1: demod_loop4<1>(job, tab, chips, j0, spans, sym, noise, in, dst); break;  // 13 B of input per LLR: HBM-bound as it is
     default: {
       // descrambling of existing LLRs: 16 per thread and step when both buffers allow 16-byte accesses
       const unsigned long long in_bits = reinterpret_cast<unsigned long long>(in);
