@@ -212,3 +212,39 @@ void oracle_descramble(unsigned c_init, unsigned n, const int8_t* in, int8_t* ou
     x2 = (x2 >> 1) | (f2 << 30);
   }
 }
+
+/* pusch_demodulator_impl::descramble with the repetition placeholders of UCI multiplexing (pusch_demodulator_impl.cpp:
+ * 100-152; placeholder positions from ulsch_placeholder_list::for_each, ulsch_placeholder_list.h:73-95): for every listed
+ * RE and layer the soft bit y = Qm (layers re + layer) + 1 repeats the scrambling chip of the bit before it, the
+ * Qm - 2 bits behind it (x placeholders) are copied as they are, and the sequence keeps running underneath (the chips of
+ * those positions are discarded). Walks the sequence exactly like the reference: segment by segment. */
+void oracle_descramble_placeholders(unsigned c_init, unsigned n, const int8_t* in, int8_t* out, unsigned mod_order,
+                                    unsigned nof_layers, unsigned nof_re, const uint16_t* re_indexes)
+{
+  uint8_t* c = (uint8_t*)malloc(n + 16);
+  oracle_gold_sequence(c_init, n + 16, c);
+  const unsigned nx = mod_order > 2 ? mod_order - 2 : 0;
+  unsigned pos = 0, chip = 0; /* next element, next chip of the sequence */
+  for (unsigned r = 0; r != nof_re; ++r) {
+    for (unsigned layer = 0; layer != nof_layers; ++layer) {
+      const unsigned y = mod_order * (nof_layers * (unsigned)re_indexes[r] + layer) + 1;
+      /* plain descrambling up to the element before the placeholder (exclusive) */
+      while (pos + 1 < y) {
+        out[pos] = c[chip] ? (int8_t)(-in[pos]) : in[pos];
+        ++pos, ++chip;
+      }
+      const int toggle = c[chip]; /* mask of the next element; then 1 + nx chips are discarded */
+      chip += 2 + nx;
+      for (unsigned k = 0; k != 2; ++k, ++pos) {
+        out[pos] = toggle ? (int8_t)(-in[pos]) : in[pos];
+      }
+      for (unsigned k = 0; k != nx; ++k, ++pos) {
+        out[pos] = in[pos];
+      }
+    }
+  }
+  for (; pos < n; ++pos, ++chip) {
+    out[pos] = c[chip] ? (int8_t)(-in[pos]) : in[pos];
+  }
+  free(c);
+}

@@ -36,6 +36,14 @@
 
 #include "phy/upper/channel_modulation/demodulation_mapper_impl.h"
 #include "phy/upper/sequence_generators/pseudo_random_generator_impl.h"
+#include "srsran/phy/upper/channel_modulation/evm_calculator.h"
+#include "srsran/phy/upper/channel_processors/pusch_demodulator.h"
+#include "srsran/phy/upper/equalization/channel_equalizer.h"
+// pusch_demodulator_impl::descramble (the placeholder-aware descrambler) is a private member: the test shim opens the class
+// for this one header, the reference's code itself is untouched.
+#define private public
+#include "phy/upper/channel_processors/pusch_demodulator_impl.h"
+#undef private
 #include <algorithm>
 #include <atomic>
 #include <map>
@@ -829,6 +837,45 @@ void ref_descramble(unsigned c_init, unsigned n, const int8_t* in, int8_t* out)
   prg.init(c_init);
   prg.apply_xor(span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(out), n),
                 span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), n));
+}
+
+namespace {
+class unused_equalizer : public channel_equalizer
+{
+public:
+  void equalize(re_list&, noise_var_list&, const re_list&, const ch_est_list&, span<const float>, float) override
+  {
+    std::abort();
+  }
+};
+} // namespace
+
+// pusch_demodulator_impl::descramble of the reference with UCI placeholders (pusch_demodulator_impl.cpp:100-152).
+void ref_descramble_placeholders(unsigned        rnti,
+                                 unsigned        n_id,
+                                 unsigned        n,
+                                 const int8_t*   in,
+                                 int8_t*         out,
+                                 unsigned        mod_order,
+                                 unsigned        nof_layers,
+                                 unsigned        nof_re,
+                                 const uint16_t* re_indexes)
+{
+  static pusch_demodulator_impl demod(std::make_unique<unused_equalizer>(),
+                                      std::make_unique<demodulation_mapper_impl>(),
+                                      nullptr,
+                                      std::make_unique<pseudo_random_generator_impl>());
+  pusch_demodulator::configuration config = {};
+  config.rnti                             = static_cast<uint16_t>(rnti);
+  config.n_id                             = n_id;
+  config.modulation                       = static_cast<modulation_scheme>(mod_order);
+  config.nof_tx_layers                    = nof_layers;
+  for (unsigned i = 0; i != nof_re; ++i) {
+    config.placeholders.push_back(re_indexes[i]);
+  }
+  demod.descramble(span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(out), n),
+                   span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), n),
+                   config);
 }
 
 } // extern "C"

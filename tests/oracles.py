@@ -55,6 +55,7 @@ class PortOracle:
         L.oracle_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p]
         L.oracle_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
         L.oracle_gold_sequence.argtypes = [c_uint, c_uint, c_void_p]
+        L.oracle_descramble_placeholders.argtypes = [c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint, c_void_p]
 
     def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False):
         """symbols: complex64 [n]; noise_vars: float32 [n]. Returns int8 [n * mod_order]."""
@@ -68,6 +69,15 @@ class PortOracle:
         llrs = np.ascontiguousarray(llrs, np.int8)
         out = np.zeros_like(llrs)
         self.lib.oracle_descramble(c_init, llrs.size, _ptr(llrs), _ptr(out))
+        return out
+
+    def descramble_placeholders(self, c_init, llrs, mod_order, nof_layers, re_indexes):
+        """pusch_demodulator_impl::descramble with the UCI repetition placeholders of the listed REs (ascending)."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        re_indexes = np.ascontiguousarray(re_indexes, np.uint16)
+        out = np.zeros_like(llrs)
+        self.lib.oracle_descramble_placeholders(c_init, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
+                                                re_indexes.size, _ptr(re_indexes))
         return out
 
     def gold_sequence(self, c_init, n):
@@ -171,6 +181,7 @@ class RefOracle:
                                        c_int, c_int, c_uint, c_uint, c_uint, c_int, c_int, c_int, c_void_p]
         L.ref_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p, c_uint]
         L.ref_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
+        L.ref_descramble_placeholders.argtypes = [c_uint, c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint, c_void_p]
         self._decoders = {}
         self._dematchers = {}
 
@@ -189,6 +200,15 @@ class RefOracle:
         llrs = np.ascontiguousarray(llrs, np.int8)
         out = np.zeros_like(llrs)
         self.lib.ref_descramble(c_init, llrs.size, _ptr(llrs), _ptr(out))
+        return out
+
+    def descramble_placeholders(self, rnti, n_id, llrs, mod_order, nof_layers, re_indexes):
+        """The reference's own pusch_demodulator_impl::descramble (c_init = rnti * 2^15 + n_id)."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        re_indexes = np.ascontiguousarray(re_indexes, np.uint16)
+        out = np.zeros_like(llrs)
+        self.lib.ref_descramble_placeholders(rnti, n_id, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
+                                             re_indexes.size, _ptr(re_indexes))
         return out
 
     def supports(self, kind):

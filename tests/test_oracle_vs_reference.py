@@ -302,3 +302,28 @@ def test_descrambler_port_equals_reference():
     for n in range(1700):
         x.append(x[n + 3] ^ x[n])
     assert (c == np.array(x[1600:1664], np.uint8)).all()
+
+
+PLACEHOLDER_CASES = [  # (mod_order, nof_layers, nof_re, placeholder REs)
+    (2, 1, 600, [0, 5, 6, 100, 599]), (4, 2, 400, [3, 4, 5, 200, 399]), (6, 1, 1366, [1, 7, 682, 1365]),
+    (8, 4, 300, [0, 1, 2, 150, 299]), (8, 1, 3000, [1024, 1025, 2047, 2048]), (1, 1, 500, [0, 2, 4, 250, 498]),
+    (6, 3, 911, [0, 455, 910]), (4, 1, 50, [])]
+
+
+def test_descrambler_with_placeholders_port_equals_reference():
+    """oracle_descramble_placeholders against the reference's own pusch_demodulator_impl::descramble
+    (pusch_demodulator_impl.cpp:100-152), which the shim calls directly."""
+    ref = O.ref()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(10)
+    for q, layers, nof_re, res in PLACEHOLDER_CASES:
+        rnti, n_id = int(rng.integers(1, 65536)), int(rng.integers(0, 1024))
+        llrs = rng.integers(-127, 128, q * layers * nof_re).astype(np.int8)
+        want = ref.descramble_placeholders(rnti, n_id, llrs, q, layers, res)
+        got = O.port().descramble_placeholders(rnti * 32768 + n_id, llrs, q, layers, res)
+        assert (got == want).all(), (q, layers, np.flatnonzero(got != want)[:8])
+        if not res:
+            assert (got == O.port().descramble(rnti * 32768 + n_id, llrs)).all()
+        else:
+            assert (got != O.port().descramble(rnti * 32768 + n_id, llrs)).any()
