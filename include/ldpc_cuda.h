@@ -284,6 +284,31 @@ int ldpc_cuda_demodulate_soft(ldpc_cuda_handle* handle,
 /* pusch_demodulator_impl::descramble without repetition placeholders, HOST buffers, synchronous (in may equal out). */
 int ldpc_cuda_descramble(ldpc_cuda_handle* handle, uint32_t c_init, uint32_t nof_llrs, const int8_t* in, int8_t* out);
 
+/* UCI repetition placeholders of pusch_demodulator_impl::descramble (lib/phy/upper/channel_processors/
+ * pusch_demodulator_impl.cpp:100-152, positions from ulsch_placeholder_list::for_each, include/srsran/phy/upper/
+ * channel_processors/ulsch_placeholder_list.h:73-95): for every listed RE and layer, soft bit
+ * y = mod_order * (nof_layers * re + layer) + 1 repeats the scrambling chip of the bit before it and the mod_order - 2 bits
+ * behind it are not descrambled. One descriptor per codeword that carries placeholders. */
+typedef struct ldpc_cuda_placeholder_desc {
+  uint64_t llr_offset; /* first LLR of the codeword, bytes from llrs_d */
+  uint32_t c_init;     /* rnti * 2^15 + n_id */
+  uint32_t nof_llrs;   /* LLRs of the codeword (placeholder bits beyond it are ignored) */
+  uint32_t first_re;   /* index of the codeword's first entry in re_indexes */
+  uint16_t nof_re;     /* number of placeholder REs (config.placeholders) */
+  uint8_t  mod_order;  /* 1, 2, 4, 6, 8 */
+  uint8_t  nof_layers; /* config.nof_tx_layers */
+} ldpc_cuda_placeholder_desc; /* 24 bytes */
+
+/* Amends, in HBM and asynchronously on the handle's stream, codewords that were descrambled as plain data
+ * (ldpc_cuda_demodulate_batch_device with descramble = 1) so that they equal the output of the reference's descramble with
+ * config.placeholders. jobs and re_indexes (HOST arrays) are consumed before the call returns. */
+int ldpc_cuda_descramble_placeholders_device(ldpc_cuda_handle*                 handle,
+                                             uint32_t                          nof_jobs,
+                                             const ldpc_cuda_placeholder_desc* jobs,
+                                             const uint16_t*                   re_indexes,
+                                             uint32_t                          nof_re_indexes,
+                                             int8_t*                           llrs_d);
+
 /* ---------------------------------------------------------------------------------------------------------------------
  * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,
  * rx_softbuffer_codeblock_pool.h). Offsets in ldpc_cuda_cb_desc::soft_offset index into it.

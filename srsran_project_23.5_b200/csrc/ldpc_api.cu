@@ -32,6 +32,7 @@ using namespace ldpc_b200;
 #endif
 constexpr unsigned MAX_CHUNKS = LDPC_MAX_CHUNKS;
 static_assert(sizeof(DemodJob) == sizeof(ldpc_cuda_demod_desc) && sizeof(DemodJob) == 32, "DemodJob mirrors the ABI struct");
+static_assert(sizeof(ldpc_cuda_placeholder_desc) == 24 && sizeof(PlaceholderWork) == 24, "placeholder descriptors");
 static_assert(sizeof(TbResult) == sizeof(ldpc_cuda_tb_result) && sizeof(ldpc_cuda_tb_result) == 8, "TbResult mirrors the ABI struct");
 
 struct ldpc_cuda_handle {
@@ -534,6 +535,38 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
   return LDPC_CUDA_OK;
 }
 
+// Pinned double-buffered staging + device buffer of the demodulator's job lists: waits until the copy that last used the
+// chosen slot has been consumed, grows the buffers if needed. The caller fills h->h_demod[slot], copies it to h->d_demod on
+// its stream and records h->ev_demod[slot] behind the copy.
+int demod_stage(ldpc_cuda_handle* h, size_t bytes, unsigned& slot_out)
+{
+  const unsigned slot = (h->demod_slot++) & 1u;
+  slot_out = slot;
+  if (h->ev_demod[slot] == nullptr) {
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_demod[slot], cudaEventDisableTiming));
+  } else {
+    CUDA_TRY(cudaEventSynchronize(h->ev_demod[slot]));
+  }
+  if (bytes > h->h_demod_cap[slot]) {
+    if (h->h_demod[slot]) {
+      CUDA_TRY(cudaFreeHost(h->h_demod[slot]));
+      h->h_demod[slot] = nullptr, h->h_demod_cap[slot] = 0;
+    }
+    CUDA_TRY(cudaHostAlloc(&h->h_demod[slot], 2 * bytes + 4096, cudaHostAllocDefault));
+    h->h_demod_cap[slot] = 2 * bytes + 4096;
+  }
+  if (bytes > h->d_demod_cap) {
+    if (h->d_demod) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      CUDA_TRY(cudaFree(h->d_demod));
+      h->d_demod = nullptr, h->d_demod_cap = 0;
+    }
+    CUDA_TRY(cudaMalloc(&h->d_demod, 2 * bytes + 4096));
+    h->d_demod_cap = 2 * bytes + 4096;
+  }
+  return LDPC_CUDA_OK;
+}
+
 // Demodulator / descrambler jobs (ldpc_demod.cuh): validation, upload through pinned double-buffered staging, launch.
 int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, const ldpc_cuda_demod_desc* jobs,
                   const float* d_symbols, const float* d_noise, const int8_t* d_in_llrs, int8_t* d_out)
@@ -566,28 +599,10 @@ int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, c
   }
   max_chunks = (max_chunks + spans - 1) / spans;
   const size_t bytes = sizeof(DemodJob) * nof_jobs;
-  const unsigned slot = (h->demod_slot++) & 1u;
-  if (h->ev_demod[slot] == nullptr) {
-    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_demod[slot], cudaEventDisableTiming));
-  } else {
-    CUDA_TRY(cudaEventSynchronize(h->ev_demod[slot]));
-  }
-  if (bytes > h->h_demod_cap[slot]) {
-    if (h->h_demod[slot]) {
-      CUDA_TRY(cudaFreeHost(h->h_demod[slot]));
-      h->h_demod[slot] = nullptr, h->h_demod_cap[slot] = 0;
-    }
-    CUDA_TRY(cudaHostAlloc(&h->h_demod[slot], 2 * bytes + 4096, cudaHostAllocDefault));
-    h->h_demod_cap[slot] = 2 * bytes + 4096;
-  }
-  if (bytes > h->d_demod_cap) {
-    if (h->d_demod) {
-      CUDA_TRY(cudaDeviceSynchronize());
-      CUDA_TRY(cudaFree(h->d_demod));
-      h->d_demod = nullptr, h->d_demod_cap = 0;
-    }
-    CUDA_TRY(cudaMalloc(&h->d_demod, 2 * bytes + 4096));
-    h->d_demod_cap = 2 * bytes + 4096;
+  unsigned slot = 0;
+  int rc_stage = demod_stage(h, bytes, slot);
+  if (rc_stage != LDPC_CUDA_OK) {
+    return rc_stage;
   }
   DemodJob* hj = reinterpret_cast<DemodJob*>(h->h_demod[slot]);
   for (uint32_t i = 0; i != nof_jobs; ++i) {
@@ -608,6 +623,60 @@ int enqueue_demod(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs, c
   ldpc_demod_kernel<<<grid, DEMOD_THREADS, 0, stream>>>(reinterpret_cast<const DemodJob*>(h->d_demod),
                                                          reinterpret_cast<const float2*>(d_symbols), d_noise, d_in_llrs,
                                                          d_out, spans);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+// UCI repetition placeholders (ldpc_demod.cuh, ldpc_demod_placeholder_kernel): one work item per (RE, layer).
+int enqueue_placeholders(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_jobs,
+                         const ldpc_cuda_placeholder_desc* jobs, const uint16_t* re_indexes, uint32_t nof_re_indexes,
+                         int8_t* d_llrs)
+{
+  size_t total = 0;
+  for (uint32_t i = 0; i != nof_jobs; ++i) {
+    const ldpc_cuda_placeholder_desc& j = jobs[i];
+    const bool mod_ok = j.mod_order == 1 || j.mod_order == 2 || j.mod_order == 4 || j.mod_order == 6 || j.mod_order == 8;
+    if (!mod_ok || j.nof_layers == 0 || j.nof_layers > 8 || (uint64_t)j.first_re + j.nof_re > nof_re_indexes ||
+        (j.nof_re != 0 && re_indexes == nullptr)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    total += (size_t)j.nof_re * j.nof_layers;
+  }
+  if (total == 0) {
+    return LDPC_CUDA_OK;
+  }
+  if (total > 0x7fffffffu) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  const size_t bytes = sizeof(PlaceholderWork) * total;
+  unsigned slot = 0;
+  int rc = demod_stage(h, bytes, slot);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  PlaceholderWork* hw = reinterpret_cast<PlaceholderWork*>(h->h_demod[slot]);
+  size_t k = 0;
+  for (uint32_t i = 0; i != nof_jobs; ++i) {
+    const ldpc_cuda_placeholder_desc& j = jobs[i];
+    for (uint32_t r = 0; r != j.nof_re; ++r) {
+      for (uint32_t layer = 0; layer != j.nof_layers; ++layer) {
+        PlaceholderWork& w = hw[k++];
+        // ulsch_placeholder_list::for_each (ulsch_placeholder_list.h:73-95): the y placeholder is the second bit of the symbol
+        w.llr_offset = j.llr_offset;
+        w.y = (uint32_t)j.mod_order * ((uint32_t)j.nof_layers * re_indexes[j.first_re + r] + layer) + 1u;
+        w.c_init = j.c_init;
+        w.nof_llrs = j.nof_llrs;
+        w.nx = j.mod_order > 2 ? j.mod_order - 2u : 0u;
+      }
+    }
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_demod, hw, bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaEventRecord(h->ev_demod[slot], stream));
+  const unsigned warps_per_block = 4;
+  const unsigned grid = (unsigned)((total + warps_per_block - 1) / warps_per_block);
+  ldpc_demod_placeholder_kernel<<<grid, 32 * warps_per_block, 0, stream>>>(
+      reinterpret_cast<const PlaceholderWork*>(h->d_demod), (unsigned)total, d_llrs);
   CUDA_TRY(cudaGetLastError());
   h->launches += 1;
   return LDPC_CUDA_OK;
@@ -1114,6 +1183,19 @@ int ldpc_cuda_descramble(ldpc_cuda_handle* h, uint32_t c_init, uint32_t nof_llrs
   ldpc_cuda_demod_desc job = {};
   job.mod_order = 0, job.descramble = 1, job.nof_symbols = nof_llrs, job.c_init = c_init;
   return demod_host(h, job, in, nof_llrs, nullptr, 0, out, nof_llrs);
+}
+
+int ldpc_cuda_descramble_placeholders_device(ldpc_cuda_handle* h, uint32_t nof_jobs, const ldpc_cuda_placeholder_desc* jobs,
+                                             const uint16_t* re_indexes, uint32_t nof_re_indexes, int8_t* llrs_d)
+{
+  if (h == nullptr || (nof_jobs != 0 && (jobs == nullptr || llrs_d == nullptr))) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_jobs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  return enqueue_placeholders(h, h->stream, nof_jobs, jobs, re_indexes, nof_re_indexes, llrs_d);
 }
 
 // ---- drop-in single codeblock ---------------------------------------------------------------------------------------

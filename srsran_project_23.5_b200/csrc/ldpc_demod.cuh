@@ -632,4 +632,44 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
   }
 }
 
+// UCI repetition placeholders (pusch_demodulator_impl.cpp:100-152) as an amendment of LLRs that were descrambled as plain
+// data: a placeholder at soft bit y must carry the chip of bit y - 1 instead of its own, and the nx bits behind it no chip
+// at all. One warp per placeholder: jump both registers to chip y - 1 (the state holds the next 31 chips), lane 0 flips
+// bit y if chips y - 1 and y differ, lane k (1..nx) flips bit y + k back if its chip was 1.
+struct PlaceholderWork {
+  unsigned long long llr_offset;
+  unsigned y;
+  unsigned c_init;
+  unsigned nof_llrs;
+  unsigned nx;
+};
+
+__global__ void __launch_bounds__(128) ldpc_demod_placeholder_kernel(const PlaceholderWork* __restrict__ work, unsigned n,
+                                                                     int8_t* llrs)
+{
+  const unsigned idx = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+  if (idx >= n) {
+    return;
+  }
+  const PlaceholderWork w = work[idx];
+  const unsigned pos = 1600u + w.y - 1u;
+  unsigned s1 = 1u, s2 = w.c_init & 0x7fffffffu;
+  for (unsigned jb = 0; jb < 32; ++jb) {
+    if ((pos >> jb) & 1u) {
+      const unsigned r1 = g_prg_pow[0][jb][lane], r2 = g_prg_pow[1][jb][lane];
+      s1 = __ballot_sync(0xffffffffu, __popc(r1 & s1) & 1);
+      s2 = __ballot_sync(0xffffffffu, __popc(r2 & s2) & 1);
+    }
+  }
+  const unsigned chips = s1 ^ s2;  // bit k = chip of soft bit y - 1 + k, k < 31
+  const unsigned q = w.y + lane;
+  if (lane <= w.nx && q < w.nof_llrs) {
+    const unsigned flip = (lane == 0) ? ((chips ^ (chips >> 1)) & 1u) : ((chips >> (lane + 1u)) & 1u);
+    if (flip) {
+      int8_t* p = llrs + w.llr_offset + q;
+      *p = (int8_t)(-*p);
+    }
+  }
+}
+
 }  // namespace ldpc_b200

@@ -33,6 +33,10 @@ DEMOD_DESC = np.dtype([("mod_order", "u1"), ("pi2_bpsk", "u1"), ("descramble", "
                        ("nof_symbols", "<u4"), ("c_init", "<u4"), ("reserved2", "<u4"), ("symbol_offset", "<u8"),
                        ("llr_offset", "<u8")], align=True)
 assert DEMOD_DESC.itemsize == 32
+# ldpc_cuda_placeholder_desc (24 bytes)
+PLACEHOLDER_DESC = np.dtype([("llr_offset", "<u8"), ("c_init", "<u4"), ("nof_llrs", "<u4"), ("first_re", "<u4"),
+                             ("nof_re", "<u2"), ("mod_order", "u1"), ("nof_layers", "u1")], align=True)
+assert PLACEHOLDER_DESC.itemsize == 24
 
 
 class LdpcCudaError(RuntimeError):
@@ -98,6 +102,7 @@ def library():
         L.ldpc_cuda_tb_assemble_device.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, vp]
         L.ldpc_cuda_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp]
         L.ldpc_cuda_demodulate_batch_device.argtypes = [vp, u32, vp, vp, vp, vp, vp]
+        L.ldpc_cuda_descramble_placeholders_device.argtypes = [vp, u32, vp, vp, u32, vp]
         L.ldpc_cuda_demodulate_soft.argtypes = [vp, i32, i32, u32, vp, vp, vp]
         L.ldpc_cuda_descramble.argtypes = [vp, u32, u32, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
@@ -289,6 +294,15 @@ class LdpcCuda:
         jobs = np.ascontiguousarray(jobs, DEMOD_DESC)
         self._check(self._L.ldpc_cuda_demodulate_batch_device(self._h, jobs.size, _ptr(jobs), symbols_ptr, noise_ptr,
                                                               in_llrs_ptr, llrs_ptr), "ldpc_cuda_demodulate_batch_device")
+
+    def descramble_placeholders_device(self, jobs, re_indexes, llrs_ptr):
+        """UCI repetition placeholders (pusch_demodulator_impl.cpp:100-152) applied to codewords in HBM that were
+        descrambled as plain data; asynchronous on the handle's stream."""
+        jobs = np.ascontiguousarray(jobs, PLACEHOLDER_DESC)
+        re_indexes = np.ascontiguousarray(re_indexes, np.uint16)
+        self._check(self._L.ldpc_cuda_descramble_placeholders_device(self._h, jobs.size, _ptr(jobs), _ptr(re_indexes),
+                                                                     re_indexes.size, llrs_ptr),
+                    "ldpc_cuda_descramble_placeholders_device")
 
     # -- transmit side (encoder + rate matcher) ------------------------------------------------------------------------
     def encode(self, bg, Z, msg_bits):

@@ -32,6 +32,8 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layout_matches_header():
     assert pkg.CB_DESC.itemsize == 48 and pkg.CB_RESULT.itemsize == 4
     assert pkg.CB_DESC.fields["in_offset"][1] == 24 and pkg.CB_DESC.fields["out_offset"][1] == 40
+    assert pkg.PLACEHOLDER_DESC.itemsize == 24 and pkg.PLACEHOLDER_DESC.fields["nof_re"][1] == 20
+    assert pkg.PLACEHOLDER_DESC.fields["mod_order"][1] == 22 and pkg.PLACEHOLDER_DESC.fields["nof_layers"][1] == 23
 
 
 def test_no_product_source_touches_the_oracle():

@@ -171,6 +171,63 @@ def test_demodulate_batch_device_many_jobs(dec, nof_jobs):
         assert (out[off + w.size:(off + w.size + 15) // 8 * 8] == 0x55).all()
 
 
+def test_descramble_with_uci_placeholders(dec):
+    """pusch_demodulator_impl::descramble with config.placeholders (pusch_demodulator_impl.cpp:100-152): codewords are
+    demodulated + descrambled as plain data in one launch, ldpc_cuda_descramble_placeholders_device then amends the
+    placeholder bits in HBM. Against the oracle restatement (pinned to the reference's own function on the CPU) and, when
+    oracle/_ref is built, against that function directly."""
+    import torch
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(77)
+    cases = [(2, 1, 600, [0, 5, 6, 100, 599]), (4, 2, 400, [3, 4, 5, 200, 399]), (6, 1, 1366, [1, 7, 682, 1365]),
+             (8, 4, 300, [0, 1, 2, 150, 299]), (8, 1, 3000, [1024, 1025, 2047, 2048]), (1, 1, 500, [0, 2, 4, 250, 498]),
+             (6, 3, 911, [0, 455, 910]), (4, 1, 50, []), (8, 2, 9000, list(range(0, 9000, 7)))]
+    jobs = np.zeros(len(cases), pkg.DEMOD_DESC)
+    ph = np.zeros(len(cases), pkg.PLACEHOLDER_DESC)
+    syms, nvs, res_all, want, so, lo = [], [], [], [], 0, 0
+    for i, (q, layers, nof_re, res) in enumerate(cases):
+        n = nof_re * layers
+        rnti, n_id = int(rng.integers(1, 65536)), int(rng.integers(0, 1024))
+        sym, nv = O.random_symbols(rng, q, n, 0.05)
+        j = jobs[i]
+        j["mod_order"], j["descramble"], j["nof_symbols"], j["c_init"] = q, 1, n, rnti * 32768 + n_id
+        j["symbol_offset"], j["llr_offset"] = so, lo
+        p = ph[i]
+        p["llr_offset"], p["c_init"], p["nof_llrs"], p["first_re"] = lo, rnti * 32768 + n_id, n * q, len(res_all)
+        p["nof_re"], p["mod_order"], p["nof_layers"] = len(res), q, layers
+        res_all += res
+        llrs = O.port().demodulate_soft(q, sym, nv)
+        w = O.port().descramble_placeholders(rnti * 32768 + n_id, llrs, q, layers, res)
+        if O.ref() is not None:
+            assert (w == O.ref().descramble_placeholders(rnti, n_id, llrs, q, layers, res)).all()
+        want.append((lo, w))
+        syms.append(sym)
+        nvs.append(nv)
+        so += n
+        lo += n * q + 5
+    sym_d = torch.from_numpy(np.concatenate(syms).view(np.float32)).to(dev)
+    nv_d = torch.from_numpy(np.concatenate(nvs)).to(dev)
+    out_d = torch.full((lo,), 0x55, dtype=torch.int8, device=dev)
+    torch.cuda.synchronize()
+    dec.demodulate_batch_device(jobs, sym_d.data_ptr(), nv_d.data_ptr(), 0, out_d.data_ptr())
+    dec.descramble_placeholders_device(ph, np.array(res_all, np.uint16), out_d.data_ptr())
+    dec.synchronize()
+    out = out_d.cpu().numpy()
+    for i, (off, w) in enumerate(want):
+        bad = np.flatnonzero(out[off:off + w.size] != w)
+        assert bad.size == 0, (i, cases[i][:3], bad[:8])
+        assert (out[off + w.size:off + w.size + 5] == 0x55).all()
+    # argument checks: RE list shorter than a descriptor claims, unsupported modulation order
+    bad = ph[:1].copy()
+    bad["first_re"] = len(res_all)
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.descramble_placeholders_device(bad, np.array(res_all, np.uint16), out_d.data_ptr())
+    bad = ph[:1].copy()
+    bad["mod_order"] = 3
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.descramble_placeholders_device(bad, np.array(res_all, np.uint16), out_d.data_ptr())
+
+
 QAM_BITS = {2: 1, 4: 2, 6: 3, 8: 4}
 
 
