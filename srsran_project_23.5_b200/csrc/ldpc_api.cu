@@ -150,6 +150,7 @@ int upload_constants()
         dt.nof_intervals[m][k] = n;
         dt.width[m][k] = (float)(fine ? 4 : 2) * d;
         dt.rcp_width[m][k] = 1.0f / dt.width[m][k];
+        dt.rcp_width_lo[m][k] = (float)(1.0 / (double)dt.width[m][k] - (double)dt.rcp_width[m][k]);
         for (int i = 0; i != n; ++i) {
           // nearest level with bit k = 0 / 1 from the middle of interval i (distances doubled to stay integer)
           const int mid2 = fine ? 2 * (4 * (i - L / 4) + 2) : 2 * (2 * (i - L / 2) + 1);

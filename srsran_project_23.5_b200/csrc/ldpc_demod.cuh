@@ -45,7 +45,8 @@ struct DemodJob {
 // from the TS 38.211 5.1 bit mapping (build_demod_tables in ldpc_api.cu) with the reference's float expressions.
 struct DemodTables {
   float width[2][4];
-  float rcp_width[2][4];  // RN(1 / width)
+  float rcp_width[2][4];     // hi = RN(1 / width)
+  float rcp_width_lo[2][4];  // lo = RN(1 / width - hi)
   int nof_intervals[2][4];
   float slope[2][4][16];
   float intercept[2][4][16];
@@ -80,18 +81,27 @@ __device__ __forceinline__ float demod_div(float a, float b, float rb)
   return (fabsf(q0) < 1e30f && fabsf(rb) > 1e-30f) ? q : __fdiv_rn(a, b);
 }
 
-// Same for a constant divisor and a bounded dividend (interval width, quantiser range): no fallback needed.
-__device__ __forceinline__ float demod_div_const(float a, float b, float rb)
+// Same without the fallback, for operands known to stay in range.
+__device__ __forceinline__ float demod_div_markstein(float a, float b, float rb)
 {
   const float q0 = __fmul_rn(a, rb);
   return __fmaf_rn(__fmaf_rn(-b, q0, a), rb, q0);
+}
+
+// a / d correctly rounded for a CONSTANT divisor in two operations (Brisebarre-Muller: 1 / d = hi + lo with
+// hi = RN(1 / d), lo = RN(1 / d - hi); q = RN(a hi + RN(a lo))). Unlike Markstein's sequence this is not correct for
+// every divisor: it is verified exhaustively, over all 2^23 significands, for the four divisors used here (quantiser
+// ranges 20 and 24, coarse interval widths of 64QAM and 256QAM) by tests/test_demod_constants.py.
+__device__ __forceinline__ float demod_div_const(float a, float hi, float lo)
+{
+  return __fmaf_rn(a, hi, __fmul_rn(a, lo));
 }
 
 // log_likelihood_ratio::quantize (log_likelihood_ratio.cpp:87-96): clip to +-RANGE, / RANGE * 120, std::round (half away
 // from zero), int8. Every step is odd in the value, so magnitude and sign are carried apart: the magnitude of 4 LLRs is
 // formed here, the sign bits join the scrambling chips in one byte mask (demod_quantize4).
 //   y  = min(|value|, RANGE)                      (= |clipped|)
-//   a  = RN(y / RANGE)                            (Markstein with RCP = RN(1 / RANGE))
+//   a  = RN(y / RANGE)                            (two-operation division by a constant, demod_div_const)
 //   b  = RN(a * 120) * 2^17 = RN(a * 15728640)    (scaling by a power of two commutes with the rounding)
 //   |q| = floor(b / 2^17 + 0.5) = bits 16-22 of RZ(b + 2^16 + 2^24): the sum lies in [2^24, 2^25), unit in the last place
 //         2, so one round-toward-zero addition leaves floor((b + 2^16) / 2) in the mantissa
@@ -102,16 +112,17 @@ __device__ __forceinline__ float demod_div_const(float a, float b, float rb)
 template <int RANGE, bool NANSAFE>
 __device__ __forceinline__ unsigned demod_qmag(float value)
 {
-  constexpr float range_limit = (float)RANGE, rcp = 1.0f / (float)RANGE;
+  constexpr float range_limit = (float)RANGE, hi = 1.0f / (float)RANGE,
+                  lo = (float)(1.0 / (double)RANGE - (double)(1.0f / (float)RANGE));
   float a;
   if (NANSAFE) {
     const float y = fminf(fmaxf(fabsf(value), 0.0f), range_limit);  // fmaxf drops a NaN
-    a = demod_div_const(y, range_limit, rcp);
+    a = demod_div_const(y, hi, lo);
   } else {
     // min(RN(|value| / RANGE), 1) = RN(min(|value|, RANGE) / RANGE) (rounding is monotone): the clip rides on the last
-    // multiply-add of the division as its saturation modifier. Needs |value| * rcp finite (|value| < 1e30).
-    const float y = fabsf(value), q0 = __fmul_rn(y, rcp);
-    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(a) : "f"(__fmaf_rn(-range_limit, q0, y)), "f"(rcp), "f"(q0));
+    // multiply-add of the division as its saturation modifier. Needs |value| * hi finite (|value| < 1e30).
+    const float y = fabsf(value);
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(a) : "f"(y), "f"(hi), "f"(__fmul_rn(y, lo)));
   }
   const float b = __fmul_rn(a, 15728640.0f);
   return __float_as_uint(__fadd_rz(b, 16842752.0f));
@@ -174,7 +185,7 @@ template <int NB, bool FINITE>
 __device__ __forceinline__ int demod_interval_index(float value)
 {
   constexpr int L = 1 << NB, m = NB - 3;
-  const float q = demod_div_const(value, c_demod.width[m][0], c_demod.rcp_width[m][0]);
+  const float q = demod_div_const(value, c_demod.rcp_width[m][0], c_demod.rcp_width_lo[m][0]);
   const int i = (FINITE || q == q) ? __float2int_rd(q) : (int)0x80000000;
   return max(0, min(L - 1, (int)((unsigned)i + (unsigned)(L / 2))));
 }
@@ -371,16 +382,16 @@ __device__ __forceinline__ void demod_loop8(const DemodJob& job, const DemodSmem
           if (fabsf(z[i].y) > th) {
             l1 = __fsub_rn(__fmul_rn(2.0f, l1), copysignf(0.8f, z[i].y));
           }
-          l[4 * i] = demod_div_const(l0, nv[i], rcp[i]);
-          l[4 * i + 1] = demod_div_const(l1, nv[i], rcp[i]);
-          l[4 * i + 2] = demod_div_const(__fmaf_rn(-g, fabsf(z[i].x), 0.8f), nv[i], rcp[i]);
-          l[4 * i + 3] = demod_div_const(__fmaf_rn(-g, fabsf(z[i].y), 0.8f), nv[i], rcp[i]);
+          l[4 * i] = demod_div_markstein(l0, nv[i], rcp[i]);
+          l[4 * i + 1] = demod_div_markstein(l1, nv[i], rcp[i]);
+          l[4 * i + 2] = demod_div_markstein(__fmaf_rn(-g, fabsf(z[i].x), 0.8f), nv[i], rcp[i]);
+          l[4 * i + 3] = demod_div_markstein(__fmaf_rn(-g, fabsf(z[i].y), 0.8f), nv[i], rcp[i]);
         } else if (Q == 2) {
-          l[2 * i] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, z[i].x), nv[i], rcp[i]);
-          l[2 * i + 1] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, z[i].y), nv[i], rcp[i]);
+          l[2 * i] = demod_div_markstein(__fmul_rn(DEMOD_2SQRT2, z[i].x), nv[i], rcp[i]);
+          l[2 * i + 1] = demod_div_markstein(__fmul_rn(DEMOD_2SQRT2, z[i].y), nv[i], rcp[i]);
         } else {
           const float sum = (job.pi2 && (i & 1u)) ? __fadd_rn(z[i].y, -z[i].x) : __fadd_rn(z[i].x, z[i].y);
-          l[i] = demod_div_const(__fmul_rn(DEMOD_2SQRT2, sum), nv[i], rcp[i]);
+          l[i] = demod_div_markstein(__fmul_rn(DEMOD_2SQRT2, sum), nv[i], rcp[i]);
         }
       }
       constexpr int RANGE = (Q == 4) ? 20 : 24;
