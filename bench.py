@@ -302,12 +302,41 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
     n_cb = 2 * n_a * C
     bits = n_cb * (Kb - F)
     slots = 2 * sets
+    launches_per_step = (dec.launch_count - launches0) // steps
+    # the same two slots end to end through the host entry (pinned host buffers: rate-matched LLRs in, codeblock bytes,
+    # transport blocks and verdicts out; soft buffers stay in the HBM arena): SURVEY 8(e)'s host-fed figure for cfg 3
+    try:
+        rm_a_h = torch.empty(rm_a.shape, dtype=torch.int8, pin_memory=True).copy_(rm_a)
+        rm_b_h = torch.empty(rm_b.shape, dtype=torch.int8, pin_memory=True).copy_(rm_b)
+        out_h = torch.empty(n_a * C * kb, dtype=torch.uint8, pin_memory=True)
+        tb_out_h = torch.empty(n_a * tb_stride, dtype=torch.uint8, pin_memory=True)
+        res_h, tbres_h = np.zeros(n_a * C, pkg.CB_RESULT), np.zeros(n_a, pkg.TB_RESULT)
+        torch.cuda.synchronize()
+
+        def host_step():
+            dec.dematch_decode_tb_batch(d_a, rm_a_h.numpy().reshape(-1), out_h.numpy(), tbd, tb_out_h.numpy(), res_h, tbres_h)
+            dec.dematch_decode_tb_batch(d_b, rm_b_h.numpy().reshape(-1), out_h.numpy(), tbd, tb_out_h.numpy(), res_h, tbres_h)
+
+        host_step()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            host_step()
+        secs = (time.perf_counter() - t0) / steps
+        e2e = {"value": bits / secs / 1e9, "unit": "Gb/s", "ms_per_slot_16_cells": secs * 1e3 / slots,
+               "h2d_bytes_per_step": int(rm_a_h.numel() + rm_b_h.numel() + 2 * n_a * C * 48 + 2 * n_a * 24),
+               "d2h_bytes_per_step": int(2 * (out_h.numel() + tb_out_h.numel() + n_a * C * 4 + n_a * 8)),
+               "tb_crc_ok_rate_slot_b": float(tbres_h["tb_crc_ok"].mean()),
+               "timer": "host wall clock around the synchronous C-ABI calls (copies inside)"}
+        del rm_a_h, rm_b_h, out_h, tb_out_h
+    except Exception as exc:  # the extra must never take the headline line down with it
+        e2e = {"error": repr(exc)}
     return {"what": "configs 3+5: fused rate-dematch + HARQ combine (HBM arena) + decode + CRC24B early stop + TB assembly and "
                     "TB CRC24A on the device, 16 cells x 152-codeblock full-slot TBs (BG1 Z=384 F=16, E 8960/8992, "
                     "R=0.94), 12.5% retransmissions (rv2)",
             "value": bits / (ms * 1e-3) / 1e9, "unit": "Gb/s", "ms_per_slot_16_cells": ms / slots,
             "codeblocks_per_step": n_cb, "rm_llr_bytes_per_step": int(2 * n_a * tb_bytes),
-            "soft_buffer_arena_bytes": int(n_buf * C * Nsoft), "launches_per_step": (dec.launch_count - launches0) // steps,
+            "soft_buffer_arena_bytes": int(n_buf * C * Nsoft), "launches_per_step": launches_per_step,
+            "e2e": e2e,
             "cells_in_real_time_at_0.5ms_slots": cells * 0.5 / (ms / slots),
             "crc_pass_rate": {"new_good_snr": float(ra[~bad_a]["crc_ok"].mean()), "new_bad_snr": float(ra[bad_a]["crc_ok"].mean()),
                               "retransmission": float(rb[bad_a]["crc_ok"].mean())},

@@ -910,8 +910,9 @@ int ldpc_cuda_dematch_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const
 // decoded as a unit.
 struct Chunk {
   uint32_t b, e;            // range in launch order
-  uint64_t in_lo, in_hi;    // host input bytes
+  uint64_t in_lo, in_hi;    // host input bytes (hull)
   uint64_t out_lo, out_hi;  // host output bytes
+  std::vector<std::pair<uint64_t, uint64_t>> in_runs;  // contiguous input pieces to copy; empty: the hull
 };
 
 static inline void cb_ranges(const ldpc_cuda_cb_desc& d, bool fused, uint64_t& in_end, uint64_t& out_end)
@@ -921,45 +922,74 @@ static inline void cb_ranges(const ldpc_cuda_cb_desc& d, bool fused, uint64_t& i
 }
 
 // Splits the staged groups into at most MAX_CHUNKS chunks of about equal input size. Chunks are only formed when the
-// caller's layout is monotone in launch order (every codeblock's input and output ranges lie behind its predecessor's),
-// so that the byte ranges of different chunks are disjoint; otherwise each group is one chunk over the whole span.
+// caller's OUTPUT layout is monotone in launch order (every codeblock's message lies behind its predecessor's), so that
+// the output byte ranges of different chunks are disjoint; otherwise each group is one chunk over the whole span. The
+// INPUT may lie anywhere (e.g. retransmissions and new transport blocks in different host buffers' regions): a chunk
+// copies the contiguous runs of its codeblocks' inputs one by one.
 static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused,
                         std::vector<Chunk>& chunks)
 {
   chunks.clear();
   bool monotone = true;
-  uint64_t in_prev = 0, out_prev = 0, in_lo = ~0ull, in_hi = 0, out_lo = ~0ull, out_hi = 0;
+  uint64_t out_prev = 0, in_lo = ~0ull, in_hi = 0, out_lo = ~0ull, out_hi = 0, total_in = 0;
   for (uint32_t k = 0; k != n; ++k) {
     const ldpc_cuda_cb_desc& d = descs[h->order[k]];
     uint64_t ie, oe;
     cb_ranges(d, fused, ie, oe);
-    monotone = monotone && (k == 0 || (d.in_offset >= in_prev && d.out_offset >= out_prev));
-    in_prev = ie, out_prev = oe;
+    monotone = monotone && (k == 0 || d.out_offset >= out_prev);
+    out_prev = oe;
+    total_in += ie - d.in_offset;
     in_lo = std::min(in_lo, d.in_offset), in_hi = std::max(in_hi, ie);
     out_lo = std::min(out_lo, d.out_offset), out_hi = std::max(out_hi, oe);
   }
   const size_t nof_groups = h->group_begin.size() - 1;
-  const uint64_t total_in = in_hi - in_lo;
   constexpr uint64_t MIN_CHUNK_BYTES = 8ull << 20;
+  constexpr uint64_t RUN_GAP = 4096;
+  constexpr size_t MAX_RUNS = 4096;  // copies per call; beyond that the layout is too scattered to be worth it
+  auto single = [&]() {
+    chunks.clear();
+    chunks.push_back({0, n, in_lo, in_hi, out_lo, out_hi, {}});  // one copy in, all launches, one copy out
+  };
   if (!monotone || 2 * nof_groups > MAX_CHUNKS || total_in < 2 * MIN_CHUNK_BYTES) {
-    chunks.push_back({0, n, in_lo, in_hi, out_lo, out_hi});  // one copy in, all launches, one copy out
+    single();
     return;
   }
   // a chunk closes when it reaches the target size or at the end of its group: at most MAX_CHUNKS chunks
   const uint64_t by_size = MAX_CHUNKS - nof_groups;
   const uint64_t target = std::max<uint64_t>(MIN_CHUNK_BYTES, (total_in + by_size - 1) / by_size);
+  size_t runs = 0;
   for (size_t g = 0; g != nof_groups; ++g) {
     uint32_t b = h->group_begin[g];
     const uint32_t ge = h->group_begin[g + 1];
     while (b != ge) {
-      Chunk c = {b, b, descs[h->order[b]].in_offset, 0, descs[h->order[b]].out_offset, 0};
+      Chunk c = {b, b, ~0ull, 0, descs[h->order[b]].out_offset, 0, {}};
+      uint64_t bytes = 0;
       do {
-        cb_ranges(descs[h->order[c.e]], fused, c.in_hi, c.out_hi);
+        const ldpc_cuda_cb_desc& d = descs[h->order[c.e]];
+        uint64_t ie;
+        cb_ranges(d, fused, ie, c.out_hi);
+        if (ie > d.in_offset) {
+          // continues the current run (small gaps, e.g. alignment padding between codeblocks, are copied along)
+          if (!c.in_runs.empty() && d.in_offset >= c.in_runs.back().first && d.in_offset <= c.in_runs.back().second + RUN_GAP) {
+            c.in_runs.back().second = std::max(c.in_runs.back().second, ie);
+          } else {
+            c.in_runs.push_back({d.in_offset, ie});
+          }
+          c.in_lo = std::min(c.in_lo, d.in_offset), c.in_hi = std::max(c.in_hi, ie);
+          bytes += ie - d.in_offset;
+        }
         ++c.e;
-      } while (c.e != ge && (c.in_hi - c.in_lo < target || chunks.size() + 1 == MAX_CHUNKS));
+      } while (c.e != ge && (bytes < target || chunks.size() + 1 == MAX_CHUNKS));
+      if (c.in_hi < c.in_lo) {
+        c.in_lo = c.in_hi = in_lo;  // nothing to copy
+      }
+      runs += c.in_runs.size();
       chunks.push_back(c);
       b = c.e;
     }
+  }
+  if (runs > MAX_RUNS) {
+    single();
   }
 }
 
@@ -987,10 +1017,10 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   if (chunks.empty() || chunks.size() > MAX_CHUNKS) {
     return LDPC_CUDA_ERR_ARG;
   }
-  const uint64_t in_lo = chunks.front().in_lo, out_lo = chunks.front().out_lo;
-  uint64_t in_hi = 0, out_hi = 0;
+  uint64_t in_lo = ~0ull, in_hi = 0, out_hi = 0;
+  const uint64_t out_lo = chunks.front().out_lo;
   for (const Chunk& c : chunks) {
-    in_hi = std::max(in_hi, c.in_hi), out_hi = std::max(out_hi, c.out_hi);
+    in_lo = std::min(in_lo, c.in_lo), in_hi = std::max(in_hi, c.in_hi), out_hi = std::max(out_hi, c.out_hi);
   }
   rc = ensure_capacity(h, in_hi - in_lo, out_hi - out_lo);
   if (rc != LDPC_CUDA_OK) {
@@ -1012,9 +1042,16 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   CUDA_TRY(cudaStreamWaitEvent(h->stream2, h->ev_misc, 0));
   for (size_t ci = 0; ci != chunks.size(); ++ci) {
     const Chunk& c = chunks[ci];
-    if (c.in_hi > c.in_lo) {
-      CUDA_TRY(cudaMemcpyAsync(h->d_in + (c.in_lo - in_lo), in + c.in_lo, c.in_hi - c.in_lo, cudaMemcpyHostToDevice,
-                               h->h2d_stream));
+    if (c.in_runs.empty()) {
+      if (c.in_hi > c.in_lo) {
+        CUDA_TRY(cudaMemcpyAsync(h->d_in + (c.in_lo - in_lo), in + c.in_lo, c.in_hi - c.in_lo, cudaMemcpyHostToDevice,
+                                 h->h2d_stream));
+      }
+    } else {
+      for (const auto& run : c.in_runs) {
+        CUDA_TRY(cudaMemcpyAsync(h->d_in + (run.first - in_lo), in + run.first, run.second - run.first,
+                                 cudaMemcpyHostToDevice, h->h2d_stream));
+      }
     }
     if (preserve) {
       CUDA_TRY(cudaMemcpyAsync(h->d_out + (c.out_lo - out_lo), out + c.out_lo, c.out_hi - c.out_lo,

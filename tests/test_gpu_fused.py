@@ -202,6 +202,43 @@ def test_host_entry_pipelined_chunks_two_groups(dec):
         assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, i
 
 
+def test_host_entry_chunks_with_scattered_inputs(dec):
+    """The host entry also pipelines when the INPUT layout is not monotone in launch order (new transmissions and
+    retransmissions in different regions of the caller's buffer, padding between codeblocks): a chunk then copies the
+    contiguous runs of its codeblocks' inputs one by one. Segments of 40 codeblocks placed in a permuted order with gaps;
+    results must equal the oracle's for every codeblock."""
+    rng = np.random.default_rng(35)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    bg, Z, distinct, reps, seg = 1, 384, 20, 50, 40
+    N, kb = O.BG_N_SHORT[bg] * Z, O.BG_K[bg] * Z // 8
+    base = []
+    for i in range(distinct):
+        msg, cw = O.make_codeword(rng, bg, Z, 0, O.CRC24B)
+        x = O.awgn_llrs(rng, cw, -2.0 + 0.25 * (i % 8))
+        base.append((x, O.port().decode(bg, Z, x, crc=O.CRC24B, out_init=0x33)))
+    n = distinct * reps
+    stride = N + 64                                  # padding between codeblocks
+    nseg = n // seg
+    place = rng.permutation(nseg)                    # segment s of the launch order lives at slot place[s]
+    seg_bytes = seg * stride + 100000                # and a gap between segments (larger than the run-merging distance)
+    buf = np.zeros(nseg * seg_bytes, np.int8)
+    descs = pkg.make_descs(n, bg, Z, crc_poly=pkg.CRC24B)
+    for i in range(n):
+        off = int(place[i // seg]) * seg_bytes + (i % seg) * stride
+        descs["in_offset"][i] = off
+        buf[off:off + N] = base[i % distinct][0]
+    assert n * N > (16 << 20)
+    out = np.full(n * kb, 0x33, np.uint8)
+    launches0 = dec.launch_count
+    out, res = dec.decode_batch(descs, buf, out=out)
+    assert dec.launch_count - launches0 > 2, "expected several chunks"
+    for i in range(n):
+        bits, it = base[i % distinct][1]
+        o = int(descs["out_offset"][i])
+        assert (out[o:o + bits.size] == bits).all(), i
+        assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, i
+
+
 @pytest.mark.parametrize("misaligned", [False, True])
 def test_fused_prologue_dematch_all_cases_with_stale_priors(dec, misaligned):
     """Every rate-dematcher case of test_gpu_parity.RM_CASES through the FUSED entry: the arena is pre-filled with arbitrary
