@@ -229,7 +229,9 @@ int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle*          handle,
                                  ldpc_cuda_tb_result*       tb_results_d);
 
 /* ldpc_cuda_dematch_decode_batch followed by the assembly of its transport blocks in the same call, HOST buffers:
- * out_bits / results as in ldpc_cuda_dematch_decode_batch; tb_out / tb_results receive the assembled blocks. */
+ * out_bits / results as in ldpc_cuda_dematch_decode_batch; tb_out / tb_results receive the assembled blocks.
+ * out_bits may be NULL when no codeblock has skip_decode set: the codeblock messages then stay in device memory and only
+ * the assembled blocks and the verdicts are copied back (less PCIe traffic in both directions). */
 int ldpc_cuda_dematch_decode_tb_batch(ldpc_cuda_handle*        handle,
                                       uint32_t                 nof_codeblocks,
                                       const ldpc_cuda_cb_desc* descs,

@@ -1000,12 +1000,22 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   if (nof_tbs != 0 && (tbs == nullptr || tb_out == nullptr || tb_results == nullptr)) {
     return LDPC_CUDA_ERR_ARG;
   }
-  if (h == nullptr || descs == nullptr || in == nullptr || out == nullptr || results == nullptr ||
+  // out == nullptr (transport-block variant only): the codeblock messages stay in device memory, only the assembled blocks
+  // and the verdicts travel back. A codeblock with skip_decode needs its message from the caller, so it excludes that.
+  const bool keep_messages = (out == nullptr);
+  if (h == nullptr || descs == nullptr || in == nullptr || (keep_messages && nof_tbs == 0) || results == nullptr ||
       (fused && h->arena == nullptr)) {
     return LDPC_CUDA_ERR_ARG;
   }
   if (n == 0) {
     return LDPC_CUDA_OK;
+  }
+  if (keep_messages) {
+    for (uint32_t i = 0; i != n; ++i) {
+      if (descs[i].skip_decode) {
+        return LDPC_CUDA_ERR_ARG;
+      }
+    }
   }
   CUDA_TRY(cudaSetDevice(h->device));
   int rc = stage_work(h, n, descs, fused);
@@ -1029,7 +1039,7 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   // Output bytes / bits a codeblock does not write (skip_decode, all-zero input with a CRC, the bits of the last byte
   // beyond a message that is not a whole number of bytes) must keep the caller's contents.
   bool preserve = false;
-  for (uint32_t i = 0; i != n && !preserve; ++i) {
+  for (uint32_t i = 0; i != n && !preserve && !keep_messages; ++i) {
     preserve = descs[i].skip_decode || descs[i].crc_poly != LDPC_CUDA_CRC_NONE ||
                (bg_K(descs[i].base_graph) * descs[i].lifting_size) % 8 != 0;
   }
@@ -1037,6 +1047,10 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   uint8_t* d_out0 = h->d_out - out_lo;     // device address of host output byte 0
   // work list upload + result reset on the main stream come first; the copy streams start behind earlier work
   CUDA_TRY(cudaMemsetAsync(h->d_results, 0, sizeof(CbResult) * n, h->stream));
+  if (keep_messages) {
+    // messages a codeblock does not write (all-zero input with a CRC) read as zeros in the assembly
+    CUDA_TRY(cudaMemsetAsync(h->d_out, 0, out_hi - out_lo, h->stream));
+  }
   CUDA_TRY(cudaEventRecord(h->ev_misc, h->stream));
   CUDA_TRY(cudaStreamWaitEvent(h->h2d_stream, h->ev_misc, 0));
   CUDA_TRY(cudaStreamWaitEvent(h->stream2, h->ev_misc, 0));
@@ -1077,8 +1091,10 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
     }
     CUDA_TRY(cudaEventRecord(h->ev_done[ci], ks));
     CUDA_TRY(cudaStreamWaitEvent(h->d2h_stream, h->ev_done[ci], 0));
-    CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo, cudaMemcpyDeviceToHost,
-                             h->d2h_stream));
+    if (!keep_messages) {
+      CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo,
+                               cudaMemcpyDeviceToHost, h->d2h_stream));
+    }
   }
   if (nof_tbs != 0) {
     // transport blocks are assembled from the messages in device memory once every chunk has been decoded (the copy-out

@@ -262,6 +262,7 @@ class LdpcCuda:
                     "ldpc_cuda_tb_assemble_device")
 
     def dematch_decode_tb_batch(self, descs, rm_llrs, out, tbs, tb_out, results=None, tb_results=None):
+        """out=None: the codeblock messages stay on the device (no skip_decode codeblocks allowed)."""
         descs = np.ascontiguousarray(descs, CB_DESC)
         tbs = np.ascontiguousarray(tbs, TB_DESC)
         rm_llrs = np.ascontiguousarray(rm_llrs, np.int8)
@@ -269,7 +270,8 @@ class LdpcCuda:
             results = np.zeros(descs.size, CB_RESULT)
         if tb_results is None:
             tb_results = np.zeros(tbs.size, TB_RESULT)
-        self._check(self._L.ldpc_cuda_dematch_decode_tb_batch(self._h, descs.size, _ptr(descs), _ptr(rm_llrs), _ptr(out),
+        self._check(self._L.ldpc_cuda_dematch_decode_tb_batch(self._h, descs.size, _ptr(descs), _ptr(rm_llrs),
+                                                              None if out is None else _ptr(out),
                                                               _ptr(results), tbs.size, _ptr(tbs), _ptr(tb_out),
                                                               _ptr(tb_results)), "ldpc_cuda_dematch_decode_tb_batch")
         return out, results, tb_out, tb_results

@@ -228,3 +228,15 @@ def test_dematch_decode_tb_batch_pipelined_in_chunks(dec):
             assert int(tbres[b]["tb_crc_ok"]) == 1, b
             assert (tb_out[b * stride:b * stride + tbs // 8] == tb).all(), b
             assert int(tbres[b]["crc_remainder"]) == 0
+    # the same call with the codeblock messages left on the device (out = NULL): identical blocks and verdicts
+    tb_out2 = np.zeros(n_tb * stride, np.uint8)
+    _, res2, tb_out2, tbres2 = dec.dematch_decode_tb_batch(descs, np.concatenate(rms), None, tbs_arr, tb_out2)
+    assert (res2 == res).all() and (tbres2 == tbres).all()
+    ok = np.flatnonzero(tbres["tb_crc_ok"])
+    for b in ok:
+        assert (tb_out2[b * stride:(b + 1) * stride] == tb_out[b * stride:(b + 1) * stride]).all(), b
+    # ... which a codeblock with skip_decode (its message would have to come from the caller) excludes
+    d_skip = descs.copy()
+    d_skip["skip_decode"][3] = 1
+    with pytest.raises(pkg.LdpcCudaError):
+        dec.dematch_decode_tb_batch(d_skip, np.concatenate(rms), None, tbs_arr, tb_out2)
