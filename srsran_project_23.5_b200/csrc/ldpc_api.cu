@@ -1054,6 +1054,83 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
   CUDA_TRY(cudaEventRecord(h->ev_misc, h->stream));
   CUDA_TRY(cudaStreamWaitEvent(h->h2d_stream, h->ev_misc, 0));
   CUDA_TRY(cudaStreamWaitEvent(h->stream2, h->ev_misc, 0));
+  // Transport blocks (if any): assembled from the messages in device memory on the copy-out stream and copied back as whole
+  // blocks. When the blocks' codeblocks are decoded in block order, groups of blocks are assembled and sent back as soon as
+  // the chunk holding their last codeblock has been decoded, so that only the last group remains behind the last chunk.
+  TbResult* d_tb_res = nullptr;
+  uint8_t* d_tb_bytes = nullptr;
+  uint64_t tb_lo = ~0ull;
+  uint32_t tb_next = 0;                 // first block not yet assembled
+  std::vector<uint32_t> tb_ready;       // chunk after which block t is complete (empty: assemble everything at the end)
+  if (nof_tbs != 0) {
+    uint64_t tb_hi = 0;
+    for (uint32_t t = 0; t != nof_tbs; ++t) {
+      tb_lo = std::min<uint64_t>(tb_lo, tbs[t].tb_offset);
+      tb_hi = std::max<uint64_t>(tb_hi, tbs[t].tb_offset + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0));
+    }
+    const size_t need = (size_t)(tb_hi - tb_lo) + sizeof(TbResult) * nof_tbs + 16;
+    if (need > h->d_tb_out_cap) {
+      if (h->d_tb_out) {
+        CUDA_TRY(cudaDeviceSynchronize());
+        CUDA_TRY(cudaFree(h->d_tb_out));
+        h->d_tb_out = nullptr, h->d_tb_out_cap = 0;
+      }
+      CUDA_TRY(cudaMalloc(&h->d_tb_out, need + (need >> 2)));
+      h->d_tb_out_cap = need + (need >> 2);
+    }
+    d_tb_res = reinterpret_cast<TbResult*>(h->d_tb_out);  // results first (aligned), blocks behind them
+    d_tb_bytes = h->d_tb_out + ((sizeof(TbResult) * nof_tbs + 15) & ~(size_t)15);
+    if (chunks.size() > 1) {
+      std::vector<uint32_t> chunk_of(n);  // by caller index
+      for (size_t ci = 0; ci != chunks.size(); ++ci) {
+        for (uint32_t k = chunks[ci].b; k != chunks[ci].e; ++k) {
+          chunk_of[h->order[k]] = (uint32_t)ci;
+        }
+      }
+      tb_ready.resize(nof_tbs);
+      bool in_order = true;
+      for (uint32_t t = 0; t != nof_tbs && in_order; ++t) {
+        const ldpc_cuda_tb_desc& tb = tbs[t];
+        if (tb.nof_codeblocks == 0 || tb.first_codeblock >= n || tb.nof_codeblocks > n - tb.first_codeblock) {
+          in_order = false;  // left to the argument checks of the assembly
+          break;
+        }
+        uint32_t last = 0;
+        for (uint32_t r = 0; r != tb.nof_codeblocks; ++r) {
+          last = std::max(last, chunk_of[tb.first_codeblock + r]);
+        }
+        tb_ready[t] = last;
+        // groups are copied back as one byte range: blocks must be complete, and laid out, in index order
+        in_order = t == 0 || (tb_ready[t] >= tb_ready[t - 1] && tb.tb_offset >= tbs[t - 1].tb_offset);
+      }
+      if (!in_order) {
+        tb_ready.clear();
+      }
+    }
+  }
+  // assembles blocks [t0, t1) on the copy-out stream (which has waited for their chunks) and sends them back
+  auto assemble_tbs = [&](uint32_t t0, uint32_t t1) -> int {
+    if (t0 >= t1) {
+      return LDPC_CUDA_OK;
+    }
+    int arc = enqueue_tb_assemble(h, h->d2h_stream, t1 - t0, tbs + t0, n, descs, d_out0, h->d_results, d_tb_bytes - tb_lo,
+                                  d_tb_res + t0);
+    if (arc != LDPC_CUDA_OK) {
+      cudaStreamSynchronize(h->d2h_stream);
+      cudaStreamSynchronize(h->stream2);
+      cudaStreamSynchronize(h->stream);
+      return arc;
+    }
+    uint64_t lo = ~0ull, hi = 0;
+    for (uint32_t t = t0; t != t1; ++t) {
+      lo = std::min<uint64_t>(lo, tbs[t].tb_offset);
+      hi = std::max<uint64_t>(hi, tbs[t].tb_offset + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0));
+    }
+    CUDA_TRY(cudaMemcpyAsync(tb_out + lo, d_tb_bytes + (lo - tb_lo), hi - lo, cudaMemcpyDeviceToHost, h->d2h_stream));
+    tb_next = t1;
+    return LDPC_CUDA_OK;
+  };
+  const uint32_t tb_group = std::max<uint32_t>(1, (nof_tbs + 3) / 4);  // at most ~4 early groups
   for (size_t ci = 0; ci != chunks.size(); ++ci) {
     const Chunk& c = chunks[ci];
     if (c.in_runs.empty()) {
@@ -1095,34 +1172,26 @@ static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* 
       CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo,
                                cudaMemcpyDeviceToHost, h->d2h_stream));
     }
+    if (!tb_ready.empty() && ci + 1 != chunks.size()) {
+      uint32_t t1 = tb_next;
+      while (t1 != nof_tbs && tb_ready[t1] <= ci) {
+        ++t1;
+      }
+      if (t1 - tb_next >= tb_group) {
+        rc = assemble_tbs(tb_next, t1);
+        if (rc != LDPC_CUDA_OK) {
+          return rc;
+        }
+      }
+    }
   }
   if (nof_tbs != 0) {
-    // transport blocks are assembled from the messages in device memory once every chunk has been decoded (the copy-out
-    // stream already waits for all of them) and leave as whole blocks
-    uint64_t tb_lo = ~0ull, tb_hi = 0;
-    for (uint32_t t = 0; t != nof_tbs; ++t) {
-      tb_lo = std::min<uint64_t>(tb_lo, tbs[t].tb_offset);
-      tb_hi = std::max<uint64_t>(tb_hi, tbs[t].tb_offset + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0));
-    }
-    const size_t need = (size_t)(tb_hi - tb_lo) + sizeof(TbResult) * nof_tbs + 16;
-    if (need > h->d_tb_out_cap) {
-      if (h->d_tb_out) {
-        CUDA_TRY(cudaFree(h->d_tb_out));
-        h->d_tb_out = nullptr, h->d_tb_out_cap = 0;
-      }
-      CUDA_TRY(cudaMalloc(&h->d_tb_out, need + (need >> 2)));
-      h->d_tb_out_cap = need + (need >> 2);
-    }
-    TbResult* d_tb_res = reinterpret_cast<TbResult*>(h->d_tb_out);  // results first (aligned), blocks behind them
-    uint8_t* d_tb_bytes = h->d_tb_out + ((sizeof(TbResult) * nof_tbs + 15) & ~(size_t)15);
-    rc = enqueue_tb_assemble(h, h->d2h_stream, nof_tbs, tbs, n, descs, d_out0, h->d_results, d_tb_bytes - tb_lo, d_tb_res);
+    // transport blocks not assembled behind their own chunk (see above) are assembled once every chunk has been decoded
+    // (the copy-out stream already waits for all of them)
+    rc = assemble_tbs(tb_next, nof_tbs);
     if (rc != LDPC_CUDA_OK) {
-      cudaStreamSynchronize(h->d2h_stream);
-      cudaStreamSynchronize(h->stream2);
-      cudaStreamSynchronize(h->stream);
       return rc;
     }
-    CUDA_TRY(cudaMemcpyAsync(tb_out + tb_lo, d_tb_bytes, tb_hi - tb_lo, cudaMemcpyDeviceToHost, h->d2h_stream));
     CUDA_TRY(cudaMemcpyAsync(tb_results, d_tb_res, sizeof(TbResult) * nof_tbs, cudaMemcpyDeviceToHost, h->d2h_stream));
   }
   CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->d2h_stream));
