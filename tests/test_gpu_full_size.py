@@ -90,3 +90,26 @@ def test_cfg4_full_size_round_trip_and_batch_independence():
             assert (out6_h[i] == bits6).all(), i
     finally:
         dec.close()
+
+
+def test_cfg3_cfg5_full_slots_harq_properties():
+    """BASELINE configs 3 + 5 at full size through the fused entry (bench.py's pusch_slot workload: 16 cells x 152-codeblock
+    full-slot transport blocks per slot, soft buffers in the HBM arena, 12.5 % retransmissions): transport blocks sent
+    above threshold pass their CRC24A and come back identical to what was sent; those sent below threshold fail with
+    every codeblock running all 6 iterations; their rv 2 retransmissions, soft-combined with the stored rv 0 LLRs, pass
+    (HARQ gain), also through the host entry."""
+    import torch
+    import bench
+    dev = torch.device("cuda", 0)
+    dec = pkg.LdpcCuda(device=0, max_codeblocks=20000)
+    try:
+        stream = torch.cuda.ExternalStream(dec.stream, device=dev)
+        r = bench.pusch_slot_extra(torch, pkg, dec, dev, stream, 1)
+    finally:
+        dec.close()
+    assert r["crc_pass_rate"] == {"new_good_snr": 1.0, "new_bad_snr": 0.0, "retransmission": 1.0}
+    assert r["tb_crc_ok_rate"]["new_good_snr"] == 1.0 and r["tb_crc_ok_rate"]["new_bad_snr"] == 0.0
+    assert r["tb_crc_ok_rate"]["slot_b_incl_retransmissions"] == 1.0
+    assert r["tb_crc_ok_rate"]["assembled_blocks_identical_to_sent"] is True
+    assert r["mean_iterations"]["new_bad_snr"] == 6.0 and r["mean_iterations"]["new_good_snr"] < 3.0
+    assert r["e2e"].get("tb_crc_ok_rate_slot_b") == 1.0, r["e2e"]
