@@ -311,6 +311,18 @@ int ldpc_cuda_descramble_placeholders_device(ldpc_cuda_handle*                 h
                                              uint32_t                          nof_re_indexes,
                                              int8_t*                           llrs_d);
 
+/* pusch_demodulator_impl::descramble WITH config.placeholders, HOST buffers, synchronous (in may equal out):
+ * ldpc_cuda_descramble followed by the placeholder amendment before the LLRs leave the device. */
+int ldpc_cuda_descramble_uci(ldpc_cuda_handle* handle,
+                             uint32_t          c_init,
+                             uint32_t          nof_llrs,
+                             int               mod_order,
+                             uint32_t          nof_layers,
+                             uint32_t          nof_re,
+                             const uint16_t*   re_indexes,
+                             const int8_t*     in,
+                             int8_t*           out);
+
 /* ---------------------------------------------------------------------------------------------------------------------
  * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,
  * rx_softbuffer_codeblock_pool.h). Offsets in ldpc_cuda_cb_desc::soft_offset index into it.

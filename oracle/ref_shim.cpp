@@ -878,4 +878,36 @@ void ref_descramble_placeholders(unsigned        rnti,
                    config);
 }
 
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+// The same call through the product's adaptor descramble_cuda(mapper, out, in, config) (drop-in library only).
+int dropin_descramble_placeholders(unsigned        rnti,
+                                   unsigned        n_id,
+                                   unsigned        n,
+                                   const int8_t*   in,
+                                   int8_t*         out,
+                                   unsigned        mod_order,
+                                   unsigned        nof_layers,
+                                   unsigned        nof_re,
+                                   const uint16_t* re_indexes)
+{
+  std::unique_ptr<demodulation_mapper> mapper = create_demodulation_mapper_cuda(0);
+  if (!mapper) {
+    return -2;
+  }
+  pusch_demodulator::configuration config = {};
+  config.rnti                             = static_cast<uint16_t>(rnti);
+  config.n_id                             = n_id;
+  config.modulation                       = static_cast<modulation_scheme>(mod_order);
+  config.nof_tx_layers                    = nof_layers;
+  for (unsigned i = 0; i != nof_re; ++i) {
+    config.placeholders.push_back(re_indexes[i]);
+  }
+  descramble_cuda(*mapper,
+                  span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(out), n),
+                  span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), n),
+                  config);
+  return 0;
+}
+#endif
+
 } // extern "C"

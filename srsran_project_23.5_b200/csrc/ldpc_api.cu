@@ -1308,6 +1308,40 @@ int ldpc_cuda_descramble(ldpc_cuda_handle* h, uint32_t c_init, uint32_t nof_llrs
   return demod_host(h, job, in, nof_llrs, nullptr, 0, out, nof_llrs);
 }
 
+int ldpc_cuda_descramble_uci(ldpc_cuda_handle* h, uint32_t c_init, uint32_t nof_llrs, int mod_order, uint32_t nof_layers,
+                             uint32_t nof_re, const uint16_t* re_indexes, const int8_t* in, int8_t* out)
+{
+  if (h == nullptr || in == nullptr || out == nullptr || nof_re > 0xffffu || nof_layers == 0 || nof_layers > 8 ||
+      (nof_re != 0 && re_indexes == nullptr)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_llrs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  int rc = ensure_capacity(h, nof_llrs, nof_llrs);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  ldpc_cuda_demod_desc job = {};
+  job.mod_order = 0, job.descramble = 1, job.nof_symbols = nof_llrs, job.c_init = c_init;
+  ldpc_cuda_placeholder_desc ph = {};
+  ph.c_init = c_init, ph.nof_llrs = nof_llrs, ph.nof_re = (uint16_t)nof_re, ph.mod_order = (uint8_t)mod_order;
+  ph.nof_layers = (uint8_t)nof_layers;
+  CUDA_TRY(cudaMemcpyAsync(h->d_in, in, nof_llrs, cudaMemcpyHostToDevice, h->stream));
+  rc = enqueue_demod(h, h->stream, 1, &job, nullptr, nullptr, h->d_in, reinterpret_cast<int8_t*>(h->d_out));
+  if (rc == LDPC_CUDA_OK) {
+    rc = enqueue_placeholders(h, h->stream, 1, &ph, re_indexes, nof_re, reinterpret_cast<int8_t*>(h->d_out));
+  }
+  if (rc != LDPC_CUDA_OK) {
+    cudaStreamSynchronize(h->stream);
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(out, h->d_out, nof_llrs, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
+}
+
 int ldpc_cuda_descramble_placeholders_device(ldpc_cuda_handle* h, uint32_t nof_jobs, const ldpc_cuda_placeholder_desc* jobs,
                                              const uint16_t* re_indexes, uint32_t nof_re_indexes, int8_t* llrs_d)
 {

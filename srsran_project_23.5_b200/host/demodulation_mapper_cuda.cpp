@@ -1,5 +1,6 @@
 // See demodulation_mapper_cuda.h.
 #include "demodulation_mapper_cuda.h"
+#include <vector>
 
 #include "../../include/ldpc_cuda.h"
 #include "srsran/ran/modulation_scheme.h"
@@ -77,4 +78,36 @@ void srsran::descramble_cuda(demodulation_mapper&             handle_owner,
                              reinterpret_cast<const int8_t*>(in.data()),
                              reinterpret_cast<int8_t*>(out.data())),
         "ldpc_cuda_descramble");
+}
+
+void srsran::descramble_cuda(demodulation_mapper&                    handle_owner,
+                             span<log_likelihood_ratio>              out,
+                             span<const log_likelihood_ratio>        in,
+                             const pusch_demodulator::configuration& config)
+{
+  auto* owner = dynamic_cast<demodulation_mapper_cuda*>(&handle_owner);
+  if (owner == nullptr || in.size() != out.size()) {
+    check(LDPC_CUDA_ERR_ARG, "descramble_cuda: not a cuda mapper or incompatible lengths");
+  }
+  // The list only exposes its entries through for_each (ulsch_placeholder_list.h:73-95), as soft-bit positions
+  // Qm (layers re + layer) + 1; the RE indexes are recovered from the entries of layer 0.
+  const unsigned            qm     = get_bits_per_symbol(config.modulation);
+  const unsigned            layers = config.nof_tx_layers;
+  std::vector<uint16_t>     re_indexes;
+  config.placeholders.for_each(config.modulation, layers, [&](unsigned i_bit, unsigned /* nof_x */) {
+    const unsigned symbol = (i_bit - 1) / qm;
+    if (symbol % layers == 0) {
+      re_indexes.push_back(static_cast<uint16_t>(symbol / layers));
+    }
+  });
+  check(ldpc_cuda_descramble_uci(owner->handle(),
+                                 config.rnti * 32768U + config.n_id,
+                                 static_cast<uint32_t>(in.size()),
+                                 static_cast<int>(qm),
+                                 layers,
+                                 static_cast<uint32_t>(re_indexes.size()),
+                                 re_indexes.data(),
+                                 reinterpret_cast<const int8_t*>(in.data()),
+                                 reinterpret_cast<int8_t*>(out.data())),
+        "ldpc_cuda_descramble_uci");
 }

@@ -9,6 +9,7 @@
 #pragma once
 
 #include "srsran/phy/upper/channel_modulation/demodulation_mapper.h"
+#include "srsran/phy/upper/channel_processors/pusch_demodulator.h"
 
 #include <memory>
 
@@ -24,5 +25,13 @@ void descramble_cuda(demodulation_mapper&             handle_owner,
                      span<log_likelihood_ratio>       out,
                      span<const log_likelihood_ratio> in,
                      unsigned                         c_init);
+
+/// pusch_demodulator_impl::descramble (lib/phy/upper/channel_processors/pusch_demodulator_impl.cpp:100-152) as a whole:
+/// c_init = rnti * 2^15 + n_id and the repetition placeholders of \c config.placeholders for \c config.modulation and
+/// \c config.nof_tx_layers, on the device.
+void descramble_cuda(demodulation_mapper&                    handle_owner,
+                     span<log_likelihood_ratio>              out,
+                     span<const log_likelihood_ratio>        in,
+                     const pusch_demodulator::configuration& config);
 
 } // namespace srsran

@@ -103,6 +103,7 @@ def library():
         L.ldpc_cuda_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp]
         L.ldpc_cuda_demodulate_batch_device.argtypes = [vp, u32, vp, vp, vp, vp, vp]
         L.ldpc_cuda_descramble_placeholders_device.argtypes = [vp, u32, vp, vp, u32, vp]
+        L.ldpc_cuda_descramble_uci.argtypes = [vp, u32, u32, ctypes.c_int, u32, u32, vp, vp, vp]
         L.ldpc_cuda_demodulate_soft.argtypes = [vp, i32, i32, u32, vp, vp, vp]
         L.ldpc_cuda_descramble.argtypes = [vp, u32, u32, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
@@ -290,6 +291,15 @@ class LdpcCuda:
         llrs = np.ascontiguousarray(llrs, np.int8)
         out = np.zeros_like(llrs)
         self._check(self._L.ldpc_cuda_descramble(self._h, c_init, llrs.size, _ptr(llrs), _ptr(out)), "ldpc_cuda_descramble")
+        return out
+
+    def descramble_uci(self, c_init, llrs, mod_order, nof_layers, re_indexes):
+        """pusch_demodulator_impl::descramble with the repetition placeholders of the listed REs, host buffers."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        re_indexes = np.ascontiguousarray(re_indexes, np.uint16)
+        out = np.zeros_like(llrs)
+        self._check(self._L.ldpc_cuda_descramble_uci(self._h, c_init, llrs.size, mod_order, nof_layers, re_indexes.size,
+                                                     _ptr(re_indexes), _ptr(llrs), _ptr(out)), "ldpc_cuda_descramble_uci")
         return out
 
     def demodulate_batch_device(self, jobs, symbols_ptr, noise_ptr, in_llrs_ptr, llrs_ptr):

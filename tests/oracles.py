@@ -182,6 +182,9 @@ class RefOracle:
         L.ref_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p, c_uint]
         L.ref_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
         L.ref_descramble_placeholders.argtypes = [c_uint, c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint, c_void_p]
+        if hasattr(L, "dropin_descramble_placeholders"):  # oracle/_ref/libdropin.so only
+            L.dropin_descramble_placeholders.argtypes = [c_uint, c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint,
+                                                         c_void_p]
         self._decoders = {}
         self._dematchers = {}
 
@@ -202,11 +205,17 @@ class RefOracle:
         self.lib.ref_descramble(c_init, llrs.size, _ptr(llrs), _ptr(out))
         return out
 
-    def descramble_placeholders(self, rnti, n_id, llrs, mod_order, nof_layers, re_indexes):
-        """The reference's own pusch_demodulator_impl::descramble (c_init = rnti * 2^15 + n_id)."""
+    def descramble_placeholders(self, rnti, n_id, llrs, mod_order, nof_layers, re_indexes, cuda=False):
+        """The reference's own pusch_demodulator_impl::descramble (c_init = rnti * 2^15 + n_id); cuda=True (drop-in library):
+        the product's descramble_cuda(mapper, out, in, config) adaptor on the same configuration."""
         llrs = np.ascontiguousarray(llrs, np.int8)
         re_indexes = np.ascontiguousarray(re_indexes, np.uint16)
         out = np.zeros_like(llrs)
+        if cuda:
+            rc = self.lib.dropin_descramble_placeholders(rnti, n_id, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
+                                                         re_indexes.size, _ptr(re_indexes))
+            assert rc == 0
+            return out
         self.lib.ref_descramble_placeholders(rnti, n_id, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
                                              re_indexes.size, _ptr(re_indexes))
         return out

@@ -217,6 +217,12 @@ def test_descramble_with_uci_placeholders(dec):
         bad = np.flatnonzero(out[off:off + w.size] != w)
         assert bad.size == 0, (i, cases[i][:3], bad[:8])
         assert (out[off + w.size:off + w.size + 5] == 0x55).all()
+    # the host-buffer entry (ldpc_cuda_descramble_uci) on the first cases
+    for i, (q, layers, nof_re, res) in enumerate(cases[:4]):
+        c_init = int(jobs[i]["c_init"])
+        llrs = rng.integers(-127, 128, q * layers * nof_re).astype(np.int8)
+        assert (dec.descramble_uci(c_init, llrs, q, layers, res) ==
+                O.port().descramble_placeholders(c_init, llrs, q, layers, res)).all(), i
     # argument checks: RE list shorter than a descriptor claims, unsupported modulation order
     bad = ph[:1].copy()
     bad["first_re"] = len(res_all)

@@ -226,3 +226,18 @@ def test_demodulation_mapper_interface(lib, mod_order, pi2, batch):
     assert (got == want).all()
     simd = lib.demodulate_soft(mod_order, sym, nv, pi2, 0)
     assert np.abs(simd.astype(np.int16) - got).max() <= 1
+
+
+def test_descramble_with_placeholders_interface(lib):
+    """descramble_cuda(mapper, out, in, pusch_demodulator::configuration) against the reference's own
+    pusch_demodulator_impl::descramble (pusch_demodulator_impl.cpp:100-152) on the same configuration: rnti / n_id,
+    modulation, layers and a ulsch_placeholder_list."""
+    rng = np.random.default_rng(50)
+    for q, layers, nof_re, res in [(2, 1, 600, [0, 5, 6, 100, 599]), (4, 2, 400, [3, 4, 5, 200, 399]),
+                                   (6, 1, 1366, [1, 7, 682, 1365]), (8, 4, 300, [0, 1, 2, 150, 299]),
+                                   (1, 1, 500, [0, 2, 4, 250, 498]), (8, 2, 40000, list(range(3, 40000, 97))), (4, 1, 50, [])]:
+        rnti, n_id = int(rng.integers(1, 65536)), int(rng.integers(0, 1024))
+        llrs = rng.integers(-127, 128, q * layers * nof_re).astype(np.int8)
+        want = lib.descramble_placeholders(rnti, n_id, llrs, q, layers, res)
+        got = lib.descramble_placeholders(rnti, n_id, llrs, q, layers, res, cuda=True)
+        assert (got == want).all(), (q, layers, np.flatnonzero(got != want)[:8])
