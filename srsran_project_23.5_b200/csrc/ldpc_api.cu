@@ -171,6 +171,23 @@ int upload_constants()
     dt.qam16_gain = 4 * s10;
     dt.qam16_threshold = 2 * s10;
     CUDA_TRY(cudaMemcpyToSymbol(c_demod, &dt, sizeof(dt)));
+    // x1 words from chip Nc = 1600 on (TS 38.211 5.2.1: x1(n + 31) = x1(n + 3) ^ x1(n), x1(0) = 1, x1(1..30) = 0)
+    {
+      static std::vector<unsigned> x1w(DEMOD_X1_WORDS);
+      uint32_t x1 = 1u;
+      for (unsigned n = 0; n != 1600u; ++n) {
+        x1 = (x1 >> 1) | ((((x1 >> 3) ^ x1) & 1u) << 30);
+      }
+      for (unsigned w = 0; w != DEMOD_X1_WORDS; ++w) {
+        unsigned word = 0;
+        for (unsigned b = 0; b != 32u; ++b) {
+          word |= (x1 & 1u) << b;
+          x1 = (x1 >> 1) | ((((x1 >> 3) ^ x1) & 1u) << 30);
+        }
+        x1w[w] = word;
+      }
+      CUDA_TRY(cudaMemcpyToSymbol(g_x1_words, x1w.data(), sizeof(unsigned) * DEMOD_X1_WORDS));
+    }
     // A^(2^j) of the two shift registers (state bit i = x(n + i); row i = state bits whose XOR is the new bit i)
     static unsigned pw[2][32][32];
     std::memset(pw, 0, sizeof(pw));

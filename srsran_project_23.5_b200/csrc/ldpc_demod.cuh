@@ -58,6 +58,11 @@ __constant__ DemodTables c_demod;
 // Rows of A^(2^j) for the x1 (index 0) and x2 (index 1) shift registers, state bit i = x(n + i).
 __device__ unsigned g_prg_pow[2][32][32];
 
+// 32-chip words of the x1 sequence from chip Nc = 1600 on (word w = chips 1600 + 32 w ... + 31, chip i = bit i): x1 starts
+// from a fixed state, so its first 2^21 chips are computed once on the host (256 KB, L2-resident).
+constexpr unsigned DEMOD_X1_WORDS = 1u << 16;
+__device__ __align__(16) unsigned g_x1_words[DEMOD_X1_WORDS];
+
 constexpr int DEMOD_THREADS = 256;
 constexpr int DEMOD_CHUNK = DEMOD_THREADS * 32;  // LLRs per block and span
 #ifndef DEMOD_MIN_BLOCKS
@@ -464,6 +469,73 @@ __device__ __forceinline__ void demod_loop_qam64(const DemodJob& job, const Demo
   }
 }
 
+// Phase 1 of a warp: the 32-chip words of its spans x 1024 chips starting at chip j0 + first of the job, into
+// chips[(first / 32) ...]. A warp owns spans x 1024 consecutive chips. The state of the registers at chip 1600 + first chip
+// of the warp (Nc = 1600, TS 38.211 5.2.1) is reached with the matrix powers A^(2^j) (one row per lane, ballot = matrix x
+// vector). The chips then form groups of 256 (4 per span, at most 32): lane L owns group L; its start state is reached by L
+// co-operative products with A^256 (the rows stay in registers, every lane keeps the state of its own step); from there
+// the lane produces its eight words alone, advancing by 28 + 4 chips in between. (Earlier versions: every lane stepping
+// from the warp's start, up to 36 steps, was a third of the kernel's instructions; groups of 4 lanes per span with 8
+// products per span still a quarter: profiles/r01_ncu_demod_summary.txt.) X1_TABLE: only x2 is generated, the words of x1
+// come from g_x1_words.
+template <bool X1_TABLE>
+__device__ __forceinline__ void demod_chip_words(const DemodJob& job, unsigned* chips, unsigned j0, unsigned first,
+                                                 unsigned spans, unsigned lane)
+{
+  const unsigned n = 1600u + j0 + first;
+  unsigned s1 = 1u, s2 = job.c_init & 0x7fffffffu;
+  for (unsigned jb = 0; jb < 32; ++jb) {
+    if ((n >> jb) & 1u) {
+      if (!X1_TABLE) {
+        s1 = __ballot_sync(0xffffffffu, __popc(g_prg_pow[0][jb][lane] & s1) & 1);
+      }
+      s2 = __ballot_sync(0xffffffffu, __popc(g_prg_pow[1][jb][lane] & s2) & 1);
+    }
+  }
+  const unsigned left = (j0 + first < job.nof_llrs) ? job.nof_llrs - (j0 + first) : 0u;
+  const unsigned groups = min(4u * spans, (left + 255u) / 256u);
+  const unsigned q1 = X1_TABLE ? 0u : g_prg_pow[0][8][lane], q2 = g_prg_pow[1][8][lane];
+  unsigned m1 = s1, m2 = s2;
+  for (unsigned g = 1; g < groups; ++g) {
+    if (!X1_TABLE) {
+      s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
+    }
+    s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
+    if (lane == g) {
+      m1 = s1, m2 = s2;
+    }
+  }
+  if (lane < groups) {
+    uint4* dst_words = reinterpret_cast<uint4*>(&chips[first / 32u + 8u * lane]);
+    const uint4* x1_words = reinterpret_cast<const uint4*>(&g_x1_words[X1_TABLE ? (j0 + first) / 32u + 8u * lane : 0u]);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      unsigned w[4];
+      uint4 x1 = make_uint4(0u, 0u, 0u, 0u);
+      if (X1_TABLE) {
+        x1 = __ldg(x1_words + h);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const unsigned b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
+        if (X1_TABLE) {
+          w[k] = (k == 0 ? x1.x : k == 1 ? x1.y : k == 2 ? x1.z : x1.w) ^ (m2 | (b2 << 31));
+        } else {
+          const unsigned b1 = ((m1 >> 3) ^ m1) & 1u;
+          w[k] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
+        }
+        if (h == 0 || k < 3) {
+          if (!X1_TABLE) {
+            m1 = prg_advance(prg_advance(m1, 28u, false), 4u, false);
+          }
+          m2 = prg_advance(prg_advance(m2, 28u, true), 4u, true);
+        }
+      }
+      dst_words[h] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
 // grid (chunks, jobs). in_llrs: input of descramble-only jobs.
 __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_kernel(const DemodJob* __restrict__ jobs,
                                                                    const float2* __restrict__ symbols,
@@ -487,50 +559,13 @@ __global__ void __launch_bounds__(DEMOD_THREADS, DEMOD_MIN_BLOCKS) ldpc_demod_ke
     tab.line[k][t & 15] = make_float2(c_demod.slope[m][k][i], c_demod.intercept[m][k][i]);
   }
   if (job.descramble) {
-    // A warp owns spans x 1024 consecutive chips. State of both registers at chip 1600 + first chip of the warp
-    // (Nc = 1600, TS 38.211 5.2.1):
+    // x1 does not depend on c_init: while the warp's chips lie inside the precomputed part of its sequence, its words
+    // are read from a table and only x2 is generated
     const unsigned first = (t >> 5) * 1024u * spans;
-    const unsigned n = 1600u + j0 + first;
-    unsigned s1 = 1u, s2 = job.c_init & 0x7fffffffu;
-    for (unsigned jb = 0; jb < 32; ++jb) {
-      if ((n >> jb) & 1u) {
-        const unsigned r1 = g_prg_pow[0][jb][lane], r2 = g_prg_pow[1][jb][lane];
-        s1 = __ballot_sync(0xffffffffu, __popc(r1 & s1) & 1);
-        s2 = __ballot_sync(0xffffffffu, __popc(r2 & s2) & 1);
-      }
-    }
-    // The warp's chips form groups of 256 (4 per span, at most 32): lane L owns group L. Its start state is reached by L
-    // co-operative products with A^256 (the rows stay in registers, every lane keeps the state of its own step); from
-    // there the lane produces its eight 32-chip words alone, advancing by 28 + 4 chips in between. (Earlier versions:
-    // every lane stepping from the warp's start, up to 36 steps, was a third of the kernel's instructions; groups of 4
-    // lanes per span with 8 products per span still a quarter: profiles/r01_ncu_demod_summary.txt.)
-    const unsigned left = (j0 + first < job.nof_llrs) ? job.nof_llrs - (j0 + first) : 0u;
-    const unsigned groups = min(4u * spans, (left + 255u) / 256u);
-    const unsigned q1 = g_prg_pow[0][8][lane], q2 = g_prg_pow[1][8][lane];
-    unsigned m1 = s1, m2 = s2;
-    for (unsigned g = 1; g < groups; ++g) {
-      s1 = __ballot_sync(0xffffffffu, __popc(q1 & s1) & 1);
-      s2 = __ballot_sync(0xffffffffu, __popc(q2 & s2) & 1);
-      if (lane == g) {
-        m1 = s1, m2 = s2;
-      }
-    }
-    if (lane < groups) {
-      uint4* dst_words = reinterpret_cast<uint4*>(&chips[(t >> 5) * 32u * spans + 8u * lane]);
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        unsigned w[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const unsigned b1 = ((m1 >> 3) ^ m1) & 1u, b2 = ((m2 >> 3) ^ (m2 >> 2) ^ (m2 >> 1) ^ m2) & 1u;
-          w[k] = (m1 ^ m2) | ((b1 ^ b2) << 31);  // chip i of the word = bit i
-          if (h == 0 || k < 3) {
-            m1 = prg_advance(prg_advance(m1, 28u, false), 4u, false);
-            m2 = prg_advance(prg_advance(m2, 28u, true), 4u, true);
-          }
-        }
-        dst_words[h] = make_uint4(w[0], w[1], w[2], w[3]);
-      }
+    if ((j0 + first) / 32u + 32u * spans <= DEMOD_X1_WORDS) {
+      demod_chip_words<true>(job, chips, j0, first, spans, lane);
+    } else {
+      demod_chip_words<false>(job, chips, j0, first, spans, lane);
     }
   } else {
     for (unsigned k = t; k < DEMOD_THREADS * spans; k += DEMOD_THREADS) {

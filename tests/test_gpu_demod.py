@@ -75,7 +75,8 @@ def test_demodulate_soft_special_values(dec, mod_order):
 
 
 @pytest.mark.parametrize("c_init,n", [(0, 1), (1, 31), (0x7fffffff, 33), ((0x4601 << 15) + 935, 100001),
-                                      (0x12345678, 8192), (77, 8193), ((0xffff << 15) + 1023, 1362816)])
+                                      (0x12345678, 8192), (77, 8193), ((0xffff << 15) + 1023, 1362816),
+                                      (0x2468ace, (1 << 21) + 70001)])  # beyond the precomputed x1 words
 def test_descramble_bit_exact(dec, c_init, n):
     rng = np.random.default_rng(n)
     llrs = rng.integers(-127, 128, n).astype(np.int8)
