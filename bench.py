@@ -30,7 +30,7 @@ EDGES_BG1 = 316
 ALG_BYTES_PER_CB = N_LLR + OUT_BYTES  # 25344 B in + 1056 B out = 26400 B / codeblock
 INT_OPS_PER_EMU = 20                  # SURVEY.md 8(d) canonical cost of one edge-message update
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the decode kernel over 65536 codeblocks, from the
-# `ncu --set full` capture summarised in profiles/r01_ncu_tmem_head_summary.txt (1.6712 GB + 0.0717 GB)
+# `ncu --set full` capture summarised in profiles/r01_ncu_tmem_head_summary.txt (final build: 1.6708 GB + 0.0704 GB)
 NCU_TRAFFIC_BYTES_PER_CB = 1.7412e9 / 65536
 METRIC = "LDPC decoded info Gb/s (BG1 Z=384, 6 iters)"
 
