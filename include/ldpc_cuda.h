@@ -228,6 +228,31 @@ int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle*          handle,
                                  uint8_t*                   tb_out_d,
                                  ldpc_cuda_tb_result*       tb_results_d);
 
+/* ldpc_cuda_tb_assemble_device for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * Same arguments, same results, same kernels; the work records and per-chunk CRC remainders live in one fixed array in
+ * device memory (file-scope `static __device__`, about 100 KB, held by every GPU that loads the library until exit) and
+ * the records are staged through a fixed host array, so the call performs no cudaMalloc / cudaFree / cudaHostAlloc.
+ * Limits per call (beyond them: LDPC_CUDA_ERR_CAPACITY and a message on stderr, nothing is enqueued):
+ * LDPC_CUDA_NOALLOC_MAX_TBS transport blocks, LDPC_CUDA_NOALLOC_MAX_CBS codeblocks (= nof_codeblocks, the length of
+ * descs), LDPC_CUDA_NOALLOC_MAX_CHUNKS chunks of 1024 assembled bytes summed over the blocks (a 16-cell slot of full-band
+ * blocks needs 16 / 2432 / 2512). The array is shared by all handles of a device and keeps the last call's contents (the
+ * remainders a call reads are cleared first): calls on one stream are ordered by it; calls whose GPU work may overlap
+ * (different handles or streams of one device) race on it and must be serialised by the caller. The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress); make it once before capturing a graph. */
+#define LDPC_CUDA_NOALLOC_MAX_TBS 64u
+#define LDPC_CUDA_NOALLOC_MAX_CBS 4096u
+#define LDPC_CUDA_NOALLOC_MAX_CHUNKS 8192u
+int ldpc_cuda_tb_assemble_device_noalloc(ldpc_cuda_handle*          handle,
+                                         uint32_t                   nof_tbs,
+                                         const ldpc_cuda_tb_desc*   tbs,
+                                         uint32_t                   nof_codeblocks,
+                                         const ldpc_cuda_cb_desc*   descs,
+                                         const uint8_t*             out_bits_d,
+                                         const ldpc_cuda_cb_result* results_d,
+                                         uint8_t*                   tb_out_d,
+                                         ldpc_cuda_tb_result*       tb_results_d);
+
 /* ldpc_cuda_dematch_decode_batch followed by the assembly of its transport blocks in the same call, HOST buffers:
  * out_bits / results as in ldpc_cuda_dematch_decode_batch; tb_out / tb_results receive the assembled blocks.
  * out_bits may be NULL when no codeblock has skip_decode set: the codeblock messages then stay in device memory and only

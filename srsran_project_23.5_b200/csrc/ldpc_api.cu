@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1256,6 +1257,132 @@ int ldpc_cuda_tb_assemble_device(ldpc_cuda_handle* h, uint32_t nof_tbs, const ld
   CUDA_TRY(cudaSetDevice(h->device));
   return enqueue_tb_assemble(h, h->stream, nof_tbs, tbs, n, descs, out_bits_d, reinterpret_cast<const CbResult*>(results_d),
                              tb_out_d, reinterpret_cast<TbResult*>(tb_results_d));
+}
+
+// ---- transport-block assembly without any allocation -------------------------------------------------------------------
+// Same kernels as ldpc_cuda_tb_assemble_device, but the work records and the per-chunk partial remainders live in ONE
+// file-scope device array of fixed size instead of the handle's growable cudaMalloc'd buffer, and the records are staged
+// through a fixed host array instead of pinned memory that grows on demand: no cudaMalloc / cudaFree / cudaHostAlloc on
+// any call. Every handle of a device shares the array, and it keeps the previous call's contents.
+static_assert(LDPC_CUDA_NOALLOC_MAX_TBS <= 65535u, "transport blocks index blockIdx.y");
+constexpr size_t NOALLOC_OFF_CB = sizeof(TbWork) * LDPC_CUDA_NOALLOC_MAX_TBS;
+constexpr size_t NOALLOC_OFF_PARTIAL = (NOALLOC_OFF_CB + sizeof(TbCb) * LDPC_CUDA_NOALLOC_MAX_CBS + 255) & ~(size_t)255;
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_OFF_PARTIAL + sizeof(unsigned) * LDPC_CUDA_NOALLOC_MAX_CHUNKS;
+static __device__ __align__(256) unsigned char g_tb_noalloc_scratch[NOALLOC_SCRATCH_BYTES];  // ~100 KB per GPU
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex s_noalloc_mutex;                                 // guards the two host-side objects below
+static unsigned char* s_noalloc_dev[NOALLOC_MAX_DEVICES] = {};     // device address of the array, per device
+static unsigned char s_noalloc_stage[NOALLOC_OFF_PARTIAL];         // host staging of the work records (pageable)
+
+// In host code `g_tb_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address a kernel can
+// use is resolved once per device, with that device current.
+static int noalloc_scratch_of(int device, unsigned char** ptr)
+{
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  if (s_noalloc_dev[device] == nullptr) {
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_tb_noalloc_scratch));
+    s_noalloc_dev[device] = static_cast<unsigned char*>(p);
+  }
+  *ptr = s_noalloc_dev[device];
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_tb_assemble_device_noalloc(ldpc_cuda_handle* h, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs, uint32_t n,
+                                         const ldpc_cuda_cb_desc* descs, const uint8_t* out_bits_d,
+                                         const ldpc_cuda_cb_result* results_d, uint8_t* tb_out_d,
+                                         ldpc_cuda_tb_result* tb_results_d)
+{
+  if (h == nullptr || tbs == nullptr || descs == nullptr || out_bits_d == nullptr || results_d == nullptr ||
+      tb_out_d == nullptr || tb_results_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (nof_tbs == 0) {
+    return LDPC_CUDA_OK;
+  }
+  uint64_t total_chunks = 0;
+  for (uint32_t t = 0; t != nof_tbs; ++t) {
+    total_chunks += ((uint64_t)tbs[t].tbs_bits / 8 + 3 + TB_CHUNK - 1) / TB_CHUNK;
+  }
+  if (nof_tbs > LDPC_CUDA_NOALLOC_MAX_TBS || n > LDPC_CUDA_NOALLOC_MAX_CBS || total_chunks > LDPC_CUDA_NOALLOC_MAX_CHUNKS) {
+    std::fprintf(stderr,
+                 "ldpc_cuda_tb_assemble_device_noalloc: %u transport blocks / %u codeblocks / %llu chunks of %d bytes exceed "
+                 "the fixed scratch (%u / %u / %u): use ldpc_cuda_tb_assemble_device or split the call\n",
+                 nof_tbs, n, (unsigned long long)total_chunks, TB_CHUNK, LDPC_CUDA_NOALLOC_MAX_TBS,
+                 LDPC_CUDA_NOALLOC_MAX_CBS, LDPC_CUDA_NOALLOC_MAX_CHUNKS);
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  std::lock_guard<std::mutex> lock(s_noalloc_mutex);
+  unsigned char* scratch = nullptr;
+  int rc = noalloc_scratch_of(h->device, &scratch);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  // work records, validated like ldpc_cuda_tb_assemble_device's
+  const size_t bytes = NOALLOC_OFF_CB + sizeof(TbCb) * n;
+  std::memset(s_noalloc_stage, 0, bytes);
+  TbWork* tw = reinterpret_cast<TbWork*>(s_noalloc_stage);
+  TbCb* tc = reinterpret_cast<TbCb*>(s_noalloc_stage + NOALLOC_OFF_CB);
+  unsigned max_chunks = 0, chunk_base = 0;
+  for (uint32_t t = 0; t != nof_tbs; ++t) {
+    const ldpc_cuda_tb_desc& tb = tbs[t];
+    if (tb.nof_codeblocks == 0 || tb.first_codeblock > n || tb.nof_codeblocks > n - tb.first_codeblock ||
+        tb.tbs_bits == 0 || tb.tbs_bits % 8 != 0 || (tb.nof_cb_crc_bits != 16 && tb.nof_cb_crc_bits != 24) ||
+        (tb.nof_codeblocks > 1 && tb.nof_cb_crc_bits != 24)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const ldpc_cuda_cb_desc& d0 = descs[tb.first_codeblock];
+    if ((d0.base_graph != 1 && d0.base_graph != 2) || lifting_set_of(d0.lifting_size) < 0) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const unsigned K = bg_K(d0.base_graph) * d0.lifting_size;
+    if (K <= tb.nof_cb_crc_bits + d0.nof_filler_bits) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    const unsigned data_bits = K - tb.nof_cb_crc_bits - d0.nof_filler_bits;
+    const uint64_t total = (uint64_t)tb.tbs_bits + (tb.nof_codeblocks > 1 ? 24u : 0u);
+    if ((uint64_t)data_bits * tb.nof_codeblocks < total || total / 8 > 0x7fffffffu) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    for (uint32_t r = 0; r != tb.nof_codeblocks; ++r) {
+      const ldpc_cuda_cb_desc& d = descs[tb.first_codeblock + r];
+      if (d.base_graph != d0.base_graph || d.lifting_size != d0.lifting_size || d.nof_filler_bits != d0.nof_filler_bits) {
+        return LDPC_CUDA_ERR_ARG;
+      }
+      TbCb& c = tc[tb.first_codeblock + r];
+      c.src_offset = d.out_offset;
+      c.already_ok = d.skip_decode ? 1u : 0u;
+      c.result_index = tb.first_codeblock + r;
+    }
+    tw[t].tb_offset = tb.tb_offset;
+    tw[t].first_cb = tb.first_codeblock;
+    tw[t].nof_cbs = tb.nof_codeblocks;
+    tw[t].data_bits = data_bits;
+    tw[t].nbytes = (unsigned)(total / 8);
+    tw[t].chunk_base = chunk_base;
+    const unsigned chunks = (tw[t].nbytes + TB_CHUNK - 1) / TB_CHUNK;
+    chunk_base += chunks;
+    max_chunks = std::max(max_chunks, chunks);
+  }
+  // Stream order keeps this behind the kernels of an earlier call on the same stream that still read the array. The
+  // source is pageable memory: the copy has left s_noalloc_stage when the call returns.
+  CUDA_TRY(cudaMemcpyAsync(scratch, s_noalloc_stage, bytes, cudaMemcpyHostToDevice, h->stream));
+  unsigned* d_partial = reinterpret_cast<unsigned*>(scratch + NOALLOC_OFF_PARTIAL);
+  // the array holds the last call's remainders: the ones this call reads start from zero
+  CUDA_TRY(cudaMemsetAsync(d_partial, 0, sizeof(unsigned) * chunk_base, h->stream));
+  const TbWork* d_tw = reinterpret_cast<const TbWork*>(scratch);
+  const TbCb* d_tc = reinterpret_cast<const TbCb*>(scratch + NOALLOC_OFF_CB);
+  const dim3 grid(max_chunks, nof_tbs);
+  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, h->stream>>>(d_tw, d_tc, out_bits_d, tb_out_d, d_partial);
+  CUDA_TRY(cudaGetLastError());
+  ldpc_tb_finish_kernel<<<nof_tbs, 128, 0, h->stream>>>(d_tw, d_tc, reinterpret_cast<const CbResult*>(results_d), d_partial,
+                                                        reinterpret_cast<TbResult*>(tb_results_d));
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 2;
+  return LDPC_CUDA_OK;
 }
 
 // ---- soft demodulator + descrambler (demodulation_mapper::demodulate_soft, pusch_demodulator_impl::descramble) -----------

@@ -11,6 +11,8 @@ CRC_NONE, CRC16, CRC24A, CRC24B = 0, 1, 2, 3
 SCALE_GENERIC, SCALE_AVX, SCALE_NEON = 0, 1, 2
 FLAG_FORCE_SCALAR = 1
 
+NOALLOC_MAX_TBS, NOALLOC_MAX_CBS, NOALLOC_MAX_CHUNKS = 64, 4096, 8192  # ldpc_cuda_tb_assemble_device_noalloc
+
 BG_K = {1: 22, 2: 10}
 BG_N_SHORT = {1: 66, 2: 50}
 
@@ -100,6 +102,7 @@ def library():
         for name in ("ldpc_cuda_encode", "ldpc_cuda_rate_match"):
             getattr(L, name).argtypes = [vp, vp, vp, vp]
         L.ldpc_cuda_tb_assemble_device.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, vp]
+        L.ldpc_cuda_tb_assemble_device_noalloc.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, vp]
         L.ldpc_cuda_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp]
         L.ldpc_cuda_demodulate_batch_device.argtypes = [vp, u32, vp, vp, vp, vp, vp]
         L.ldpc_cuda_descramble_placeholders_device.argtypes = [vp, u32, vp, vp, u32, vp]
@@ -261,6 +264,14 @@ class LdpcCuda:
         self._check(self._L.ldpc_cuda_tb_assemble_device(self._h, tbs.size, _ptr(tbs), descs.size, _ptr(descs), out_ptr,
                                                          results_ptr, tb_out_ptr, tb_results_ptr),
                     "ldpc_cuda_tb_assemble_device")
+
+    def tb_assemble_device_noalloc(self, tbs, descs, out_ptr, results_ptr, tb_out_ptr, tb_results_ptr):
+        """tb_assemble_device on a fixed device array: no allocation in the call (limits: NOALLOC_MAX_*)."""
+        tbs = np.ascontiguousarray(tbs, TB_DESC)
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        self._check(self._L.ldpc_cuda_tb_assemble_device_noalloc(self._h, tbs.size, _ptr(tbs), descs.size, _ptr(descs),
+                                                                 out_ptr, results_ptr, tb_out_ptr, tb_results_ptr),
+                    "ldpc_cuda_tb_assemble_device_noalloc")
 
     def dematch_decode_tb_batch(self, descs, rm_llrs, out, tbs, tb_out, results=None, tb_results=None):
         """out=None: the codeblock messages stay on the device (no skip_decode codeblocks allowed)."""
