@@ -2,6 +2,7 @@
 // No CPU fallback: every compute entry point needs an sm_100 device and fails with LDPC_CUDA_ERR_CUDA otherwise.
 #include <algorithm>
 #include <cstdio>
+#include <atomic>
 #include <cstdlib>
 #include <mutex>
 #include <new>
@@ -93,7 +94,30 @@ int usable_device(int device)
   return prop.major == 10;
 }
 
-int upload_constants()
+int upload_constants_locked();
+
+// The tables in __constant__ / __device__ memory are per device and immutable: they are uploaded by the first handle
+// created on a device and never again (later uploads would rewrite them under kernels of other handles, and the static
+// host staging below is not re-entrant).
+int upload_constants(int device)
+{
+  static std::mutex mtx;
+  static bool done[TM_MAX_DEVICES] = {};
+  std::lock_guard<std::mutex> lock(mtx);
+  if (device >= 0 && device < TM_MAX_DEVICES && done[device]) {
+    return LDPC_CUDA_OK;
+  }
+  const int rc = upload_constants_locked();
+  if (rc == LDPC_CUDA_OK) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    if (device >= 0 && device < TM_MAX_DEVICES) {
+      done[device] = true;
+    }
+  }
+  return rc;
+}
+
+int upload_constants_locked()
 {
   static GraphTables gt;
   std::memset(&gt, 0, sizeof(gt));
@@ -301,7 +325,7 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
   GroupParams gp = make_group(h, bg, Z);
   if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != TM_SCALE_NONE) {
     int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_rm, d_out, d_res, pair_counter, h->sm_count,
-                                stream);
+                                h->device, stream);
     if (rc == 0) {
       h->launches += 1;
       return LDPC_CUDA_OK;
@@ -318,10 +342,12 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
     }
   }
   const size_t smem = scalar_kernel_smem_bytes(bg, Z);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<bool> attr_set[TM_MAX_DEVICES];  // per device: cudaFuncSetAttribute acts on the current one only
+  if (h->device >= TM_MAX_DEVICES || !attr_set[h->device].load(std::memory_order_acquire)) {
     CUDA_TRY(cudaFuncSetAttribute(ldpc_decode_scalar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
+    if (h->device < TM_MAX_DEVICES) {
+      attr_set[h->device].store(true, std::memory_order_release);
+    }
   }
   const int threads = std::max(32, ((Z + 31) / 32) * 32);
   const unsigned grid = std::min<unsigned>(n, (unsigned)h->sm_count * 8u);
@@ -740,6 +766,8 @@ int ldpc_cuda_device_count(void)
   return usable;
 }
 
+static int create_resources(ldpc_cuda_handle* h);
+
 int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblocks, uint32_t flags)
 {
   if (handle == nullptr || max_codeblocks == 0) {
@@ -759,12 +787,28 @@ int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblo
   h->device = device;
   h->max_cbs = max_codeblocks;
   h->flags = flags;
-  cudaDeviceProp prop;
-  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
-  h->sm_count = prop.multiProcessorCount;
-  int rc = upload_constants();
+  int rc = create_resources(h);
+  if (rc == LDPC_CUDA_OK) {
+    ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
+    rc = ldpc_cuda_set_algorithm(h, &alg);
+  }
   if (rc != LDPC_CUDA_OK) {
-    delete h;
+    ldpc_cuda_destroy(h);  // releases whatever was created before the failure
+    return rc;
+  }
+  *handle = h;
+  return LDPC_CUDA_OK;
+}
+
+// Streams, events and buffers of a new handle (the caller destroys the handle when this fails half-way).
+static int create_resources(ldpc_cuda_handle* h)
+{
+  const uint32_t max_codeblocks = h->max_cbs;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, h->device));
+  h->sm_count = prop.multiProcessorCount;
+  int rc = upload_constants(h->device);
+  if (rc != LDPC_CUDA_OK) {
     return rc;
   }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -783,9 +827,7 @@ int ldpc_cuda_create(ldpc_cuda_handle** handle, int device, uint32_t max_codeblo
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_misc, cudaEventDisableTiming));
   CUDA_TRY(cudaMalloc(&h->d_results, sizeof(CbResult) * max_codeblocks));
   CUDA_TRY(cudaMalloc(&h->pair_counter, 64));
-  ldpc_cuda_algorithm alg = {6, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
-  *handle = h;
-  return ldpc_cuda_set_algorithm(h, &alg);
+  return LDPC_CUDA_OK;
 }
 
 void ldpc_cuda_destroy(ldpc_cuda_handle* h)
@@ -1011,9 +1053,29 @@ static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc
   }
 }
 
+static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in,
+                              uint8_t* out, ldpc_cuda_cb_result* results, bool fused, uint32_t nof_tbs,
+                              const ldpc_cuda_tb_desc* tbs, uint8_t* tb_out, ldpc_cuda_tb_result* tb_results);
+
+// Every exit, also the error exits taken in the middle of the chunk loop, leaves the four streams idle: copies already
+// enqueued into the caller's buffers (or out of the pinned work slot) have finished when the caller sees the status.
 static int batch_host(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in, uint8_t* out,
                       ldpc_cuda_cb_result* results, bool fused, uint32_t nof_tbs = 0, const ldpc_cuda_tb_desc* tbs = nullptr,
                       uint8_t* tb_out = nullptr, ldpc_cuda_tb_result* tb_results = nullptr)
+{
+  const int rc = batch_host_enqueue(h, n, descs, in, out, results, fused, nof_tbs, tbs, tb_out, tb_results);
+  if (rc != LDPC_CUDA_OK && h != nullptr && h->stream != nullptr) {
+    cudaSetDevice(h->device);
+    for (cudaStream_t st : {h->h2d_stream, h->stream, h->stream2, h->d2h_stream}) {
+      cudaStreamSynchronize(st);
+    }
+  }
+  return rc;
+}
+
+static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* in,
+                              uint8_t* out, ldpc_cuda_cb_result* results, bool fused, uint32_t nof_tbs,
+                              const ldpc_cuda_tb_desc* tbs, uint8_t* tb_out, ldpc_cuda_tb_result* tb_results)
 {
   if (nof_tbs != 0 && (tbs == nullptr || tb_out == nullptr || tb_results == nullptr)) {
     return LDPC_CUDA_ERR_ARG;

@@ -17,20 +17,27 @@
 // TMEM frees shared memory for the extension nodes (no L2 round trips inside an iteration).
 //
 // Arithmetic (bit-exact with lib/phy/upper/channel_coding/ldpc/ldpc_decoder_impl.cpp:116-135 + ldpc_decoder_generic.cpp
-// :30-130 + lib/phy/upper/log_likelihood_ratio.cpp:38-85): all values are integers of magnitude <= 336, exact in fp16;
-// the LLR "infinity" (+-127, sticky) is the fp16 infinity.
-//   v2c   u = soft - c_old                     (inf stays inf)
-//   min1/min2 over |u|, capped at 120 (the reference initialises both to 120 and compares strictly, so values >= 120
-//         never win); computed as a tree of sorted pairs with VIMNMX.U16x2 / VIMNMX3.U16x2 on the (order-preserving)
-//         bit patterns of the non-negative halves
-//   c2v   c_new = sign * (|u| == min1 ? Q(min2) : Q(min1))  == the reference's argmin-index rule, because a tie for
+// :30-130 + lib/phy/upper/log_likelihood_ratio.cpp:38-85). Soft values, variable-to-check messages and the scaled minima
+// live in the SCALED domain X = 544 x: 544 x is exact in fp16 for every integer |x| <= 120 (17 x < 2048), 544 * 120 =
+// 65280 is finite and 544 * 121 = 65824 rounds to infinity, so that "|sum| > 120 -> +-127 (sticky)" of promotion_sum IS the
+// fp16 overflow of one addition; the LLR "infinity" (+-127) is the fp16 infinity.
+//   v2c   U = SOFT - 544 c_old (one FMA; overflows to +-inf when |soft - c_old| > 120);
+//         V = sign(U) min(|U|, T), T = fma(|SOFT|, 2^-12, 65280) = 65280 for a finite SOFT (the clamp at +-120 of operator-)
+//         and +inf for an infinite one (abs(a) > 120 -> a), in one FMA + one HMNMX2.XORSIGN
+//   min1/min2 over |V|, capped at 65280 (the reference initialises both to 120 and compares strictly, so values >= 120
+//         never win); computed as a tree of sorted pairs with HMNMX2 / VIMNMX3.U16x2 on the (order-preserving) bit
+//         patterns of the non-negative halves
+//   c2v   C_new = sign * (|V| == MIN1 ? Q(MIN2) : Q(MIN1))  == the reference's argmin-index rule, because a tie for
 //         the minimum implies min2 == min1
-//   soft  promote(c_new + clamp(u, +-120)): |sum| > 120 -> +-inf; lanes with u = +-inf keep u
+//   soft  SOFT' = V + C_new (promotion and stickiness by overflow / inf arithmetic)
+// Messages are stored unscaled as biased bytes: 1152 + c = fma(C, 1/544, 1152) (the rounding absorbs the inexact 1/544).
 // Row structure (degrees, columns, shifts) comes from a per-launch table in the kernel parameters (constant bank,
 // uniform loads); the row bodies are instantiated per number of high-rate edges so that the per-edge loops unroll
 // while the code stays small enough for the instruction cache (the first packed kernel unrolled all 316 edges and was
 // instruction-fetch bound, profiles/r01_ncu_packed_v1_summary.txt).
 #pragma once
+
+#include <atomic>
 
 #include <cuda_fp16.h>
 
@@ -73,6 +80,7 @@ struct TmemParams {
   unsigned short rowedge[LDPC_BG1_M];  // per row: index of its first entry in edge[]
   unsigned short rowtm[LDPC_BG1_M];    // per row: first TMEM word (relative to the warp's column block)
   unsigned rowdesc[LDPC_BG1_M + 2];    // per row: rowcls | rowedge << 8 | rowtm << 20 (one uniform load per row)
+  unsigned pairdesc[LDPC_BG1_M + 2];   // per row r: 0, or the descriptor of the pair (r, r + 1) that starts at r (pair_dispatch)
   unsigned short tm_words;             // TMEM words used per thread
   TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
 };
@@ -98,6 +106,8 @@ __device__ __forceinline__ unsigned hfma_relu_abs(unsigned a, unsigned b, unsign
   return un(__hfma2_relu(__habs2(h2(a)), h2(b), h2(c)));
 }
 __device__ __forceinline__ unsigned hfma_relu(unsigned a, unsigned b, unsigned c) { return un(__hfma2_relu(h2(a), h2(b), h2(c))); }
+__device__ __forceinline__ unsigned hfma_abs(unsigned a, unsigned b, unsigned c) { return un(__hfma2(__habs2(h2(a)), h2(b), h2(c))); }
+__device__ __forceinline__ unsigned hmul(unsigned a, unsigned b) { return un(__hmul2(h2(a), h2(b))); }
 // integer min / max on the two non-negative 16-bit halves (fp16 bit patterns of non-negative values order like integers)
 __device__ __forceinline__ unsigned umin2(unsigned a, unsigned b)
 {
@@ -213,22 +223,26 @@ __device__ __forceinline__ unsigned hmin_xorsign_abs(unsigned a, unsigned b)
   return r;
 }
 
-// Scaled magnitude Q(m), m integer-valued half2 in [0,120] (closed forms checked against the host table for every m by
-// tm_scale_selfcheck() when the algorithm is set):
-//  GENERIC 0.8: round(0.8 m) = m - round(m / 5)   (0.2 m is never at a tie, one FMA rounding is exact)
+constexpr float TM_S = 544.f;          // scaled domain: X = 544 x (see the header comment)
+constexpr float TM_CAP = 65280.f;      // 544 * 120
+
+// Scaled magnitude 544 Q(m) of M = 544 m, m integer in [0,120] (closed forms checked against the host table for every m
+// by tm_scale_selfcheck() when the algorithm is set):
+//  GENERIC 0.8: round(0.8 m) = m - round(m / 5)   (0.2 m is never at a tie: the relative error 2^-11 of the fp16 constant
+//               0.2 / 544 moves m / 5 by less than 0.012, and one FMA rounding against the magic constant is exact)
 //  AVX     0.8: (m * 52428) >> 16 = m - floor(m / 5) - [m > 0], floor(m / 5) = round((m - 2) / 5)
 // The magic constant 1536 keeps the sum in [1024, 2048) where the fp16 ulp is 1.
 template <int SCALE>
-__device__ __forceinline__ unsigned scale_q(unsigned m)
+__device__ __forceinline__ unsigned scale_q(unsigned M)
 {
-  const unsigned magic = hc(1536.f), fifth = hc(0.2f);
+  const unsigned magic = hc(1536.f), fifth = hc(0.2f / TM_S), nS = hc(-TM_S);
   if (SCALE == TM_SCALE_GENERIC_08) {
-    const unsigned r = hsub(hfma(m, fifth, magic), magic);
-    return hsub(m, r);
+    const unsigned r = hsub(hfma(M, fifth, magic), magic);
+    return hfma(r, nS, M);
   } else {
-    const unsigned r = hsub(hfma(hsub(m, hc(2.f)), fifth, magic), magic);
-    const unsigned nz = hfma_sat(m, hc(1.f), hc(0.f));
-    return hsub(hsub(m, r), nz);
+    const unsigned r = hsub(hfma(hsub(M, hc(2.f * TM_S)), fifth, magic), magic);
+    const unsigned nz = hfma_sat(M, hc(1.f), hc(0.f));
+    return hfma(nz, nS, hfma(r, nS, M));
   }
 }
 
@@ -276,109 +290,153 @@ struct Ctx {
 };
 
 // One check row: D high-rate edges (rotated accesses to shared soft values, messages in cw[]) plus, when EXT, the row's
-// private extension node. e0 / r / tmw are warp-uniform.
+// private extension node. Split into the part that does not touch shared soft values (pre: runs while slower warps finish
+// the previous row), the loads and the arithmetic, so that two rows without a common column can be interleaved between
+// one pair of barriers (pair_body). e0 / r / tmw are warp-uniform.
+template <int D, bool EXT, int SCALE>
+struct Row {
+  static constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
+  static constexpr int W = (D + 1) / 2;         // message words of the row
+  unsigned addr[D], u[NV], cw[W];
+  unsigned xaddr, tma;
+
+  __device__ __forceinline__ void pre(const Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
+  {
+    // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads
+    tma = c.tm_addr + tmw;
+    tm_load<W>(tma, cw);
+    // addresses: lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66)
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      const TmEdge ed = p.edge[e0 + k];
+      const unsigned a = c.t4 + ed.s4;
+      addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
+    }
+    // The row's extension node has degree one: its variable-to-check message is its channel LLR until the soft value
+    // LLR + c2v is promoted to +-inf (|sum| > 120), and +-inf for ever after (soft - c2v_old = LLR exactly otherwise:
+    // log_likelihood_ratio.cpp:38-85). So the node is ONE thread-private word holding that message - no soft value, no
+    // stored check-to-variable message.
+    xaddr = 0;
+    if constexpr (EXT) {
+      xaddr = c.ext_soft + (unsigned)(r - 4) * c.zpad4;
+      u[D] = lds32(xaddr);  // thread-private: no ordering with other threads needed
+    }
+  }
+
+  __device__ __forceinline__ void load()
+  {
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      u[k] = lds32(addr[k]);
+    }
+  }
+
+  // after load() and tm_wait_ld()
+  __device__ __forceinline__ void compute(const Ctx& c)
+  {
+    // previous messages: byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
+    const unsigned cap = hc(TM_CAP), nS = hc(-TM_S);
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      const unsigned tb = __byte_perm(cw[k >> 1], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+      // variable-to-check message (compute_var_to_check_msgs): difference (overflowing beyond +-120), then the clamp of
+      // operator- for a finite soft value / the pass-through of an infinite one
+      const unsigned d = hfma(hsub(tb, hc(1152.f)), nS, u[k]);
+      const unsigned lim = hfma_abs(u[k], hc(0.000244140625f), cap);  // 65280, or +inf for an infinite soft value
+      u[k] = hmin_xorsign_abs(d, lim);
+    }
+    // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
+    constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
+    MinPair pr[NP];
+#pragma unroll
+    for (int i = 0; i < NV / 2; ++i) {
+      pr[i].m1 = hmin_abs(u[2 * i], u[2 * i + 1]);
+      pr[i].m2 = hmax_abs(u[2 * i], u[2 * i + 1]);
+    }
+    if constexpr (NV & 1) {
+      pr[NP - 1].m1 = hmin_abs(u[NV - 1], cap);
+      pr[NP - 1].m2 = cap;
+    } else {
+      pr[NP - 1].m1 = cap;
+      pr[NP - 1].m2 = cap;
+    }
+    const MinPair mm = reduce_pairs<NP>(pr);
+    unsigned S = 0;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      S ^= u[k];
+    }
+    const unsigned T = S & SIGN2;
+    // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
+    const unsigned Q1 = scale_q<SCALE>(mm.m1), Q2 = scale_q<SCALE>(mm.m2);
+    const unsigned Q2s = Q2 ^ T;
+    const unsigned nD = hsub(Q1, Q2) ^ T;
+    const unsigned nM1 = mm.m1 ^ SIGN2;
+    // compute_check_to_var_msgs (:93-116) + compute_soft_bits (:118-130)
+    unsigned tn[D + 1];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const unsigned uk = u[k];
+      const unsigned indp = hadd_sat_abs(uk, nM1);  // 0 where |v2c| == min1, 1 elsewhere (differences are 0 or >= 544)
+      const unsigned cm = hfma(indp, nD, Q2s);
+      const unsigned cn = cm ^ (uk & SIGN2);
+      // promotion_sum: |sum| > 120 overflows to +-inf, an infinite v2c stays infinite
+      const unsigned n = hadd(uk, cn);
+      if (k < D) {
+        if (c.active) {
+          sts32(addr[k], n);
+        }
+        tn[k] = hfma(cn, hc(1.f / TM_S), hc(1152.f));
+      } else {
+        // the message becomes +-inf once the soft value is promoted (sign of the sum = sign of the message then)
+        const unsigned prom = __heq2_mask(__habs2(h2(n)), h2(0x7c007c00u));
+        sts32(xaddr, (n & prom) | (uk & ~prom));
+      }
+    }
+    if constexpr (D & 1) {
+      tn[D] = tn[D - 1];
+    }
+    unsigned wv[W];
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      wv[i] = __byte_perm(tn[2 * i], tn[2 * i + 1], 0x6420);
+    }
+    tm_store<W>(tma, wv);
+  }
+};
+
 template <int D, bool EXT, int SCALE>
 __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw, int bar_id, int zpad)
 {
-  constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
-  constexpr int W = (D + 1) / 2;         // message words of the row
-  unsigned addr[D], u[NV], cw[W];
-  // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads below
-  tm_load<W>(c.tm_addr + tmw, cw);
-  // addresses and soft values: lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66)
-#pragma unroll
-  for (int k = 0; k < D; ++k) {
-    const TmEdge ed = p.edge[e0 + k];
-    const unsigned a = c.t4 + ed.s4;
-    addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
-  }
-  // The row's extension node has degree one: its variable-to-check message is its channel LLR until the soft value
-  // LLR + c2v is promoted to +-inf (|sum| > 120), and +-inf for ever after (soft - c2v_old = LLR exactly otherwise:
-  // log_likelihood_ratio.cpp:38-85). So the node is ONE thread-private word holding that message - no soft value, no
-  // stored check-to-variable message.
-  unsigned xaddr = 0;
-  if constexpr (EXT) {
-    xaddr = c.ext_soft + (unsigned)(r - 4) * c.zpad4;
-    u[D] = lds32(xaddr);  // thread-private: no ordering with other threads needed
-  }
+  Row<D, EXT, SCALE> R;
+  R.pre(c, p, r, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
   group_barrier(bar_id, zpad);
-#pragma unroll
-  for (int k = 0; k < D; ++k) {
-    u[k] = lds32(addr[k]);
-  }
-  // previous messages: byte b = 128 + c_old; 0x6400 | b is the fp16 number 1152 + c_old
+  R.load();
   tm_wait_ld();
-#pragma unroll
-  for (int k = 0; k < D; ++k) {
-    const unsigned tb = __byte_perm(cw[k >> 1], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
-    u[k] = hadd(hsub(u[k], tb), hc(1152.f));  // variable-to-check message (compute_var_to_check_msgs)
-  }
-  // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
-  constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
-  MinPair pr[NP];
-  const unsigned c120 = hc(120.f);
-#pragma unroll
-  for (int i = 0; i < NV / 2; ++i) {
-    pr[i].m1 = hmin_abs(u[2 * i], u[2 * i + 1]);
-    pr[i].m2 = hmax_abs(u[2 * i], u[2 * i + 1]);
-  }
-  if constexpr (NV & 1) {
-    pr[NP - 1].m1 = hmin_abs(u[NV - 1], c120);
-    pr[NP - 1].m2 = c120;
-  } else {
-    pr[NP - 1].m1 = c120;
-    pr[NP - 1].m2 = c120;
-  }
-  const MinPair mm = reduce_pairs<NP>(pr);
-  unsigned S = 0;
-#pragma unroll
-  for (int k = 0; k < NV; ++k) {
-    S ^= u[k];
-  }
-  const unsigned T = S & SIGN2;
-  // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
-  const unsigned Q1 = scale_q<SCALE>(mm.m1), Q2 = scale_q<SCALE>(mm.m2);
-  const unsigned Q2s = Q2 ^ T;
-  const unsigned nD = hsub(Q1, Q2) ^ T;
-  const unsigned nM1 = mm.m1 ^ SIGN2;
-  // compute_check_to_var_msgs (:93-116) + compute_soft_bits (:118-130)
-  unsigned tn[D + 1];
-#pragma unroll
-  for (int k = 0; k < NV; ++k) {
-    const unsigned uk = u[k];
-    const unsigned indp = hadd_sat_abs(uk, nM1);  // 0 where |u| == min1, 1 elsewhere
-    const unsigned cm = hfma(indp, nD, Q2s);
-    const unsigned cn = cm ^ (uk & SIGN2);
-    // clamp to +-120 in one HMNMX2.XORSIGN (the two-instruction min/max form was 1.3 % slower: profiles/r01_icache_microbench.md)
-    const unsigned v = hmin_xorsign_abs(uk, c120);
-    const unsigned s = hadd(v, cn);
-    const unsigned rp = hfma_relu_abs(s, hc(544.f), hc(-65280.f));  // > 0 iff |s| > 120
-    const unsigned n1 = hfma(rp, s, s);                              // promotion to +-inf
-    if (k < D) {
-      // lanes frozen at +-inf stay there (HSET2.BM + LOP3 on the ALU pipe: the FP16 pipe is the busier one in this pass)
-      const unsigned isinf = __heq2_mask(__habs2(h2(uk)), h2(0x7c007c00u));
-      const unsigned n = (uk & isinf) | (n1 & ~isinf);
-      if (c.active) {
-        sts32(addr[k], n);
-      }
-      tn[k] = hadd(cn, hc(1152.f));
-    } else {
-      // the message becomes +-inf once the soft value is promoted (sign of s = sign of u when u is already infinite)
-      const unsigned prom = __heq2_mask(__habs2(h2(n1)), h2(0x7c007c00u));
-      sts32(xaddr, (n1 & prom) | (uk & ~prom));
-    }
-  }
-  if constexpr (D & 1) {
-    tn[D] = tn[D - 1];
-  }
-  unsigned wv[W];
-#pragma unroll
-  for (int i = 0; i < W; ++i) {
-    wv[i] = __byte_perm(tn[2 * i], tn[2 * i + 1], 0x6420);
-  }
-  tm_store<W>(c.tm_addr + tmw, wv);
+  R.compute(c);
+}
+
+// Two consecutive rows WITHOUT a common high-rate column (their extension columns are private anyway): they read and
+// write disjoint soft values, so running them side by side between one pair of barriers gives exactly the result of
+// running them one after the other - two independent dependency chains per thread, half the barriers and half the loop /
+// dispatch work for these (short) rows. In both 5G base graphs most rows of the extension part are pairwise orthogonal
+// to their successor (BG1: 14 pairs among rows 16-45, BG2: 13).
+template <int DA, int DB, int SCALE>
+__device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, int e0A, unsigned tmwA, int rB, int e0B,
+                                          unsigned tmwB, int bar_id, int zpad)
+{
+  Row<DA, true, SCALE> A;
+  Row<DB, true, SCALE> B;
+  A.pre(c, p, rA, e0A, tmwA);
+  B.pre(c, p, rB, e0B, tmwB);
+  group_barrier(bar_id, zpad);
+  A.load();
+  B.load();
+  tm_wait_ld();
+  A.compute(c);
+  B.compute(c);
 }
 
 template <int SCALE>
@@ -409,7 +467,65 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
   }
 }
 
-__device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, v, 0); }
+// pd: pair class (16 * DA + DB, DA >= DB) | row index of A << 8 | row index of B << 16; the rows' own descriptors give
+// their edge / TMEM offsets.
+template <int SCALE>
+__device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int bar_id, int zpad, unsigned pd, unsigned rdA,
+                                              unsigned rdB)
+{
+  const int cls = pd & 0xffu, rA = (pd >> 8) & 0xffu, rB = (pd >> 16) & 0xffu;
+  const int e0A = (rdA >> 8) & 0xfffu, e0B = (rdB >> 8) & 0xfffu;
+  const unsigned tmwA = rdA >> 20, tmwB = rdB >> 20;
+  switch (cls) {
+#define LDPC_TM_PAIR(DA, DB)                                                                   \
+  case 16 * (DA) + (DB):                                                                       \
+    pair_body<DA, DB, SCALE>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
+    break;
+    LDPC_TM_PAIR(5, 5)
+    LDPC_TM_PAIR(5, 4)
+    LDPC_TM_PAIR(4, 4)
+    LDPC_TM_PAIR(4, 3)
+    LDPC_TM_PAIR(4, 2)
+    LDPC_TM_PAIR(3, 3)
+    LDPC_TM_PAIR(3, 2)
+#undef LDPC_TM_PAIR
+    default:
+      break;
+  }
+}
+constexpr bool tm_pair_supported(int da, int db)
+{
+  return (da == 5 && (db == 5 || db == 4)) || (da == 4 && db >= 2 && db <= 4) || (da == 3 && (db == 3 || db == 2));
+}
+
+// Byte j of a and of b (selector 0x0400 + 0x0101 j) as a scaled half2: byte ^ 0x80 under a 0x64 high byte is the fp16
+// number 1024 + (value + 128); the multiplication by 544 overflows to +-inf exactly for |value| > 120 (the "infinite" LLR
+// +-127, log_likelihood_ratio.h:239).
+__device__ __forceinline__ unsigned convert_bytes(unsigned a, unsigned b, unsigned selector)
+{
+  const unsigned w = (__byte_perm(a, b, selector) & 0x00ff00ffu) ^ 0x64806480u;
+  return hmul(hadd(w, hc(-1152.f)), hc(TM_S));
+}
+
+// 16 LLRs at in + i0 (16-byte aligned) of a codeblock with len LLRs; positions at or beyond len read as zero.
+__device__ __forceinline__ uint4 load16(const int8_t* in, unsigned i0, unsigned len)
+{
+  uint4 r = make_uint4(0u, 0u, 0u, 0u);
+  if (i0 + 16u <= len) {
+    r = __ldg(reinterpret_cast<const uint4*>(in + i0));
+  } else if (i0 < len) {
+    unsigned w[4] = {0u, 0u, 0u, 0u};
+    for (unsigned k = 0; i0 + k < len; ++k) {
+      w[k >> 2] |= (unsigned)(unsigned char)__ldg(in + i0 + k) << (8u * (k & 3u));
+    }
+    r = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  return r;
+}
+
+// Warp-uniform value that the compiler can also see as uniform (the result of a warp reduction lives in a uniform
+// register), so that loops and branches on it use the uniform datapath. v >= 0.
+__device__ __forceinline__ int uniform(int v) { return (int)__reduce_max_sync(0xffffffffu, (unsigned)v); }
 
 }  // namespace tm
 
@@ -519,14 +635,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     const int8_t* inA = p.llr_base + wA.in_offset;
     const int8_t* inB = p.llr_base + wB.in_offset;
     unsigned lastA = 0, lastB = 0;
-    // int8 pair -> half2 without conversion instructions: byte ^ 0x80 under a 0x64 high byte is the fp16 number
-    // 1024 + (value + 128); |value| > 120 (the "infinite" LLR +-127, log_likelihood_ratio.h:239) becomes +-inf.
-    auto convert = [](int a, int b) {
-      const unsigned w = (__byte_perm((unsigned)a, (unsigned)b, 0x0400) & 0x00ff00ffu) ^ 0x64806480u;
-      const unsigned v = tm::hadd(w, tm::hc(-1152.f));
-      const unsigned m = __hgt2_mask(__habs2(tm::h2(v)), tm::h2(tm::hc(120.f)));
-      return (v & (~m | tm::SIGN2)) | (m & 0x7c007c00u);
-    };
+    auto convert = [](int a, int b) { return tm::convert_bytes((unsigned)a, (unsigned)b, 0x0400); };
     auto put = [&](int n, unsigned v) {
       if (n < HRR) {
         soft_w[n * Z + t] = v;
@@ -542,8 +651,46 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       soft_w[t] = 0, soft_w[Z + t] = 0;  // punctured columns
     }
     if constexpr (!FUSED) {
-      if (c.active) {
-        const unsigned lenA = useA ? wA.in_length : 0u, lenB = useB ? wB.in_length : 0u;
+      const unsigned lenA = useA ? wA.in_length : 0u, lenB = useB ? wB.in_length : 0u;
+      const bool vec16 = tm::uniform(((Z & 15) == 0 && ((reinterpret_cast<size_t>(inA) | reinterpret_cast<size_t>(inB)) & 15) == 0) ? 1 : 0);
+      if (vec16) {
+        // Z is a multiple of 16 and both inputs are 16-byte aligned: a thread takes 16 consecutive LLRs (16 lanes of one
+        // column) of both codeblocks with two 16-byte loads and writes their 16 half2 words with four 16-byte stores.
+        // Input byte 16 v .. 16 v + 15 = lanes 16 (v mod Z/16) .. of stored column v / (Z/16). The trailing-zero scan only
+        // has to be exact to the vector: the number of layers depends on the input size rounded up to a multiple of Z.
+        const unsigned V = (unsigned)Z >> 4, nvec = (unsigned)(K + M - 2) * V;
+        constexpr int UV = 3;
+#pragma unroll 1
+        for (unsigned v0 = (unsigned)t; v0 < nvec; v0 += UV * (unsigned)zpad) {
+          uint4 a[UV], b[UV];
+#pragma unroll
+          for (int j = 0; j < UV; ++j) {
+            const unsigned v = v0 + (unsigned)(j * zpad), i0 = 16u * v;
+            a[j] = tm::load16(inA, i0, v < nvec ? lenA : 0u);
+            b[j] = tm::load16(inB, i0, v < nvec ? lenB : 0u);
+          }
+#pragma unroll
+          for (int j = 0; j < UV; ++j) {
+            const unsigned v = v0 + (unsigned)(j * zpad);
+            if (v < nvec) {
+              lastA = ((a[j].x | a[j].y) | (a[j].z | a[j].w)) ? 16u * (v + 1) : lastA;
+              lastB = ((b[j].x | b[j].y) | (b[j].z | b[j].w)) ? 16u * (v + 1) : lastB;
+              const unsigned n = 2u + v / V, lane0 = 16u * (v - (n - 2u) * V);
+              unsigned* dst = (n < (unsigned)HRR) ? soft_w + n * (unsigned)Z + lane0 : ext_soft_w + (n - HRR) * (unsigned)zpad + lane0;
+              const unsigned aw[4] = {a[j].x, a[j].y, a[j].z, a[j].w}, bw[4] = {b[j].x, b[j].y, b[j].z, b[j].w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 o;
+                o.x = tm::convert_bytes(aw[q], bw[q], 0x0400);
+                o.y = tm::convert_bytes(aw[q], bw[q], 0x0501);
+                o.z = tm::convert_bytes(aw[q], bw[q], 0x0602);
+                o.w = tm::convert_bytes(aw[q], bw[q], 0x0703);
+                *reinterpret_cast<uint4*>(dst + 4 * q) = o;
+              }
+            }
+          }
+        }
+      } else if (c.active) {
 #pragma unroll 1
         for (int n0 = 2; n0 < K + M; n0 += U) {
           int a[U], b[U];
@@ -701,11 +848,16 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
 
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
-      unsigned rd = p.rowdesc[0];
-      for (int r = 0; r < nof_layers; ++r) {
-        const unsigned rd_next = p.rowdesc[r + 1];  // fetched a whole row ahead of its use
-        tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad, rd);  // the barrier that orders row r after row r - 1 is inside
-        rd = rd_next;
+      for (int r = 0; r < nof_layers;) {
+        // the barrier that orders a row after its predecessor is inside the bodies
+        const unsigned rd = p.rowdesc[r], pd = p.pairdesc[r];
+        if (pd != 0 && r + 1 < nof_layers) {
+          tm::pair_dispatch<SCALE>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
+          r += 2;
+        } else {
+          tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad, rd);
+          r += 1;
+        }
       }
       tm::group_barrier(bar_id, zpad);
       tm::tm_wait_st();
@@ -874,8 +1026,8 @@ __global__ void tm_scale_selfcheck_kernel(unsigned char* out)
 {
   const int m = threadIdx.x;
   if (m <= LLR_MAX) {
-    const unsigned q = tm::scale_q<SCALE>(tm::hc((float)m));
-    out[m] = (unsigned char)__half2float(__low2half(tm::h2(q)));
+    const unsigned q = tm::scale_q<SCALE>(tm::hc(tm::TM_S * (float)m));
+    out[m] = (unsigned char)(__half2float(__low2half(tm::h2(q))) * (1.f / tm::TM_S) + 0.25f);
   }
 }
 
@@ -940,24 +1092,49 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
     tmw += (d + 1) / 2;
   }
   p.tm_words = (unsigned short)tmw;
+  // pairs of consecutive rows (both with an extension node) that share no high-rate column, chosen greedily in row order;
+  // A is the row with the larger high-rate degree (the order inside a pair does not matter)
+  for (int r = 4; r + 1 < M;) {
+    bool disjoint = true;
+    for (int a = row_ptr[r]; a != row_ptr[r + 1] && disjoint; ++a) {
+      for (int b = row_ptr[r + 1]; b != row_ptr[r + 2] && disjoint; ++b) {
+        disjoint = !(col[a] == col[b] && col[a] < hrr);
+      }
+    }
+    const int d0 = p.rowcls[r] >> 1, d1 = p.rowcls[r + 1] >> 1;
+    const int da = d0 >= d1 ? d0 : d1, db = d0 >= d1 ? d1 : d0;
+    if (disjoint && tm::tm_pair_supported(da, db)) {
+      const int rA = d0 >= d1 ? r : r + 1, rB = d0 >= d1 ? r + 1 : r;
+      p.pairdesc[r] = (unsigned)(16 * da + db) | ((unsigned)rA << 8) | ((unsigned)rB << 16);
+      r += 2;
+    } else {
+      r += 1;
+    }
+  }
   return ((tmw + 7) & ~7u) <= (unsigned)TM_COLS_PER_WARP;
 }
 
 constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100
 constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block per SM owns all 512 TMEM columns
 
+// cudaFuncSetAttribute applies to the CURRENT device only: the opt-in is tracked per device (a process may hold handles on
+// several GPUs, and several host threads may launch at once).
+constexpr int TM_MAX_DEVICES = 64;
+
 template <int BG, int SCALE, bool FUSED>
-static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, cudaStream_t stream)
+static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
 {
   auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<bool> attr_set[TM_MAX_DEVICES];
+  if (device < 0 || device >= TM_MAX_DEVICES || !attr_set[device].load(std::memory_order_acquire)) {
     const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM_LIMIT);
     if (e != cudaSuccess) {
       std::fprintf(stderr, "ldpc_cuda: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(e));
       return -1;
     }
-    attr_set = true;
+    if (device >= 0 && device < TM_MAX_DEVICES) {
+      attr_set[device].store(true, std::memory_order_release);
+    }
   }
   kernel<<<grid, p.groups * p.zpad, smem, stream>>>(p);
   const cudaError_t e = cudaGetLastError();
@@ -969,10 +1146,11 @@ static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned g
 }
 
 template <int BG, int SCALE>
-static inline int tm_launch_fused_or_not(bool fused, const TmemParams& p, size_t smem, unsigned grid, cudaStream_t stream)
+static inline int tm_launch_fused_or_not(bool fused, const TmemParams& p, size_t smem, unsigned grid, int device,
+                                         cudaStream_t stream)
 {
-  return fused ? tm_launch_variant<BG, SCALE, true>(p, smem, grid, stream)
-               : tm_launch_variant<BG, SCALE, false>(p, smem, grid, stream);
+  return fused ? tm_launch_variant<BG, SCALE, true>(p, smem, grid, device, stream)
+               : tm_launch_variant<BG, SCALE, false>(p, smem, grid, device, stream);
 }
 
 // Returns 0 when launched, > 0 when the configuration is not covered (caller uses the general kernel), < 0 on CUDA error.
@@ -980,7 +1158,7 @@ static inline int tm_launch_fused_or_not(bool fused, const TmemParams& p, size_t
 // LLRs at d_rm before decoding.
 static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, const CbWork* d_work, unsigned n,
                                      const int8_t* d_llr, const int8_t* d_rm, uint8_t* d_out, CbResult* d_res,
-                                     unsigned* d_pair_counter, int sm_count, cudaStream_t stream)
+                                     unsigned* d_pair_counter, int sm_count, int device, cudaStream_t stream)
 {
   if (scale_variant == TM_SCALE_NONE || d_pair_counter == nullptr) {
     return 1;
@@ -1013,11 +1191,11 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   }
   const bool gen = scale_variant == TM_SCALE_GENERIC_08;
   if (gp.bg == 1) {
-    return gen ? tm_launch_fused_or_not<1, TM_SCALE_GENERIC_08>(fused, p, smem, grid, stream)
-               : tm_launch_fused_or_not<1, TM_SCALE_AVX_08>(fused, p, smem, grid, stream);
+    return gen ? tm_launch_fused_or_not<1, TM_SCALE_GENERIC_08>(fused, p, smem, grid, device, stream)
+               : tm_launch_fused_or_not<1, TM_SCALE_AVX_08>(fused, p, smem, grid, device, stream);
   }
-  return gen ? tm_launch_fused_or_not<2, TM_SCALE_GENERIC_08>(fused, p, smem, grid, stream)
-             : tm_launch_fused_or_not<2, TM_SCALE_AVX_08>(fused, p, smem, grid, stream);
+  return gen ? tm_launch_fused_or_not<2, TM_SCALE_GENERIC_08>(fused, p, smem, grid, device, stream)
+             : tm_launch_fused_or_not<2, TM_SCALE_AVX_08>(fused, p, smem, grid, device, stream);
 }
 
 }  // namespace ldpc_b200
