@@ -131,9 +131,11 @@ __device__ __forceinline__ unsigned lds32(unsigned addr)
 }
 __device__ __forceinline__ void sts32(unsigned addr, unsigned v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 
+// FULL: the block is one group of 384 lanes, all of them live (Z = 384): barrier 1 with immediate operands.
+template <bool FULL = false>
 __device__ __forceinline__ void group_barrier(int id, int nthreads)
 {
-  if (nthreads == 384) {  // one group per block: barrier 1 with immediate operands (no operand register to rebuild per row)
+  if (FULL || nthreads == 384) {  // one group per block (no operand register to rebuild per row)
     asm volatile("bar.sync 1, 384;" ::: "memory");
   } else {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -293,7 +295,7 @@ struct Ctx {
 // private extension node. Split into the part that does not touch shared soft values (pre: runs while slower warps finish
 // the previous row), the loads and the arithmetic, so that two rows without a common column can be interleaved between
 // one pair of barriers (pair_body). e0 / r / tmw are warp-uniform.
-template <int D, bool EXT, int SCALE>
+template <int D, bool EXT, int SCALE, bool FULL>
 struct Row {
   static constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
   static constexpr int W = (D + 1) / 2;         // message words of the row
@@ -310,7 +312,7 @@ struct Row {
     for (int k = 0; k < D; ++k) {
       const TmEdge ed = p.edge[e0 + k];
       const unsigned a = c.t4 + ed.s4;
-      addr[k] = min(a, a - c.Z4) + (ed.cb + c.soft_base);
+      addr[k] = min(a, a - (FULL ? 4u * MAX_Z : c.Z4)) + (ed.cb + c.soft_base);
     }
     // The row's extension node has degree one: its variable-to-check message is its channel LLR until the soft value
     // LLR + c2v is promoted to +-inf (|sum| > 120), and +-inf for ever after (soft - c2v_old = LLR exactly otherwise:
@@ -318,7 +320,7 @@ struct Row {
     // stored check-to-variable message.
     xaddr = 0;
     if constexpr (EXT) {
-      xaddr = c.ext_soft + (unsigned)(r - 4) * c.zpad4;
+      xaddr = c.ext_soft + (unsigned)(r - 4) * (FULL ? 4u * MAX_Z : c.zpad4);
       u[D] = lds32(xaddr);  // thread-private: no ordering with other threads needed
     }
   }
@@ -383,7 +385,7 @@ struct Row {
       // promotion_sum: |sum| > 120 overflows to +-inf, an infinite v2c stays infinite
       const unsigned n = hadd(uk, cn);
       if (k < D) {
-        if (c.active) {
+        if (FULL || c.active) {
           sts32(addr[k], n);
         }
         tn[k] = hfma(cn, hc(1.f / TM_S), hc(1152.f));
@@ -405,14 +407,14 @@ struct Row {
   }
 };
 
-template <int D, bool EXT, int SCALE>
+template <int D, bool EXT, int SCALE, bool FULL>
 __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw, int bar_id, int zpad)
 {
-  Row<D, EXT, SCALE> R;
+  Row<D, EXT, SCALE, FULL> R;
   R.pre(c, p, r, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
-  group_barrier(bar_id, zpad);
+  group_barrier<FULL>(bar_id, zpad);
   R.load();
   tm_wait_ld();
   R.compute(c);
@@ -423,15 +425,15 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
 // running them one after the other - two independent dependency chains per thread, half the barriers and half the loop /
 // dispatch work for these (short) rows. In both 5G base graphs most rows of the extension part are pairwise orthogonal
 // to their successor (BG1: 14 pairs among rows 16-45, BG2: 13).
-template <int DA, int DB, int SCALE>
+template <int DA, int DB, int SCALE, bool FULL>
 __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, int e0A, unsigned tmwA, int rB, int e0B,
                                           unsigned tmwB, int bar_id, int zpad)
 {
-  Row<DA, true, SCALE> A;
-  Row<DB, true, SCALE> B;
+  Row<DA, true, SCALE, FULL> A;
+  Row<DB, true, SCALE, FULL> B;
   A.pre(c, p, rA, e0A, tmwA);
   B.pre(c, p, rB, e0B, tmwB);
-  group_barrier(bar_id, zpad);
+  group_barrier<FULL>(bar_id, zpad);
   A.load();
   B.load();
   tm_wait_ld();
@@ -439,7 +441,7 @@ __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, i
   B.compute(c);
 }
 
-template <int SCALE>
+template <int SCALE, bool FULL>
 __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad, unsigned rd)
 {
   const int cls = rd & 0xffu;
@@ -448,7 +450,7 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
   switch (cls) {
 #define LDPC_TM_CASE(D, EXT)                        \
   case 2 * (D) + (EXT):                             \
-    row_body<D, (EXT) != 0, SCALE>(c, p, r, e0, tmw, bar_id, zpad); \
+    row_body<D, (EXT) != 0, SCALE, FULL>(c, p, r, e0, tmw, bar_id, zpad); \
     break;
     LDPC_TM_CASE(2, 1)
     LDPC_TM_CASE(3, 1)
@@ -469,7 +471,7 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
 
 // pd: pair class (16 * DA + DB, DA >= DB) | row index of A << 8 | row index of B << 16; the rows' own descriptors give
 // their edge / TMEM offsets.
-template <int SCALE>
+template <int SCALE, bool FULL>
 __device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int bar_id, int zpad, unsigned pd, unsigned rdA,
                                               unsigned rdB)
 {
@@ -479,7 +481,7 @@ __device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int b
   switch (cls) {
 #define LDPC_TM_PAIR(DA, DB)                                                                   \
   case 16 * (DA) + (DB):                                                                       \
-    pair_body<DA, DB, SCALE>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
+    pair_body<DA, DB, SCALE, FULL>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
     break;
     LDPC_TM_PAIR(5, 5)
     LDPC_TM_PAIR(5, 4)
@@ -554,14 +556,16 @@ constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base ad
 // FUSED: the prologue is the rate dematcher (ldpc_rate_dematcher_impl.cpp:43-254): every soft-buffer position is combined
 // with the new transmission in the HBM arena and handed to the decoder in the same pass (no separate kernel, the soft
 // buffer is read once and written once).
-template <int BG, int SCALE, bool FUSED>
+// FULL: Z = 384 (one group of 12 warps, every lane live) with Z, the barrier operands and the all-lanes-active predicate
+// folded at compile time - the configuration BASELINE.json's metric is quoted on.
+template <int BG, int SCALE, bool FUSED, bool FULL>
 __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
 {
   constexpr int K = (BG == 2) ? 10 : 22, M = (BG == 2) ? LDPC_BG2_M : LDPC_BG1_M, HRR = K + 4;
   extern __shared__ __align__(16) unsigned char smem[];
-  const int Z = p.Z, zpad = p.zpad, tid = threadIdx.x;
+  const int Z = FULL ? MAX_Z : p.Z, zpad = FULL ? MAX_Z : p.zpad, tid = threadIdx.x;
   const int warp = tid >> 5;
-  const int grp = tm::uniform(tid / zpad);
+  const int grp = FULL ? 0 : tm::uniform(tid / zpad);
   const int t = tid - grp * zpad;
   const int wig = tm::uniform(t >> 5);   // warp index inside the group
   const int bar_id = 1 + grp;
@@ -593,7 +597,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   c.zpad4 = 4u * (unsigned)zpad;
   const unsigned tmem_base = *reinterpret_cast<volatile unsigned*>(smem + 3 * 256 * 4);
   c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * TM_COLS_PER_WARP;
-  c.active = t < Z;
+  c.active = FULL || t < Z;
 
   // FUSED: the pair after the current one is claimed one pair early so that its rate-matched LLRs (and previous soft
   // bits) can be pulled into L2 while this pair is decoded (+3.4 % on the full-slot workload; for the plain decoder the
@@ -616,7 +620,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       flags[4] = cur;
       flags[0] = 0, flags[1] = 0, flags[8] = 0, flags[9] = 0, flags[10] = 0, flags[11] = 0;
     }
-    tm::group_barrier(bar_id, zpad);
+    tm::group_barrier<FULL>(bar_id, zpad);
     const unsigned pair = (unsigned)tm::uniform((int)flags[4]);
     if (2 * pair >= p.nof_cbs) {
       break;
@@ -627,7 +631,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     const CbWork wB = p.work[hasB ? 2 * pair + 1 : 2 * pair];
     const bool useA = !wA.skip_decode, useB = hasB && !wB.skip_decode;
     if (!FUSED && !useA && !useB) {
-      tm::group_barrier(bar_id, zpad);
+      tm::group_barrier<FULL>(bar_id, zpad);
       continue;
     }
     // load_soft_bits (ldpc_decoder_impl.cpp:148-173) for both codeblocks: int8 -> fp16, +-127 -> +-inf; punctured and
@@ -728,7 +732,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       if (hasB) {
         dematch_stage_in(gB, softB, stB, (unsigned)t, (unsigned)zpad);
       }
-      tm::group_barrier(bar_id, zpad);
+      tm::group_barrier<FULL>(bar_id, zpad);
       // phase B: one pass in input order when no position is hit twice, else lap by lap
       const bool onceA = dematch_single_pass(gA), onceB = hasB && dematch_single_pass(gB);
       if (onceA) {
@@ -746,10 +750,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
           dematch_scatter_lap(gB, rmB, stB, lap, (unsigned)t, (unsigned)zpad);
         }
         if (lap + 1 < max(lapsA, lapsB)) {
-          tm::group_barrier(bar_id, zpad);
+          tm::group_barrier<FULL>(bar_id, zpad);
         }
       }
-      tm::group_barrier(bar_id, zpad);
+      tm::group_barrier<FULL>(bar_id, zpad);
       // phase C: back to the arena, and on to the decoder
       dematch_stage_out(gA, stA, softA, (unsigned)t, (unsigned)zpad);
       if (hasB) {
@@ -773,7 +777,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       }
     }
     if (FUSED && !useA && !useB) {  // combined only (both CRCs already passed in an earlier transmission)
-      tm::group_barrier(bar_id, zpad);
+      tm::group_barrier<FULL>(bar_id, zpad);
       continue;
     }
     if (lastA) {
@@ -782,7 +786,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     if (lastB) {
       atomicMax(const_cast<unsigned*>(&flags[1]), lastB);
     }
-    tm::group_barrier(bar_id, zpad);
+    tm::group_barrier<FULL>(bar_id, zpad);
     const unsigned inszA = flags[0], inszB = flags[1];  // one past the last non-zero LLR (ldpc_decoder_impl.cpp:86-94)
     bool doneA = !useA, doneB = !useB;
     CbResult resA = {0, 0, 0}, resB = {0, 0, 0};
@@ -852,14 +856,14 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         // the barrier that orders a row after its predecessor is inside the bodies
         const unsigned rd = p.rowdesc[r], pd = p.pairdesc[r];
         if (pd != 0 && r + 1 < nof_layers) {
-          tm::pair_dispatch<SCALE>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
+          tm::pair_dispatch<SCALE, FULL>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
           r += 2;
         } else {
-          tm::row_dispatch<SCALE>(c, p, r, bar_id, zpad, rd);
+          tm::row_dispatch<SCALE, FULL>(c, p, r, bar_id, zpad, rd);
           r += 1;
         }
       }
-      tm::group_barrier(bar_id, zpad);
+      tm::group_barrier<FULL>(bar_id, zpad);
       tm::tm_wait_st();
       ++it;
       const bool last = (it == p.max_iterations);
@@ -953,7 +957,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
             flags[acc_a ^ 2] = 0, flags[acc_b ^ 2] = 0;
           }
         }
-        tm::group_barrier(bar_id, zpad);
+        tm::group_barrier<FULL>(bar_id, zpad);
         const bool okA = crcA && flags[acc_a] == 0, okB = crcB && flags[acc_b] == 0;
         // the message bytes are only formed for a codeblock that finishes now
         if ((chkA && (okA || last)) || (chkB && (okB || last))) {
@@ -998,10 +1002,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         if (chkB) {
           finish(wB, resB, doneB, hard + msg_bytes16, okB);
         }
-        tm::group_barrier(bar_id, zpad);
+        tm::group_barrier<FULL>(bar_id, zpad);
       }
     }
-    tm::group_barrier(bar_id, zpad);  // flags / hard bits are reused by the next pair
+    tm::group_barrier<FULL>(bar_id, zpad);  // flags / hard bits are reused by the next pair
   }
   __syncthreads();
   if (warp == 0) {
@@ -1121,10 +1125,10 @@ constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block
 // several GPUs, and several host threads may launch at once).
 constexpr int TM_MAX_DEVICES = 64;
 
-template <int BG, int SCALE, bool FUSED>
-static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
+template <int BG, int SCALE, bool FUSED, bool FULL>
+static inline int tm_launch_full(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
 {
-  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED>;
+  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED, FULL>;
   static std::atomic<bool> attr_set[TM_MAX_DEVICES];
   if (device < 0 || device >= TM_MAX_DEVICES || !attr_set[device].load(std::memory_order_acquire)) {
     const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM_LIMIT);
@@ -1143,6 +1147,13 @@ static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned g
     return -1;
   }
   return 0;
+}
+
+template <int BG, int SCALE, bool FUSED>
+static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
+{
+  return (p.Z == MAX_Z && p.groups == 1) ? tm_launch_full<BG, SCALE, FUSED, true>(p, smem, grid, device, stream)
+                                         : tm_launch_full<BG, SCALE, FUSED, false>(p, smem, grid, device, stream);
 }
 
 template <int BG, int SCALE>
