@@ -507,6 +507,10 @@ def run_ours(args):
     es = {"value": total_bits / (ms_es / args.steps * 1e-3) / 1e9, "unit": "Gb/s",
           "mean_iterations": float(res_h["iterations"].mean()), "crc_pass_rate": float(res_h["crc_ok"].mean()),
           "what": "same LLRs, CRC24B early stop after every iteration (pusch_decoder default), max %d" % args.max_iters}
+    it_h = res_h["iterations"].astype(np.int64)
+    es["iteration_histogram"] = np.bincount(it_h, minlength=args.max_iters + 1).tolist()
+    # two codeblocks share a thread's registers: without re-pairing a pair would run the larger of its two counts
+    es["mean_of_pair_max_in_input_order"] = float(np.maximum(it_h[0::2], it_h[1::2]).mean()) if n_cb % 2 == 0 else None
 
     # end to end through the public host entry: pinned host LLRs -> H2D -> decode -> D2H bits + results
     e2e = None
