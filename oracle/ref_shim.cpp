@@ -784,6 +784,45 @@ void ref_pool_run_slot(void* handle, unsigned slot_count)
   static_cast<pool_handle*>(handle)->pool->run_slot(slot_point(1, slot_count % (1024 * 20)));
 }
 
+// Counters of the product's pool: out[6] = reservations, refused_in_use, refused_no_buffer, refused_no_slots, expired,
+// released. Returns 0, or -1 for a pool without them (the reference's).
+int ref_pool_stats(void* handle, unsigned long long* out)
+{
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  rx_softbuffer_pool_cuda_stats st = {};
+  if (get_rx_softbuffer_pool_cuda_stats(*static_cast<pool_handle*>(handle)->pool, st)) {
+    out[0] = st.reservations, out[1] = st.refused_in_use, out[2] = st.refused_no_buffer, out[3] = st.refused_no_slots;
+    out[4] = st.expired, out[5] = st.released;
+    return 0;
+  }
+#endif
+  (void)handle, (void)out;
+  return -1;
+}
+
+// Mean time in nanoseconds of reserve_softbuffer(nof_codeblocks) + release + run_slot on a pool whose first `occupied`
+// codeblock entries are taken by another reservation (how far a first-fit scan would have to walk).
+double ref_pool_time_reserve(void* handle, unsigned occupied, unsigned nof_codeblocks, unsigned repetitions)
+{
+  auto*      h = static_cast<pool_handle*>(handle);
+  slot_point slot(1, 0);
+  auto       blocker = h->pool->reserve_softbuffer(slot, {1, 0}, occupied);
+  if (occupied != 0 && !blocker.is_valid()) {
+    return -1.0;
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  for (unsigned i = 0; i != repetitions; ++i) {
+    auto buf = h->pool->reserve_softbuffer(slot, {2, 0}, nof_codeblocks);
+    if (!buf.is_valid()) {
+      return -1.0;
+    }
+    buf.release();
+    h->pool->run_slot(slot);
+  }
+  const auto t1 = std::chrono::steady_clock::now();
+  return std::chrono::duration<double, std::nano>(t1 - t0).count() / repetitions;
+}
+
 
 // ---- upstream producer of the LLRs: soft demodulator + descrambler ---------------------------------
 // demodulation_mapper_impl::demodulate_soft (lib/phy/upper/channel_modulation/demodulation_mapper_impl.cpp:74-106).

@@ -7,6 +7,7 @@
 #include "srsran/ran/modulation_scheme.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,6 +37,8 @@ void require(bool cond, const char* what)
     std::abort();
   }
 }
+
+std::atomic<uint64_t> private_arena_evictions{0};
 
 // Device soft-buffer arena in units of one codeblock slot, keyed by the caller's rx_softbuffer object.
 class arena_index
@@ -72,6 +75,15 @@ public:
         }
       }
       require(victim != table.end(), "transport block larger than the device soft-buffer arena");
+      // Not silent: the reference's pool refuses the reservation when it is out of entries (rx_softbuffer_impl.h:141-150);
+      // this private arena instead drops the oldest HARQ process, whose next retransmission combines into zeros.
+      const uint64_t n = private_arena_evictions.fetch_add(1, std::memory_order_relaxed);
+      if (n == 0) {
+        std::fprintf(stderr,
+                     "pusch_decoder_cuda: private soft-buffer arena full, dropping the soft bits of the least recently used "
+                     "HARQ process (further drops are counted only: pusch_decoder_cuda_private_arena_evictions()); raise "
+                     "arena_codeblocks or use create_rx_softbuffer_pool_cuda\n");
+      }
       release(victim->second);
       table.erase(victim);
     }
@@ -306,4 +318,9 @@ srsran::create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration
     return nullptr;
   }
   return std::make_shared<pusch_decoder_factory_cuda>(config);
+}
+
+uint64_t srsran::pusch_decoder_cuda_private_arena_evictions()
+{
+  return private_arena_evictions.load(std::memory_order_relaxed);
 }

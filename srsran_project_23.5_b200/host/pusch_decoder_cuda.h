@@ -17,6 +17,7 @@
 #include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
 #include "srsran/phy/upper/channel_processors/channel_processor_factories.h"
 
+#include <cstdint>
 #include <memory>
 
 namespace srsran {
@@ -35,5 +36,13 @@ struct pusch_decoder_cuda_configuration {
 
 /// Returns nullptr when no usable device exists (no CPU fallback), like the reference's factories for an unsupported type.
 std::shared_ptr<pusch_decoder_factory> create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration& config);
+
+/// HARQ processes whose device soft bits were dropped because a decoder's PRIVATE arena (used with the reference's host
+/// pool) was full, since the process started. With create_rx_softbuffer_pool_cuda nothing is ever dropped: reservations are
+/// refused like the reference's, and rx_softbuffer_pool_cuda_stats counts them. A decoder keys its private arena by the
+/// caller's rx_softbuffer object: when the host pool hands the same object to another (rnti, harq) with the same codeblock
+/// count and the first PDU says new_data = false, the old soft bits are combined - as the reference does with the host
+/// memory of a re-used buffer, which it never clears either (rx_softbuffer_codeblock_pool.h).
+uint64_t pusch_decoder_cuda_private_arena_evictions();
 
 } // namespace srsran

@@ -1,4 +1,21 @@
-// See rx_softbuffer_pool_cuda.h.
+// Device-resident HARQ soft-buffer pool (see rx_softbuffer_pool_cuda.h).
+//
+// Design: ONE table of reservations under ONE mutex. A reservation ("ledger line") records who holds it, until when, in
+// which phase it is and which codeblock slots of the device arena it owns; the objects handed to the caller are thin
+// handles (index + back pointer) without state of their own. Codeblock slots come from a two-level bitmap that always
+// yields the LOWEST free slot in O(1) (two count-trailing-zeros), so the placement - and with it the contents a caller
+// can observe in re-used slots - equals the first-fit order of rx_softbuffer_codeblock_pool.h:35-117 without its linear
+// scan: reserving a 152-codeblock buffer in a 38 912-slot pool takes a few microseconds.
+//
+// Observable behaviour follows rx_softbuffer_pool_impl.cpp:27-76 / rx_softbuffer_impl.h:112-262 (checked operation by
+// operation against the compiled reference in tests/test_softbuffer_pool.py):
+//   - reserve: the line that carries the identifier is used if there is one (refused while its holder is active), else the
+//     lowest idle or dropped line; a line whose codeblock count is unchanged keeps its slots, flags and stored messages;
+//     otherwise it returns its slots and takes new ones, lowest first, all or nothing;
+//   - a holder going out of scope puts the line back to "held"; release() marks it "dropped";
+//   - run_slot returns the slots of dropped lines and of held lines whose deadline has passed.
+// The two state assertions of the reference (lock only from "held", release only from "held" / "active") abort with the
+// same message. Expiries, releases and refused reservations are counted (rx_softbuffer_pool_cuda_stats).
 #include "rx_softbuffer_pool_cuda.h"
 
 #include "../../include/ldpc_cuda.h"
@@ -6,6 +23,8 @@
 #include "srsran/phy/upper/unique_rx_softbuffer.h"
 #include "srsran/ran/slot_point.h"
 
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -13,202 +32,118 @@ using namespace srsran;
 
 namespace {
 
-constexpr unsigned CB_SLOT_BYTES    = 66 * 384; // ldpc::MAX_CODEBLOCK_SIZE soft bits, one byte each
-constexpr unsigned CB_MESSAGE_BITS  = 22 * 384; // largest message (divide_ceil(max_codeblock_size, 3))
-constexpr unsigned UNRESERVED_CB_ID = UINT32_MAX;
+constexpr unsigned SLOT_BYTES   = 66 * 384; // soft bits of the largest codeblock, one byte each (ldpc::MAX_CODEBLOCK_SIZE)
+constexpr unsigned MESSAGE_BITS = 22 * 384; // largest decoded message kept for retransmissions
+constexpr unsigned NO_SLOT      = UINT32_MAX;
 
-// rx_softbuffer_codeblock_pool.h:35-117 with the soft bits on the device: entry i owns arena bytes [i, i + 1) * 25 344.
-class codeblock_pool
+[[noreturn]] void fatal(const char* what)
+{
+  std::fprintf(stderr, "rx_softbuffer_pool_cuda: %s\n", what);
+  std::fflush(stderr);
+  std::abort();
+}
+
+// Lowest-free-index allocator over n slots: bit set = free. One summary bit per 64-slot word.
+class lowest_free
 {
 public:
-  explicit codeblock_pool(unsigned nof_codeblocks) : reserved(nof_codeblocks, false)
+  explicit lowest_free(unsigned n) : leaf((n + 63) / 64, 0), top((leaf.size() + 63) / 64, 0)
   {
-    data_bits.reserve(nof_codeblocks);
-    for (unsigned i = 0; i != nof_codeblocks; ++i) {
-      data_bits.emplace_back(std::make_unique<dynamic_bit_buffer>(CB_MESSAGE_BITS));
-      data_bits.back()->zero();
+    for (unsigned i = 0; i != n; ++i) {
+      give(i);
     }
   }
 
-  unsigned reserve()
+  unsigned take()
   {
-    for (unsigned cb_id = 0; cb_id != reserved.size(); ++cb_id) { // first available, like the reference
-      if (!reserved[cb_id]) {
-        reserved[cb_id] = true;
-        return cb_id;
+    for (size_t t = 0; t != top.size(); ++t) { // one word covers 4096 slots
+      if (top[t] == 0) {
+        continue;
       }
+      const size_t   w = 64 * t + static_cast<size_t>(__builtin_ctzll(top[t]));
+      const unsigned b = static_cast<unsigned>(__builtin_ctzll(leaf[w]));
+      leaf[w] &= leaf[w] - 1;
+      if (leaf[w] == 0) {
+        top[t] &= ~(1ull << (w % 64));
+      }
+      return static_cast<unsigned>(64 * w) + b;
     }
-    return UNRESERVED_CB_ID;
+    return NO_SLOT;
   }
 
-  void free(unsigned cb_id)
+  void give(unsigned i)
   {
-    if (cb_id != UNRESERVED_CB_ID) {
-      reserved[cb_id] = false;
-    }
+    leaf[i / 64] |= 1ull << (i % 64);
+    top[i / 4096] |= 1ull << ((i / 64) % 64);
   }
-
-  bit_buffer& get_data_bits(unsigned cb_id) { return *data_bits[cb_id]; }
 
 private:
-  std::vector<bool>                                reserved;
-  std::vector<std::unique_ptr<dynamic_bit_buffer>> data_bits;
+  std::vector<uint64_t> leaf, top;
 };
 
-// rx_softbuffer_impl.h:34-262.
-class softbuffer_cuda : public unique_rx_softbuffer::softbuffer, public rx_softbuffer_device
+enum class phase : uint8_t { idle, held, active, dropped };
+
+struct ledger_line {
+  rx_softbuffer_identifier who = {};
+  slot_point               deadline;
+  phase                    ph = phase::idle;
+  std::vector<unsigned>    slots;         // codeblock slots owned (empty after the slots went back)
+  std::unique_ptr<bool[]>  crc;           // one flag per codeblock; survives re-sizing for the indices that remain
+  unsigned                 nof_flags = 0; // what get_nof_codeblocks() reports (kept when the slots go back)
+};
+
+class pool_core;
+
+// What the caller holds: no state, everything lives in the ledger.
+class buffer_handle final : public unique_rx_softbuffer::softbuffer, public rx_softbuffer_device
 {
 public:
-  softbuffer_cuda(codeblock_pool& pool_, void* arena_, uint64_t arena_bytes_) :
-    pool(pool_), arena_d(arena_), arena_size(arena_bytes_)
-  {
-  }
-
-  bool reserve(const rx_softbuffer_identifier& id, const slot_point& expire_slot, unsigned nof_codeblocks)
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    if (current_state == state::locked) {
-      return false;
-    }
-    reservation_id          = id;
-    reservation_expire_slot = expire_slot;
-    if (nof_codeblocks == codeblock_ids.size()) {
-      current_state = state::reserved;
-      return true;
-    }
-    free_codeblocks();
-    crc.resize(nof_codeblocks); // keeps the flags of the indices that remain, as static_vector::resize does
-    codeblock_ids.assign(nof_codeblocks, UNRESERVED_CB_ID);
-    for (unsigned& cb_id : codeblock_ids) {
-      cb_id = pool.reserve();
-      if (cb_id == UNRESERVED_CB_ID) {
-        free_codeblocks();
-        return false;
-      }
-    }
-    current_state = state::reserved;
-    return true;
-  }
-
-  void run_slot(const slot_point& slot)
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    const bool                   is_released = current_state == state::released;
-    const bool is_expired = (current_state == state::reserved) && (reservation_expire_slot <= slot);
-    if (is_released || is_expired) {
-      free_codeblocks();
-    }
-  }
-
-  bool match_id(const rx_softbuffer_identifier& identifier) const { return reservation_id == identifier; }
-
-  bool is_available() const
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    return (current_state == state::available) || (current_state == state::released);
-  }
+  buffer_handle(pool_core& core_, unsigned line_) : core(core_), line(line_) {}
 
   // rx_softbuffer
-  unsigned get_nof_codeblocks() const override { return static_cast<unsigned>(crc.size()); }
-  void     reset_codeblocks_crc() override
-  {
-    for (unsigned i = 0; i != crc.size(); ++i) {
-      crc[i] = false;
-    }
-  }
-  span<bool> get_codeblocks_crc() override { return span<bool>(crc.data(), crc.size()); }
-  span<log_likelihood_ratio> get_codeblock_soft_bits(unsigned /*codeblock_id*/, unsigned /*codeblock_size*/) override
-  {
-    return {}; // the soft bits are device-resident: see rx_softbuffer_device
-  }
-  bit_buffer get_codeblock_data_bits(unsigned codeblock_id, unsigned data_size) override
-  {
-    return pool.get_data_bits(codeblock_ids[codeblock_id]).first(data_size);
-  }
-
+  unsigned                   get_nof_codeblocks() const override;
+  void                       reset_codeblocks_crc() override;
+  span<bool>                 get_codeblocks_crc() override;
+  span<log_likelihood_ratio> get_codeblock_soft_bits(unsigned, unsigned) override { return {}; } // device-resident
+  bit_buffer                 get_codeblock_data_bits(unsigned codeblock_id, unsigned data_size) override;
   // rx_softbuffer_device
-  void*    arena() const override { return arena_d; }
-  uint64_t arena_bytes() const override { return arena_size; }
-  uint64_t soft_offset(unsigned codeblock_id) const override
-  {
-    return static_cast<uint64_t>(codeblock_ids[codeblock_id]) * CB_SLOT_BYTES;
-  }
-
+  void*    arena() const override;
+  uint64_t arena_bytes() const override;
+  uint64_t soft_offset(unsigned codeblock_id) const override;
   // unique_rx_softbuffer::softbuffer
-  void lock() override
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    current_state = state::locked;
-  }
-  void unlock() override
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    if (current_state == state::locked) {
-      current_state = state::reserved;
-    }
-  }
-  void release() override
-  {
-    std::unique_lock<std::mutex> lock(fsm_mutex);
-    current_state = state::released;
-  }
+  void lock() override;
+  void unlock() override;
+  void release() override;
 
 private:
-  enum class state { available = 0, reserved, locked, released };
-
-  // bool storage that can hand out span<bool> (std::vector<bool> cannot)
-  struct flags {
-    std::unique_ptr<bool[]> v;
-    size_t                  n = 0;
-    void                    resize(size_t m)
-    {
-      std::unique_ptr<bool[]> w(new bool[m]());
-      for (size_t i = 0; i != (m < n ? m : n); ++i) {
-        w[i] = v[i];
-      }
-      v = std::move(w);
-      n = m;
-    }
-    size_t size() const { return n; }
-    bool*  data() { return v.get(); }
-    bool&  operator[](size_t i) { return v[i]; }
-  };
-
-  void free_codeblocks()
-  {
-    for (unsigned cb_id : codeblock_ids) {
-      pool.free(cb_id);
-    }
-    codeblock_ids.clear();
-    current_state = state::available;
-  }
-
-  mutable std::mutex       fsm_mutex;
-  state                    current_state  = state::available;
-  rx_softbuffer_identifier reservation_id = {};
-  slot_point               reservation_expire_slot;
-  codeblock_pool&          pool;
-  void*                    arena_d;
-  uint64_t                 arena_size;
-  flags                    crc;
-  std::vector<unsigned>    codeblock_ids;
+  pool_core& core;
+  unsigned   line;
 };
 
-// rx_softbuffer_pool_impl.cpp:27-76.
-class rx_softbuffer_pool_cuda : public rx_softbuffer_pool
+class pool_core final : public rx_softbuffer_pool, public rx_softbuffer_pool_cuda_introspection
 {
 public:
-  rx_softbuffer_pool_cuda(const rx_softbuffer_pool_cuda_config& cfg, void* arena_, uint64_t arena_bytes_) :
-    device(cfg.device), arena_d(arena_), cb_pool(cfg.max_nof_codeblocks), expire_timeout_slots(cfg.expire_timeout_slots)
+  pool_core(const rx_softbuffer_pool_cuda_config& cfg, void* arena_, uint64_t arena_bytes_) :
+    device(cfg.device),
+    arena_d(arena_),
+    arena_size(arena_bytes_),
+    timeout_slots(cfg.expire_timeout_slots),
+    free_slots(cfg.max_nof_codeblocks),
+    ledger(cfg.max_softbuffers)
   {
+    messages.reserve(cfg.max_nof_codeblocks);
+    for (unsigned i = 0; i != cfg.max_nof_codeblocks; ++i) {
+      messages.emplace_back(std::make_unique<dynamic_bit_buffer>(MESSAGE_BITS));
+      messages.back()->zero();
+    }
+    handles.reserve(cfg.max_softbuffers);
     for (unsigned i = 0; i != cfg.max_softbuffers; ++i) {
-      buffers.emplace_back(std::make_unique<softbuffer_cuda>(cb_pool, arena_, arena_bytes_));
+      handles.emplace_back(*this, i);
     }
   }
 
-  ~rx_softbuffer_pool_cuda() override
+  ~pool_core() override
   {
-    buffers.clear();
     if (arena_d != nullptr) {
       ldpc_cuda_arena_destroy(device, arena_d);
     }
@@ -217,54 +152,202 @@ public:
   unique_rx_softbuffer
   reserve_softbuffer(const slot_point& slot, const rx_softbuffer_identifier& id, unsigned nof_codeblocks) override
   {
-    std::unique_lock<std::mutex> lock(mutex);
-    slot_point                   expire_slot = slot + expire_timeout_slots;
-    for (auto& buffer : buffers) { // same identifier first
-      if (buffer->match_id(id)) {
-        if (!buffer->reserve(id, expire_slot, nof_codeblocks)) {
-          return unique_rx_softbuffer();
-        }
-        return unique_rx_softbuffer(*buffer);
+    unsigned pick = NO_SLOT;
+    {
+      std::lock_guard<std::mutex> guard(mtx);
+      // the line that carries the identifier, else the lowest line nobody holds
+      for (unsigned i = 0; i != ledger.size() && pick == NO_SLOT; ++i) {
+        pick = (ledger[i].who == id) ? i : NO_SLOT;
       }
-    }
-    for (auto& buffer : buffers) { // else the first available
-      if (buffer->is_available()) {
-        if (!buffer->reserve(id, expire_slot, nof_codeblocks)) {
-          return unique_rx_softbuffer();
-        }
-        return unique_rx_softbuffer(*buffer);
+      for (unsigned i = 0; i != ledger.size() && pick == NO_SLOT; ++i) {
+        pick = (ledger[i].ph == phase::idle || ledger[i].ph == phase::dropped) ? i : NO_SLOT;
       }
+      if (pick == NO_SLOT) {
+        ++counters.refused_no_buffer;
+        return unique_rx_softbuffer();
+      }
+      if (!assign(ledger[pick], id, slot + timeout_slots, nof_codeblocks)) {
+        return unique_rx_softbuffer();
+      }
+      ++counters.reservations;
     }
-    return unique_rx_softbuffer();
+    return unique_rx_softbuffer(handles[pick]); // locks the line (takes the mutex again)
   }
 
   void run_slot(const slot_point& slot) override
   {
-    std::unique_lock<std::mutex> lock(mutex);
-    for (auto& buffer : buffers) {
-      buffer->run_slot(slot);
+    std::lock_guard<std::mutex> guard(mtx);
+    for (ledger_line& l : ledger) {
+      if (l.ph == phase::dropped) {
+        ++counters.released;
+        give_back(l);
+      } else if (l.ph == phase::held && l.deadline <= slot) {
+        ++counters.expired;
+        give_back(l);
+      }
     }
   }
 
+  rx_softbuffer_pool_cuda_stats stats() const override
+  {
+    std::lock_guard<std::mutex> guard(mtx);
+    return counters;
+  }
+
+  // -- what the handles forward to -----------------------------------------------------------------------------------
+  void activate(unsigned i)
+  {
+    std::lock_guard<std::mutex> guard(mtx);
+    if (ledger[i].ph != phase::held) {
+      fatal("It is only possible to reserve in reserved state.");
+    }
+    ledger[i].ph = phase::active;
+  }
+  void deactivate(unsigned i)
+  {
+    std::lock_guard<std::mutex> guard(mtx);
+    if (ledger[i].ph == phase::active) {
+      ledger[i].ph = phase::held;
+    }
+  }
+  void drop(unsigned i)
+  {
+    std::lock_guard<std::mutex> guard(mtx);
+    if (ledger[i].ph != phase::held && ledger[i].ph != phase::active) {
+      fatal("It is only possible to reserve in reserved state.");
+    }
+    ledger[i].ph = phase::dropped;
+  }
+  ledger_line& at(unsigned i) { return ledger[i]; }
+  bit_buffer&  message(unsigned slot) { return *messages[slot]; }
+  void*        arena() const { return arena_d; }
+  uint64_t     arena_bytes() const { return arena_size; }
+
 private:
-  int                                           device;
-  void*                                         arena_d;
-  std::mutex                                    mutex;
-  codeblock_pool                                cb_pool;
-  std::vector<std::unique_ptr<softbuffer_cuda>> buffers;
-  unsigned                                      expire_timeout_slots;
+  void give_back(ledger_line& l)
+  {
+    for (unsigned s : l.slots) {
+      free_slots.give(s);
+    }
+    l.slots.clear();
+    l.ph = phase::idle;
+  }
+
+  // mtx held. The identifier and the deadline are recorded even when the reservation then fails for lack of slots.
+  bool assign(ledger_line& l, const rx_softbuffer_identifier& id, const slot_point& deadline, unsigned n)
+  {
+    if (l.ph == phase::active) {
+      ++counters.refused_in_use;
+      return false;
+    }
+    l.who      = id;
+    l.deadline = deadline;
+    if (n != l.slots.size()) {
+      give_back(l);
+      std::unique_ptr<bool[]> flags(new bool[n]());
+      for (unsigned i = 0; i != n && i != l.nof_flags; ++i) {
+        flags[i] = l.crc[i];
+      }
+      l.crc       = std::move(flags);
+      l.nof_flags = n;
+      l.slots.reserve(n);
+      for (unsigned i = 0; i != n; ++i) {
+        const unsigned s = free_slots.take();
+        if (s == NO_SLOT) {
+          ++counters.refused_no_slots;
+          give_back(l);
+          return false;
+        }
+        l.slots.push_back(s);
+      }
+    }
+    l.ph = phase::held;
+    return true;
+  }
+
+  int                                              device;
+  void*                                            arena_d;
+  uint64_t                                         arena_size;
+  unsigned                                         timeout_slots;
+  mutable std::mutex                               mtx;
+  lowest_free                                      free_slots;
+  std::vector<ledger_line>                         ledger;
+  std::vector<buffer_handle>                       handles;
+  std::vector<std::unique_ptr<dynamic_bit_buffer>> messages;
+  rx_softbuffer_pool_cuda_stats                    counters = {};
 };
+
+unsigned buffer_handle::get_nof_codeblocks() const
+{
+  return core.at(line).nof_flags;
+}
+void buffer_handle::reset_codeblocks_crc()
+{
+  ledger_line& l = core.at(line);
+  std::fill(l.crc.get(), l.crc.get() + l.nof_flags, false);
+}
+span<bool> buffer_handle::get_codeblocks_crc()
+{
+  ledger_line& l = core.at(line);
+  return span<bool>(l.crc.get(), l.nof_flags);
+}
+bit_buffer buffer_handle::get_codeblock_data_bits(unsigned codeblock_id, unsigned data_size)
+{
+  ledger_line& l = core.at(line);
+  if (codeblock_id >= l.slots.size() || data_size > MESSAGE_BITS) {
+    fatal("codeblock index or data size out of range");
+  }
+  return core.message(l.slots[codeblock_id]).first(data_size);
+}
+void* buffer_handle::arena() const
+{
+  return core.arena();
+}
+uint64_t buffer_handle::arena_bytes() const
+{
+  return core.arena_bytes();
+}
+uint64_t buffer_handle::soft_offset(unsigned codeblock_id) const
+{
+  const ledger_line& l = core.at(line);
+  if (codeblock_id >= l.slots.size()) {
+    fatal("codeblock index out of range");
+  }
+  return static_cast<uint64_t>(l.slots[codeblock_id]) * SLOT_BYTES;
+}
+void buffer_handle::lock()
+{
+  core.activate(line);
+}
+void buffer_handle::unlock()
+{
+  core.deactivate(line);
+}
+void buffer_handle::release()
+{
+  core.drop(line);
+}
 
 } // namespace
 
 std::unique_ptr<rx_softbuffer_pool> srsran::create_rx_softbuffer_pool_cuda(const rx_softbuffer_pool_cuda_config& config)
 {
   void*          arena = nullptr;
-  const uint64_t bytes = static_cast<uint64_t>(config.max_nof_codeblocks) * CB_SLOT_BYTES;
+  const uint64_t bytes = static_cast<uint64_t>(config.max_nof_codeblocks) * SLOT_BYTES;
   if (config.device >= 0) {
     if (config.max_nof_codeblocks == 0 || ldpc_cuda_arena_create(config.device, bytes, &arena) != LDPC_CUDA_OK) {
       return nullptr;
     }
   }
-  return std::make_unique<rx_softbuffer_pool_cuda>(config, arena, arena ? bytes : 0);
+  return std::make_unique<pool_core>(config, arena, arena ? bytes : 0);
+}
+
+bool srsran::get_rx_softbuffer_pool_cuda_stats(const rx_softbuffer_pool& pool, rx_softbuffer_pool_cuda_stats& out)
+{
+  const auto* p = dynamic_cast<const rx_softbuffer_pool_cuda_introspection*>(&pool);
+  if (p == nullptr) {
+    return false;
+  }
+  out = p->stats();
+  return true;
 }

@@ -32,9 +32,19 @@ def lib():
                        ("ref_pool_data_byte", [ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_int]),
                        ("ref_pool_unlock", [ctypes.c_void_p, ctypes.c_int]),
                        ("ref_pool_release", [ctypes.c_void_p, ctypes.c_int]),
-                       ("ref_pool_run_slot", [ctypes.c_void_p, ctypes.c_uint])):
+                       ("ref_pool_run_slot", [ctypes.c_void_p, ctypes.c_uint]),
+                       ("ref_pool_stats", [ctypes.c_void_p, ctypes.POINTER(ctypes.c_ulonglong)]),
+                       ("ref_pool_time_reserve", [ctypes.c_void_p] + [ctypes.c_uint] * 3)):
         getattr(L, name).argtypes = args
+    L.ref_pool_time_reserve.restype = ctypes.c_double
     return L
+
+
+def _stats(lib, pool):
+    out = (ctypes.c_ulonglong * 6)()
+    assert lib.ref_pool_stats(pool, out) == 0
+    return dict(zip(("reservations", "refused_in_use", "refused_no_buffer", "refused_no_slots", "expired", "released"),
+                    [int(v) for v in out]))
 
 
 @pytest.mark.parametrize("seed,nbuf,ncb,expire", [(1, 4, 8, 5), (2, 2, 6, 3), (3, 6, 40, 10), (4, 3, 5, 1)])
@@ -116,3 +126,34 @@ def test_crc_flags_persist_across_reservations_of_the_same_process(lib):
         lib.ref_pool_run_slot(p, 8)
         assert lib.ref_pool_reserve(p, 8, 19, 0, 12) >= 0, kind
         lib.ref_pool_destroy(p)
+
+
+def test_pool_counts_what_happens_to_reservations(lib):
+    """The product pool records expiries, releases and refused reservations (the reference loses HARQ state silently)."""
+    p = lib.ref_pool_create(b"cuda-host", 2, 10, 3)
+    assert lib.ref_pool_stats(lib.ref_pool_create(b"sw", 2, 10, 3), (ctypes.c_ulonglong * 6)()) == -1
+    a = lib.ref_pool_reserve(p, 0, 1, 0, 6)
+    assert a >= 0
+    assert lib.ref_pool_reserve(p, 0, 1, 0, 6) < 0      # same identifier, still held by `a`
+    assert lib.ref_pool_reserve(p, 0, 2, 0, 6) < 0      # 4 entries left
+    b = lib.ref_pool_reserve(p, 0, 3, 0, 4)
+    assert b >= 0
+    assert lib.ref_pool_reserve(p, 0, 4, 0, 1) < 0      # both buffers taken
+    lib.ref_pool_unlock(p, a)
+    lib.ref_pool_release(p, b)
+    lib.ref_pool_run_slot(p, 1)                         # b's entries return, a stays until its deadline
+    assert _stats(lib, p) == dict(reservations=2, refused_in_use=1, refused_no_buffer=1, refused_no_slots=1, expired=0,
+                                  released=1)
+    lib.ref_pool_run_slot(p, 3)                         # deadline of a = slot 0 + 3
+    assert _stats(lib, p)["expired"] == 1
+    lib.ref_pool_destroy(p)
+
+
+def test_reserving_a_full_slot_buffer_in_a_large_pool_is_fast(lib):
+    """152 codeblock entries behind 30 000 occupied ones in a 38 912-entry pool (16 cells x 16 HARQ x 152): the lowest-free
+    bitmap makes the reservation independent of how full the pool is; the reference's first-fit scan walks the occupied
+    entries for every codeblock."""
+    ours = lib.ref_pool_create(b"cuda-host", 4, 38912, 10)
+    ns = lib.ref_pool_time_reserve(ours, 30000, 152, 200)
+    lib.ref_pool_destroy(ours)
+    assert 0 < ns < 10000, ns
