@@ -369,6 +369,61 @@ int ldpc_cuda_arena_destroy(int device, void* arena_d);
 int ldpc_cuda_softbuffer_attach(ldpc_cuda_handle* handle, void* arena_d, uint64_t nof_bytes);
 
 /* ---------------------------------------------------------------------------------------------------------------------
+ * Several GPUs of one box from ONE process (BASELINE.json north_star: "a slot's transport blocks are sharded
+ * round-robin across the 8 GPUs of one box by host streams, with no NCCL on the decode path"). Replaces nothing in the
+ * reference, whose unit of concurrency is one decoder object per uplink thread (apps/gnb/gnb_appconfig.h:367
+ * nof_ul_threads, lib/phy/upper/uplink_processor_impl.cpp:155-171); what makes the split legal is that the codeblock loop
+ * of pusch_decoder_impl::decode (lib/phy/upper/channel_processors/pusch_decoder_impl.cpp:156-201) carries nothing from one
+ * codeblock to the next. A pool owns one handle + one host thread per device; its calls are synchronous like the
+ * single-device host entries and take the same HOST buffers and descriptors: every device copies its share straight from /
+ * to the caller's buffers (pitched copies for interleaved shares), nothing is exchanged between devices.
+ * A pool is not thread-safe (one caller at a time).
+ */
+typedef struct ldpc_cuda_pool ldpc_cuda_pool;
+
+/* devices: distinct CUDA ordinals (sm_100). max_codeblocks_per_device: as ldpc_cuda_create. */
+int      ldpc_cuda_pool_create(ldpc_cuda_pool** pool, const int* devices, uint32_t nof_devices,
+                               uint32_t max_codeblocks_per_device, uint32_t flags);
+void     ldpc_cuda_pool_destroy(ldpc_cuda_pool* pool);
+uint32_t ldpc_cuda_pool_nof_devices(const ldpc_cuda_pool* pool);
+/* The handle of device number index (0 .. nof_devices - 1), e.g. for ldpc_cuda_softbuffer_read; owned by the pool. */
+ldpc_cuda_handle* ldpc_cuda_pool_handle(ldpc_cuda_pool* pool, uint32_t index);
+int      ldpc_cuda_pool_set_algorithm(ldpc_cuda_pool* pool, const ldpc_cuda_algorithm* alg);
+/* A soft-buffer arena of nof_bytes_per_device on EVERY device (zeroed); forgets where HARQ processes live. soft_offset of
+ * a descriptor is an offset into the arena of whichever device the transport block is routed to, so a caller lays out ONE
+ * arena and every device mirrors it (180 GB per GPU: cfg 5 needs 1 GB). */
+int      ldpc_cuda_pool_softbuffer_reserve(ldpc_cuda_pool* pool, uint64_t nof_bytes_per_device);
+uint64_t ldpc_cuda_pool_launch_count(const ldpc_cuda_pool* pool);
+/* Codeblocks each device has processed since creation (counts[nof_counts >= nof_devices]). */
+int      ldpc_cuda_pool_codeblocks_per_device(const ldpc_cuda_pool* pool, uint64_t* counts, uint32_t nof_counts);
+/* Device number that holds the soft buffers of HARQ process harq_key, -1 when the pool has not seen it. */
+int      ldpc_cuda_pool_device_of(const ldpc_cuda_pool* pool, uint64_t harq_key);
+
+/* ldpc_cuda_decode_batch over all devices: codeblock i runs on device i mod nof_devices (SURVEY.md 8d cfg 4). */
+int ldpc_cuda_pool_decode_batch(ldpc_cuda_pool*          pool,
+                                uint32_t                 nof_codeblocks,
+                                const ldpc_cuda_cb_desc* descs,
+                                const int8_t*            llrs,
+                                uint8_t*                 out_bits,
+                                ldpc_cuda_cb_result*     results);
+
+/* ldpc_cuda_dematch_decode_tb_batch over all devices: transport blocks stay whole (a block is assembled and CRC-checked
+ * where its codeblocks ran). harq_keys[t] names the HARQ process of block t (any injective code of (cell, rnti, harq_id)):
+ * a block whose codeblocks all have new_data = 1 goes to the next device in turn and that device becomes the home of the
+ * process; every later block of the process goes to its home, where its soft buffers are. */
+int ldpc_cuda_pool_dematch_decode_tb_batch(ldpc_cuda_pool*          pool,
+                                           uint32_t                 nof_codeblocks,
+                                           const ldpc_cuda_cb_desc* descs,
+                                           const int8_t*            rm_llrs,
+                                           uint8_t*                 out_bits, /* may be NULL, see the single-device entry */
+                                           ldpc_cuda_cb_result*     results,
+                                           uint32_t                 nof_tbs,
+                                           const ldpc_cuda_tb_desc* tbs,
+                                           const uint64_t*          harq_keys,
+                                           uint8_t*                 tb_out,
+                                           ldpc_cuda_tb_result*     tb_results);
+
+/* ---------------------------------------------------------------------------------------------------------------------
  * Transmit side (also how bench.py builds its synthetic codewords without leaving the device).
  * Bits are unpacked, one per byte, as in the reference's encoder chain; filler bits are 254
  * (include/srsran/phy/upper/channel_coding/ldpc/ldpc.h:113).

@@ -973,12 +973,62 @@ struct Chunk {
   uint64_t in_lo, in_hi;    // host input bytes (hull)
   uint64_t out_lo, out_hi;  // host output bytes
   std::vector<std::pair<uint64_t, uint64_t>> in_runs;  // contiguous input pieces to copy; empty: the hull
+  // Contiguous output pieces; empty: the hull [out_lo, out_hi). More than one piece when the chunk's messages are not
+  // adjacent in the caller's buffer (e.g. the transport blocks in between belong to another device of a pool): the bytes
+  // in between are then neither read nor written.
+  std::vector<std::pair<uint64_t, uint64_t>> out_runs;
+  // Equally long pieces at a constant stride (a batch sharded round-robin over several devices: codeblock i, i + G, ...):
+  // ONE pitched copy instead of thousands of small ones. rows == 0: not in this form.
+  uint64_t in_stride = 0, in_width = 0, in_rows = 0;
+  uint64_t out_stride = 0, out_width = 0, out_rows = 0;  // outputs likewise; never the hull then (it belongs to others too)
 };
+
+// Pitched host <-> device copy with the same pitch on both sides (the device buffers mirror the host layout).
+static cudaError_t copy_rows(void* dst, const void* src, uint64_t stride, uint64_t width, uint64_t rows, cudaMemcpyKind kind,
+                             cudaStream_t stream)
+{
+  return cudaMemcpy2DAsync(dst, stride, src, stride, width, rows, kind, stream);
+}
 
 static inline void cb_ranges(const ldpc_cuda_cb_desc& d, bool fused, uint64_t& in_end, uint64_t& out_end)
 {
   in_end = d.in_offset + (fused ? d.rm_length : d.in_length);
   out_end = d.out_offset + ((uint64_t)bg_K(d.base_graph) * d.lifting_size + 7) / 8;
+}
+
+// Recognises a chunk whose codeblocks lie at a constant stride in the caller's buffers (input pieces of equal length,
+// output messages of equal length, gaps in between that belong to somebody else) and records the pitched form.
+static void strided_form(const ldpc_cuda_handle* h, const ldpc_cuda_cb_desc* descs, bool fused, Chunk& c)
+{
+  const uint32_t n = c.e - c.b;
+  if (n < 2) {
+    return;
+  }
+  const ldpc_cuda_cb_desc& d0 = descs[h->order[c.b]];
+  const ldpc_cuda_cb_desc& d1 = descs[h->order[c.b + 1]];
+  uint64_t ie0, oe0;
+  cb_ranges(d0, fused, ie0, oe0);
+  const uint64_t iw = ie0 - d0.in_offset, ow = oe0 - d0.out_offset;
+  if (d1.in_offset <= d0.in_offset || d1.out_offset <= d0.out_offset) {
+    return;
+  }
+  const uint64_t is = d1.in_offset - d0.in_offset, os = d1.out_offset - d0.out_offset;
+  bool in_ok = iw != 0 && is > iw, out_ok = os > ow;  // dense layouts keep the plain range copies
+  for (uint32_t k = 1; k != n && (in_ok || out_ok); ++k) {
+    const ldpc_cuda_cb_desc& d = descs[h->order[c.b + k]];
+    uint64_t ie, oe;
+    cb_ranges(d, fused, ie, oe);
+    in_ok = in_ok && d.in_offset == d0.in_offset + k * is && ie - d.in_offset == iw;
+    out_ok = out_ok && d.out_offset == d0.out_offset + k * os && oe - d.out_offset == ow;
+  }
+  if (in_ok) {
+    c.in_stride = is, c.in_width = iw, c.in_rows = n;
+    c.in_runs.clear();
+    c.in_runs.push_back({d0.in_offset, d0.in_offset + iw});  // counted as one copy
+  }
+  if (out_ok) {
+    c.out_stride = os, c.out_width = ow, c.out_rows = n;
+  }
 }
 
 // Splits the staged groups into at most MAX_CHUNKS chunks of about equal input size. Chunks are only formed when the
@@ -1009,6 +1059,25 @@ static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc
   auto single = [&]() {
     chunks.clear();
     chunks.push_back({0, n, in_lo, in_hi, out_lo, out_hi, {}});  // one copy in, all launches, one copy out
+    Chunk& c = chunks.back();
+    strided_form(h, descs, fused, c);
+    c.in_runs.clear();
+    // output pieces in launch order (exactly adjacent messages merge); too scattered: the hull, as for one device alone
+    if (c.out_rows == 0) {
+      for (uint32_t k = 0; k != n && c.out_runs.size() <= MAX_RUNS; ++k) {
+        const ldpc_cuda_cb_desc& d = descs[h->order[k]];
+        uint64_t ie, oe;
+        cb_ranges(d, fused, ie, oe);
+        if (!c.out_runs.empty() && d.out_offset == c.out_runs.back().second) {
+          c.out_runs.back().second = oe;
+        } else {
+          c.out_runs.push_back({d.out_offset, oe});
+        }
+      }
+      if (c.out_runs.size() == 1 || c.out_runs.size() > MAX_RUNS) {
+        c.out_runs.clear();
+      }
+    }
   };
   if (!monotone || 2 * nof_groups > MAX_CHUNKS || total_in < 2 * MIN_CHUNK_BYTES) {
     single();
@@ -1038,12 +1107,21 @@ static void plan_chunks(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc
           c.in_lo = std::min(c.in_lo, d.in_offset), c.in_hi = std::max(c.in_hi, ie);
           bytes += ie - d.in_offset;
         }
+        if (!c.out_runs.empty() && d.out_offset == c.out_runs.back().second) {
+          c.out_runs.back().second = c.out_hi;
+        } else {
+          c.out_runs.push_back({d.out_offset, c.out_hi});
+        }
         ++c.e;
       } while (c.e != ge && (bytes < target || chunks.size() + 1 == MAX_CHUNKS));
       if (c.in_hi < c.in_lo) {
         c.in_lo = c.in_hi = in_lo;  // nothing to copy
       }
-      runs += c.in_runs.size();
+      strided_form(h, descs, fused, c);
+      if (c.out_rows != 0 || c.out_runs.size() == 1) {
+        c.out_runs.clear();  // one pitched copy / the hull is exact
+      }
+      runs += c.in_runs.size() + c.out_runs.size();
       chunks.push_back(c);
       b = c.e;
     }
@@ -1201,19 +1279,34 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
       cudaStreamSynchronize(h->stream);
       return arc;
     }
-    uint64_t lo = ~0ull, hi = 0;
+    // block by block (exactly adjacent blocks as one copy): the bytes between two blocks of this call may belong to
+    // somebody else, e.g. to the blocks another device of a pool assembles into the same buffer
+    uint64_t lo = 0, hi = 0;
     for (uint32_t t = t0; t != t1; ++t) {
-      lo = std::min<uint64_t>(lo, tbs[t].tb_offset);
-      hi = std::max<uint64_t>(hi, tbs[t].tb_offset + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0));
+      const uint64_t b = tbs[t].tb_offset, e = b + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0);
+      if (hi != lo && b == hi) {
+        hi = e;
+        continue;
+      }
+      if (hi != lo) {
+        CUDA_TRY(cudaMemcpyAsync(tb_out + lo, d_tb_bytes + (lo - tb_lo), hi - lo, cudaMemcpyDeviceToHost, h->d2h_stream));
+      }
+      lo = b, hi = e;
     }
-    CUDA_TRY(cudaMemcpyAsync(tb_out + lo, d_tb_bytes + (lo - tb_lo), hi - lo, cudaMemcpyDeviceToHost, h->d2h_stream));
+    if (hi != lo) {
+      CUDA_TRY(cudaMemcpyAsync(tb_out + lo, d_tb_bytes + (lo - tb_lo), hi - lo, cudaMemcpyDeviceToHost, h->d2h_stream));
+    }
     tb_next = t1;
     return LDPC_CUDA_OK;
   };
   const uint32_t tb_group = std::max<uint32_t>(1, (nof_tbs + 3) / 4);  // at most ~4 early groups
   for (size_t ci = 0; ci != chunks.size(); ++ci) {
     const Chunk& c = chunks[ci];
-    if (c.in_runs.empty()) {
+    if (c.in_rows != 0) {
+      const uint64_t first = descs[h->order[c.b]].in_offset;
+      CUDA_TRY(copy_rows(h->d_in + (first - in_lo), in + first, c.in_stride, c.in_width, c.in_rows, cudaMemcpyHostToDevice,
+                         h->h2d_stream));
+    } else if (c.in_runs.empty()) {
       if (c.in_hi > c.in_lo) {
         CUDA_TRY(cudaMemcpyAsync(h->d_in + (c.in_lo - in_lo), in + c.in_lo, c.in_hi - c.in_lo, cudaMemcpyHostToDevice,
                                  h->h2d_stream));
@@ -1225,8 +1318,19 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
       }
     }
     if (preserve) {
-      CUDA_TRY(cudaMemcpyAsync(h->d_out + (c.out_lo - out_lo), out + c.out_lo, c.out_hi - c.out_lo,
-                               cudaMemcpyHostToDevice, h->h2d_stream));
+      if (c.out_rows != 0) {
+        const uint64_t first = descs[h->order[c.b]].out_offset;
+        CUDA_TRY(copy_rows(h->d_out + (first - out_lo), out + first, c.out_stride, c.out_width, c.out_rows,
+                           cudaMemcpyHostToDevice, h->h2d_stream));
+      } else if (!c.out_runs.empty()) {
+        for (const auto& run : c.out_runs) {
+          CUDA_TRY(cudaMemcpyAsync(h->d_out + (run.first - out_lo), out + run.first, run.second - run.first,
+                                   cudaMemcpyHostToDevice, h->h2d_stream));
+        }
+      } else {
+        CUDA_TRY(cudaMemcpyAsync(h->d_out + (c.out_lo - out_lo), out + c.out_lo, c.out_hi - c.out_lo,
+                                 cudaMemcpyHostToDevice, h->h2d_stream));
+      }
     }
     CUDA_TRY(cudaEventRecord(h->ev_in[ci], h->h2d_stream));
     // kernels of consecutive chunks alternate between two streams (and two work counters) so that the blocks of chunk
@@ -1249,8 +1353,19 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     CUDA_TRY(cudaEventRecord(h->ev_done[ci], ks));
     CUDA_TRY(cudaStreamWaitEvent(h->d2h_stream, h->ev_done[ci], 0));
     if (!keep_messages) {
-      CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo,
-                               cudaMemcpyDeviceToHost, h->d2h_stream));
+      if (c.out_rows != 0) {
+        const uint64_t first = descs[h->order[c.b]].out_offset;
+        CUDA_TRY(copy_rows(out + first, h->d_out + (first - out_lo), c.out_stride, c.out_width, c.out_rows,
+                           cudaMemcpyDeviceToHost, h->d2h_stream));
+      } else if (!c.out_runs.empty()) {
+        for (const auto& run : c.out_runs) {
+          CUDA_TRY(cudaMemcpyAsync(out + run.first, h->d_out + (run.first - out_lo), run.second - run.first,
+                                   cudaMemcpyDeviceToHost, h->d2h_stream));
+        }
+      } else {
+        CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo,
+                                 cudaMemcpyDeviceToHost, h->d2h_stream));
+      }
     }
     if (!tb_ready.empty() && ci + 1 != chunks.size()) {
       uint32_t t1 = tb_next;

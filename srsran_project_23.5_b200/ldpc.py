@@ -111,6 +111,21 @@ def library():
         L.ldpc_cuda_descramble.argtypes = [vp, u32, u32, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
         L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
+        L.ldpc_cuda_pool_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(i32), u32, u32, u32]
+        L.ldpc_cuda_pool_destroy.argtypes = [vp]
+        L.ldpc_cuda_pool_destroy.restype = None
+        L.ldpc_cuda_pool_nof_devices.argtypes = [vp]
+        L.ldpc_cuda_pool_nof_devices.restype = u32
+        L.ldpc_cuda_pool_handle.argtypes = [vp, u32]
+        L.ldpc_cuda_pool_handle.restype = vp
+        L.ldpc_cuda_pool_set_algorithm.argtypes = [vp, ctypes.POINTER(_Algorithm)]
+        L.ldpc_cuda_pool_softbuffer_reserve.argtypes = [vp, u64]
+        L.ldpc_cuda_pool_launch_count.argtypes = [vp]
+        L.ldpc_cuda_pool_launch_count.restype = u64
+        L.ldpc_cuda_pool_codeblocks_per_device.argtypes = [vp, vp, u32]
+        L.ldpc_cuda_pool_device_of.argtypes = [vp, u64]
+        L.ldpc_cuda_pool_decode_batch.argtypes = [vp, u32, vp, vp, vp, vp]
+        L.ldpc_cuda_pool_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -376,3 +391,88 @@ class LdpcCuda:
     @property
     def softbuffer_ptr(self):
         return self._L.ldpc_cuda_softbuffer_ptr(self._h)
+
+
+class LdpcCudaPool:
+    """Several GPUs of one box from one process (ldpc_cuda_pool_*): one handle + one host thread per device, codeblocks of
+    a decode-only batch round-robin (i -> device i mod G), transport blocks whole with HARQ affinity. Host buffers."""
+
+    def __init__(self, devices, max_codeblocks_per_device=1024, flags=0, max_iterations=6, scaling_factor=0.8,
+                 scale_mode=SCALE_GENERIC):
+        self._L = library()
+        devs = (ctypes.c_int * len(devices))(*devices)
+        p = ctypes.c_void_p()
+        rc = self._L.ldpc_cuda_pool_create(ctypes.byref(p), devs, len(devices), max_codeblocks_per_device, flags)
+        if rc != 0:
+            raise LdpcCudaError(rc, "ldpc_cuda_pool_create")
+        self._p = p
+        self.devices = list(devices)
+        alg = _Algorithm(max_iterations, scaling_factor, scale_mode, 0)
+        self._check(self._L.ldpc_cuda_pool_set_algorithm(self._p, ctypes.byref(alg)), "ldpc_cuda_pool_set_algorithm")
+
+    def close(self):
+        if getattr(self, "_p", None):
+            self._L.ldpc_cuda_pool_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, where):
+        if rc != 0:
+            raise LdpcCudaError(rc, where)
+
+    @property
+    def nof_devices(self):
+        return self._L.ldpc_cuda_pool_nof_devices(self._p)
+
+    @property
+    def launch_count(self):
+        return self._L.ldpc_cuda_pool_launch_count(self._p)
+
+    def codeblocks_per_device(self):
+        out = np.zeros(self.nof_devices, np.uint64)
+        self._check(self._L.ldpc_cuda_pool_codeblocks_per_device(self._p, _ptr(out), out.size),
+                    "ldpc_cuda_pool_codeblocks_per_device")
+        return out
+
+    def device_of(self, harq_key):
+        return self._L.ldpc_cuda_pool_device_of(self._p, harq_key)
+
+    def softbuffer_reserve(self, nbytes_per_device):
+        self._check(self._L.ldpc_cuda_pool_softbuffer_reserve(self._p, nbytes_per_device),
+                    "ldpc_cuda_pool_softbuffer_reserve")
+
+    def softbuffer_read(self, index, offset, nbytes):
+        """Soft bits in the arena of device number `index`."""
+        dst = np.zeros(nbytes, np.int8)
+        h = self._L.ldpc_cuda_pool_handle(self._p, index)
+        self._check(self._L.ldpc_cuda_softbuffer_read(h, offset, _ptr(dst), nbytes), "ldpc_cuda_softbuffer_read")
+        return dst
+
+    def decode_batch(self, descs, llrs, out, results=None):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        if results is None:
+            results = np.zeros(descs.size, CB_RESULT)
+        self._check(self._L.ldpc_cuda_pool_decode_batch(self._p, descs.size, _ptr(descs), _ptr(llrs), _ptr(out),
+                                                        _ptr(results)), "ldpc_cuda_pool_decode_batch")
+        return out, results
+
+    def dematch_decode_tb_batch(self, descs, rm_llrs, out, tbs, harq_keys, tb_out, results=None, tb_results=None):
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        tbs = np.ascontiguousarray(tbs, TB_DESC)
+        rm_llrs = np.ascontiguousarray(rm_llrs, np.int8)
+        harq_keys = np.ascontiguousarray(harq_keys, np.uint64)
+        assert harq_keys.size == tbs.size
+        if results is None:
+            results = np.zeros(descs.size, CB_RESULT)
+        if tb_results is None:
+            tb_results = np.zeros(tbs.size, TB_RESULT)
+        self._check(self._L.ldpc_cuda_pool_dematch_decode_tb_batch(
+            self._p, descs.size, _ptr(descs), _ptr(rm_llrs), None if out is None else _ptr(out), _ptr(results), tbs.size,
+            _ptr(tbs), _ptr(harq_keys), _ptr(tb_out), _ptr(tb_results)), "ldpc_cuda_pool_dematch_decode_tb_batch")
+        return out, results, tb_out, tb_results
