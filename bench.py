@@ -29,9 +29,15 @@ OUT_BYTES = K_BITS // 8
 EDGES_BG1 = 316
 ALG_BYTES_PER_CB = N_LLR + OUT_BYTES  # 25344 B in + 1056 B out = 26400 B / codeblock
 INT_OPS_PER_EMU = 20                  # SURVEY.md 8(d) canonical cost of one edge-message update
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the decode kernel over 65536 codeblocks, from the
-# `ncu --set full` capture summarised in profiles/r01_ncu_tmem_head_summary.txt (final build: 1.6708 GB + 0.0704 GB)
-NCU_TRAFFIC_BYTES_PER_CB = 1.7412e9 / 65536
+# From the `ncu --set full` capture of ONE launch of the decode kernel over 65536 codeblocks (fixed 6 iterations) summarised
+# in profiles/r02_ncu_tmem_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, warp instructions executed, and the
+# share of issue slots that were active.
+NCU_PROFILE = "profiles/r02_ncu_tmem_summary.txt"
+NCU_TRAFFIC_BYTES_PER_CB = 1.7409e9 / 65536
+NCU_WARP_INSTR_PER_CB = 20.057e9 / 65536
+NCU_ISSUE_SLOTS_ACTIVE = 0.624
+REF_BUILD = ("oracle/Makefile: g++ -O3 -DNDEBUG -mavx2 -mfma -mpclmul (+ -mavx512f -mavx512bw in the reference's own avx512 "
+             "units), built in the build container and shipped as a binary - portable flags, not -march=native")
 METRIC = "LDPC decoded info Gb/s (BG1 Z=384, 6 iters)"
 
 
@@ -47,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-pusch-extra", action="store_true")
+    ap.add_argument("--no-checks", action="store_true", help="skip the oracle spot check and the AVX2 agreement sample")
+    ap.add_argument("--no-strong", action="store_true", help="skip the single-process strong-scaling extra (N > 1)")
     return ap.parse_args()
 
 
@@ -329,13 +337,37 @@ def pusch_slot_extra(torch, pkg, dec, dev, stream, steps):
         del rm_a_h, rm_b_h, tb_out_h
     except Exception as exc:  # the extra must never take the headline line down with it
         e2e = {"error": repr(exc)}
+    # "fused configs time rate_dematch + decode per codeblock": the reference's dematcher + decoder (CRC24B early
+    # stop) on the codeblocks of 8 good-SNR transport blocks of slot A, all host threads, one object pair per thread
+    cpu = None
+    try:
+        import oracles as O
+        ref = O.ref()
+        if ref is not None:
+            kind = "avx512" if ref.supports("avx512") else ("avx2" if ref.supports("avx2") else "generic")
+            threads = len(os.sched_getaffinity(0))
+            take = [i for i in range(n_a) if (i % cells) >= n_bad][:8]
+            rm_h = rm_a[take].cpu().numpy()
+            secs = 0.0
+            for e_len in sorted(set(int(e) for e in E)):
+                rows = np.stack([rm_h[k, tb_off[r]:tb_off[r] + e_len] for k in range(len(take)) for r in range(C)
+                                 if int(E[r]) == e_len])
+                best = min(ref.dematch_decode_batch_mt(kind, threads, 1, Zs, rows, rv=0, Qm=Qm, fillers=F, crc=O.CRC24B,
+                                                       max_iters=6)[0] for _ in range(3))
+                secs += best
+            cpu = {"value": len(take) * C * (Kb - F) / secs / 1e9, "unit": "Gb/s", "cores": threads, "kind": "reference",
+                   "sample": "%d codeblocks (%d new-data transport blocks at the good SNR of slot A): reference %s "
+                             "rate_dematch + decode with CRC24B early stop per codeblock, %d threads, best of 3"
+                             % (len(take) * C, len(take), kind, threads), "build": REF_BUILD}
+    except Exception as exc:
+        cpu = {"error": repr(exc)}
     return {"what": "configs 3+5: fused rate-dematch + HARQ combine (HBM arena) + decode + CRC24B early stop + TB assembly and "
                     "TB CRC24A on the device, 16 cells x 152-codeblock full-slot TBs (BG1 Z=384 F=16, E 8960/8992, "
                     "R=0.94), 12.5% retransmissions (rv2)",
             "value": bits / (ms * 1e-3) / 1e9, "unit": "Gb/s", "ms_per_slot_16_cells": ms / slots,
             "codeblocks_per_step": n_cb, "rm_llr_bytes_per_step": int(2 * n_a * tb_bytes),
             "soft_buffer_arena_bytes": int(n_buf * C * Nsoft), "launches_per_step": launches_per_step,
-            "e2e": e2e,
+            "e2e": e2e, "cpu_baseline": cpu,
             "cells_in_real_time_at_0.5ms_slots": cells * 0.5 / (ms / slots),
             "crc_pass_rate": {"new_good_snr": float(ra[~bad_a]["crc_ok"].mean()), "new_bad_snr": float(ra[bad_a]["crc_ok"].mean()),
                               "retransmission": float(rb[bad_a]["crc_ok"].mean())},
@@ -356,8 +388,11 @@ def demod_extra(torch, pkg, dec, dev, stream, steps, hbm_peak):
     g = torch.Generator(device=dev)
     g.manual_seed(5)
     lv = (torch.randint(0, 16, (n_jobs * n_sym, 2), generator=g, device=dev) * 2 - 15).float() / (170.0 ** 0.5)
-    sym = (lv + torch.randn(lv.shape, generator=g, device=dev) * 0.02).contiguous()
-    nv = torch.full((n_jobs * n_sym,), 8e-4, dtype=torch.float32, device=dev)
+    # 17 dB: few LLRs clip at +-120, so nearly every symbol takes the general (guarded) path of the kernel; at the 31 dB of
+    # round 1 95 % of the LLRs were saturated
+    sigma_c = 0.1
+    sym = (lv + torch.randn(lv.shape, generator=g, device=dev) * sigma_c).contiguous()
+    nv = torch.full((n_jobs * n_sym,), 2 * sigma_c * sigma_c, dtype=torch.float32, device=dev)
     out = torch.empty(n_jobs * n_sym * q, dtype=torch.int8, device=dev)
     jobs = np.zeros(n_jobs, pkg.DEMOD_DESC)
     jobs["mod_order"], jobs["descramble"], jobs["nof_symbols"] = q, 1, n_sym
@@ -383,6 +418,7 @@ def demod_extra(torch, pkg, dec, dev, stream, steps, hbm_peak):
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
                          "algorithmic_bytes_per_launch": alg_bytes,
                          "note": "inputs (262 MB) + outputs (174 MB) per launch exceed the 126 MB L2"},
+            "snr_db": float(-10 * np.log10(2 * sigma_c * sigma_c)),
             "saturated_llr_fraction": float((out[:1 << 22].abs() >= 120).float().mean())}
 
 
@@ -439,6 +475,77 @@ def run_reference(args):
             "e2e": {"value": value, "unit": "Gb/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def correctness_checks(pkg, dec, dev, torch, llr_d, max_iters):
+    """After the timed regions: (1) a 16-codeblock spot check of the bench's own output against the oracle port (bits, CRC
+    verdict, iteration count), (2) agreement with the reference's AVX2 decoder on 2048 codeblocks of the bench LLRs
+    (north_star: "agreement with the AVX2 variant is reported"): the AVX2 / AVX-512 variants scale check-to-variable
+    messages as (m * 52428) >> 16 instead of round(0.8 m), so they are a different decoder on blocks near the threshold."""
+    import oracles as O
+    n = 2048
+    descs = pkg.make_descs(n, BG, Z, crc_poly=pkg.CRC24B, early_stop=1)
+    out = torch.zeros((n, OUT_BYTES), dtype=torch.uint8, device=dev)
+    res = torch.zeros((n,), dtype=torch.int32, device=dev)
+    dec.decode_batch_device(descs, llr_d.data_ptr(), out.data_ptr(), res.data_ptr())
+    dec.synchronize()
+    bits = out.cpu().numpy()
+    r = res.cpu().numpy().view(pkg.CB_RESULT)
+    llrs = llr_d[:n].cpu().numpy()
+    spot_ok = True
+    for i in range(16):
+        want_bits, want_it = O.port().decode(BG, Z, llrs[i], crc=O.CRC24B, max_iters=max_iters)
+        got_it = int(r["iterations"][i]) if r["crc_ok"][i] else 0
+        spot_ok = spot_ok and got_it == want_it and bool((bits[i] == want_bits).all())
+    agreement = None
+    ref = O.ref()
+    if ref is not None and ref.supports("avx2"):
+        threads = len(os.sched_getaffinity(0))
+        _, ref_bits, ref_it = ref.decode_batch_mt("avx2", threads, BG, Z, llrs, crc=O.CRC24B, max_iters=max_iters)
+        ours_it = np.where(r["crc_ok"] != 0, r["iterations"], 0).astype(np.int64)
+        same_bits = (bits == ref_bits).all(axis=1)
+        agreement = {"codeblocks": n, "what": "this decoder (generic arithmetic, the parity target) against the reference "
+                     "avx2 decoder on the same LLRs, CRC24B early stop, max %d iterations" % max_iters,
+                     "all_bits_equal": float(same_bits.mean()), "iterations_equal": float((ours_it == ref_it).mean()),
+                     "crc_verdict_equal": float(((ours_it > 0) == (ref_it > 0)).mean()),
+                     "mean_iterations": {"ours": float(r["iterations"].mean()),
+                                         "avx2": float(np.where(ref_it > 0, ref_it, max_iters).mean())}}
+    return spot_ok, agreement
+
+
+def strong_scaling_extra(torch, pkg, llr_h, n_cb, world, max_iters, steps):
+    """ONE batch of n_cb codeblocks split over all GPUs of the box by ONE process (ldpc_cuda_pool_decode_batch: codeblock
+    i -> device i mod G, SURVEY 8d cfg 4), host buffers, against the same call on one device and against the copy-only
+    ceiling of the same byte movement (LDPC_CUDA_FLAG_COPY_ONLY: identical copies, no kernels)."""
+    out_h = torch.empty((n_cb, OUT_BYTES), dtype=torch.uint8, pin_memory=True)
+    res = np.zeros(n_cb, pkg.CB_RESULT)
+    descs = pkg.make_descs(n_cb, BG, Z, crc_poly=pkg.CRC_NONE)
+    bits = float(n_cb) * K_BITS
+    table = {}
+    for g in sorted({1, world}):
+        for label, flags in (("decode", 0), ("copy_only", pkg.FLAG_COPY_ONLY)):
+            pool = pkg.LdpcCudaPool(list(range(g)), max_codeblocks_per_device=(n_cb + g - 1) // g, flags=flags,
+                                    max_iterations=max_iters)
+            try:
+                for _ in range(2):
+                    pool.decode_batch(descs, llr_h.numpy(), out_h.numpy().reshape(-1), res)
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    pool.decode_batch(descs, llr_h.numpy(), out_h.numpy().reshape(-1), res)
+                secs = (time.perf_counter() - t0) / steps
+                per_dev = pool.codeblocks_per_device().tolist()
+            finally:
+                pool.close()
+            table.setdefault(str(g), {})[label] = {"value": bits / secs / 1e9, "unit": "Gb/s", "ms_per_batch": secs * 1e3}
+            if label == "decode":
+                table[str(g)]["codeblocks_per_device"] = [int(x // (steps + 2)) for x in per_dev]
+    one, many = table["1"], table[str(world)]
+    return {"what": "ONE %d-codeblock batch from pinned host memory, one process, ldpc_cuda_pool over %d GPUs (codeblock i -> "
+                    "GPU i mod %d), timed around the synchronous call" % (n_cb, world, world),
+            "scaling": "strong", "per_gpus": table,
+            "speedup": many["decode"]["value"] / one["decode"]["value"],
+            "efficiency": many["decode"]["value"] / one["decode"]["value"] / world,
+            "fraction_of_copy_ceiling": many["decode"]["value"] / many["copy_only"]["value"]}
 
 
 def run_ours(args):
@@ -534,7 +641,36 @@ def run_ours(args):
             secs = float(t.item())
         e2e = {"value": total_bits * args.steps / secs / 1e9, "unit": "Gb/s",
                "h2d_bytes_per_step": int(n_cb) * N_LLR + n_cb * 48, "d2h_bytes_per_step": int(n_cb) * (OUT_BYTES + 4),
-               "timer": "host wall clock around the synchronous C-ABI call (copies inside)"}
+               "timer": "host wall clock around the synchronous C-ABI call (copies inside)",
+               "host_memory": "pinned (caller-allocated)"}
+
+        def timed_host(engine, llr_np, out_np, steps):
+            for _ in range(1):
+                engine.decode_batch(descs_fixed, llr_np, out_np, res_hh)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                engine.decode_batch(descs_fixed, llr_np, out_np, res_hh)
+            barrier()
+            secs = time.perf_counter() - t0
+            if world > 1:
+                t = torch.tensor([secs], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                secs = float(t.item())
+            return total_bits * steps / secs / 1e9
+
+        # the same byte movement without the kernels, all ranks at once: what the host-fed figure can reach on this box
+        probe = pkg.LdpcCuda(device=local, max_codeblocks=n_cb, flags=pkg.FLAG_COPY_ONLY, max_iterations=args.max_iters)
+        e2e["copy_only_ceiling"] = timed_host(probe, llr_h.numpy(), out_h.numpy(), args.steps)
+        probe.close()
+        e2e["fraction_of_copy_ceiling"] = e2e["value"] / e2e["copy_only_ceiling"]
+        e2e["h2d_gbytes_per_s_per_gpu"] = e2e["value"] / world * 1e9 / K_BITS * N_LLR / 1e9
+        if world == 1:
+            # what the reference's spans are: ordinary (pageable) memory - the copies go through the driver's staging
+            llr_pg, out_pg = np.array(llr_h.numpy()), np.zeros((n_cb, OUT_BYTES), np.uint8)
+            e2e["pageable"] = {"value": timed_host(dec, llr_pg, out_pg, 2), "unit": "Gb/s",
+                               "host_memory": "pageable numpy arrays (no cudaHostRegister)"}
+            del llr_pg, out_pg
 
     hbm_peak, sm_max_mhz, peak_src = peaks()
     alg_bytes = float(n_cb) * ALG_BYTES_PER_CB
@@ -542,7 +678,7 @@ def run_ours(args):
     emu = float(n_cb) * args.max_iters * EDGES_BG1 * Z
     emu_per_s = emu / (kernel_ms * 1e-3)
     sm_mhz = clocks.get("sm_mhz") or sm_max_mhz
-    alu_peak = 148 * 64 * sm_mhz * 1e6  # measured: 64 ALU-pipe thread-instr / clk / SM (profiles/r01_pipes_microbench.md)
+    lane_peak = 148 * 128 * sm_mhz * 1e6
     line = {"metric": METRIC, "value": value, "unit": "Gb/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
@@ -552,16 +688,38 @@ def run_ours(args):
                        "l2": "inputs (%.2f GB) larger than L2" % (n_cb * N_LLR / 1e9)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES_PER_CB * n_cb,
-                         "traffic_unit": "bytes per launch (ncu dram read+write, profiles/r01_ncu_tmem_head_summary.txt)",
+                         "traffic_unit": "bytes per launch (ncu dram read+write, %s)" % NCU_PROFILE,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                          "kernel": "decode kernel of the (BG1, Z=384) group, %d launch(es) per step" % (launches // args.steps),
                          "note": "the path is integer-ALU-issue bound, not HBM bound: see roofline_alu"},
             "roofline_alu": {"emu_per_s": emu_per_s, "int_ops_per_s_canonical": emu_per_s * INT_OPS_PER_EMU,
-                             "alu_pipe_peak_instr_per_s": alu_peak,
-                             "canonical_ops_over_alu_peak": emu_per_s * INT_OPS_PER_EMU / alu_peak},
+                             "what": "SURVEY 8(d): edge-message updates x 20 canonical integer ops against 148 SM x 128 "
+                                     "INT32 lanes x SM clock, for 1 / 2 / 4 values per 32-bit lane; the kernel computes 2 "
+                                     "per lane (fp16x2), which is what sm_100 has natively",
+                             "lane_peak_ops_per_s": lane_peak,
+                             "frac_scalar_lane": emu_per_s * INT_OPS_PER_EMU / lane_peak,
+                             "frac_2_wide": emu_per_s * INT_OPS_PER_EMU / (2 * lane_peak),
+                             "frac_4_wide": emu_per_s * INT_OPS_PER_EMU / (4 * lane_peak),
+                             "issue_slots_active": NCU_ISSUE_SLOTS_ACTIVE,
+                             "thread_instr_per_emu": NCU_WARP_INSTR_PER_CB * 32 / (args.max_iters * EDGES_BG1 * Z),
+                             "ncu": NCU_PROFILE},
             "early_stop": es, "clocks": clocks, "gpu_launches": int(launches)}
     if e2e is not None:
         line["e2e"] = e2e
+    if rank == 0 and not args.no_checks:
+        try:
+            line["parity_spot"], line["avx2_agreement"] = correctness_checks(pkg, dec, dev, torch, llr_d, args.max_iters)
+        except Exception as exc:  # a check must never take the headline line down with it
+            line["parity_spot"] = "error: %r" % (exc,)
+    if world > 1 and not args.no_strong and not args.no_e2e:
+        barrier()
+        if rank == 0:  # the other ranks wait at the barrier below with their GPUs idle
+            try:
+                line["strong_scaling"] = strong_scaling_extra(torch, pkg, llr_h, n_cb, world, args.max_iters,
+                                                              max(2, args.steps // 2))
+            except Exception as exc:
+                line["strong_scaling"] = {"error": repr(exc)}
+        barrier()
     llrs_sample = llr_d[:2048].cpu().numpy() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
     if rank == 0 and world == 1 and not args.no_pusch_extra:
         del llr_d, out_d
@@ -573,7 +731,8 @@ def run_ours(args):
         llrs = llrs_sample
         gbps, kind, threads, desc = cpu_reference_run(llrs, args.max_iters, 3)
         line["cpu_baseline"] = {"value": gbps, "unit": "Gb/s", "cores": threads, "kind": kind,
-                                "sample": "first %d codeblocks of the same workload, best of 3, %s" % (sample, desc)}
+                                "sample": "first %d codeblocks of the same workload, best of 3, %s" % (sample, desc),
+                                "build": REF_BUILD}
     if rank == 0:
         print(json.dumps(line))
     dec.close()

@@ -120,6 +120,9 @@ int         ldpc_cuda_device_count(void);
 
 /* flags for ldpc_cuda_create */
 #define LDPC_CUDA_FLAG_FORCE_SCALAR 1u /* always use the general one-lane-per-thread kernel (cross-check / debugging) */
+#define LDPC_CUDA_FLAG_COPY_ONLY 2u    /* measurement aid: the host entries perform every copy of a call (same chunks, same
+                                          streams) but launch no decode kernel, so outputs and results are undefined; gives
+                                          the copy-only ceiling of the end-to-end figures (bench.py) */
 
 /* device: CUDA ordinal. max_codeblocks: largest batch a single call may carry (device scratch and pinned staging are
  * sized for it: max_codeblocks * (25344 + 1056 + descriptors) bytes). */

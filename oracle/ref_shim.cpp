@@ -412,6 +412,73 @@ void ref_dematcher_run(void*         handle,
                   meta);
 }
 
+// What pusch_decoder_impl::decode does per codeblock of a first transmission (pusch_decoder_impl.cpp:156-201): rate dematch
+// into the codeblock's soft buffer, then decode with CRC early stop - for a batch of codeblocks of one geometry, nthreads
+// workers with one dematcher + one decoder object each on disjoint slices (the reference runs one pusch_decoder per uplink
+// thread). Codeblock i: rm_length rate-matched LLRs at rm + i * rm_stride; every worker keeps ONE soft buffer, as new data
+// overwrites it. Returns the wall seconds of the region; iters[i] = iterations or 0.
+double ref_dematch_decode_batch_mt(const char*   dematcher_type,
+                                   const char*   decoder_type,
+                                   unsigned      nthreads,
+                                   unsigned      ncb,
+                                   int           bg,
+                                   int           Z,
+                                   int           rv,
+                                   int           Qm,
+                                   unsigned      nof_filler_bits,
+                                   int           crc_poly_code,
+                                   unsigned      max_iterations,
+                                   const int8_t* rm,
+                                   unsigned      rm_stride,
+                                   unsigned      rm_length,
+                                   uint8_t*      out_packed,
+                                   unsigned      out_stride,
+                                   int*          iters)
+{
+  nthreads = nthreads == 0 ? 1 : nthreads;
+  const unsigned     N = ((bg == 2) ? 50 : 66) * Z;
+  std::vector<void*> dec(nthreads), dem(nthreads);
+  for (unsigned t = 0; t != nthreads; ++t) {
+    dec[t] = ref_decoder_create(decoder_type);
+    dem[t] = ref_dematcher_create(dematcher_type);
+    if (dec[t] == nullptr || dem[t] == nullptr) {
+      return -1.0;
+    }
+  }
+  std::atomic<unsigned>    ready{0};
+  std::atomic<bool>        go{false};
+  std::vector<std::thread> workers;
+  for (unsigned t = 0; t != nthreads; ++t) {
+    workers.emplace_back([&, t]() {
+      const unsigned      begin = static_cast<unsigned>((static_cast<uint64_t>(ncb) * t) / nthreads);
+      const unsigned      end   = static_cast<unsigned>((static_cast<uint64_t>(ncb) * (t + 1)) / nthreads);
+      std::vector<int8_t> soft(N, 0);
+      ready.fetch_add(1);
+      while (!go.load(std::memory_order_acquire)) {
+      }
+      for (unsigned i = begin; i != end; ++i) {
+        ref_dematcher_run(dem[t], soft.data(), N, rm + static_cast<size_t>(i) * rm_stride, rm_length, 1, bg, Z, rv, Qm, 0,
+                          nof_filler_bits);
+        iters[i] = ref_decoder_decode(dec[t], bg, Z, nof_filler_bits, crc_poly_code, max_iterations, 0.8f, soft.data(), N,
+                                      out_packed + static_cast<size_t>(i) * out_stride);
+      }
+    });
+  }
+  while (ready.load() != nthreads) {
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  go.store(true, std::memory_order_release);
+  for (auto& w : workers) {
+    w.join();
+  }
+  const auto t1 = std::chrono::steady_clock::now();
+  for (unsigned t = 0; t != nthreads; ++t) {
+    ref_decoder_destroy(dec[t]);
+    ref_dematcher_destroy(dem[t]);
+  }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // Transmit side, used only to make test signals: encoder (ldpc_encoder.h) and rate matcher (ldpc_rate_matcher.h).
 // Bits are unpacked, one per byte; filler bits in the message are 254 (ldpc.h:113).

@@ -7,10 +7,10 @@ device, every compute call raises.
 The directory name contains a dot, so it is loaded through ``__graft_entry__.load_package()`` (importlib) under the module
 name ``srsran_project_23_5_b200``.
 """
-from .ldpc import (CRC16, CRC24A, CRC24B, CRC_NONE, SCALE_AVX, SCALE_GENERIC, SCALE_NEON, FLAG_FORCE_SCALAR, CB_DESC,
+from .ldpc import (CRC16, CRC24A, CRC24B, CRC_NONE, SCALE_AVX, SCALE_GENERIC, SCALE_NEON, FLAG_FORCE_SCALAR, FLAG_COPY_ONLY, CB_DESC,
                    CB_RESULT, TB_DESC, TB_RESULT, DEMOD_DESC, PLACEHOLDER_DESC, LdpcCuda, LdpcCudaPool, LdpcCudaError, device_count, graph_shift, library, library_path, make_descs,
                    segment)
 
-__all__ = ["CRC16", "CRC24A", "CRC24B", "CRC_NONE", "SCALE_AVX", "SCALE_GENERIC", "SCALE_NEON", "FLAG_FORCE_SCALAR",
+__all__ = ["CRC16", "CRC24A", "CRC24B", "CRC_NONE", "SCALE_AVX", "SCALE_GENERIC", "SCALE_NEON", "FLAG_FORCE_SCALAR", "FLAG_COPY_ONLY",
            "CB_DESC", "CB_RESULT", "TB_DESC", "TB_RESULT", "DEMOD_DESC", "PLACEHOLDER_DESC", "LdpcCuda", "LdpcCudaPool", "LdpcCudaError", "device_count", "graph_shift", "library", "library_path",
            "make_descs", "segment"]

@@ -322,6 +322,9 @@ int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_wor
 int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work, uint32_t n, const int8_t* d_llr,
                         const int8_t* d_rm, uint8_t* d_out, CbResult* d_res, cudaStream_t stream, unsigned* pair_counter)
 {
+  if (h->flags & LDPC_CUDA_FLAG_COPY_ONLY) {
+    return LDPC_CUDA_OK;  // measurement aid: the host entries move their bytes, nothing is decoded
+  }
   GroupParams gp = make_group(h, bg, Z);
   if (!(h->flags & LDPC_CUDA_FLAG_FORCE_SCALAR) && h->packed_scale != TM_SCALE_NONE) {
     int rc = launch_tmem_decode(gp, h->packed_scale, d_work, n, d_llr, d_rm, d_out, d_res, pair_counter, h->sm_count,

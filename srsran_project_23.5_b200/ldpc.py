@@ -10,6 +10,7 @@ import numpy as np
 CRC_NONE, CRC16, CRC24A, CRC24B = 0, 1, 2, 3
 SCALE_GENERIC, SCALE_AVX, SCALE_NEON = 0, 1, 2
 FLAG_FORCE_SCALAR = 1
+FLAG_COPY_ONLY = 2
 
 NOALLOC_MAX_TBS, NOALLOC_MAX_CBS, NOALLOC_MAX_CHUNKS = 64, 4096, 8192  # ldpc_cuda_tb_assemble_device_noalloc
 

@@ -165,6 +165,9 @@ class RefOracle:
         L.ref_decoder_decode_batch_mt.restype = c_double
         L.ref_decoder_decode_batch_mt.argtypes = [c_char_p, c_uint, c_uint, c_int, c_int, c_uint, c_int, c_uint,
                                                   c_float, c_void_p, c_uint, c_uint, c_void_p, c_uint, c_void_p]
+        L.ref_dematch_decode_batch_mt.restype = c_double
+        L.ref_dematch_decode_batch_mt.argtypes = [c_char_p, c_char_p, c_uint, c_uint, c_int, c_int, c_int, c_int, c_uint,
+                                                  c_int, c_uint, c_void_p, c_uint, c_uint, c_void_p, c_uint, c_void_p]
         L.ref_dematcher_create.restype = c_void_p
         L.ref_dematcher_create.argtypes = [c_char_p]
         L.ref_dematcher_destroy.argtypes = [c_void_p]
@@ -275,6 +278,20 @@ class RefOracle:
         secs = self.lib.ref_decoder_decode_batch_mt(kind.encode(), nthreads, ncb, bg, Z, fillers, crc, max_iters, sf,
                                                     _ptr(llrs2d), n, n, _ptr(out), kb, _ptr(iters))
         assert secs >= 0, "reference decoder type %s unavailable" % kind
+        return secs, out, iters
+
+    def dematch_decode_batch_mt(self, kind, nthreads, bg, Z, rm2d, rv=0, Qm=1, fillers=0, crc=CRC_NONE, max_iters=6):
+        """rate_dematch (new data) + decode with CRC early stop per codeblock, nthreads workers on disjoint slices (what
+        pusch_decoder_impl::decode does per codeblock, pusch_decoder_impl.cpp:156-201). rm2d: [ncb, E] int8."""
+        rm2d = np.ascontiguousarray(rm2d, np.int8)
+        ncb, E = rm2d.shape
+        kb = (BG_K[bg] * Z + 7) // 8
+        out = np.zeros((ncb, kb), np.uint8)
+        iters = np.zeros(ncb, np.int32)
+        dm = kind if kind in ("avx2", "avx512") else "generic"
+        secs = self.lib.ref_dematch_decode_batch_mt(dm.encode(), kind.encode(), nthreads, ncb, bg, Z, rv, Qm, fillers, crc,
+                                                    max_iters, _ptr(rm2d), E, E, _ptr(out), kb, _ptr(iters))
+        assert secs >= 0, "reference type %s unavailable" % kind
         return secs, out, iters
 
     def rate_dematch(self, soft, llrs, new_data, bg, Z, rv=0, Qm=1, Nref=0, fillers=0, kind="generic"):
