@@ -713,12 +713,18 @@ def run_ours(args):
             line["parity_spot"] = "error: %r" % (exc,)
     if world > 1 and not args.no_strong and not args.no_e2e:
         barrier()
-        if rank == 0:  # the other ranks wait at the barrier below with their GPUs idle
+        # The other ranks must leave their GPUs IDLE meanwhile: an NCCL barrier would park a spinning kernel on every
+        # waiting GPU, so they wait on the rendezvous store (host only) instead.
+        store = dist.distributed_c10d._get_default_store()
+        if rank == 0:
             try:
                 line["strong_scaling"] = strong_scaling_extra(torch, pkg, llr_h, n_cb, world, args.max_iters,
                                                               max(2, args.steps // 2))
             except Exception as exc:
                 line["strong_scaling"] = {"error": repr(exc)}
+            store.set("strong_scaling_done", "1")
+        else:
+            store.wait(["strong_scaling_done"])
         barrier()
     llrs_sample = llr_d[:2048].cpu().numpy() if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
     if rank == 0 and world == 1 and not args.no_pusch_extra:
