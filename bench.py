@@ -539,8 +539,38 @@ def strong_scaling_extra(torch, pkg, llr_h, n_cb, world, max_iters, steps):
             table.setdefault(str(g), {})[label] = {"value": bits / secs / 1e9, "unit": "Gb/s", "ms_per_batch": secs * 1e3}
             if label == "decode":
                 table[str(g)]["codeblocks_per_device"] = [int(x // (steps + 2)) for x in per_dev]
+    # the same split with the LLRs resident in every device's HBM (as when the demodulator writes them there): kernels only
+    resident = {}
+    for g in sorted({1, world}):
+        pool = pkg.LdpcCudaPool(list(range(g)), max_codeblocks_per_device=(n_cb + g - 1) // g, max_iterations=max_iters)
+        try:
+            ins, outs, ress = [], [], []
+            for k in range(g):
+                dk = torch.device("cuda", k)
+                ins.append(llr_h.to(dk, non_blocking=False))
+                outs.append(torch.zeros((n_cb, OUT_BYTES), dtype=torch.uint8, device=dk))
+                ress.append(torch.zeros(((n_cb + g - 1) // g,), dtype=torch.int32, device=dk))
+                torch.cuda.synchronize(dk)
+            ptrs = lambda ts: [t.data_ptr() for t in ts]
+            for _ in range(2):
+                pool.decode_batch_device(descs, ptrs(ins), ptrs(outs), ptrs(ress))
+            pool.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                pool.decode_batch_device(descs, ptrs(ins), ptrs(outs), ptrs(ress))
+            pool.synchronize()
+            secs = (time.perf_counter() - t0) / steps
+            resident[str(g)] = {"value": bits / secs / 1e9, "unit": "Gb/s", "ms_per_batch": secs * 1e3}
+            del ins, outs, ress
+        finally:
+            pool.close()
     one, many = table["1"], table[str(world)]
-    return {"what": "ONE %d-codeblock batch from pinned host memory, one process, ldpc_cuda_pool over %d GPUs (codeblock i -> "
+    res_eff = resident[str(world)]["value"] / resident["1"]["value"] / world
+    return {"device_resident": {"per_gpus": resident, "speedup": resident[str(world)]["value"] / resident["1"]["value"],
+                                "efficiency": res_eff,
+                                "what": "same batch and split, LLRs already in each GPU's HBM (ldpc_cuda_pool_decode_batch_device), "
+                                        "host wall clock around enqueue + synchronize"},
+            "what": "ONE %d-codeblock batch from pinned host memory, one process, ldpc_cuda_pool over %d GPUs (codeblock i -> "
                     "GPU i mod %d), timed around the synchronous call" % (n_cb, world, world),
             "scaling": "strong", "per_gpus": table,
             "speedup": many["decode"]["value"] / one["decode"]["value"],

@@ -410,6 +410,18 @@ int ldpc_cuda_pool_decode_batch(ldpc_cuda_pool*          pool,
                                 uint8_t*                 out_bits,
                                 ldpc_cuda_cb_result*     results);
 
+/* The same split with inputs and outputs in DEVICE memory (LLRs written there by the demodulator, ldpc_cuda_demodulate_*):
+ * asynchronous, kernels only. llrs_d[g] / out_bits_d[g] are buffers on device number g addressed with the callers' offsets
+ * (descs[i].in_offset / out_offset for the codeblocks i = g, g + G, ... it runs); results_d[g][k] receives the result of
+ * codeblock g + k * G. Wait with ldpc_cuda_pool_synchronize. */
+int ldpc_cuda_pool_decode_batch_device(ldpc_cuda_pool*             pool,
+                                       uint32_t                    nof_codeblocks,
+                                       const ldpc_cuda_cb_desc*    descs,
+                                       const int8_t* const*        llrs_d,
+                                       uint8_t* const*             out_bits_d,
+                                       ldpc_cuda_cb_result* const* results_d);
+int ldpc_cuda_pool_synchronize(ldpc_cuda_pool* pool);
+
 /* ldpc_cuda_dematch_decode_tb_batch over all devices: transport blocks stay whole (a block is assembled and CRC-checked
  * where its codeblocks ran). harq_keys[t] names the HARQ process of block t (any injective code of (cell, rnti, harq_id)):
  * a block whose codeblocks all have new_data = 1 goes to the next device in turn and that device becomes the home of the

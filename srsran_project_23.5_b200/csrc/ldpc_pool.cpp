@@ -287,6 +287,54 @@ int ldpc_cuda_pool_decode_batch(ldpc_cuda_pool* p, uint32_t n, const ldpc_cuda_c
   return LDPC_CUDA_OK;
 }
 
+// ---- decode-only batch, inputs already in device memory (e.g. written there by the demodulator): kernels only -------------
+int ldpc_cuda_pool_decode_batch_device(ldpc_cuda_pool* p, uint32_t n, const ldpc_cuda_cb_desc* descs,
+                                       const int8_t* const* llrs_d, uint8_t* const* out_bits_d,
+                                       ldpc_cuda_cb_result* const* results_d)
+{
+  if (p == nullptr || descs == nullptr || llrs_d == nullptr || out_bits_d == nullptr || results_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  const uint32_t G = static_cast<uint32_t>(p->handles.size());
+  for (uint32_t g = 0; g != G; ++g) {
+    shard& s = p->shards[g];
+    s.descs.clear(), s.origin.clear();
+    for (uint32_t i = g; i < n; i += G) {
+      s.descs.push_back(descs[i]);
+    }
+    if (!s.descs.empty() && (llrs_d[g] == nullptr || out_bits_d[g] == nullptr || results_d[g] == nullptr)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+  }
+  const int rc = run_on_devices(
+      p, [p](uint32_t g) { return !p->shards[g].descs.empty(); },
+      [p, llrs_d, out_bits_d, results_d](uint32_t g) {
+        shard& s = p->shards[g];
+        return ldpc_cuda_decode_batch_device(p->handles[g], static_cast<uint32_t>(s.descs.size()), s.descs.data(), llrs_d[g],
+                                             out_bits_d[g], results_d[g]);
+      });
+  for (uint32_t g = 0; g != G && rc == LDPC_CUDA_OK; ++g) {
+    p->codeblocks_done[g] += p->shards[g].descs.size();
+  }
+  return rc;
+}
+
+int ldpc_cuda_pool_synchronize(ldpc_cuda_pool* p)
+{
+  if (p == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  int rc = LDPC_CUDA_OK;
+  for (ldpc_cuda_handle* h : p->handles) {
+    const int r = ldpc_cuda_synchronize(h);
+    rc          = (rc == LDPC_CUDA_OK) ? r : rc;
+  }
+  return rc;
+}
+
 // ---- fused transport-block batch: whole blocks per device, HARQ affinity ------------------------------------------------
 int ldpc_cuda_pool_dematch_decode_tb_batch(ldpc_cuda_pool* p, uint32_t n, const ldpc_cuda_cb_desc* descs,
                                            const int8_t* rm_llrs, uint8_t* out_bits, ldpc_cuda_cb_result* results,

@@ -126,6 +126,8 @@ def library():
         L.ldpc_cuda_pool_codeblocks_per_device.argtypes = [vp, vp, u32]
         L.ldpc_cuda_pool_device_of.argtypes = [vp, u64]
         L.ldpc_cuda_pool_decode_batch.argtypes = [vp, u32, vp, vp, vp, vp]
+        L.ldpc_cuda_pool_decode_batch_device.argtypes = [vp, u32, vp, vp, vp, vp]
+        L.ldpc_cuda_pool_synchronize.argtypes = [vp]
         L.ldpc_cuda_pool_dematch_decode_tb_batch.argtypes = [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp, vp]
         _lib = L
     return _lib
@@ -462,6 +464,17 @@ class LdpcCudaPool:
         self._check(self._L.ldpc_cuda_pool_decode_batch(self._p, descs.size, _ptr(descs), _ptr(llrs), _ptr(out),
                                                         _ptr(results)), "ldpc_cuda_pool_decode_batch")
         return out, results
+
+    def decode_batch_device(self, descs, llr_ptrs, out_ptrs, result_ptrs):
+        """Inputs / outputs in device memory, one pointer per device (raw addresses); asynchronous: call synchronize()."""
+        descs = np.ascontiguousarray(descs, CB_DESC)
+        arr = lambda ptrs: (ctypes.c_void_p * len(ptrs))(*ptrs)
+        a, b, c = arr(llr_ptrs), arr(out_ptrs), arr(result_ptrs)
+        self._check(self._L.ldpc_cuda_pool_decode_batch_device(self._p, descs.size, _ptr(descs), a, b, c),
+                    "ldpc_cuda_pool_decode_batch_device")
+
+    def synchronize(self):
+        self._check(self._L.ldpc_cuda_pool_synchronize(self._p), "ldpc_cuda_pool_synchronize")
 
     def dematch_decode_tb_batch(self, descs, rm_llrs, out, tbs, harq_keys, tb_out, results=None, tb_results=None):
         descs = np.ascontiguousarray(descs, CB_DESC)

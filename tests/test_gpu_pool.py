@@ -74,6 +74,39 @@ def test_pool_decode_batch_equals_one_device(ndev):
         one.close()
 
 
+@pytest.mark.parametrize("ndev", [1, 2, 8])
+def test_pool_decode_batch_device_equals_one_device(ndev):
+    """Inputs resident in every device's memory, kernels only: same bits and results as one device."""
+    if ndev > NDEV:
+        pytest.skip("needs %d devices, the box has %d" % (ndev, NDEV))
+    import torch
+    rng = np.random.default_rng(40 + ndev)
+    n = 130
+    descs, llrs, kb = _decode_only_batch(rng, n)
+    one = pkg.LdpcCuda(device=0, max_codeblocks=n)
+    pool = pkg.LdpcCudaPool(list(range(ndev)), max_codeblocks_per_device=n)
+    try:
+        want_out, want_res = one.decode_batch(descs, llrs)
+        ins = [torch.from_numpy(llrs).to("cuda:%d" % g) for g in range(ndev)]
+        outs = [torch.zeros(n * kb, dtype=torch.uint8, device="cuda:%d" % g) for g in range(ndev)]
+        ress = [torch.zeros(n, dtype=torch.int32, device="cuda:%d" % g) for g in range(ndev)]
+        for g in range(ndev):
+            torch.cuda.synchronize(g)
+        pool.decode_batch_device(descs, [t.data_ptr() for t in ins], [t.data_ptr() for t in outs],
+                                 [t.data_ptr() for t in ress])
+        pool.synchronize()
+        want_out = want_out.reshape(n, kb)
+        for g in range(ndev):
+            mine = np.arange(g, n, ndev)
+            got = outs[g].cpu().numpy().reshape(n, kb)
+            r = ress[g].cpu().numpy().view(pkg.CB_RESULT)[:mine.size]
+            assert (got[mine] == want_out[mine]).all(), g
+            assert (r["iterations"] == want_res["iterations"][mine]).all() and (r["crc_ok"] == want_res["crc_ok"][mine]).all()
+    finally:
+        pool.close()
+        one.close()
+
+
 def _tb_slot(rng, geom, rv, new_data, esn0, cws):
     """One slot of transport blocks of one geometry; block t is transmission rv[t] (new_data[t]) of codewords cws[t] (None:
     draw new ones) at Es/N0 esn0[t]. Returns descriptors, rate-matched noisy LLRs, TB descriptors, codewords, sizes."""
