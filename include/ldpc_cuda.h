@@ -27,6 +27,8 @@
  *                                   pusch_demodulator_impl::descramble
  *                                   lib/phy/upper/channel_processors/pusch_demodulator_impl.cpp:100-152 - the producer of
  *                                   the LLRs, so that they are born in device memory
+ *   ldpc_cuda_ulsch_*          <->  ulsch_demultiplex::demultiplex / get_placeholders
+ *                                   lib/phy/upper/channel_processors/ulsch_demultiplex_impl.cpp:316-453
  *   ldpc_cuda_segment          <->  ldpc_segmenter_rx::segment geometry
  *                                   lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_impl.cpp:226-308 (no 52-CB cap)
  *
@@ -350,6 +352,65 @@ int ldpc_cuda_descramble_uci(ldpc_cuda_handle* handle,
                              const uint16_t*   re_indexes,
                              const int8_t*     in,
                              int8_t*           out);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * UL-SCH demultiplexing (TS 38.212 6.2.7) on the device: ulsch_demultiplex::demultiplex / get_placeholders
+ * (include/srsran/phy/upper/channel_processors/ulsch_demultiplex.h:37-103,
+ *  lib/phy/upper/channel_processors/ulsch_demultiplex_impl.cpp:316-453; called at pusch_processor_impl.cpp:259) - between
+ * the descrambler and the rate dematcher, so that a PUSCH with HARQ-ACK / CSI multiplexed keeps its LLRs in device memory.
+ */
+typedef struct {
+  uint8_t  mod_order;                   /* bits per symbol of config.modulation: 1, 2, 4, 6, 8 */
+  uint8_t  nof_layers;                  /* config.nof_layers */
+  uint8_t  start_symbol_index;          /* config.start_symbol_index */
+  uint8_t  nof_symbols;                 /* config.nof_symbols */
+  uint8_t  dmrs_type;                   /* config.dmrs: 1 or 2 */
+  uint8_t  nof_cdm_groups_without_data; /* config.nof_cdm_groups_without_data */
+  uint16_t dmrs_symbol_mask;            /* config.dmrs_symbol_mask, bit l = OFDM symbol l carries DM-RS */
+  uint16_t nof_prb;                     /* config.nof_prb */
+  uint16_t reserved;
+  uint32_t nof_harq_ack_rvd;            /* config.nof_harq_ack_rvd (G_rvd^ACK) */
+  uint32_t nof_enc_harq_ack_bits;       /* harq_ack.size()  = message_information::nof_enc_harq_ack_bits */
+  uint32_t nof_enc_csi_part1_bits;      /* csi_part1.size() */
+  uint32_t nof_enc_csi_part2_bits;      /* csi_part2.size() */
+  uint64_t in_offset;                   /* byte offset of the codeword's soft bits in the input buffer */
+  uint64_t sch_offset;                  /* byte offset of its SCH data in the SCH output buffer */
+  uint64_t harq_ack_offset;             /* byte offsets of the three UCI fields in the UCI output buffer */
+  uint64_t csi_part1_offset;
+  uint64_t csi_part2_offset;
+} ldpc_cuda_ulsch_desc; /* 72 bytes */
+
+/* Sizes that follow from a descriptor: soft bits read (= input.size()), SCH data soft bits written (= sch_data.size()).
+ * Returns LDPC_CUDA_ERR_ARG for a configuration the reference asserts on (no DM-RS symbol, fields that do not fit). */
+int ldpc_cuda_ulsch_sizes(const ldpc_cuda_ulsch_desc* desc, uint32_t* nof_input_bits, uint32_t* nof_sch_bits);
+
+/* DEVICE buffers, asynchronous on the handle's stream; descs are host memory, consumed before the call returns. sch_d may
+ * be handed to ldpc_cuda_dematch_decode_batch_device as rm_llrs_d. */
+int ldpc_cuda_ulsch_demultiplex_batch_device(ldpc_cuda_handle*           handle,
+                                             uint32_t                    nof_codewords,
+                                             const ldpc_cuda_ulsch_desc* descs,
+                                             const int8_t*               in_llrs_d,
+                                             int8_t*                     sch_d,
+                                             int8_t*                     uci_d);
+
+/* ulsch_demultiplex::demultiplex, HOST buffers, synchronous (the offsets in desc are ignored). */
+int ldpc_cuda_ulsch_demultiplex(ldpc_cuda_handle*           handle,
+                                const ldpc_cuda_ulsch_desc* desc,
+                                const int8_t*               input,
+                                int8_t*                     sch_data,
+                                int8_t*                     harq_ack,
+                                int8_t*                     csi_part1,
+                                int8_t*                     csi_part2);
+
+/* ulsch_demultiplex::get_placeholders (host only, no GPU needed): resource-element indexes (in units of elements of the
+ * codeword, as ulsch_placeholder_list holds them) of the fields that carry exactly ONE information bit. nof_*_bits = O_ACK,
+ * O_CSI-1, O_CSI-2. Returns the number of indexes (written up to max_indexes) or a negative status. */
+int ldpc_cuda_ulsch_placeholders(const ldpc_cuda_ulsch_desc* desc,
+                                 uint32_t                    nof_harq_ack_bits,
+                                 uint32_t                    nof_csi_part1_bits,
+                                 uint32_t                    nof_csi_part2_bits,
+                                 uint16_t*                   re_indexes,
+                                 uint32_t                    max_indexes);
 
 /* ---------------------------------------------------------------------------------------------------------------------
  * HBM-resident soft-buffer arena (storage behind rx_softbuffer; zero-initialised once, like the reference pool,

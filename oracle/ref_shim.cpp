@@ -32,6 +32,7 @@
 #include "../srsran_project_23.5_b200/host/pusch_decoder_cuda.h"
 #include "../srsran_project_23.5_b200/host/rx_softbuffer_pool_cuda.h"
 #include "../srsran_project_23.5_b200/host/demodulation_mapper_cuda.h"
+#include "../srsran_project_23.5_b200/host/ulsch_demultiplex_cuda.h"
 #endif
 
 #include "phy/upper/channel_modulation/demodulation_mapper_impl.h"
@@ -43,6 +44,7 @@
 // for this one header, the reference's code itself is untouched.
 #define private public
 #include "phy/upper/channel_processors/pusch_demodulator_impl.h"
+#include "phy/upper/channel_processors/ulsch_demultiplex_impl.h"
 #undef private
 #include <algorithm>
 #include <atomic>
@@ -890,6 +892,100 @@ double ref_pool_time_reserve(void* handle, unsigned occupied, unsigned nof_codeb
   return std::chrono::duration<double, std::nano>(t1 - t0).count() / repetitions;
 }
 
+
+// ---- UL-SCH demultiplexer (ulsch_demultiplex.h:37-103, ulsch_demultiplex_impl.cpp:316-453) ------------------------------
+// cfg[9] = mod_order, nof_layers, nof_prb, start_symbol, nof_symbols, dmrs_type (1/2), nof_cdm_groups_without_data,
+// dmrs_symbol_mask, nof_harq_ack_rvd.
+static ulsch_demultiplex::configuration ulsch_config_of(const unsigned* cfg)
+{
+  ulsch_demultiplex::configuration c;
+  switch (cfg[0]) {
+    case 1: c.modulation = modulation_scheme::BPSK; break;
+    case 2: c.modulation = modulation_scheme::QPSK; break;
+    case 4: c.modulation = modulation_scheme::QAM16; break;
+    case 6: c.modulation = modulation_scheme::QAM64; break;
+    default: c.modulation = modulation_scheme::QAM256; break;
+  }
+  c.nof_layers                  = cfg[1];
+  c.nof_prb                     = cfg[2];
+  c.start_symbol_index          = cfg[3];
+  c.nof_symbols                 = cfg[4];
+  c.dmrs                        = cfg[5] == 1 ? dmrs_type::TYPE1 : dmrs_type::TYPE2;
+  c.nof_cdm_groups_without_data = cfg[6];
+  c.dmrs_symbol_mask            = symbol_slot_mask(14);
+  for (unsigned l = 0; l != 14; ++l) {
+    if ((cfg[7] >> l) & 1u) {
+      c.dmrs_symbol_mask.set(l);
+    }
+  }
+  c.nof_harq_ack_rvd = cfg[8];
+  return c;
+}
+
+static void ulsch_run(ulsch_demultiplex& demux, const unsigned* cfg, const int8_t* in, unsigned in_len, int8_t* sch,
+                      unsigned sch_len, int8_t* ack, unsigned ack_len, int8_t* csi1, unsigned csi1_len, int8_t* csi2,
+                      unsigned csi2_len)
+{
+  auto sp = [](int8_t* p, unsigned n) { return span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(p), n); };
+  demux.demultiplex(sp(sch, sch_len), sp(ack, ack_len), sp(csi1, csi1_len), sp(csi2, csi2_len),
+                    span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(in), in_len),
+                    ulsch_config_of(cfg));
+}
+
+// info[6] = O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2. Returns the number of placeholder elements.
+static int ulsch_list(ulsch_demultiplex& demux, const unsigned* cfg, const unsigned* info, uint16_t* list, unsigned list_max)
+{
+  ulsch_demultiplex::message_information mi;
+  mi.nof_harq_ack_bits = info[0], mi.nof_enc_harq_ack_bits = info[1];
+  mi.nof_csi_part1_bits = info[2], mi.nof_enc_csi_part1_bits = info[3];
+  mi.nof_csi_part2_bits = info[4], mi.nof_enc_csi_part2_bits = info[5];
+  ulsch_placeholder_list pl = demux.get_placeholders(mi, ulsch_config_of(cfg));
+  unsigned               n  = 0;
+  pl.for_each(modulation_scheme::QPSK, 1, [&](unsigned i_bit, unsigned) {
+    // QPSK, one layer: the callback receives bit index 2 * re + 1 (ulsch_placeholder_list.h:73-95)
+    if (n < list_max) {
+      list[n] = static_cast<uint16_t>((i_bit - 1) / 2);
+    }
+    ++n;
+  });
+  return static_cast<int>(n);
+}
+
+void ref_ulsch_demultiplex(const unsigned* cfg, const int8_t* in, unsigned in_len, int8_t* sch, unsigned sch_len, int8_t* ack,
+                           unsigned ack_len, int8_t* csi1, unsigned csi1_len, int8_t* csi2, unsigned csi2_len)
+{
+  ulsch_demultiplex_impl demux;
+  ulsch_run(demux, cfg, in, in_len, sch, sch_len, ack, ack_len, csi1, csi1_len, csi2, csi2_len);
+}
+
+int ref_ulsch_placeholders(const unsigned* cfg, const unsigned* info, uint16_t* list, unsigned list_max)
+{
+  ulsch_demultiplex_impl demux;
+  return ulsch_list(demux, cfg, info, list, list_max);
+}
+
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+// The product's "cuda" demultiplexer behind the same reference interface (host/ulsch_demultiplex_cuda.h).
+int dropin_ulsch_demultiplex(const unsigned* cfg, const int8_t* in, unsigned in_len, int8_t* sch, unsigned sch_len, int8_t* ack,
+                             unsigned ack_len, int8_t* csi1, unsigned csi1_len, int8_t* csi2, unsigned csi2_len)
+{
+  std::unique_ptr<ulsch_demultiplex> demux = create_ulsch_demultiplex_cuda(0);
+  if (!demux) {
+    return -1;
+  }
+  ulsch_run(*demux, cfg, in, in_len, sch, sch_len, ack, ack_len, csi1, csi1_len, csi2, csi2_len);
+  return 0;
+}
+
+int dropin_ulsch_placeholders(const unsigned* cfg, const unsigned* info, uint16_t* list, unsigned list_max)
+{
+  std::unique_ptr<ulsch_demultiplex> demux = create_ulsch_demultiplex_cuda(0);
+  if (!demux) {
+    return -1;
+  }
+  return ulsch_list(*demux, cfg, info, list, list_max);
+}
+#endif
 
 // ---- upstream producer of the LLRs: soft demodulator + descrambler ---------------------------------
 // demodulation_mapper_impl::demodulate_soft (lib/phy/upper/channel_modulation/demodulation_mapper_impl.cpp:74-106).

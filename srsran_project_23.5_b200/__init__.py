@@ -8,9 +8,9 @@ The directory name contains a dot, so it is loaded through ``__graft_entry__.loa
 name ``srsran_project_23_5_b200``.
 """
 from .ldpc import (CRC16, CRC24A, CRC24B, CRC_NONE, SCALE_AVX, SCALE_GENERIC, SCALE_NEON, FLAG_FORCE_SCALAR, FLAG_COPY_ONLY, CB_DESC,
-                   CB_RESULT, TB_DESC, TB_RESULT, DEMOD_DESC, PLACEHOLDER_DESC, LdpcCuda, LdpcCudaPool, LdpcCudaError, device_count, graph_shift, library, library_path, make_descs,
+                   CB_RESULT, TB_DESC, TB_RESULT, DEMOD_DESC, PLACEHOLDER_DESC, ULSCH_DESC, ulsch_desc, ulsch_sizes, ulsch_placeholders, LdpcCuda, LdpcCudaPool, LdpcCudaError, device_count, graph_shift, library, library_path, make_descs,
                    segment)
 
 __all__ = ["CRC16", "CRC24A", "CRC24B", "CRC_NONE", "SCALE_AVX", "SCALE_GENERIC", "SCALE_NEON", "FLAG_FORCE_SCALAR", "FLAG_COPY_ONLY",
-           "CB_DESC", "CB_RESULT", "TB_DESC", "TB_RESULT", "DEMOD_DESC", "PLACEHOLDER_DESC", "LdpcCuda", "LdpcCudaPool", "LdpcCudaError", "device_count", "graph_shift", "library", "library_path",
+           "CB_DESC", "CB_RESULT", "TB_DESC", "TB_RESULT", "DEMOD_DESC", "PLACEHOLDER_DESC", "ULSCH_DESC", "ulsch_desc", "ulsch_sizes", "ulsch_placeholders", "LdpcCuda", "LdpcCudaPool", "LdpcCudaError", "device_count", "graph_shift", "library", "library_path",
            "make_descs", "segment"]

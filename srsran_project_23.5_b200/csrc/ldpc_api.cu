@@ -15,6 +15,7 @@
 #include "ldpc_encode.cuh"
 #include "ldpc_tb.cuh"
 #include "ldpc_demod.cuh"
+#include "ldpc_ulsch.cuh"
 #include <cmath>
 
 using namespace ldpc_b200;
@@ -35,6 +36,7 @@ using namespace ldpc_b200;
 constexpr unsigned MAX_CHUNKS = LDPC_MAX_CHUNKS;
 static_assert(sizeof(DemodJob) == sizeof(ldpc_cuda_demod_desc) && sizeof(DemodJob) == 32, "DemodJob mirrors the ABI struct");
 static_assert(sizeof(ldpc_cuda_placeholder_desc) == 24 && sizeof(PlaceholderWork) == 24, "placeholder descriptors");
+static_assert(sizeof(ldpc_cuda_ulsch_desc) == 72, "ldpc_cuda_ulsch_desc layout");
 static_assert(sizeof(TbResult) == sizeof(ldpc_cuda_tb_result) && sizeof(ldpc_cuda_tb_result) == 8, "TbResult mirrors the ABI struct");
 
 struct ldpc_cuda_handle {
@@ -1677,6 +1679,190 @@ int ldpc_cuda_descramble_placeholders_device(ldpc_cuda_handle* h, uint32_t nof_j
   }
   CUDA_TRY(cudaSetDevice(h->device));
   return enqueue_placeholders(h, h->stream, nof_jobs, jobs, re_indexes, nof_re_indexes, llrs_d);
+}
+
+// ---- UL-SCH demultiplexing (ulsch_demultiplex_impl.cpp:316-453) ------------------------------------------------------------
+static UlschGeometry ulsch_geometry(const ldpc_cuda_ulsch_desc& d)
+{
+  UlschGeometry g;
+  g.mod_order = d.mod_order, g.nof_layers = d.nof_layers, g.nof_prb = d.nof_prb, g.start_symbol = d.start_symbol_index;
+  g.nof_symbols = d.nof_symbols, g.dmrs_type = d.dmrs_type, g.nof_cdm_groups_without_data = d.nof_cdm_groups_without_data;
+  g.dmrs_symbol_mask = d.dmrs_symbol_mask, g.nof_harq_ack_rvd = d.nof_harq_ack_rvd;
+  g.nof_enc_harq_ack = d.nof_enc_harq_ack_bits, g.nof_enc_csi1 = d.nof_enc_csi_part1_bits;
+  g.nof_enc_csi2 = d.nof_enc_csi_part2_bits;
+  return g;
+}
+
+static bool ulsch_valid(const ldpc_cuda_ulsch_desc& d)
+{
+  const bool mod_ok = d.mod_order == 1 || d.mod_order == 2 || d.mod_order == 4 || d.mod_order == 6 || d.mod_order == 8;
+  return mod_ok && d.nof_layers >= 1 && d.nof_layers <= 4 && d.nof_prb >= 1 && d.nof_prb <= 275 && d.nof_symbols >= 1;
+}
+
+int ldpc_cuda_ulsch_sizes(const ldpc_cuda_ulsch_desc* desc, uint32_t* nof_input_bits, uint32_t* nof_sch_bits)
+{
+  if (desc == nullptr || !ulsch_valid(*desc)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  std::vector<UlschSymbol> plan;
+  UlschTotals tot;
+  if (!ulsch_plan(ulsch_geometry(*desc), 0, plan, tot)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  const unsigned bpr = (unsigned)desc->mod_order * desc->nof_layers;
+  if (nof_input_bits) {
+    *nof_input_bits = tot.in_re * bpr;
+  }
+  if (nof_sch_bits) {
+    *nof_sch_bits = tot.sch_re * bpr;
+  }
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_ulsch_placeholders(const ldpc_cuda_ulsch_desc* desc, uint32_t nof_harq_ack_bits, uint32_t nof_csi_part1_bits,
+                                 uint32_t nof_csi_part2_bits, uint16_t* re_indexes, uint32_t max_indexes)
+{
+  if (desc == nullptr || !ulsch_valid(*desc) || (re_indexes == nullptr && max_indexes != 0)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  // no placeholders below QPSK, nor when no field carries exactly one bit (ulsch_demultiplex_impl.cpp:399-408)
+  if (desc->mod_order < 2 || (nof_harq_ack_bits != 1 && nof_csi_part1_bits != 1 && nof_csi_part2_bits != 1)) {
+    return 0;
+  }
+  std::vector<UlschSymbol> plan;
+  UlschTotals tot;
+  if (!ulsch_plan(ulsch_geometry(*desc), 0, plan, tot)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  // An element's index in the placeholder list counts the elements that consume input before it, which is every element:
+  // the zero-filled element underneath a punctured reserved one does not advance the counter (:413-445).
+  uint32_t count = 0;
+  for (const UlschSymbol& s : plan) {
+    if (!(s.rvd_n | s.ack_n | s.csi1_n | s.csi2_n)) {
+      continue;
+    }
+    for (unsigned i = 0; i != s.n_re; ++i) {
+      const UlschWhere w = ulsch_classify(s, i);
+      const bool one = (w.field == ULSCH_ACK && nof_harq_ack_bits == 1) || (w.field == ULSCH_CSI1 && nof_csi_part1_bits == 1) ||
+                       (w.field == ULSCH_CSI2 && nof_csi_part2_bits == 1);
+      if (one) {
+        if (count < max_indexes) {
+          re_indexes[count] = (uint16_t)(s.in_base + i);
+        }
+        ++count;
+      }
+    }
+  }
+  return (int)count;
+}
+
+// Plans every codeword, uploads symbols + jobs through the demodulator's pinned staging and launches the kernel.
+static int enqueue_ulsch(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t n, const ldpc_cuda_ulsch_desc* descs,
+                         const int8_t* d_in, int8_t* d_sch, int8_t* d_uci)
+{
+  std::vector<UlschSymbol> plan;
+  std::vector<UlschJob> jobs(n);
+  unsigned max_re = 0;
+  for (uint32_t k = 0; k != n; ++k) {
+    const ldpc_cuda_ulsch_desc& d = descs[k];
+    UlschTotals tot;
+    if (!ulsch_valid(d) || !ulsch_plan(ulsch_geometry(d), k, plan, tot)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+    jobs[k].in_offset = d.in_offset, jobs[k].sch_offset = d.sch_offset, jobs[k].ack_offset = d.harq_ack_offset;
+    jobs[k].csi1_offset = d.csi_part1_offset, jobs[k].csi2_offset = d.csi_part2_offset;
+    jobs[k].bits_per_re = (unsigned)d.mod_order * d.nof_layers, jobs[k].reserved = 0;
+  }
+  if (plan.empty()) {
+    return LDPC_CUDA_OK;
+  }
+  if (plan.size() > 65535u) {
+    return LDPC_CUDA_ERR_CAPACITY;
+  }
+  for (const UlschSymbol& s : plan) {
+    max_re = std::max(max_re, s.n_re);
+  }
+  const size_t sym_bytes = sizeof(UlschSymbol) * plan.size(), off_jobs = (sym_bytes + 15) & ~(size_t)15;
+  const size_t bytes = off_jobs + sizeof(UlschJob) * n;
+  unsigned slot = 0;
+  const int rc = demod_stage(h, bytes, slot);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  std::memcpy(h->h_demod[slot], plan.data(), sym_bytes);
+  std::memcpy(h->h_demod[slot] + off_jobs, jobs.data(), sizeof(UlschJob) * n);
+  CUDA_TRY(cudaMemcpyAsync(h->d_demod, h->h_demod[slot], bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaEventRecord(h->ev_demod[slot], stream));
+  const dim3 grid((max_re + 255) / 256, (unsigned)plan.size());
+  ldpc_ulsch_demux_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const UlschSymbol*>(h->d_demod),
+                                                     reinterpret_cast<const UlschJob*>(h->d_demod + off_jobs), d_in, d_sch,
+                                                     d_uci);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 1;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_ulsch_demultiplex_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_ulsch_desc* descs,
+                                             const int8_t* in_llrs_d, int8_t* sch_d, int8_t* uci_d)
+{
+  if (h == nullptr || descs == nullptr || in_llrs_d == nullptr || sch_d == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  if (n == 0) {
+    return LDPC_CUDA_OK;
+  }
+  for (uint32_t k = 0; k != n; ++k) {
+    if (uci_d == nullptr && (descs[k].nof_enc_harq_ack_bits | descs[k].nof_enc_csi_part1_bits | descs[k].nof_enc_csi_part2_bits)) {
+      return LDPC_CUDA_ERR_ARG;
+    }
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  return enqueue_ulsch(h, h->stream, n, descs, in_llrs_d, sch_d, uci_d);
+}
+
+int ldpc_cuda_ulsch_demultiplex(ldpc_cuda_handle* h, const ldpc_cuda_ulsch_desc* desc, const int8_t* input, int8_t* sch_data,
+                                int8_t* harq_ack, int8_t* csi_part1, int8_t* csi_part2)
+{
+  if (h == nullptr || desc == nullptr || input == nullptr || sch_data == nullptr ||
+      (desc->nof_enc_harq_ack_bits != 0 && harq_ack == nullptr) || (desc->nof_enc_csi_part1_bits != 0 && csi_part1 == nullptr) ||
+      (desc->nof_enc_csi_part2_bits != 0 && csi_part2 == nullptr)) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  uint32_t in_bits = 0, sch_bits = 0;
+  int rc = ldpc_cuda_ulsch_sizes(desc, &in_bits, &sch_bits);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  // device staging: input | then outputs SCH, HARQ-ACK, CSI 1, CSI 2 one after the other
+  const size_t a = desc->nof_enc_harq_ack_bits, c1 = desc->nof_enc_csi_part1_bits, c2 = desc->nof_enc_csi_part2_bits;
+  rc = ensure_capacity(h, in_bits, sch_bits + a + c1 + c2 + 16);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  ldpc_cuda_ulsch_desc d = *desc;
+  d.in_offset = 0, d.sch_offset = 0, d.harq_ack_offset = sch_bits, d.csi_part1_offset = sch_bits + a;
+  d.csi_part2_offset = sch_bits + a + c1;
+  int8_t* d_out = reinterpret_cast<int8_t*>(h->d_out);
+  CUDA_TRY(cudaMemcpyAsync(h->d_in, input, in_bits, cudaMemcpyHostToDevice, h->stream));
+  rc = enqueue_ulsch(h, h->stream, 1, &d, h->d_in, d_out, d_out);
+  if (rc != LDPC_CUDA_OK) {
+    cudaStreamSynchronize(h->stream);
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(sch_data, d_out, sch_bits, cudaMemcpyDeviceToHost, h->stream));
+  if (a) {
+    CUDA_TRY(cudaMemcpyAsync(harq_ack, d_out + d.harq_ack_offset, a, cudaMemcpyDeviceToHost, h->stream));
+  }
+  if (c1) {
+    CUDA_TRY(cudaMemcpyAsync(csi_part1, d_out + d.csi_part1_offset, c1, cudaMemcpyDeviceToHost, h->stream));
+  }
+  if (c2) {
+    CUDA_TRY(cudaMemcpyAsync(csi_part2, d_out + d.csi_part2_offset, c2, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return LDPC_CUDA_OK;
 }
 
 // ---- drop-in single codeblock ---------------------------------------------------------------------------------------

@@ -36,6 +36,14 @@ DEMOD_DESC = np.dtype([("mod_order", "u1"), ("pi2_bpsk", "u1"), ("descramble", "
                        ("nof_symbols", "<u4"), ("c_init", "<u4"), ("reserved2", "<u4"), ("symbol_offset", "<u8"),
                        ("llr_offset", "<u8")], align=True)
 assert DEMOD_DESC.itemsize == 32
+# ldpc_cuda_ulsch_desc (72 bytes)
+ULSCH_DESC = np.dtype([("mod_order", "u1"), ("nof_layers", "u1"), ("start_symbol_index", "u1"), ("nof_symbols", "u1"),
+                       ("dmrs_type", "u1"), ("nof_cdm_groups_without_data", "u1"), ("dmrs_symbol_mask", "<u2"),
+                       ("nof_prb", "<u2"), ("reserved", "<u2"), ("nof_harq_ack_rvd", "<u4"),
+                       ("nof_enc_harq_ack_bits", "<u4"), ("nof_enc_csi_part1_bits", "<u4"),
+                       ("nof_enc_csi_part2_bits", "<u4"), ("in_offset", "<u8"), ("sch_offset", "<u8"),
+                       ("harq_ack_offset", "<u8"), ("csi_part1_offset", "<u8"), ("csi_part2_offset", "<u8")], align=True)
+assert ULSCH_DESC.itemsize == 72
 # ldpc_cuda_placeholder_desc (24 bytes)
 PLACEHOLDER_DESC = np.dtype([("llr_offset", "<u8"), ("c_init", "<u4"), ("nof_llrs", "<u4"), ("first_re", "<u4"),
                              ("nof_re", "<u2"), ("mod_order", "u1"), ("nof_layers", "u1")], align=True)
@@ -112,6 +120,10 @@ def library():
         L.ldpc_cuda_descramble.argtypes = [vp, u32, u32, vp, vp]
         L.ldpc_cuda_segment.argtypes = [u32, i32, i32, i32, u32, u32, u32, vp, u32, vp]
         L.ldpc_cuda_graph_shift.argtypes = [i32, i32, i32, i32]
+        L.ldpc_cuda_ulsch_sizes.argtypes = [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]
+        L.ldpc_cuda_ulsch_demultiplex_batch_device.argtypes = [vp, u32, vp, vp, vp, vp]
+        L.ldpc_cuda_ulsch_demultiplex.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.ldpc_cuda_ulsch_placeholders.argtypes = [vp, u32, u32, u32, vp, u32]
         L.ldpc_cuda_pool_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(i32), u32, u32, u32]
         L.ldpc_cuda_pool_destroy.argtypes = [vp]
         L.ldpc_cuda_pool_destroy.restype = None
@@ -155,6 +167,31 @@ def segment(tbs, bg, mod_order, nof_layers, nof_ch_symbols, rv=0, Nref=0):
     crc_bits = np.zeros(C, np.uint32)
     L.ldpc_cuda_segment(tbs, bg, rv, mod_order, Nref, nof_layers, nof_ch_symbols, _ptr(descs), C, _ptr(crc_bits))
     return descs, crc_bits
+
+
+def ulsch_desc(mod_order, nof_layers, nof_prb, start_symbol, nof_symbols, dmrs_type, cdm, dmrs_mask, rvd, G_ack=0, G_csi1=0,
+               G_csi2=0):
+    """One ldpc_cuda_ulsch_desc (ulsch_demultiplex::configuration + the sizes of the three UCI fields)."""
+    d = np.zeros(1, ULSCH_DESC)
+    d["mod_order"], d["nof_layers"], d["nof_prb"], d["start_symbol_index"] = mod_order, nof_layers, nof_prb, start_symbol
+    d["nof_symbols"], d["dmrs_type"], d["nof_cdm_groups_without_data"], d["dmrs_symbol_mask"] = nof_symbols, dmrs_type, cdm, dmrs_mask
+    d["nof_harq_ack_rvd"], d["nof_enc_harq_ack_bits"] = rvd, G_ack
+    d["nof_enc_csi_part1_bits"], d["nof_enc_csi_part2_bits"] = G_csi1, G_csi2
+    return d
+
+
+def ulsch_sizes(desc):
+    """(input soft bits, SCH soft bits) of a descriptor, or None for a configuration the reference asserts on."""
+    a, b = ctypes.c_uint32(0), ctypes.c_uint32(0)
+    rc = library().ldpc_cuda_ulsch_sizes(_ptr(desc), ctypes.byref(a), ctypes.byref(b))
+    return None if rc != 0 else (a.value, b.value)
+
+
+def ulsch_placeholders(desc, O_ack, O_csi1, O_csi2):
+    """ulsch_demultiplex::get_placeholders (host only): RE indexes, or None for an inconsistent configuration."""
+    lst = np.zeros(1 << 16, np.uint16)
+    n = library().ldpc_cuda_ulsch_placeholders(_ptr(desc), O_ack, O_csi1, O_csi2, _ptr(lst), lst.size)
+    return None if n < 0 else lst[:n].copy()
 
 
 def make_descs(n, bg, Z, **fields):
@@ -330,6 +367,26 @@ class LdpcCuda:
         self._check(self._L.ldpc_cuda_descramble_uci(self._h, c_init, llrs.size, mod_order, nof_layers, re_indexes.size,
                                                      _ptr(re_indexes), _ptr(llrs), _ptr(out)), "ldpc_cuda_descramble_uci")
         return out
+
+    def ulsch_demultiplex(self, desc, llrs):
+        """ulsch_demultiplex::demultiplex, host buffers. Returns (sch_data, harq_ack, csi_part1, csi_part2)."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        sizes = ulsch_sizes(desc)
+        if sizes is None or sizes[0] != llrs.size:
+            raise LdpcCudaError(-1, "ldpc_cuda_ulsch_sizes")
+        sch = np.zeros(sizes[1], np.int8)
+        ack = np.zeros(int(desc["nof_enc_harq_ack_bits"][0]), np.int8)
+        c1 = np.zeros(int(desc["nof_enc_csi_part1_bits"][0]), np.int8)
+        c2 = np.zeros(int(desc["nof_enc_csi_part2_bits"][0]), np.int8)
+        self._check(self._L.ldpc_cuda_ulsch_demultiplex(self._h, _ptr(desc), _ptr(llrs), _ptr(sch),
+                                                        _ptr(ack) if ack.size else None, _ptr(c1) if c1.size else None,
+                                                        _ptr(c2) if c2.size else None), "ldpc_cuda_ulsch_demultiplex")
+        return sch, ack, c1, c2
+
+    def ulsch_demultiplex_batch_device(self, descs, in_ptr, sch_ptr, uci_ptr):
+        descs = np.ascontiguousarray(descs, ULSCH_DESC)
+        self._check(self._L.ldpc_cuda_ulsch_demultiplex_batch_device(self._h, descs.size, _ptr(descs), in_ptr, sch_ptr,
+                                                                     uci_ptr), "ldpc_cuda_ulsch_demultiplex_batch_device")
 
     def demodulate_batch_device(self, jobs, symbols_ptr, noise_ptr, in_llrs_ptr, llrs_ptr):
         jobs = np.ascontiguousarray(jobs, DEMOD_DESC)

@@ -56,6 +56,9 @@ class PortOracle:
         L.oracle_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
         L.oracle_gold_sequence.argtypes = [c_uint, c_uint, c_void_p]
         L.oracle_descramble_placeholders.argtypes = [c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint, c_void_p]
+        L.oracle_ulsch_demultiplex.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_void_p, c_uint, c_void_p, c_void_p,
+                                               c_void_p, c_void_p, c_void_p, c_void_p]
+        L.oracle_ulsch_placeholders.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_uint, c_uint, c_uint, c_void_p, c_uint]
 
     def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False):
         """symbols: complex64 [n]; noise_vars: float32 [n]. Returns int8 [n * mod_order]."""
@@ -79,6 +82,31 @@ class PortOracle:
         self.lib.oracle_descramble_placeholders(c_init, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
                                                 re_indexes.size, _ptr(re_indexes))
         return out
+
+    @staticmethod
+    def _ulsch_cfg(cfg):
+        """cfg: dict(mod_order, nof_layers, nof_prb, start_symbol, nof_symbols, dmrs_type, cdm, dmrs_mask, rvd)."""
+        return np.array([cfg["mod_order"], cfg["nof_layers"], cfg["nof_prb"], cfg["start_symbol"], cfg["nof_symbols"],
+                         cfg["dmrs_type"], cfg["cdm"], cfg["dmrs_mask"], cfg["rvd"]], np.uint32)
+
+    def ulsch_demultiplex(self, cfg, G_ack, G_csi1, G_csi2, llrs):
+        """Returns (sch, ack, csi1, csi2) or None where the reference asserts."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        c = self._ulsch_cfg(cfg)
+        sch = np.zeros(llrs.size + 64, np.int8)
+        ack, c1, c2 = np.zeros(G_ack + 64, np.int8), np.zeros(G_csi1 + 64, np.int8), np.zeros(G_csi2 + 64, np.int8)
+        used, slen = ctypes.c_uint(0), ctypes.c_uint(0)
+        rc = self.lib.oracle_ulsch_demultiplex(_ptr(c), G_ack, G_csi1, G_csi2, _ptr(llrs), llrs.size, _ptr(sch), _ptr(ack),
+                                               _ptr(c1), _ptr(c2), ctypes.byref(used), ctypes.byref(slen))
+        if rc != 0 or used.value != llrs.size:
+            return None
+        return sch[:slen.value], ack[:G_ack], c1[:G_csi1], c2[:G_csi2]
+
+    def ulsch_placeholders(self, cfg, O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2):
+        c = self._ulsch_cfg(cfg)
+        lst = np.zeros(1 << 16, np.uint16)
+        n = self.lib.oracle_ulsch_placeholders(_ptr(c), O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2, _ptr(lst), lst.size)
+        return None if n < 0 else lst[:n].copy()
 
     def gold_sequence(self, c_init, n):
         c = np.zeros(n, np.uint8)
@@ -183,8 +211,14 @@ class RefOracle:
         L.ref_pusch_decode.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_int,
                                        c_int, c_int, c_uint, c_uint, c_uint, c_int, c_int, c_int, c_void_p]
         L.ref_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p, c_uint]
+        L.ref_ulsch_demultiplex.argtypes = [c_void_p, c_void_p, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_void_p, c_uint,
+                                            c_void_p, c_uint]
+        L.ref_ulsch_placeholders.argtypes = [c_void_p, c_void_p, c_void_p, c_uint]
         L.ref_descramble.argtypes = [c_uint, c_uint, c_void_p, c_void_p]
         L.ref_descramble_placeholders.argtypes = [c_uint, c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint, c_void_p]
+        if hasattr(L, "dropin_ulsch_demultiplex"):  # oracle/_ref/libdropin.so only
+            L.dropin_ulsch_demultiplex.argtypes = L.ref_ulsch_demultiplex.argtypes
+            L.dropin_ulsch_placeholders.argtypes = L.ref_ulsch_placeholders.argtypes
         if hasattr(L, "dropin_descramble_placeholders"):  # oracle/_ref/libdropin.so only
             L.dropin_descramble_placeholders.argtypes = [c_uint, c_uint, c_uint, c_void_p, c_void_p, c_uint, c_uint, c_uint,
                                                          c_void_p]
@@ -222,6 +256,31 @@ class RefOracle:
         self.lib.ref_descramble_placeholders(rnti, n_id, llrs.size, _ptr(llrs), _ptr(out), mod_order, nof_layers,
                                              re_indexes.size, _ptr(re_indexes))
         return out
+
+    def ulsch_demultiplex(self, cfg, llrs, sch_len, G_ack, G_csi1, G_csi2, cuda=False):
+        """The reference's own ulsch_demultiplex_impl::demultiplex (sizes must be consistent: it asserts otherwise);
+        cuda=True (drop-in library): the product's create_ulsch_demultiplex_cuda() behind the same interface."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        c = PortOracle._ulsch_cfg(cfg)
+        sch, ack = np.zeros(sch_len, np.int8), np.zeros(G_ack, np.int8)
+        c1, c2 = np.zeros(G_csi1, np.int8), np.zeros(G_csi2, np.int8)
+        if cuda:
+            rc = self.lib.dropin_ulsch_demultiplex(_ptr(c), _ptr(llrs), llrs.size, _ptr(sch), sch_len, _ptr(ack), G_ack,
+                                                   _ptr(c1), G_csi1, _ptr(c2), G_csi2)
+            assert rc == 0
+            return sch, ack, c1, c2
+        self.lib.ref_ulsch_demultiplex(_ptr(c), _ptr(llrs), llrs.size, _ptr(sch), sch_len, _ptr(ack), G_ack, _ptr(c1), G_csi1,
+                                       _ptr(c2), G_csi2)
+        return sch, ack, c1, c2
+
+    def ulsch_placeholders(self, cfg, O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2, cuda=False):
+        c = PortOracle._ulsch_cfg(cfg)
+        info = np.array([O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2], np.uint32)
+        lst = np.zeros(1 << 16, np.uint16)
+        fn = self.lib.dropin_ulsch_placeholders if cuda else self.lib.ref_ulsch_placeholders
+        n = fn(_ptr(c), _ptr(info), _ptr(lst), lst.size)
+        assert n >= 0
+        return lst[:n].copy()
 
     def supports(self, kind):
         return bool(self.lib.ref_cpu_supports(kind.encode()))
@@ -446,3 +505,32 @@ def build_transport_block(rng, tbs_bits, bg, Qm, nof_layers, nof_ch_symbols):
         msg = np.concatenate([tb_all[r * per_cb:(r + 1) * per_cb], np.zeros(24, np.uint8), np.full(F, 254, np.uint8)])
         cws.append(port().encode(bg, Z, attach_crc(msg, CRC24B, F)))
     return np.packbits(tb_bits), cws, meta
+
+
+def ulsch_cases(rng, n):
+    """Random UL-SCH multiplexing configurations over the space ulsch_demultiplex takes (TS 38.212 6.2.7): modulation, 1-4
+    layers, DM-RS type and positions, HARQ-ACK with / without reserved elements (O_ACK <= 2 reserves), CSI part 1 / 2.
+    Yields (cfg, O_ack, G_ack, O_csi1, G_csi1, O_csi2, G_csi2); inconsistent draws are left to the caller to skip."""
+    masks = [0b0000000000000100, 0b0000100000000100, 0b0000000000001100, 0b0000100100000100, 0b0000000000000001]
+    out = []
+    while len(out) < n:
+        Qm = int(rng.choice([1, 2, 4, 6, 8]))
+        nl = int(rng.integers(1, 5))
+        bpr = Qm * nl
+        dmrs_type = int(rng.integers(1, 3))
+        cfg = dict(mod_order=Qm, nof_layers=nl, nof_prb=int(rng.choice([1, 2, 5, 24, 52, 106, 273])),
+                   start_symbol=int(rng.choice([0, 0, 1, 2])), nof_symbols=0, dmrs_type=dmrs_type,
+                   cdm=int(rng.integers(1, 3 if dmrs_type == 1 else 4)), dmrs_mask=int(rng.choice(masks)), rvd=0)
+        cfg["nof_symbols"] = int(rng.integers(4, 15 - cfg["start_symbol"]))
+        re_total = cfg["nof_prb"] * 12 * cfg["nof_symbols"]
+        mode = int(rng.integers(0, 4))
+        O_ack = int(rng.choice([0, 1, 2, 3, 11])) if mode else 0
+        G_ack = bpr * int(rng.integers(1, max(2, re_total // 20))) if O_ack else 0
+        if O_ack in (1, 2) or (O_ack == 0 and rng.integers(0, 3) == 0):
+            cfg["rvd"] = max(G_ack, bpr * int(rng.integers(1, max(2, re_total // 16))))
+        O_c1 = int(rng.choice([0, 1, 4, 20]))
+        G_c1 = bpr * int(rng.integers(1, max(2, re_total // 12))) if O_c1 else 0
+        O_c2 = int(rng.choice([0, 1, 7])) if O_c1 else 0
+        G_c2 = bpr * int(rng.integers(1, max(2, re_total // 12))) if O_c2 else 0
+        out.append((cfg, O_ack, G_ack, O_c1, G_c1, O_c2, G_c2))
+    return out

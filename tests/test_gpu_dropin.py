@@ -241,3 +241,31 @@ def test_descramble_with_placeholders_interface(lib):
         want = lib.descramble_placeholders(rnti, n_id, llrs, q, layers, res)
         got = lib.descramble_placeholders(rnti, n_id, llrs, q, layers, res, cuda=True)
         assert (got == want).all(), (q, layers, np.flatnonzero(got != want)[:8])
+
+
+def test_ulsch_demultiplex_interface(lib):
+    """ulsch_demultiplex (ulsch_demultiplex.h:37-103) created by create_ulsch_demultiplex_cuda(): demultiplex and
+    get_placeholders against the reference's own ulsch_demultiplex_impl on the same configuration, as
+    ulsch_demultiplex_test.cpp does with its vectors (every soft bit of the four fields, every placeholder index)."""
+    rng = np.random.default_rng(31)
+    checked = with_pl = 0
+    for cfg, O_ack, G_ack, O_c1, G_c1, O_c2, G_c2 in O.ulsch_cases(rng, 160):
+        bpr = cfg["mod_order"] * cfg["nof_layers"]
+        n_in = 0
+        for l in range(cfg["start_symbol"], cfg["start_symbol"] + cfg["nof_symbols"]):
+            dm = (cfg["dmrs_mask"] >> l) & 1
+            n_in += (12 - dm * cfg["cdm"] * (6 if cfg["dmrs_type"] == 1 else 4)) * cfg["nof_prb"] * bpr
+        llrs = rng.integers(-120, 121, n_in).astype(np.int8)
+        port = O.port().ulsch_demultiplex(cfg, G_ack, G_c1, G_c2, llrs)
+        if port is None:
+            continue  # the reference asserts on this draw (and so does the adaptor)
+        want = lib.ulsch_demultiplex(cfg, llrs, port[0].size, G_ack, G_c1, G_c2)
+        got = lib.ulsch_demultiplex(cfg, llrs, port[0].size, G_ack, G_c1, G_c2, cuda=True)
+        for name, a, b in zip(("sch", "ack", "csi1", "csi2"), got, want):
+            assert (a == b).all(), (name, cfg)
+        wpl = lib.ulsch_placeholders(cfg, O_ack, G_ack, O_c1, G_c1, O_c2, G_c2)
+        gpl = lib.ulsch_placeholders(cfg, O_ack, G_ack, O_c1, G_c1, O_c2, G_c2, cuda=True)
+        assert gpl.size == wpl.size and (gpl == wpl).all(), cfg
+        with_pl += wpl.size > 0
+        checked += 1
+    assert checked > 60 and with_pl > 5
