@@ -1003,6 +1003,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
           finish(wB, resB, doneB, hard + msg_bytes16, okB);
         }
         tm::group_barrier<FULL>(bar_id, zpad);
+      } else if (t == 0) {
+        // No check after this iteration (one half decodes without early stop, the other has finished): the accumulators
+        // the next iteration would use may still hold the remainder of an earlier check of the same parity.
+        flags[8 + 2 * ((it + 1) & 1)] = 0, flags[9 + 2 * ((it + 1) & 1)] = 0;
       }
     }
     tm::group_barrier<FULL>(bar_id, zpad);  // flags / hard bits are reused by the next pair

@@ -291,3 +291,39 @@ def test_fused_prologue_dematch_all_cases_with_stale_priors(dec, misaligned):
         assert (int(res["iterations"][i]) if res["crc_ok"][i] else 0) == it, (i, c["case"])
         if want.any():
             assert (out[o:o + c["kb"]] == bits).all(), (i, c["case"])
+
+
+@pytest.mark.parametrize("bg,Z", [(1, 384), (1, 60), (2, 15)])
+def test_no_early_stop_half_beside_an_early_finisher(dec, bg, Z):
+    """A codeblock decoded without early stop (CRC checked once, after the last iteration; pusch_decoder_impl.cpp:109-118)
+    that shares its thread pair with one that stops early: iterations in between run no check at all, and the check after
+    the last one must not see what an earlier check left behind. (Found by tests/test_gpu_sweep.py: crc_ok was reported 0
+    for correctly decoded bits when the early finisher stopped on an iteration of the same parity as the last.)"""
+    rng = np.random.default_rng(77 + Z)
+    K, N = O.BG_K[bg], O.BG_N_SHORT[bg] * Z
+    for max_iters in (4, 6, 7):
+        dec.set_algorithm(max_iters, 0.8, O.SCALE_GENERIC)
+        n = 8
+        descs = np.zeros(n, pkg.CB_DESC)
+        rm_all, want = [], []
+        dec.softbuffer_reserve(n * N)
+        for i in range(n):
+            crc = [O.CRC16, O.CRC24B][i % 2]
+            F = (3 * i) % Z
+            msg, cw = O.make_codeword(rng, bg, Z, F, crc)
+            rm = O.awgn_llrs(rng, O.port().rate_match(cw, N, 0, 2, 0, F), 1.0 + (i // 2))
+            d = descs[i]
+            d["base_graph"], d["lifting_size"], d["nof_filler_bits"], d["crc_poly"] = bg, Z, F, crc
+            d["early_stop"], d["mod_order"], d["new_data"], d["rm_length"] = i % 2, 2, 1, N  # halves of a pair differ
+            d["in_offset"], d["out_offset"], d["soft_offset"], d["in_length"] = i * N, i * ((K * Z + 7) // 8), i * N, N
+            rm_all.append(rm)
+            soft = np.zeros(N, np.int8)
+            want.append(_oracle_tx(soft, rm, 1, bg, Z, 0, 2, 0, F, crc, i % 2, max_iters))
+        out, res = dec.dematch_decode_batch(descs, np.concatenate(rm_all), np.zeros(n * ((K * Z + 7) // 8), np.uint8))
+        kb = (K * Z + 7) // 8
+        stopped_early = 0
+        for i, (bits, ok, it) in enumerate(want):
+            assert bool(res["crc_ok"][i]) == ok and int(res["iterations"][i]) == it, (max_iters, i, res[i], ok, it)
+            assert (out[i * kb:(i + 1) * kb] == bits).all()
+            stopped_early += ok and it < max_iters - 1
+        assert stopped_early >= 2 and all(w[1] for w in want)
