@@ -17,6 +17,7 @@
 #include "phy/upper/channel_coding/ldpc/ldpc_luts_impl.h"
 #include "phy/upper/channel_processors/pusch_decoder_impl.h"
 #include "srsran/phy/upper/channel_coding/channel_coding_factories.h"
+#include "srsran/phy/upper/channel_processors/channel_processor_factories.h"
 #include "srsran/phy/upper/log_likelihood_ratio.h"
 #include "srsran/phy/upper/rx_softbuffer_pool.h"
 #include "srsran/phy/upper/unique_rx_softbuffer.h"
@@ -51,6 +52,7 @@
 #include <map>
 #include <chrono>
 #include <cstring>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -748,6 +750,197 @@ int ref_pusch_decode(void*         handle,
   }
   h->pool->run_slot(slot);
   return 0;
+}
+
+// K pusch_decoder objects of ONE factory on K threads, as uplink_processor_impl.cpp:155-171 runs them (one PUSCH per
+// executor thread), sharing one soft-buffer pool. Thread k decodes `reps` transport blocks, each sent nof_tx times
+// (rv 0, 2, 3, 1; new_data on the first) as (rnti = k + 1, harq = rep % 8).
+//   decoder_type: "generic" | "avx2" | "avx512" (the reference's pusch_decoder_impl) | "cuda-batched" (one launch per
+//                 decode()) | "cuda-aggregated" (the factory's slot aggregator, `aggregate_blocks` staging blocks)
+//   pool_type:    "sw" (the reference's host pool) | "cuda-pool" (the product's device pool, takes > 52 codeblocks)
+//   llrs:         [K][reps][nof_tx][nof_llrs];  tb_out: [K][reps][tb_bytes] (of the last transmission);
+//   warm_reps:    untimed repetitions per thread before the clock starts;
+//   stats_out:    [K][reps][nof_tx][6] as ref_pusch_decode;  agg_out[8]: launches, transport blocks, max TBs per launch,
+//                 then join_wait / stage / follow / drain / launch nanoseconds (pusch_decoder_cuda_aggregator_stats).
+// Returns the wall-clock seconds from a common start to the last thread's end, < 0 on failure.
+double ref_pusch_concurrent(const char*   decoder_type,
+                            const char*   pool_type,
+                            unsigned      K,
+                            unsigned      reps,
+                            unsigned      nof_tx,
+                            unsigned      tb_bytes,
+                            const int8_t* llrs,
+                            unsigned      nof_llrs,
+                            int           bg,
+                            int           Qm,
+                            unsigned      nof_layers,
+                            unsigned      nof_ldpc_iterations,
+                            int           use_early_stop,
+                            unsigned      aggregate_blocks,
+                            unsigned      warm_reps,
+                            uint8_t*      tb_out,
+                            unsigned*     stats_out,
+                            uint64_t*     agg_out)
+{
+  const unsigned nof_cbs = ldpc::compute_nof_codeblocks(units::bits(tb_bytes * 8), to_bg(bg));
+  auto           crc_f   = create_crc_calculator_factory_sw("auto");
+  std::vector<std::unique_ptr<pusch_decoder>> decs(K);
+  std::shared_ptr<pusch_decoder_factory>      cuda_factory;
+  const std::string                           type(decoder_type);
+  if (type == "cuda-batched" || type == "cuda-aggregated") {
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+    pusch_decoder_cuda_configuration pc = {};
+    pc.crc_factory                      = crc_f;
+    pc.arena_codeblocks                 = std::max(256u, K * 8 * nof_cbs);
+    pc.max_codeblocks_per_tb            = std::max(256u, nof_cbs);
+    if (type == "cuda-aggregated") {
+      pc.aggregate_codeblocks = std::max(1024u, K * nof_cbs);
+      pc.aggregate_blocks     = aggregate_blocks;
+    }
+    cuda_factory = create_pusch_decoder_factory_cuda(pc);
+    for (auto& d : decs) {
+      d = cuda_factory ? cuda_factory->create() : nullptr;
+    }
+#endif
+  } else {
+    auto dec_f = decoder_factory_of(decoder_type);
+    auto dem_f = dematcher_factory_of(decoder_type);
+    auto seg_f = create_ldpc_segmenter_rx_factory_sw();
+    for (auto& d : decs) {
+      auto decoder = dec_f ? dec_f->create() : nullptr;
+      auto demat   = dem_f ? dem_f->create() : nullptr;
+      if (!decoder || !demat) {
+        return -1.0;
+      }
+      pusch_decoder_impl::sch_crc crcs;
+      crcs.crc16  = crc_f->create(crc_generator_poly::CRC16);
+      crcs.crc24A = crc_f->create(crc_generator_poly::CRC24A);
+      crcs.crc24B = crc_f->create(crc_generator_poly::CRC24B);
+      d = std::make_unique<pusch_decoder_impl>(seg_f->create(), std::move(demat), std::move(decoder), std::move(crcs));
+    }
+  }
+  for (auto& d : decs) {
+    if (!d) {
+      return -1.0;
+    }
+  }
+  std::unique_ptr<rx_softbuffer_pool> pool;
+  if (std::strcmp(pool_type, "cuda-pool") == 0) {
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+    rx_softbuffer_pool_cuda_config cc = {};
+    cc.max_softbuffers                = K * 8;
+    cc.max_nof_codeblocks             = K * 8 * nof_cbs;
+    cc.expire_timeout_slots           = 100000;
+    pool                              = create_rx_softbuffer_pool_cuda(cc);
+#endif
+  } else {
+    if (nof_cbs > MAX_NOF_SEGMENTS) {
+      return -2.0;
+    }
+    rx_softbuffer_pool_config rc = {};
+    rc.max_codeblock_size        = ldpc::MAX_CODEBLOCK_SIZE;
+    rc.max_softbuffers           = K * 8;
+    rc.max_nof_codeblocks        = K * 8 * nof_cbs;
+    rc.expire_timeout_slots      = 100000;
+    pool                         = create_rx_softbuffer_pool(rc);
+  }
+  if (!pool) {
+    return -1.0;
+  }
+  static const unsigned rvs[4] = {0, 2, 3, 1};
+  std::atomic<unsigned> arrived{0};
+  std::atomic<int>      failed{0};
+  std::vector<std::chrono::steady_clock::time_point> t_begin(K), t_end(K);
+  std::atomic<unsigned> warmed{0};
+  auto worker = [&](unsigned k) {
+    arrived.fetch_add(1);
+    while (arrived.load() < K) { // common start
+    }
+    // untimed repetitions first (they decode the first transport blocks, which are decoded again below): lazy
+    // allocations and the first launches of every handle are out of the way when the clock starts
+    for (unsigned w = 0; w != warm_reps + reps; ++w) {
+      if (w == warm_reps) {
+        warmed.fetch_add(1);
+        while (warmed.load() < K && !failed.load()) {
+        }
+        t_begin[k] = std::chrono::steady_clock::now();
+      }
+      const unsigned rep = w < warm_reps ? w % reps : w - warm_reps;
+      rx_softbuffer_identifier id  = {static_cast<uint16_t>(k + 1), static_cast<uint8_t>(rep % 8)};
+      slot_point               slot(1, rep % 10240);
+      unique_rx_softbuffer     buf = pool->reserve_softbuffer(slot, id, nof_cbs);
+      if (!buf.is_valid()) {
+        failed.store(1);
+        break;
+      }
+      bool released = false;
+      for (unsigned t = 0; t != nof_tx; ++t) {
+        const size_t                 item = (static_cast<size_t>(k) * reps + rep) * nof_tx + t;
+        pusch_decoder::configuration cfg  = {};
+        cfg.segmenter_cfg.base_graph      = to_bg(bg);
+        cfg.segmenter_cfg.rv              = rvs[t % 4];
+        cfg.segmenter_cfg.mod             = static_cast<modulation_scheme>(Qm);
+        cfg.segmenter_cfg.Nref            = 0;
+        cfg.segmenter_cfg.nof_layers      = nof_layers;
+        cfg.segmenter_cfg.nof_ch_symbols  = nof_llrs / Qm;
+        cfg.nof_ldpc_iterations           = nof_ldpc_iterations;
+        cfg.use_early_stop                = use_early_stop != 0;
+        cfg.new_data                      = t == 0;
+        pusch_decoder_result stats        = {};
+        if (released) {
+          // the block passed in an earlier transmission and its buffer was released (uplink_processor_impl.cpp:168-170)
+          std::memset(stats_out + item * 6, 0xff, 6 * sizeof(unsigned));
+          continue;
+        }
+        decs[k]->decode(span<uint8_t>(tb_out + (static_cast<size_t>(k) * reps + rep) * tb_bytes, tb_bytes),
+                        stats,
+                        &buf.get(),
+                        span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs) + item * nof_llrs,
+                                                         nof_llrs),
+                        cfg);
+        unsigned* so = stats_out + item * 6;
+        so[0]        = stats.tb_crc_ok ? 1 : 0;
+        so[1]        = stats.nof_codeblocks_total;
+        so[2]        = stats.ldpc_decoder_stats.get_nof_observations();
+        so[3] = so[4] = so[5] = 0;
+        if (so[2] > 0) {
+          so[3] = stats.ldpc_decoder_stats.get_min();
+          so[4] = stats.ldpc_decoder_stats.get_max();
+          so[5] = static_cast<unsigned>(stats.ldpc_decoder_stats.get_mean() * 1000.0 + 0.5);
+        }
+        if (stats.tb_crc_ok) {
+          buf.release();
+          released = true;
+        }
+      }
+      if (!released) {
+        buf.release();
+      }
+    }
+    t_end[k] = std::chrono::steady_clock::now();
+  };
+  std::vector<std::thread> threads;
+  for (unsigned k = 0; k != K; ++k) {
+    threads.emplace_back(worker, k);
+  }
+  for (auto& t : threads) {
+    t.join();
+  }
+  if (failed.load()) {
+    return -3.0;
+  }
+  std::memset(agg_out, 0, 8 * sizeof(uint64_t));
+#ifdef DROPIN_WITH_CUDA_FACTORIES
+  if (cuda_factory) {
+    const pusch_decoder_cuda_aggregator_stats as = get_pusch_decoder_cuda_aggregator_stats(*cuda_factory);
+    agg_out[0] = as.nof_launches, agg_out[1] = as.nof_transport_blocks, agg_out[2] = as.max_transport_blocks_per_launch;
+    agg_out[3] = as.join_wait_ns, agg_out[4] = as.stage_ns, agg_out[5] = as.follow_ns, agg_out[6] = as.drain_ns;
+    agg_out[7] = as.launch_ns;
+  }
+#endif
+  const auto first = *std::min_element(t_begin.begin(), t_begin.end());
+  const auto last  = *std::max_element(t_end.begin(), t_end.end());
+  return std::chrono::duration<double>(last - first).count();
 }
 
 // ---- soft-buffer pool state machine, reference ("sw") or the product's device pool without device memory ("cuda-host") -----

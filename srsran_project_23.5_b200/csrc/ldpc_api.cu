@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <mutex>
 #include <new>
@@ -1181,10 +1182,14 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     }
   }
   CUDA_TRY(cudaSetDevice(h->device));
+  // LDPC_CUDA_TRACE=1: one line per host-entry call on stderr with where its wall-clock time went
+  static const bool trace = std::getenv("LDPC_CUDA_TRACE") != nullptr;
+  const auto t_enter = std::chrono::steady_clock::now();
   int rc = stage_work(h, n, descs, fused);
   if (rc != LDPC_CUDA_OK) {
     return rc;
   }
+  const auto t_staged = std::chrono::steady_clock::now();
   std::vector<Chunk> chunks;
   plan_chunks(h, n, descs, fused, chunks);
   if (chunks.empty() || chunks.size() > MAX_CHUNKS) {
@@ -1395,10 +1400,26 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     CUDA_TRY(cudaMemcpyAsync(tb_results, d_tb_res, sizeof(TbResult) * nof_tbs, cudaMemcpyDeviceToHost, h->d2h_stream));
   }
   CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->d2h_stream));
+  const auto t_enqueued = std::chrono::steady_clock::now();
   CUDA_TRY(cudaStreamSynchronize(h->d2h_stream));
   // everything of this call has finished (the last copy waited for every kernel); later calls may use any stream
   CUDA_TRY(cudaStreamSynchronize(h->stream2));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (trace) {
+    const auto t_done = std::chrono::steady_clock::now();
+    auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::micro>(b - a).count();
+    };
+    size_t runs = 0;
+    for (const Chunk& c : chunks) {
+      runs += c.in_runs.size() + c.out_runs.size();
+    }
+    std::fprintf(stderr,
+                 "ldpc_cuda trace: %u codeblocks, %u transport blocks, %zu chunks (%zu copy runs), in %llu B, preserve %d: "
+                 "work list %.0f us, plan+enqueue %.0f us, wait %.0f us\n",
+                 n, nof_tbs, chunks.size(), runs, (unsigned long long)(in_hi - in_lo), (int)preserve, us(t_enter, t_staged),
+                 us(t_staged, t_enqueued), us(t_enqueued, t_done));
+  }
   return LDPC_CUDA_OK;
 }
 
@@ -1996,6 +2017,55 @@ int ldpc_cuda_arena_create(int device, uint64_t nof_bytes, void** arena_d)
   // zero-initialised once, like the reference pool (rx_softbuffer_codeblock_pool.h)
   CUDA_TRY(cudaMemset(ptr, 0, nof_bytes));
   *arena_d = ptr;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_reserve_staging(ldpc_cuda_handle* h, uint64_t in_bytes, uint64_t out_bytes, uint64_t tb_bytes)
+{
+  if (h == nullptr) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  CUDA_TRY(cudaSetDevice(h->device));
+  CUDA_TRY(cudaDeviceSynchronize());  // the buffers may be in use by earlier asynchronous calls
+  const int rc = ensure_capacity(h, in_bytes, out_bytes);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  const size_t need = (size_t)tb_bytes + sizeof(TbResult) * h->max_cbs + 16;
+  if (tb_bytes != 0 && need > h->d_tb_out_cap) {
+    if (h->d_tb_out) {
+      CUDA_TRY(cudaFree(h->d_tb_out));
+      h->d_tb_out = nullptr, h->d_tb_out_cap = 0;
+    }
+    CUDA_TRY(cudaMalloc(&h->d_tb_out, need));
+    h->d_tb_out_cap = need;
+  }
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_host_alloc(uint64_t nof_bytes, uint32_t flags, void** ptr)
+{
+  if (ptr == nullptr || nof_bytes == 0 || (flags & ~LDPC_CUDA_HOST_WRITE_COMBINED) != 0) {
+    return LDPC_CUDA_ERR_ARG;
+  }
+  *ptr = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return LDPC_CUDA_ERR_CUDA;
+  }
+  void* p = nullptr;
+  CUDA_TRY(cudaHostAlloc(&p, nof_bytes,
+                         cudaHostAllocPortable | ((flags & LDPC_CUDA_HOST_WRITE_COMBINED) ? cudaHostAllocWriteCombined : 0)));
+  *ptr = p;
+  return LDPC_CUDA_OK;
+}
+
+int ldpc_cuda_host_free(void* ptr)
+{
+  if (ptr != nullptr) {
+    CUDA_TRY(cudaFreeHost(ptr));
+  }
   return LDPC_CUDA_OK;
 }
 

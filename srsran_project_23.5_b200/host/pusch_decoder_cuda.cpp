@@ -2,7 +2,9 @@
 #include "pusch_decoder_cuda.h"
 
 #include "../../include/ldpc_cuda.h"
+#include "device_arena_index.h"
 #include "rx_softbuffer_pool_cuda.h"
+#include "slot_aggregator.h"
 #include "srsran/phy/upper/channel_processors/pusch_decoder.h"
 #include "srsran/ran/modulation_scheme.h"
 
@@ -12,14 +14,16 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <unordered_map>
 #include <vector>
 
 using namespace srsran;
+using srsran::cuda_detail::arena_index;
+using srsran::cuda_detail::CB_SLOT_BYTES;
 
 namespace {
 
-constexpr unsigned CB_SLOT_BYTES = 66 * 384; // largest soft buffer of one codeblock (ldpc::MAX_CODEBLOCK_SIZE)
 constexpr unsigned LONG_CRC_BITS = 24;
 
 void check(int status, const char* what)
@@ -38,111 +42,23 @@ void require(bool cond, const char* what)
   }
 }
 
-std::atomic<uint64_t> private_arena_evictions{0};
-
-// Device soft-buffer arena in units of one codeblock slot, keyed by the caller's rx_softbuffer object.
-class arena_index
-{
-public:
-  explicit arena_index(unsigned nof_slots) { free_ranges[0] = nof_slots; }
-
-  struct entry {
-    unsigned first = 0, count = 0;
-    uint64_t last_use = 0;
-  };
-
-  // Returns the entry of key; fresh is set when it had to be (re)allocated - its slots then hold foreign data.
-  entry& get(const void* key, unsigned count, bool& fresh)
-  {
-    ++tick;
-    auto it = table.find(key);
-    if (it != table.end() && it->second.count == count) {
-      it->second.last_use = tick;
-      fresh               = false;
-      return it->second;
-    }
-    if (it != table.end()) {
-      release(it->second);
-      table.erase(it);
-    }
-    unsigned first = 0;
-    while (!allocate(count, first)) {
-      // evict the least recently used HARQ process (equivalent to a soft-buffer expiry)
-      auto victim = table.end();
-      for (auto v = table.begin(); v != table.end(); ++v) {
-        if (victim == table.end() || v->second.last_use < victim->second.last_use) {
-          victim = v;
-        }
-      }
-      require(victim != table.end(), "transport block larger than the device soft-buffer arena");
-      // Not silent: the reference's pool refuses the reservation when it is out of entries (rx_softbuffer_impl.h:141-150);
-      // this private arena instead drops the oldest HARQ process, whose next retransmission combines into zeros.
-      const uint64_t n = private_arena_evictions.fetch_add(1, std::memory_order_relaxed);
-      if (n == 0) {
-        std::fprintf(stderr,
-                     "pusch_decoder_cuda: private soft-buffer arena full, dropping the soft bits of the least recently used "
-                     "HARQ process (further drops are counted only: pusch_decoder_cuda_private_arena_evictions()); raise "
-                     "arena_codeblocks or use create_rx_softbuffer_pool_cuda\n");
-      }
-      release(victim->second);
-      table.erase(victim);
-    }
-    entry& e   = table[key];
-    e.first    = first;
-    e.count    = count;
-    e.last_use = tick;
-    fresh      = true;
-    return e;
-  }
-
-private:
-  bool allocate(unsigned count, unsigned& first)
-  {
-    for (auto it = free_ranges.begin(); it != free_ranges.end(); ++it) {
-      if (it->second >= count) {
-        first              = it->first;
-        const unsigned rem = it->second - count;
-        free_ranges.erase(it);
-        if (rem != 0) {
-          free_ranges[first + count] = rem;
-        }
-        return true;
-      }
-    }
-    return false;
-  }
-
-  void release(const entry& e)
-  {
-    auto it = free_ranges.emplace(e.first, e.count).first;
-    auto nx = std::next(it);
-    if (nx != free_ranges.end() && it->first + it->second == nx->first) {
-      it->second += nx->second;
-      free_ranges.erase(nx);
-    }
-    if (it != free_ranges.begin()) {
-      auto pv = std::prev(it);
-      if (pv->first + pv->second == it->first) {
-        pv->second += it->second;
-        free_ranges.erase(it);
-      }
-    }
-  }
-
-  std::unordered_map<const void*, entry> table;
-  std::map<unsigned, unsigned>           free_ranges; // first slot -> number of slots
-  uint64_t                               tick = 0;
-};
-
 class pusch_decoder_cuda : public pusch_decoder
 {
 public:
-  pusch_decoder_cuda(ldpc_cuda_handle* h_, unsigned arena_cbs_, unsigned max_cbs) :
-    h(h_), arena_cbs(arena_cbs_), index(arena_cbs_), descs(max_cbs), results(max_cbs),
-    crc_bits(max_cbs)
+  /// Either its own handle h_ (one launch per decode()), or - h_ == nullptr - the factory's slot aggregator.
+  pusch_decoder_cuda(ldpc_cuda_handle*                             h_,
+                     std::shared_ptr<cuda_detail::slot_aggregator> agg_,
+                     unsigned                                      arena_cbs_,
+                     unsigned                                      max_cbs) :
+    h(h_), agg(std::move(agg_)), arena_cbs(arena_cbs_), index(arena_cbs_), descs(max_cbs), results(max_cbs), crc_bits(max_cbs)
   {
   }
-  ~pusch_decoder_cuda() override { ldpc_cuda_destroy(h); }
+  ~pusch_decoder_cuda() override
+  {
+    if (h != nullptr) {
+      ldpc_cuda_destroy(h);
+    }
+  }
 
   // pusch_decoder interface (pusch_decoder.h:66-74); reference implementation pusch_decoder_impl.cpp:121-225.
   void decode(span<uint8_t>                    transport_block,
@@ -181,7 +97,12 @@ public:
     // decoder's private arena, indexed by the rx_softbuffer object with least-recently-used eviction.
     const auto* dev_sb = dynamic_cast<const rx_softbuffer_device*>(soft_codeword);
     unsigned    first_slot = 0;
-    if (dev_sb != nullptr && dev_sb->arena() != nullptr) {
+    if (dev_sb != nullptr && dev_sb->arena() == nullptr) {
+      dev_sb = nullptr;
+    }
+    if (agg) {
+      // the aggregator attaches the arena (the pool's, or its own private one shared by the factory's decoders)
+    } else if (dev_sb != nullptr) {
       if (attached != dev_sb->arena()) {
         check(ldpc_cuda_softbuffer_attach(h, dev_sb->arena(), dev_sb->arena_bytes()), "ldpc_cuda_softbuffer_attach");
         attached      = dev_sb->arena();
@@ -195,7 +116,6 @@ public:
         private_arena = true;
         index         = arena_index(arena_cbs);
       }
-      dev_sb            = nullptr;
       bool        fresh = false;
       const auto& slot  = index.get(soft_codeword, nof_cbs, fresh);
       first_slot        = slot.first;
@@ -218,28 +138,50 @@ public:
       bit_buffer message = soft_codeword->get_codeblock_data_bits(r, K);
       std::memcpy(&cb_out[d.out_offset], message.get_buffer().data(), kb);
     }
-    if (cfg.nof_ldpc_iterations != iterations) {
-      ldpc_cuda_algorithm alg = {cfg.nof_ldpc_iterations, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
-      check(ldpc_cuda_set_algorithm(h, &alg), "ldpc_cuda_set_algorithm");
-      iterations = cfg.nof_ldpc_iterations;
-    }
     // One call: rate dematch + combine + decode + codeblock CRCs, then - still on the device - the transport block
     // assembly, its CRC24A and the verdict (pusch_decoder_impl.cpp:156-222).
     const unsigned tb_and_crc_size = tb_size + (nof_cbs > 1 ? LONG_CRC_BITS : 0);
     ldpc_cuda_tb_desc tbd = {0, nof_cbs, tb_size, crc_bits[0], 0};
     ldpc_cuda_tb_result tbr = {};
     tb_tmp.assign((tb_and_crc_size + 7) / 8, 0);
-    check(ldpc_cuda_dematch_decode_tb_batch(h,
-                                            nof_cbs,
-                                            descs.data(),
-                                            reinterpret_cast<const int8_t*>(llrs.data()),
-                                            cb_out.data(),
-                                            results.data(),
-                                            1,
-                                            &tbd,
-                                            tb_tmp.data(),
-                                            &tbr),
-          "ldpc_cuda_dematch_decode_tb_batch");
+    if (agg) {
+      // ... issued by the slot aggregator together with the transport blocks of the decoders that are in decode() now
+      cuda_detail::slot_request rq;
+      rq.nof_cbs          = nof_cbs;
+      rq.descs            = descs.data();
+      rq.llrs             = reinterpret_cast<const int8_t*>(llrs.data());
+      rq.nof_llrs         = descs[nof_cbs - 1].in_offset + descs[nof_cbs - 1].rm_length;
+      rq.cb_out           = cb_out.data();
+      rq.cb_out_bytes     = cb_out.size();
+      rq.results          = results.data();
+      rq.tbd              = tbd;
+      rq.tb_out           = tb_tmp.data();
+      rq.tb_out_bytes     = tb_tmp.size();
+      rq.tbr              = &tbr;
+      rq.iterations       = cfg.nof_ldpc_iterations;
+      rq.new_data         = cfg.new_data;
+      rq.softbuffer_key   = soft_codeword;
+      rq.pool_arena       = dev_sb ? dev_sb->arena() : nullptr;
+      rq.pool_arena_bytes = dev_sb ? dev_sb->arena_bytes() : 0;
+      agg->decode(rq);
+    } else {
+      if (cfg.nof_ldpc_iterations != iterations) {
+        ldpc_cuda_algorithm alg = {cfg.nof_ldpc_iterations, 0.8f, LDPC_CUDA_SCALE_GENERIC, 0};
+        check(ldpc_cuda_set_algorithm(h, &alg), "ldpc_cuda_set_algorithm");
+        iterations = cfg.nof_ldpc_iterations;
+      }
+      check(ldpc_cuda_dematch_decode_tb_batch(h,
+                                              nof_cbs,
+                                              descs.data(),
+                                              reinterpret_cast<const int8_t*>(llrs.data()),
+                                              cb_out.data(),
+                                              results.data(),
+                                              1,
+                                              &tbd,
+                                              tb_tmp.data(),
+                                              &tbr),
+            "ldpc_cuda_dematch_decode_tb_batch");
+    }
 
     // codeblock bookkeeping of the soft buffer (pusch_decoder_impl.cpp:179-195): messages and CRC flags
     stats.nof_codeblocks_total = nof_cbs;
@@ -276,7 +218,8 @@ public:
   }
 
 private:
-  ldpc_cuda_handle*                h;
+  ldpc_cuda_handle*                             h;
+  std::shared_ptr<cuda_detail::slot_aggregator> agg;
   unsigned                         arena_cbs;
   arena_index                      index;
   const void*                      attached      = nullptr; // arena of a rx_softbuffer_pool_cuda in use
@@ -296,16 +239,35 @@ public:
 
   std::unique_ptr<pusch_decoder> create() override
   {
+    // the transport block CRC24A is computed on the device: cfg.crc_factory is not used by this decoder
+    if (cfg.aggregate_codeblocks != 0) {
+      std::lock_guard<std::mutex> lk(m);
+      if (!agg) {
+        agg = cuda_detail::slot_aggregator::create(cfg.device, std::max(cfg.aggregate_codeblocks, cfg.max_codeblocks_per_tb),
+                                                   cfg.arena_codeblocks, cfg.aggregate_blocks);
+      }
+      if (!agg) {
+        return nullptr;
+      }
+      return std::make_unique<pusch_decoder_cuda>(nullptr, agg, cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
+    }
     ldpc_cuda_handle* h = nullptr;
     if (ldpc_cuda_create(&h, cfg.device, cfg.max_codeblocks_per_tb, 0) != LDPC_CUDA_OK) {
       return nullptr;
     }
-    // the transport block CRC24A is computed on the device: cfg.crc_factory is not used by this decoder
-    return std::make_unique<pusch_decoder_cuda>(h, cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
+    return std::make_unique<pusch_decoder_cuda>(h, nullptr, cfg.arena_codeblocks, cfg.max_codeblocks_per_tb);
+  }
+
+  cuda_detail::slot_aggregator_stats aggregator_stats()
+  {
+    std::lock_guard<std::mutex> lk(m);
+    return agg ? agg->stats() : cuda_detail::slot_aggregator_stats();
   }
 
 private:
-  pusch_decoder_cuda_configuration cfg;
+  pusch_decoder_cuda_configuration              cfg;
+  std::mutex                                    m;
+  std::shared_ptr<cuda_detail::slot_aggregator> agg;
 };
 
 } // namespace
@@ -320,7 +282,21 @@ srsran::create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration
   return std::make_shared<pusch_decoder_factory_cuda>(config);
 }
 
+pusch_decoder_cuda_aggregator_stats srsran::get_pusch_decoder_cuda_aggregator_stats(pusch_decoder_factory& factory)
+{
+  pusch_decoder_cuda_aggregator_stats out = {};
+  if (auto* f = dynamic_cast<pusch_decoder_factory_cuda*>(&factory)) {
+    const cuda_detail::slot_aggregator_stats s = f->aggregator_stats();
+    out.nof_launches                           = s.nof_launches;
+    out.nof_transport_blocks                   = s.nof_transport_blocks;
+    out.max_transport_blocks_per_launch        = s.max_tbs_per_launch;
+    out.join_wait_ns = s.join_wait_ns, out.stage_ns = s.stage_ns, out.follow_ns = s.follow_ns, out.drain_ns = s.drain_ns;
+    out.launch_ns = s.launch_ns;
+  }
+  return out;
+}
+
 uint64_t srsran::pusch_decoder_cuda_private_arena_evictions()
 {
-  return private_arena_evictions.load(std::memory_order_relaxed);
+  return cuda_detail::private_arena_evictions().load(std::memory_order_relaxed);
 }

@@ -32,10 +32,29 @@ struct pusch_decoder_cuda_configuration {
   unsigned arena_codeblocks = 4096;
   /// Largest number of codeblocks of one transport block.
   unsigned max_codeblocks_per_tb = 256;
+  /// 0: every decoder owns a device handle and launches its transport block alone. > 0: the decoders of this factory
+  /// share a SLOT AGGREGATOR (slot_aggregator.h): transport blocks of decoder threads that are inside decode() at the same
+  /// time - the reference runs one PUSCH per executor thread, uplink_processor_impl.cpp:155-171 - are staged into one
+  /// page-locked block by their own threads and launched together, up to this many codeblocks per launch. decode() stays
+  /// synchronous for every caller.
+  unsigned aggregate_codeblocks = 0;
+  /// Staging blocks of the aggregator: 2 = one launch in flight while the next batch collects, 3 = two in flight.
+  unsigned aggregate_blocks = 3;
 };
 
 /// Returns nullptr when no usable device exists (no CPU fallback), like the reference's factories for an unsupported type.
 std::shared_ptr<pusch_decoder_factory> create_pusch_decoder_factory_cuda(const pusch_decoder_cuda_configuration& config);
+
+/// What the slot aggregator of a factory has done so far (all zero for a factory without one).
+struct pusch_decoder_cuda_aggregator_stats {
+  uint64_t nof_launches;
+  uint64_t nof_transport_blocks;
+  uint64_t max_transport_blocks_per_launch;
+  /// Nanoseconds summed over all transport blocks: waiting for a staging block, copying in, from staged until done,
+  /// copying out; launch_ns is summed over the launches (time inside the batched C-ABI call).
+  uint64_t join_wait_ns, stage_ns, follow_ns, drain_ns, launch_ns;
+};
+pusch_decoder_cuda_aggregator_stats get_pusch_decoder_cuda_aggregator_stats(pusch_decoder_factory& factory);
 
 /// HARQ processes whose device soft bits were dropped because a decoder's PRIVATE arena (used with the reference's host
 /// pool) was full, since the process started. With create_rx_softbuffer_pool_cuda nothing is ever dropped: reservations are

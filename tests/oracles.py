@@ -210,6 +210,9 @@ class RefOracle:
         L.ref_pusch_destroy.argtypes = [c_void_p]
         L.ref_pusch_decode.argtypes = [c_void_p, c_uint, c_uint, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_int,
                                        c_int, c_int, c_uint, c_uint, c_uint, c_int, c_int, c_int, c_void_p]
+        L.ref_pusch_concurrent.restype = c_double
+        L.ref_pusch_concurrent.argtypes = [c_char_p, c_char_p, c_uint, c_uint, c_uint, c_uint, c_void_p, c_uint, c_int, c_int,
+                                           c_uint, c_uint, c_int, c_uint, c_uint, c_void_p, c_void_p, c_void_p]
         L.ref_demodulate_soft.argtypes = [c_int, c_int, c_uint, c_void_p, c_void_p, c_void_p, c_uint]
         L.ref_ulsch_demultiplex.argtypes = [c_void_p, c_void_p, c_uint, c_void_p, c_uint, c_void_p, c_uint, c_void_p, c_uint,
                                             c_void_p, c_uint]
@@ -224,6 +227,23 @@ class RefOracle:
                                                          c_void_p]
         self._decoders = {}
         self._dematchers = {}
+
+    def pusch_concurrent(self, decoder_type, pool_type, llrs, tb_bytes, bg, Qm, nof_layers, max_iters=6, early_stop=True,
+                         aggregate_blocks=3, warm_reps=0):
+        """K pusch_decoder objects of one factory on K threads sharing one soft-buffer pool (uplink_processor_impl.cpp:
+        155-171). llrs: int8 [K][reps][nof_tx][nof_llrs]. Returns (seconds, tb_out [K][reps][tb_bytes], stats
+        [K][reps][nof_tx][6], (launches, transport blocks, max per launch, then join-wait / stage / follow / drain / launch ns) of the
+        product's slot aggregator)."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        K, reps, nof_tx, nof_llrs = llrs.shape
+        tb_out = np.zeros((K, reps, tb_bytes), np.uint8)
+        stats = np.zeros((K, reps, nof_tx, 6), np.uint32)
+        agg = np.zeros(8, np.uint64)
+        secs = self.lib.ref_pusch_concurrent(decoder_type.encode(), pool_type.encode(), K, reps, nof_tx, tb_bytes, _ptr(llrs),
+                                             nof_llrs, bg, Qm, nof_layers, max_iters, int(early_stop), aggregate_blocks,
+                                             warm_reps, _ptr(tb_out), _ptr(stats), _ptr(agg))
+        assert secs >= 0, "ref_pusch_concurrent(%s, %s) failed: %g" % (decoder_type, pool_type, secs)
+        return secs, tb_out, stats, tuple(int(x) for x in agg)
 
     def demodulate_soft(self, mod_order, symbols, noise_vars, pi2=False, batch=0):
         """demodulation_mapper_impl::demodulate_soft; batch > 0 feeds `batch` symbols per call (below the AVX2 width: the

@@ -269,3 +269,50 @@ def test_ulsch_demultiplex_interface(lib):
         with_pl += wpl.size > 0
         checked += 1
     assert checked > 60 and with_pl > 5
+
+
+def _concurrent_llrs(lib, rng, K, reps, nof_tx, bg, tbs_bytes, Qm, nsym, esn0_first, esn0_more):
+    """[K][reps][nof_tx][nsym * Qm] LLRs: every (thread, repetition) its own transport block, transmissions rv 0, 2, ..."""
+    meta = lib.segment_rx(tbs_bytes * 8, bg, Qm, 1, nsym)
+    llrs = np.zeros((K, reps, nof_tx, nsym * Qm), np.int8)
+    tbs = np.zeros((K, reps, tbs_bytes), np.uint8)
+    for k in range(K):
+        for rep in range(reps):
+            tb = rng.integers(0, 256, tbs_bytes).astype(np.uint8)
+            tbs[k, rep] = tb
+            segs = lib.segment_tx(tb, bg, Qm, 1, nsym)
+            cws = [lib.encode(bg, int(meta[c, 0]), segs[c, :O.BG_K[bg] * int(meta[c, 0])]) for c in range(len(segs))]
+            for t, rv in enumerate([0, 2, 3, 1][:nof_tx]):
+                parts = [lib.rate_match(cws[c], int(meta[c, 2]), bg, int(meta[c, 0]), rv, Qm, 0, int(meta[c, 3]))
+                         for c in range(len(segs))]
+                # every third block starts below its threshold and needs the retransmission
+                esn0 = (esn0_first - 3.0 if (k + rep) % 3 == 0 else esn0_first) if t == 0 else esn0_more
+                llrs[k, rep, t] = O.awgn_llrs(rng, np.concatenate(parts), esn0)
+    return llrs, tbs
+
+
+@pytest.mark.parametrize("K", [1, 4, 16])
+@pytest.mark.parametrize("pool", ["sw", "cuda-pool"], ids=["ref-pool", "device-pool"])
+def test_slot_aggregator_concurrent_callers_match_reference(lib, K, pool):
+    """K pusch_decoder objects of one factory on K threads (the reference runs one PUSCH per executor thread,
+    uplink_processor_impl.cpp:155-171), sharing one soft-buffer pool, each decoding its own transport blocks with a
+    retransmission where the first transmission fails: the product's decoders behind the slot aggregator
+    (host/slot_aggregator.h - transport blocks that are in decode() at the same time share one launch) against the
+    reference's pusch_decoder_impl on K threads. Transport block bytes, tb_crc_ok and the iteration statistics of every
+    call are equal; with K > 1 the aggregator really merged calls."""
+    rng = np.random.default_rng(40 + K)
+    bg, tbs_bytes, Qm, nsym = 1, 4001, 4, 12000
+    reps = 6 if K > 1 else 4
+    llrs, tbs = _concurrent_llrs(lib, rng, K, reps, 2, bg, tbs_bytes, Qm, nsym, -1.0, 1.0)
+    _, want_tb, want_st, _ = lib.pusch_concurrent("generic", "sw", llrs, tbs_bytes, bg, Qm, 1)
+    for blocks in (2, 3):
+        _, got_tb, got_st, agg = lib.pusch_concurrent("cuda-aggregated", pool, llrs, tbs_bytes, bg, Qm, 1,
+                                                      aggregate_blocks=blocks)
+        assert (got_st == want_st).all(), np.argwhere(got_st != want_st)[:5]
+        ok = want_st[:, :, :, 0].max(axis=2) == 1
+        assert ok.all() and (want_st[:, :, 0, 0] == 0).any()      # every block got through, some only when retransmitted
+        assert (got_tb == want_tb).all() and (got_tb == tbs).all()
+        calls = int((want_st[:, :, :, 1] != 0xffffffff).sum())
+        assert agg[1] == calls and agg[0] <= calls
+        if K >= 4:
+            assert agg[2] >= 2 and agg[0] < calls, agg            # calls were merged into shared launches
