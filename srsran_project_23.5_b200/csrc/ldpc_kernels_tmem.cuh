@@ -46,7 +46,7 @@
 
 namespace ldpc_b200 {
 
-enum { TM_SCALE_NONE = 0, TM_SCALE_GENERIC_08 = 1, TM_SCALE_AVX_08 = 2 };
+enum { TM_SCALE_NONE = 0, TM_SCALE_GENERIC_08 = 1, TM_SCALE_AVX_08 = 2, TM_SCALE_LUT = 3 };
 
 constexpr int TM_THREADS = 384;       // threads per block at full occupancy of the TMEM lanes (12 warps)
 constexpr int TM_COLS_PER_WARP = 170; // 512 TMEM columns / 3 warps per lane quadrant
@@ -82,6 +82,7 @@ struct TmemParams {
   unsigned rowdesc[LDPC_BG1_M + 2];    // per row: rowcls | rowedge << 8 | rowtm << 20 (one uniform load per row)
   unsigned pairdesc[LDPC_BG1_M + 2];   // per row r: 0, or the descriptor of the pair (r, r + 1) that starts at r (pair_dispatch)
   unsigned short tm_words;             // TMEM words used per thread
+  unsigned char scale_lut[LLR_MAX + 1 + 3];  // TM_SCALE_LUT: scaled magnitude for m in [0, 120] (any factor, any rounding mode)
   TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
 };
 
@@ -234,11 +235,19 @@ constexpr float TM_CAP = 65280.f;      // 544 * 120
 //               0.2 / 544 moves m / 5 by less than 0.012, and one FMA rounding against the magic constant is exact)
 //  AVX     0.8: (m * 52428) >> 16 = m - floor(m / 5) - [m > 0], floor(m / 5) = round((m - 2) / 5)
 // The magic constant 1536 keeps the sum in [1024, 2048) where the fp16 ulp is 1.
+//  LUT     any other table (scaling factor != 0.8, the NEON variant's rounding): m = M / 544 read off the mantissa of
+//          fma(M, 1/544, 1024) = 1024 + m (ulp 1), one 16-bit shared-memory load per half of 544 * lut[m] as fp16 bits
 template <int SCALE>
-__device__ __forceinline__ unsigned scale_q(unsigned M)
+__device__ __forceinline__ unsigned scale_q(unsigned M, unsigned lut = 0)
 {
   const unsigned magic = hc(1536.f), fifth = hc(0.2f / TM_S), nS = hc(-TM_S);
-  if (SCALE == TM_SCALE_GENERIC_08) {
+  if (SCALE == TM_SCALE_LUT) {
+    const unsigned idx = hfma(M, hc(1.f / TM_S), hc(1024.f));
+    unsigned qa, qb;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(qa) : "r"(lut + 2u * (idx & 0x3ffu)));
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(qb) : "r"(lut + 2u * ((idx >> 16) & 0x3ffu)));
+    return qa | (qb << 16);
+  } else if (SCALE == TM_SCALE_GENERIC_08) {
     const unsigned r = hsub(hfma(M, fifth, magic), magic);
     return hfma(r, nS, M);
   } else {
@@ -288,6 +297,7 @@ struct Ctx {
   unsigned Z4;
   unsigned zpad4;
   unsigned tm_addr;    // TMEM address of this warp's column block (lane base in the upper half)
+  unsigned lut;        // TM_SCALE_LUT: shared address of the scaling table (fp16 bit patterns of 544 * lut[m])
   bool active;         // lane < Z
 };
 
@@ -370,7 +380,7 @@ struct Row {
     }
     const unsigned T = S & SIGN2;
     // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
-    const unsigned Q1 = scale_q<SCALE>(mm.m1), Q2 = scale_q<SCALE>(mm.m2);
+    const unsigned Q1 = scale_q<SCALE>(mm.m1, c.lut), Q2 = scale_q<SCALE>(mm.m2, c.lut);
     const unsigned Q2s = Q2 ^ T;
     const unsigned nD = hsub(Q1, Q2) ^ T;
     const unsigned nM1 = mm.m1 ^ SIGN2;
@@ -578,6 +588,9 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
+  if (SCALE == TM_SCALE_LUT && tid <= LLR_MAX) {  // the first 3 KB of shared memory are free for it
+    reinterpret_cast<unsigned short*>(smem)[tid] = __half_as_ushort(__float2half_rn(tm::TM_S * (float)p.scale_lut[tid]));
+  }
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;");
@@ -597,6 +610,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   c.zpad4 = 4u * (unsigned)zpad;
   const unsigned tmem_base = *reinterpret_cast<volatile unsigned*>(smem + 3 * 256 * 4);
   c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * TM_COLS_PER_WARP;
+  c.lut = (unsigned)__cvta_generic_to_shared(smem);
   c.active = FULL || t < Z;
 
   // FUSED: the pair after the current one is claimed one pair early so that its rate-matched LLRs (and previous soft
@@ -1026,7 +1040,12 @@ static inline int tm_scale_variant(const unsigned char* lut)
     gen = gen && (lut[m] == m - r5);
     avx = avx && (lut[m] == m - m / 5 - (m > 0 ? 1 : 0));
   }
-  return gen ? TM_SCALE_GENERIC_08 : (avx ? TM_SCALE_AVX_08 : TM_SCALE_NONE);
+  // any other table with lut[m] <= m (a scaling factor below 1): table look-up inside the same kernel
+  bool shrinking = true;
+  for (int m = 0; m <= LLR_MAX; ++m) {
+    shrinking = shrinking && lut[m] <= m;
+  }
+  return gen ? TM_SCALE_GENERIC_08 : (avx ? TM_SCALE_AVX_08 : (shrinking ? TM_SCALE_LUT : TM_SCALE_NONE));
 }
 
 template <int SCALE>
@@ -1042,6 +1061,9 @@ __global__ void tm_scale_selfcheck_kernel(unsigned char* out)
 // Runs the fp16 closed form for every magnitude on the device and compares with the host table. 0 = identical.
 static inline int tm_scale_selfcheck(int variant, const unsigned char* lut, cudaStream_t stream)
 {
+  if (variant == TM_SCALE_LUT) {
+    return 0;  // a table look-up of the very table: nothing to prove
+  }
   unsigned char* d = nullptr;
   unsigned char h[LLR_MAX + 1];
   if (cudaMalloc(&d, LLR_MAX + 1) != cudaSuccess) {
@@ -1203,6 +1225,11 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   const unsigned grid = std::min<unsigned>((n_pairs + p.groups - 1) / p.groups, (unsigned)sm_count);
   if (cudaMemsetAsync(d_pair_counter, 0, sizeof(unsigned), stream) != cudaSuccess) {
     return -1;
+  }
+  if (scale_variant == TM_SCALE_LUT) {
+    std::memcpy(p.scale_lut, gp.scale_lut, LLR_MAX + 1);
+    return gp.bg == 1 ? tm_launch_fused_or_not<1, TM_SCALE_LUT>(fused, p, smem, grid, device, stream)
+                      : tm_launch_fused_or_not<2, TM_SCALE_LUT>(fused, p, smem, grid, device, stream);
   }
   const bool gen = scale_variant == TM_SCALE_GENERIC_08;
   if (gp.bg == 1) {

@@ -121,6 +121,39 @@ def test_decode_avx_and_neon_scaling_modes(dec):
     dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
 
 
+@pytest.mark.parametrize("sf,mode", [(0.5, O.SCALE_GENERIC), (0.75, O.SCALE_GENERIC), (0.9, O.SCALE_AVX), (0.95, O.SCALE_NEON),
+                                     (0.7, O.SCALE_NEON), (0.8, O.SCALE_NEON)])
+def test_decode_other_scaling_factors(dec, sf, mode):
+    """ldpc_decoder::configuration::algorithm_details::scaling_factor other than the default 0.8, and the NEON variant's
+    rounding (ldpc_decoder_neon.cpp scale): the fast kernel takes the scaled magnitude from a 121-entry table
+    (TM_SCALE_LUT) instead of its closed forms for 0.8; batches of pairs, every CRC mode, bit-exact with the oracle."""
+    rng = np.random.default_rng(int(sf * 100) + mode)
+    for bg, Z, esn0 in [(1, 384, -1.3), (2, 384, -4.0), (1, 208, -1.0), (2, 36, -3.0), (1, 7, 0.0)]:
+        dec.set_algorithm(6, sf, mode)
+        n = 6
+        K, N = O.BG_K[bg] * Z, O.BG_N_SHORT[bg] * Z
+        llrs = np.zeros((n, N), np.int8)
+        descs = pkg.make_descs(n, bg, Z, crc_poly=O.CRC24B if K > 64 else O.CRC16)
+        for i in range(n):
+            crc = int(descs[i]["crc_poly"])
+            msg, cw = O.make_codeword(rng, bg, Z, 0, crc)
+            llrs[i] = O.awgn_llrs(rng, cw, esn0 + 0.3 * i)
+            descs[i]["early_stop"] = i % 2
+        out, res = dec.decode_batch(descs, llrs.reshape(-1))
+        kb = (K + 7) // 8
+        for i in range(n):
+            crc = int(descs[i]["crc_poly"])
+            if i % 2:
+                bits, it = O.port().decode(bg, Z, llrs[i], crc=crc, max_iters=6, sf=sf, scale_mode=mode)
+                ok, iters = it > 0, (it if it else 6)
+            else:
+                bits, _ = O.port().decode(bg, Z, llrs[i], crc=O.CRC_NONE, max_iters=6, sf=sf, scale_mode=mode)
+                ok, iters = O.port().crc(crc, bits, K) == 0, 6
+            assert bool(res["crc_ok"][i]) == ok and int(res["iterations"][i]) == iters, (bg, Z, i, res[i], ok, iters)
+            assert (out[i * kb:(i + 1) * kb] == bits).all(), (bg, Z, i)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+
+
 def test_invalid_arguments_return_status(dec):
     llr = np.zeros(66 * 384, np.int8)
     with pytest.raises(pkg.LdpcCudaError):

@@ -20,7 +20,8 @@ def main():
     pkg = ge.load_package()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
-    dec = pkg.LdpcCuda(device=0, max_codeblocks=1 << 17, max_iterations=6)
+    sf = float(os.environ.get("LDPC_SWEEP_SF", "0.8"))  # != 0.8: the table-driven scaling of the fast kernel
+    dec = pkg.LdpcCuda(device=0, max_codeblocks=1 << 17, max_iterations=6, scaling_factor=sf)
     stream = torch.cuda.ExternalStream(dec.stream, device=dev)
     print("| BG | Z | codeblocks | info bits / CB | ms | decoded info Gb/s | EMU/s (1e12) |")
     print("|---|---|---|---|---|---|---|")
