@@ -699,7 +699,8 @@ def run_ours(args):
             # what the reference's spans are: ordinary (pageable) memory - the copies go through the driver's staging
             llr_pg, out_pg = np.array(llr_h.numpy()), np.zeros((n_cb, OUT_BYTES), np.uint8)
             e2e["pageable"] = {"value": timed_host(dec, llr_pg, out_pg, 2), "unit": "Gb/s",
-                               "host_memory": "pageable numpy arrays (no cudaHostRegister)"}
+                               "host_memory": "pageable numpy arrays (no cudaHostRegister): the host entry stages them through its own "
+                                              "page-locked bounce buffers (csrc/ldpc_host_stager.h)"}
             del llr_pg, out_pg
 
     hbm_peak, sm_max_mhz, peak_src = peaks()

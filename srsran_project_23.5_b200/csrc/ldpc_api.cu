@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "ldpc_host_util.h"
+#include "ldpc_host_stager.h"
 #include "ldpc_kernels_scalar.cuh"
 #include "ldpc_dematch.cuh"
 #include "ldpc_kernels_tmem.cuh"  // needs c_crc / crc_warp from the scalar header
@@ -84,6 +85,11 @@ struct ldpc_cuda_handle {
   unsigned demod_slot = 0;
   std::vector<uint32_t> order;
   std::vector<uint32_t> group_begin;
+  // pageable caller buffers of the host entries: bounce buffers + copy workers (created on first use), and a page-locked
+  // mirror of the output range
+  HostStager* stager = nullptr;
+  uint8_t* out_mirror = nullptr;
+  size_t out_mirror_cap = 0;
 };
 
 namespace {
@@ -869,6 +875,8 @@ void ldpc_cuda_destroy(ldpc_cuda_handle* h)
   if (h->ev_misc) {
     cudaEventDestroy(h->ev_misc);
   }
+  delete h->stager;
+  cudaFreeHost(h->out_mirror);
   cudaFree(h->d_results);
   cudaFree(h->d_in);
   cudaFree(h->d_out);
@@ -1213,6 +1221,66 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
   }
   const int8_t* d_in0 = h->d_in - in_lo;   // device address of host input byte 0
   uint8_t* d_out0 = h->d_out - out_lo;     // device address of host output byte 0
+  // Pageable caller memory (what the reference's callers have): inputs go through the handle's page-locked bounce buffers,
+  // filled by a few threads with non-temporal stores while the copy engine drains the previous piece
+  // (ldpc_host_stager.h); outputs land in a page-locked mirror that is copied to the caller's buffer once at the end.
+  // A pageable cudaMemcpyAsync would instead run at the driver's bounce-buffer speed on this thread and stall the
+  // pipeline of chunks at every copy.
+  const bool stage_in = !(h->flags & LDPC_CUDA_FLAG_COPY_ONLY) && is_pageable(in + in_lo);
+  const bool stage_out = !keep_messages && !(h->flags & LDPC_CUDA_FLAG_COPY_ONLY) && (out_hi - out_lo) <= (1ull << 30) &&
+                         is_pageable(out + out_lo);
+  if ((stage_in || stage_out) && h->stager == nullptr) {
+    h->stager = new (std::nothrow) HostStager;
+    if (h->stager == nullptr) {
+      return LDPC_CUDA_ERR_CUDA;
+    }
+  }
+  if (stage_out && out_hi - out_lo > h->out_mirror_cap) {
+    cudaFreeHost(h->out_mirror);
+    h->out_mirror = nullptr, h->out_mirror_cap = 0;
+    const size_t want = (size_t)(out_hi - out_lo) + ((out_hi - out_lo) >> 3) + 4096;
+    CUDA_TRY(cudaHostAlloc(&h->out_mirror, want, cudaHostAllocPortable));
+    h->out_mirror_cap = want;
+  }
+  uint8_t* const out_h = stage_out ? h->out_mirror - out_lo : out;  // where device -> host copies of messages land
+  std::vector<std::pair<uint64_t, uint64_t>> mirrored;              // output pieces to hand on to the caller at the end
+  constexpr uint64_t STAGE_PIECE = 16ull << 20;
+  // host bytes [lo, lo + len) of the input -> their place in the device staging
+  auto copy_in = [&](uint64_t lo, uint64_t len) -> cudaError_t {
+    if (!stage_in || len < (256u << 10)) {
+      return cudaMemcpyAsync(h->d_in + (lo - in_lo), in + lo, len, cudaMemcpyHostToDevice, h->h2d_stream);
+    }
+    for (uint64_t o = 0; o < len; o += STAGE_PIECE) {
+      const uint64_t piece = std::min(STAGE_PIECE, len - o);
+      unsigned slot = 0;
+      void* b = h->stager->acquire(piece, slot);
+      if (b == nullptr) {
+        return cudaErrorMemoryAllocation;
+      }
+      h->stager->copy(b, in + lo + o, piece);
+      cudaError_t e = cudaMemcpyAsync(h->d_in + (lo + o - in_lo), b, piece, cudaMemcpyHostToDevice, h->h2d_stream);
+      if (e == cudaSuccess) {
+        e = h->stager->release(slot, h->h2d_stream);
+      }
+      if (e != cudaSuccess) {
+        return e;
+      }
+    }
+    return cudaSuccess;
+  };
+  // the caller's messages (bits a decode does not write must survive) -> device; through the mirror when pageable
+  auto copy_preserved = [&](uint64_t lo, uint64_t len) -> cudaError_t {
+    if (stage_out) {
+      h->stager->copy(out_h + lo, out + lo, len);
+    }
+    return cudaMemcpyAsync(h->d_out + (lo - out_lo), out_h + lo, len, cudaMemcpyHostToDevice, h->h2d_stream);
+  };
+  auto copy_out = [&](uint64_t lo, uint64_t len) -> cudaError_t {
+    if (stage_out) {
+      mirrored.push_back({lo, lo + len});
+    }
+    return cudaMemcpyAsync(out_h + lo, h->d_out + (lo - out_lo), len, cudaMemcpyDeviceToHost, h->d2h_stream);
+  };
   // work list upload + result reset on the main stream come first; the copy streams start behind earlier work
   CUDA_TRY(cudaMemsetAsync(h->d_results, 0, sizeof(CbResult) * n, h->stream));
   if (keep_messages) {
@@ -1318,13 +1386,11 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
                          h->h2d_stream));
     } else if (c.in_runs.empty()) {
       if (c.in_hi > c.in_lo) {
-        CUDA_TRY(cudaMemcpyAsync(h->d_in + (c.in_lo - in_lo), in + c.in_lo, c.in_hi - c.in_lo, cudaMemcpyHostToDevice,
-                                 h->h2d_stream));
+        CUDA_TRY(copy_in(c.in_lo, c.in_hi - c.in_lo));
       }
     } else {
       for (const auto& run : c.in_runs) {
-        CUDA_TRY(cudaMemcpyAsync(h->d_in + (run.first - in_lo), in + run.first, run.second - run.first,
-                                 cudaMemcpyHostToDevice, h->h2d_stream));
+        CUDA_TRY(copy_in(run.first, run.second - run.first));
       }
     }
     if (preserve) {
@@ -1334,12 +1400,10 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
                            cudaMemcpyHostToDevice, h->h2d_stream));
       } else if (!c.out_runs.empty()) {
         for (const auto& run : c.out_runs) {
-          CUDA_TRY(cudaMemcpyAsync(h->d_out + (run.first - out_lo), out + run.first, run.second - run.first,
-                                   cudaMemcpyHostToDevice, h->h2d_stream));
+          CUDA_TRY(copy_preserved(run.first, run.second - run.first));
         }
       } else {
-        CUDA_TRY(cudaMemcpyAsync(h->d_out + (c.out_lo - out_lo), out + c.out_lo, c.out_hi - c.out_lo,
-                                 cudaMemcpyHostToDevice, h->h2d_stream));
+        CUDA_TRY(copy_preserved(c.out_lo, c.out_hi - c.out_lo));
       }
     }
     CUDA_TRY(cudaEventRecord(h->ev_in[ci], h->h2d_stream));
@@ -1369,12 +1433,10 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
                            cudaMemcpyDeviceToHost, h->d2h_stream));
       } else if (!c.out_runs.empty()) {
         for (const auto& run : c.out_runs) {
-          CUDA_TRY(cudaMemcpyAsync(out + run.first, h->d_out + (run.first - out_lo), run.second - run.first,
-                                   cudaMemcpyDeviceToHost, h->d2h_stream));
+          CUDA_TRY(copy_out(run.first, run.second - run.first));
         }
       } else {
-        CUDA_TRY(cudaMemcpyAsync(out + c.out_lo, h->d_out + (c.out_lo - out_lo), c.out_hi - c.out_lo,
-                                 cudaMemcpyDeviceToHost, h->d2h_stream));
+        CUDA_TRY(copy_out(c.out_lo, c.out_hi - c.out_lo));
       }
     }
     if (!tb_ready.empty() && ci + 1 != chunks.size()) {
@@ -1405,6 +1467,9 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
   // everything of this call has finished (the last copy waited for every kernel); later calls may use any stream
   CUDA_TRY(cudaStreamSynchronize(h->stream2));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  for (const auto& piece : mirrored) {
+    h->stager->copy(out + piece.first, out_h + piece.first, piece.second - piece.first);
+  }
   if (trace) {
     const auto t_done = std::chrono::steady_clock::now();
     auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
