@@ -379,8 +379,8 @@ int launch_dematch_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_wor
   return LDPC_CUDA_OK;
 }
 
-// Fills the pinned work array in group order and uploads it. fused: in_offset = soft_offset, in_length = N.
-int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused)
+// Checks every descriptor of a call and sorts the codeblocks into (BG, Z) groups (h->order, h->group_begin).
+int validate_and_group(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused)
 {
   if (n > h->max_cbs) {
     return LDPC_CUDA_ERR_CAPACITY;
@@ -400,15 +400,17 @@ int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
     }
   }
   group_codeblocks(h, n, descs);
-  // The pinned work array of this slot was last read by the upload of the call before the previous one.
-  const unsigned slot = (h->work_slot++) & 1u;
-  CUDA_TRY(cudaEventSynchronize(h->ev_work[slot]));
+  return LDPC_CUDA_OK;
+}
+
+// Work records [b, e) in launch order into the pinned array of `slot`. fused: in_offset = soft_offset, in_length = N.
+void fill_work(ldpc_cuda_handle* h, unsigned slot, uint32_t b, uint32_t e, const ldpc_cuda_cb_desc* descs, bool fused)
+{
   CbWork* h_work = h->h_work[slot];
-  for (uint32_t k = 0; k != n; ++k) {
+  for (uint32_t k = b; k != e; ++k) {
     const uint32_t i = h->order[k];
     const ldpc_cuda_cb_desc& d = descs[i];
-    CbWork& w = h_work[k];
-    std::memset(&w, 0, sizeof(w));
+    CbWork w = {};
     w.in_offset = fused ? d.soft_offset : d.in_offset;
     w.out_offset = d.out_offset;
     w.rm_offset = d.in_offset;
@@ -423,8 +425,32 @@ int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, 
     w.new_data = d.new_data;
     w.skip_decode = fused ? d.skip_decode : 0;
     w.result_index = i;
+    h_work[k] = w;
   }
-  CUDA_TRY(cudaMemcpyAsync(h->d_work, h_work, sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
+}
+
+// The pinned work array of the next slot, free again: it was last read by the upload of the call before the previous one.
+int next_work_slot(ldpc_cuda_handle* h, unsigned& slot)
+{
+  slot = (h->work_slot++) & 1u;
+  CUDA_TRY(cudaEventSynchronize(h->ev_work[slot]));
+  return LDPC_CUDA_OK;
+}
+
+// Validates, groups, fills the whole work array and uploads it on the handle's stream (device-buffer entries).
+int stage_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, bool fused)
+{
+  int rc = validate_and_group(h, n, descs, fused);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  unsigned slot = 0;
+  rc = next_work_slot(h, slot);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  fill_work(h, slot, 0, n, descs, fused);
+  CUDA_TRY(cudaMemcpyAsync(h->d_work, h->h_work[slot], sizeof(CbWork) * n, cudaMemcpyHostToDevice, h->stream));
   CUDA_TRY(cudaEventRecord(h->ev_work[slot], h->stream));
   return LDPC_CUDA_OK;
 }
@@ -489,11 +515,21 @@ int stage_tx_work(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* desc
   return LDPC_CUDA_OK;
 }
 
-// Transport-block assembly (ldpc_tb.cuh): validates the geometry, uploads the work records and launches the kernel on
-// `stream`. d_tb_results receives one TbResult per transport block.
-int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs,
-                        uint32_t n, const ldpc_cuda_cb_desc* descs, const uint8_t* d_msgs, const CbResult* d_results,
-                        uint8_t* d_tb_out, TbResult* d_tb_results)
+// Transport-block assembly (ldpc_tb.cuh) in two steps, so that the host entries can upload the work records of ALL blocks
+// of a call up front (a copy enqueued behind a stream dependency reaches the copy engine only when the dependency has
+// resolved, i.e. behind every input copy submitted in the meantime: the first group of a 16-cell slot was assembled 2 ms
+// late) and launch the kernels group by group behind the chunks that complete them.
+struct TbStaged {
+  const TbWork* d_tw = nullptr;
+  const TbCb* d_tc = nullptr;
+  unsigned* d_partial = nullptr;
+  unsigned slot = 0;
+};
+
+// Validates the geometry and uploads the work records of transport blocks [0, nof_tbs) on `stream`; h->ev_tbwork[slot] is
+// recorded behind the upload.
+int tb_stage(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs, uint32_t n,
+             const ldpc_cuda_cb_desc* descs, TbStaged& staged)
 {
   if (nof_tbs > 65535u) {
     return LDPC_CUDA_ERR_CAPACITY;
@@ -524,7 +560,7 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
   std::memset(stage, 0, bytes);
   TbWork* tw = reinterpret_cast<TbWork*>(stage);
   TbCb* tc = reinterpret_cast<TbCb*>(stage + off_cb);
-  unsigned max_chunks = 0, chunk_base = 0;
+  unsigned chunk_base = 0;
   for (uint32_t t = 0; t != nof_tbs; ++t) {
     const ldpc_cuda_tb_desc& tb = tbs[t];
     if (tb.nof_codeblocks == 0 || tb.first_codeblock > n || tb.nof_codeblocks > n - tb.first_codeblock ||
@@ -562,9 +598,7 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
     tw[t].data_bits = data_bits;
     tw[t].nbytes = (unsigned)(total / 8);
     tw[t].chunk_base = chunk_base;
-    const unsigned chunks = (tw[t].nbytes + TB_CHUNK - 1) / TB_CHUNK;
-    chunk_base += chunks;
-    max_chunks = std::max(max_chunks, chunks);
+    chunk_base += (tw[t].nbytes + TB_CHUNK - 1) / TB_CHUNK;
   }
   if (dev_bytes > h->d_tbwork_cap) {
     // the previous buffer may still be read by an earlier launch: wait for the handle's work before releasing it
@@ -579,17 +613,47 @@ int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_t
   }
   CUDA_TRY(cudaMemcpyAsync(h->d_tbwork, stage, bytes, cudaMemcpyHostToDevice, stream));
   CUDA_TRY(cudaEventRecord(h->ev_tbwork[slot], stream));
-  const TbWork* d_tw = reinterpret_cast<const TbWork*>(h->d_tbwork);
-  const TbCb* d_tc = reinterpret_cast<const TbCb*>(h->d_tbwork + off_cb);
-  unsigned* d_partial = reinterpret_cast<unsigned*>(h->d_tbwork + off_partial);
-  const dim3 grid(max_chunks, nof_tbs);
-  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, stream>>>(d_tw, d_tc, d_msgs, d_tb_out, d_partial);
-  CUDA_TRY(cudaGetLastError());
-  ldpc_tb_finish_kernel<<<nof_tbs, 128, 0, stream>>>(d_tw, d_tc, d_results, d_partial, d_tb_results);
-  CUDA_TRY(cudaGetLastError());
-  h->launches += 1;
-  h->launches += 1;
+  staged.d_tw = reinterpret_cast<const TbWork*>(h->d_tbwork);
+  staged.d_tc = reinterpret_cast<const TbCb*>(h->d_tbwork + off_cb);
+  staged.d_partial = reinterpret_cast<unsigned*>(h->d_tbwork + off_partial);
+  staged.slot = slot;
   return LDPC_CUDA_OK;
+}
+
+// Assembles the staged transport blocks [t0, t1) on `stream` (which is ordered behind the upload of tb_stage).
+// d_tb_results: the entry of block 0.
+int tb_launch(ldpc_cuda_handle* h, cudaStream_t stream, const TbStaged& staged, const ldpc_cuda_tb_desc* tbs, uint32_t t0,
+              uint32_t t1, const uint8_t* d_msgs, const CbResult* d_results, uint8_t* d_tb_out, TbResult* d_tb_results)
+{
+  if (t0 >= t1) {
+    return LDPC_CUDA_OK;
+  }
+  unsigned max_chunks = 0;
+  for (uint32_t t = t0; t != t1; ++t) {
+    const unsigned nbytes = tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3u : 0u);
+    max_chunks = std::max(max_chunks, (nbytes + TB_CHUNK - 1) / TB_CHUNK);
+  }
+  const dim3 grid(max_chunks, t1 - t0);
+  ldpc_tb_assemble_kernel<<<grid, TB_THREADS, 0, stream>>>(staged.d_tw + t0, staged.d_tc, d_msgs, d_tb_out, staged.d_partial);
+  CUDA_TRY(cudaGetLastError());
+  ldpc_tb_finish_kernel<<<t1 - t0, 128, 0, stream>>>(staged.d_tw + t0, staged.d_tc, d_results, staged.d_partial,
+                                                    d_tb_results + t0);
+  CUDA_TRY(cudaGetLastError());
+  h->launches += 2;
+  return LDPC_CUDA_OK;
+}
+
+// Both steps on one stream (device-buffer entry).
+int enqueue_tb_assemble(ldpc_cuda_handle* h, cudaStream_t stream, uint32_t nof_tbs, const ldpc_cuda_tb_desc* tbs,
+                        uint32_t n, const ldpc_cuda_cb_desc* descs, const uint8_t* d_msgs, const CbResult* d_results,
+                        uint8_t* d_tb_out, TbResult* d_tb_results)
+{
+  TbStaged staged;
+  const int rc = tb_stage(h, stream, nof_tbs, tbs, n, descs, staged);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  return tb_launch(h, stream, staged, tbs, 0, nof_tbs, d_msgs, d_results, d_tb_out, d_tb_results);
 }
 
 // Pinned double-buffered staging + device buffer of the demodulator's job lists: waits until the copy that last used the
@@ -827,7 +891,13 @@ static int create_resources(ldpc_cuda_handle* h)
   CUDA_TRY(cudaMalloc(&h->d_work, sizeof(CbWork) * max_codeblocks));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
   CUDA_TRY(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
-  CUDA_TRY(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+  // The copy-out stream also runs the transport-block assembly kernels of the host entries. The decode kernels own whole SMs
+  // (384 threads x 168 registers = the register file), and the chunks' kernels follow each other without a gap, so at
+  // equal priority an assembly kernel only got SMs when the LAST chunk had drained: the blocks of a 16-cell slot came back
+  // 0.8 ms after the last decode. At the highest priority its blocks are placed first whenever a decode block retires.
+  int prio_lo = 0, prio_hi = 0;
+  CUDA_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  CUDA_TRY(cudaStreamCreateWithPriority(&h->d2h_stream, cudaStreamNonBlocking, prio_hi));
   for (int i = 0; i != 2; ++i) {
     CUDA_TRY(cudaMallocHost(&h->h_work[i], sizeof(CbWork) * max_codeblocks));
     CUDA_TRY(cudaEventCreateWithFlags(&h->ev_work[i], cudaEventDisableTiming));
@@ -1192,8 +1262,28 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
   CUDA_TRY(cudaSetDevice(h->device));
   // LDPC_CUDA_TRACE=1: one line per host-entry call on stderr with where its wall-clock time went
   static const bool trace = std::getenv("LDPC_CUDA_TRACE") != nullptr;
+  // LDPC_CUDA_TRACE=2: additionally the device-side timeline of the chunks (when each chunk's input copy and kernel ended)
+  static const bool trace_chunks = trace && std::atoi(std::getenv("LDPC_CUDA_TRACE")) >= 2;
+  std::vector<cudaEvent_t> tl;  // [0] start, then (copy end, kernel end) per chunk
+  auto mark = [&](cudaStream_t st) {
+    if (trace_chunks) {
+      cudaEvent_t e = nullptr;
+      cudaEventCreate(&e);
+      cudaEventRecord(e, st);
+      tl.push_back(e);
+    }
+  };
   const auto t_enter = std::chrono::steady_clock::now();
-  int rc = stage_work(h, n, descs, fused);
+  // The work records are filled and uploaded chunk by chunk in front of the chunk's input copy (same stream), so that the
+  // host's share (25 ns per codeblock: 0.5 ms for a 16-cell slot, 1.7 ms for 65 536 codeblocks) hides behind the copies
+  // and kernels of the chunks before. (Uploading everything first cost that time up front; issuing input copies before a
+  // single upload delayed every kernel behind them, profiles/r01_icache_microbench.md.)
+  int rc = validate_and_group(h, n, descs, fused);
+  if (rc != LDPC_CUDA_OK) {
+    return rc;
+  }
+  unsigned work_slot = 0;
+  rc = next_work_slot(h, work_slot);
   if (rc != LDPC_CUDA_OK) {
     return rc;
   }
@@ -1203,6 +1293,7 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
   if (chunks.empty() || chunks.size() > MAX_CHUNKS) {
     return LDPC_CUDA_ERR_ARG;
   }
+  const auto t_planned = std::chrono::steady_clock::now();
   uint64_t in_lo = ~0ull, in_hi = 0, out_hi = 0;
   const uint64_t out_lo = chunks.front().out_lo;
   for (const Chunk& c : chunks) {
@@ -1295,6 +1386,7 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
   // the chunk holding their last codeblock has been decoded, so that only the last group remains behind the last chunk.
   TbResult* d_tb_res = nullptr;
   uint8_t* d_tb_bytes = nullptr;
+  TbStaged tb_staged;
   uint64_t tb_lo = ~0ull;
   uint32_t tb_next = 0;                 // first block not yet assembled
   std::vector<uint32_t> tb_ready;       // chunk after which block t is complete (empty: assemble everything at the end)
@@ -1316,6 +1408,12 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     }
     d_tb_res = reinterpret_cast<TbResult*>(h->d_tb_out);  // results first (aligned), blocks behind them
     d_tb_bytes = h->d_tb_out + ((sizeof(TbResult) * nof_tbs + 15) & ~(size_t)15);
+    // work records of every block now, in front of the input copies; the kernels follow group by group (tb_stage)
+    rc = tb_stage(h, h->h2d_stream, nof_tbs, tbs, n, descs, tb_staged);
+    if (rc != LDPC_CUDA_OK) {
+      return rc;
+    }
+    CUDA_TRY(cudaStreamWaitEvent(h->d2h_stream, h->ev_tbwork[tb_staged.slot], 0));
     if (chunks.size() > 1) {
       std::vector<uint32_t> chunk_of(n);  // by caller index
       for (size_t ci = 0; ci != chunks.size(); ++ci) {
@@ -1345,12 +1443,14 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     }
   }
   // assembles blocks [t0, t1) on the copy-out stream (which has waited for their chunks) and sends them back
+  std::vector<uint32_t> tb_calls;  // trace: transport blocks per assembly call
+  std::vector<cudaEvent_t> tl_tb;  // trace: end of each assembly call's copy back
   auto assemble_tbs = [&](uint32_t t0, uint32_t t1) -> int {
     if (t0 >= t1) {
       return LDPC_CUDA_OK;
     }
-    int arc = enqueue_tb_assemble(h, h->d2h_stream, t1 - t0, tbs + t0, n, descs, d_out0, h->d_results, d_tb_bytes - tb_lo,
-                                  d_tb_res + t0);
+    tb_calls.push_back(t1 - t0);
+    int arc = tb_launch(h, h->d2h_stream, tb_staged, tbs, t0, t1, d_out0, h->d_results, d_tb_bytes - tb_lo, d_tb_res);
     if (arc != LDPC_CUDA_OK) {
       cudaStreamSynchronize(h->d2h_stream);
       cudaStreamSynchronize(h->stream2);
@@ -1359,6 +1459,29 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     }
     // block by block (exactly adjacent blocks as one copy): the bytes between two blocks of this call may belong to
     // somebody else, e.g. to the blocks another device of a pool assembles into the same buffer
+    // blocks of one size at a constant stride (the usual layout of a slot: aligned offsets leave gaps): ONE pitched copy
+    // instead of one copy per block (5 us each: 37 full-slot blocks took 300 us instead of 120)
+    if (t1 - t0 >= 3) {
+      const uint64_t w0 = tbs[t0].tbs_bits / 8 + (tbs[t0].nof_codeblocks > 1 ? 3 : 0);
+      const uint64_t stride = tbs[t0 + 1].tb_offset - tbs[t0].tb_offset;
+      bool uniform = tbs[t0 + 1].tb_offset > tbs[t0].tb_offset && stride >= w0;
+      for (uint32_t t = t0 + 1; t != t1 && uniform; ++t) {
+        uniform = tbs[t].tb_offset == tbs[t0].tb_offset + (t - t0) * stride &&
+                  tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0) == w0;
+      }
+      if (uniform && stride != w0) {
+        CUDA_TRY(cudaMemcpy2DAsync(tb_out + tbs[t0].tb_offset, stride, d_tb_bytes + (tbs[t0].tb_offset - tb_lo), stride, w0,
+                                   t1 - t0, cudaMemcpyDeviceToHost, h->d2h_stream));
+        tb_next = t1;
+        if (trace_chunks) {
+          cudaEvent_t e = nullptr;
+          cudaEventCreate(&e);
+          cudaEventRecord(e, h->d2h_stream);
+          tl_tb.push_back(e);
+        }
+        return LDPC_CUDA_OK;
+      }
+    }
     uint64_t lo = 0, hi = 0;
     for (uint32_t t = t0; t != t1; ++t) {
       const uint64_t b = tbs[t].tb_offset, e = b + tbs[t].tbs_bits / 8 + (tbs[t].nof_codeblocks > 1 ? 3 : 0);
@@ -1375,11 +1498,24 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
       CUDA_TRY(cudaMemcpyAsync(tb_out + lo, d_tb_bytes + (lo - tb_lo), hi - lo, cudaMemcpyDeviceToHost, h->d2h_stream));
     }
     tb_next = t1;
+    if (trace_chunks) {
+      cudaEvent_t e = nullptr;
+      cudaEventCreate(&e);
+      cudaEventRecord(e, h->d2h_stream);
+      tl_tb.push_back(e);
+    }
     return LDPC_CUDA_OK;
   };
   const uint32_t tb_group = std::max<uint32_t>(1, (nof_tbs + 3) / 4);  // at most ~4 early groups
+  mark(h->h2d_stream);
   for (size_t ci = 0; ci != chunks.size(); ++ci) {
     const Chunk& c = chunks[ci];
+    fill_work(h, work_slot, c.b, c.e, descs, fused);
+    CUDA_TRY(cudaMemcpyAsync(h->d_work + c.b, h->h_work[work_slot] + c.b, sizeof(CbWork) * (c.e - c.b), cudaMemcpyHostToDevice,
+                             h->h2d_stream));
+    if (ci + 1 == chunks.size()) {
+      CUDA_TRY(cudaEventRecord(h->ev_work[work_slot], h->h2d_stream));
+    }
     if (c.in_rows != 0) {
       const uint64_t first = descs[h->order[c.b]].in_offset;
       CUDA_TRY(copy_rows(h->d_in + (first - in_lo), in + first, c.in_stride, c.in_width, c.in_rows, cudaMemcpyHostToDevice,
@@ -1407,6 +1543,7 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
       }
     }
     CUDA_TRY(cudaEventRecord(h->ev_in[ci], h->h2d_stream));
+    mark(h->h2d_stream);
     // kernels of consecutive chunks alternate between two streams (and two work counters) so that the blocks of chunk
     // c + 1 fill the SMs as the last blocks of chunk c retire
     cudaStream_t ks = (ci & 1) ? h->stream2 : h->stream;
@@ -1425,6 +1562,7 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
       }
     }
     CUDA_TRY(cudaEventRecord(h->ev_done[ci], ks));
+    mark(ks);
     CUDA_TRY(cudaStreamWaitEvent(h->d2h_stream, h->ev_done[ci], 0));
     if (!keep_messages) {
       if (c.out_rows != 0) {
@@ -1462,6 +1600,7 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     CUDA_TRY(cudaMemcpyAsync(tb_results, d_tb_res, sizeof(TbResult) * nof_tbs, cudaMemcpyDeviceToHost, h->d2h_stream));
   }
   CUDA_TRY(cudaMemcpyAsync(results, h->d_results, sizeof(CbResult) * n, cudaMemcpyDeviceToHost, h->d2h_stream));
+  mark(h->d2h_stream);
   const auto t_enqueued = std::chrono::steady_clock::now();
   CUDA_TRY(cudaStreamSynchronize(h->d2h_stream));
   // everything of this call has finished (the last copy waited for every kernel); later calls may use any stream
@@ -1481,9 +1620,35 @@ static int batch_host_enqueue(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_c
     }
     std::fprintf(stderr,
                  "ldpc_cuda trace: %u codeblocks, %u transport blocks, %zu chunks (%zu copy runs), in %llu B, preserve %d: "
-                 "work list %.0f us, plan+enqueue %.0f us, wait %.0f us\n",
+                 "validate + group %.0f us, plan %.0f us, enqueue %.0f us, wait %.0f us\n",
                  n, nof_tbs, chunks.size(), runs, (unsigned long long)(in_hi - in_lo), (int)preserve, us(t_enter, t_staged),
-                 us(t_staged, t_enqueued), us(t_enqueued, t_done));
+                 us(t_staged, t_planned), us(t_planned, t_enqueued), us(t_enqueued, t_done));
+    if (trace_chunks && tl.size() == 2 + 2 * chunks.size()) {
+      float end = 0;
+      cudaEventElapsedTime(&end, tl[0], tl.back());
+      std::fprintf(stderr, "ldpc_cuda trace: last result copied back at %.0f us; transport blocks per assembly call:", end * 1e3f);
+      for (size_t k = 0; k != tb_calls.size(); ++k) {
+        float at = 0;
+        if (k < tl_tb.size()) {
+          cudaEventElapsedTime(&at, tl[0], tl_tb[k]);
+        }
+        std::fprintf(stderr, " %u (back at %.0f us)", tb_calls[k], at * 1e3f);
+      }
+      std::fprintf(stderr, "; chunk (codeblocks): input copied / decoded at us:");
+      for (size_t ci = 0; ci != chunks.size(); ++ci) {
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, tl[0], tl[1 + 2 * ci]);
+        cudaEventElapsedTime(&b, tl[0], tl[2 + 2 * ci]);
+        std::fprintf(stderr, " %zu (%u): %.0f / %.0f;", ci, chunks[ci].e - chunks[ci].b, a * 1e3f, b * 1e3f);
+      }
+      std::fprintf(stderr, "\n");
+    }
+    for (cudaEvent_t e : tl) {
+      cudaEventDestroy(e);
+    }
+    for (cudaEvent_t e : tl_tb) {
+      cudaEventDestroy(e);
+    }
   }
   return LDPC_CUDA_OK;
 }

@@ -10,14 +10,24 @@
 
 namespace ldpc_b200 {
 
+// Lifting set index (0..7) of a lifting size, -1 if Z is none of the 51 sizes. Table look-up: the host entries validate
+// tens of thousands of descriptors per call.
 inline int lifting_set_of(int Z)
 {
-  for (int i = 0; i != LDPC_NOF_LIFTING_SIZES; ++i) {
-    if (LDPC_LIFTING_SIZES[i] == Z) {
-      return LDPC_LIFTING_SET[i];
+  struct Table {
+    signed char set[385];
+    Table()
+    {
+      for (signed char& v : set) {
+        v = -1;
+      }
+      for (int i = 0; i != LDPC_NOF_LIFTING_SIZES; ++i) {
+        set[LDPC_LIFTING_SIZES[i]] = (signed char)LDPC_LIFTING_SET[i];
+      }
     }
-  }
-  return -1;
+  };
+  static const Table table;
+  return (Z >= 0 && Z <= 384) ? table.set[Z] : -1;
 }
 
 inline unsigned bg_K(int bg) { return bg == 2 ? 10 : 22; }
