@@ -257,32 +257,32 @@ int ldpc_cuda_pool_decode_batch(ldpc_cuda_pool* p, uint32_t n, const ldpc_cuda_c
     return LDPC_CUDA_OK;
   }
   const uint32_t G = static_cast<uint32_t>(p->handles.size());
-  for (uint32_t g = 0; g != G; ++g) {
-    shard& s = p->shards[g];
-    s.descs.clear(), s.origin.clear();
-    for (uint32_t i = g; i < n; i += G) {
-      s.descs.push_back(descs[i]);
-      s.origin.push_back(i);
-    }
-    s.results.assign(s.descs.size(), ldpc_cuda_cb_result{0, 0, 0});
-  }
-  // every device reads its codeblocks from, and writes its messages to, the caller's buffers at the caller's offsets
+  // Every device thread picks its own codeblocks (i = g, g + G, ...) out of the caller's list, reads them from, and writes
+  // its messages to, the caller's buffers at the caller's offsets, and puts its results where they belong: nothing of the
+  // split runs serially on the calling thread.
   const int rc = run_on_devices(
-      p, [p](uint32_t g) { return !p->shards[g].descs.empty(); },
-      [p, llrs, out_bits](uint32_t g) {
+      p, [n](uint32_t g) { return g < n; },
+      [p, n, G, descs, llrs, out_bits, results](uint32_t g) {
         shard& s = p->shards[g];
-        return ldpc_cuda_decode_batch(p->handles[g], static_cast<uint32_t>(s.descs.size()), s.descs.data(), llrs, out_bits,
-                                      s.results.data());
+        s.descs.clear();
+        for (uint32_t i = g; i < n; i += G) {
+          s.descs.push_back(descs[i]);
+        }
+        s.results.assign(s.descs.size(), ldpc_cuda_cb_result{0, 0, 0});
+        const int r = ldpc_cuda_decode_batch(p->handles[g], static_cast<uint32_t>(s.descs.size()), s.descs.data(), llrs,
+                                             out_bits, s.results.data());
+        if (r == LDPC_CUDA_OK) {
+          for (size_t k = 0; k != s.results.size(); ++k) {
+            results[g + k * G] = s.results[k];
+          }
+        }
+        return r;
       });
   if (rc != LDPC_CUDA_OK) {
     return rc;
   }
-  for (uint32_t g = 0; g != G; ++g) {
-    const shard& s = p->shards[g];
-    for (size_t k = 0; k != s.origin.size(); ++k) {
-      results[s.origin[k]] = s.results[k];
-    }
-    p->codeblocks_done[g] += s.origin.size();
+  for (uint32_t g = 0; g != G && g < n; ++g) {
+    p->codeblocks_done[g] += (n - g + G - 1) / G;
   }
   return LDPC_CUDA_OK;
 }
@@ -299,25 +299,24 @@ int ldpc_cuda_pool_decode_batch_device(ldpc_cuda_pool* p, uint32_t n, const ldpc
     return LDPC_CUDA_OK;
   }
   const uint32_t G = static_cast<uint32_t>(p->handles.size());
-  for (uint32_t g = 0; g != G; ++g) {
-    shard& s = p->shards[g];
-    s.descs.clear(), s.origin.clear();
-    for (uint32_t i = g; i < n; i += G) {
-      s.descs.push_back(descs[i]);
-    }
-    if (!s.descs.empty() && (llrs_d[g] == nullptr || out_bits_d[g] == nullptr || results_d[g] == nullptr)) {
+  for (uint32_t g = 0; g != G && g < n; ++g) {
+    if (llrs_d[g] == nullptr || out_bits_d[g] == nullptr || results_d[g] == nullptr) {
       return LDPC_CUDA_ERR_ARG;
     }
   }
   const int rc = run_on_devices(
-      p, [p](uint32_t g) { return !p->shards[g].descs.empty(); },
-      [p, llrs_d, out_bits_d, results_d](uint32_t g) {
-        shard& s = p->shards[g];
+      p, [n](uint32_t g) { return g < n; },
+      [p, n, G, descs, llrs_d, out_bits_d, results_d](uint32_t g) {
+        shard& s = p->shards[g];  // built by the device's own thread, like everything else of the split
+        s.descs.clear();
+        for (uint32_t i = g; i < n; i += G) {
+          s.descs.push_back(descs[i]);
+        }
         return ldpc_cuda_decode_batch_device(p->handles[g], static_cast<uint32_t>(s.descs.size()), s.descs.data(), llrs_d[g],
                                              out_bits_d[g], results_d[g]);
       });
-  for (uint32_t g = 0; g != G && rc == LDPC_CUDA_OK; ++g) {
-    p->codeblocks_done[g] += p->shards[g].descs.size();
+  for (uint32_t g = 0; g != G && g < n && rc == LDPC_CUDA_OK; ++g) {
+    p->codeblocks_done[g] += (n - g + G - 1) / G;
   }
   return rc;
 }
