@@ -2273,6 +2273,19 @@ int ldpc_cuda_reserve_staging(ldpc_cuda_handle* h, uint64_t in_bytes, uint64_t o
   return LDPC_CUDA_OK;
 }
 
+#ifdef TM_PHASE_TIMING
+// Development builds only (tools/phase_timing.py): reads and clears the per-phase cycle counters of the decoder kernel.
+extern "C" int ldpc_cuda_debug_phase_cycles(unsigned long long* out16)
+{
+  unsigned long long zero[16] = {};
+  if (cudaMemcpyFromSymbol(out16, g_tm_phase, sizeof(zero)) != cudaSuccess ||
+      cudaMemcpyToSymbol(g_tm_phase, zero, sizeof(zero)) != cudaSuccess) {
+    return LDPC_CUDA_ERR_CUDA;
+  }
+  return LDPC_CUDA_OK;
+}
+#endif
+
 int ldpc_cuda_host_alloc(uint64_t nof_bytes, uint32_t flags, void** ptr)
 {
   if (ptr == nullptr || nof_bytes == 0 || (flags & ~LDPC_CUDA_HOST_WRITE_COMBINED) != 0) {

@@ -61,6 +61,22 @@ constexpr unsigned TM_CRC_POW_LEN = 22 * 384;  // longest message in bits
 // Filled once per device by upload_constants (ldpc_api.cu).
 __device__ __align__(32) unsigned g_crc_pow[3][TM_CRC_POW_LEN];
 
+// Development aid (build with -DTM_PHASE_TIMING, tools/phase_timing.py): cycles thread 0 of every group spends in the
+// phases of a pair, summed over the launch.
+#ifdef TM_PHASE_TIMING
+__device__ unsigned long long g_tm_phase[16];
+#define TM_PHASE(i)                                                                 \
+  do {                                                                              \
+    if (t == 0) {                                                                   \
+      const long long now_ = clock64();                                             \
+      atomicAdd(&g_tm_phase[i], (unsigned long long)(now_ - phase_t0_));            \
+      phase_t0_ = now_;                                                             \
+    }                                                                               \
+  } while (0)
+#else
+#define TM_PHASE(i) do { } while (0)
+#endif
+
 struct TmemParams {
   const CbWork* work;
   const int8_t* llr_base;   // decoder input LLRs; fused: the soft-buffer arena (same memory as soft_rw)
@@ -620,6 +636,9 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   if (PREFETCH && t == 0) {
     flags[5] = atomicAdd(p.pair_counter, 1u);
   }
+#ifdef TM_PHASE_TIMING
+  long long phase_t0_ = clock64();
+#endif
   for (;;) {
     // next pair of codeblocks for this group
     if (t == 0) {
@@ -741,20 +760,31 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       int8_t* softB = p.soft_rw + wB.in_offset;
       int8_t* stA = reinterpret_cast<int8_t*>(gsm + lay.stage);
       int8_t* stB = stA + lay.stage_stride;
+      TM_PHASE(0);  // claim + work records + geometry
       // phase A: staging copy of the previous content (not read at all for a fresh first transmission)
       dematch_stage_in(gA, softA, stA, (unsigned)t, (unsigned)zpad);
       if (hasB) {
         dematch_stage_in(gB, softB, stB, (unsigned)t, (unsigned)zpad);
       }
       tm::group_barrier<FULL>(bar_id, zpad);
+      TM_PHASE(1);  // stage in
       // phase B: one pass in input order when no position is hit twice, else lap by lap
       const bool onceA = dematch_single_pass(gA), onceB = hasB && dematch_single_pass(gB);
-      if (onceA) {
+      // first transmissions with word-aligned geometry (the usual case) take the word-wise scatter, both codeblocks at once
+      const bool wordA = onceA && dematch_wordwise(gA, rmA), wordB = onceB && dematch_wordwise(gB, rmB);
+      const bool pairW = wordA && wordB && gA.Qm == gB.Qm;
+      if (wordA) {
+        dematch_scatter_words(gA, rmA, stA, pairW, gB, rmB, stB, (unsigned)t, (unsigned)zpad);
+      } else if (onceA) {
         dematch_scatter_once(gA, rmA, stA, (unsigned)t, (unsigned)zpad);
       }
-      if (onceB) {
+      TM_PHASE(11);  // scatter of codeblock A (thread 0's own share; both codeblocks in the word-wise case)
+      if (wordB && !pairW) {
+        dematch_scatter_words(gB, rmB, stB, false, gB, rmB, stB, (unsigned)t, (unsigned)zpad);
+      } else if (onceB && !pairW) {
         dematch_scatter_once(gB, rmB, stB, (unsigned)t, (unsigned)zpad);
       }
+      TM_PHASE(12);  // scatter of codeblock B
       const unsigned lapsA = onceA ? 0u : dematch_nof_laps(gA), lapsB = (!hasB || onceB) ? 0u : dematch_nof_laps(gB);
       for (unsigned lap = 0; lap < max(lapsA, lapsB); ++lap) {
         if (lap < lapsA) {
@@ -768,6 +798,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         }
       }
       tm::group_barrier<FULL>(bar_id, zpad);
+      TM_PHASE(2);  // scatter / combine
       // phase C: back to the arena, and on to the decoder
       dematch_stage_out(gA, stA, softA, (unsigned)t, (unsigned)zpad);
       if (hasB) {
@@ -790,6 +821,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         }
       }
     }
+    TM_PHASE(3);  // stage out + conversion (decode-only: the whole load)
     if (FUSED && !useA && !useB) {  // combined only (both CRCs already passed in an earlier transmission)
       tm::group_barrier<FULL>(bar_id, zpad);
       continue;
@@ -864,6 +896,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       }
     }
 
+    TM_PHASE(4);  // input size, layers, TMEM reset, prefetch of the next pair
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
       for (int r = 0; r < nof_layers;) {
@@ -879,6 +912,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       }
       tm::group_barrier<FULL>(bar_id, zpad);
       tm::tm_wait_st();
+      TM_PHASE(5);  // row passes of one iteration
       ++it;
       const bool last = (it == p.max_iterations);
       const bool chkA = !doneA && ((wA.crc_poly && wA.early_stop) || last);
@@ -954,6 +988,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
               }
             }
           }
+          TM_PHASE(6);  // check: sweep over the hard bits
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) {
             ra ^= __shfl_xor_sync(0xffffffffu, ra, o);
@@ -972,9 +1007,28 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
           }
         }
         tm::group_barrier<FULL>(bar_id, zpad);
+        TM_PHASE(8);  // check: reduction + barrier
         const bool okA = crcA && flags[acc_a] == 0, okB = crcB && flags[acc_b] == 0;
         // the message bytes are only formed for a codeblock that finishes now
-        if ((chkA && (okA || last)) || (chkB && (okB || last))) {
+        if (((chkA && (okA || last)) || (chkB && (okB || last))) && (FULL || (Z & 31) == 0)) {
+          // Z a multiple of 32: lane l of warp w holds message bit n Z + 32 w + l of column n, so one ballot per column and
+          // codeblock is four message bytes (bit-reversed: the first bit of a byte is its MSB), stored by one lane. (The
+          // byte-wise loop below reads the soft values with a stride of 8 words - an 8-way bank conflict per load - and
+          // was 7 % of the fused kernel's time on full-slot transport blocks.)
+          const unsigned lane = (unsigned)t & 31u;
+#pragma unroll 2
+          for (int n = 0; n < K; ++n) {
+            const unsigned v = soft_w[(unsigned)n * Z + t];
+            const unsigned ba = __ballot_sync(0xffffffffu, (v & 0x7fffu) == 0 || (v & 0x8000u));
+            const unsigned bb = __ballot_sync(0xffffffffu, (v & 0x7fff0000u) == 0 || (v & 0x80000000u));
+            if (lane == 0) {
+              const unsigned o = ((unsigned)n * Z + (unsigned)t) >> 3;  // byte offset of the four bytes (multiple of 4)
+              *reinterpret_cast<unsigned*>(hard + o) = __byte_perm(__brev(ba), 0u, 0x0123);
+              *reinterpret_cast<unsigned*>(hard + msg_bytes16 + o) = __byte_perm(__brev(bb), 0u, 0x0123);
+            }
+          }
+          tm::group_barrier<FULL>(bar_id, zpad);  // the bytes are read by other threads than the ones that stored them
+        } else if ((chkA && (okA || last)) || (chkB && (okB || last))) {
           for (unsigned i = t; i < msg_bytes; i += zpad) {
             unsigned ba = 0, bb = 0;
 #pragma unroll
@@ -990,6 +1044,7 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
             hard[msg_bytes16 + i] = (unsigned char)bb;
           }
         }
+        TM_PHASE(9);  // finish: message bytes
         auto finish = [&](const CbWork& w, CbResult& res, bool& done, const unsigned char* bits, bool ok) {
           if (ok || last) {
             uint8_t* out = p.out_base + w.out_offset;
@@ -1022,8 +1077,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         // the next iteration would use may still hold the remainder of an earlier check of the same parity.
         flags[8 + 2 * ((it + 1) & 1)] = 0, flags[9 + 2 * ((it + 1) & 1)] = 0;
       }
+      TM_PHASE(10);  // finish: output + barrier
     }
     tm::group_barrier<FULL>(bar_id, zpad);  // flags / hard bits are reused by the next pair
+    TM_PHASE(7);
   }
   __syncthreads();
   if (warp == 0) {

@@ -11,5 +11,5 @@ cp -r "$ROOT/srsran_project_23.5_b200/csrc" "$TMP/pkg/csrc"
 cp "$ROOT/include/ldpc_cuda.h" "$TMP/include/"
 cp "$1" "$TMP/pkg/csrc/ldpc_kernels_tmem.cuh"
 cd "$TMP/pkg"
-nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --expt-relaxed-constexpr $EXTRA -Xcompiler -fPIC -shared -o "$OUT" csrc/ldpc_api.cu csrc/ldpc_geometry.cpp
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --expt-relaxed-constexpr $EXTRA -Xcompiler -fPIC -shared -o "$OUT" csrc/ldpc_api.cu csrc/ldpc_geometry.cpp csrc/ldpc_pool.cpp
 rm -rf "$TMP"
