@@ -37,7 +37,7 @@ __host__ __device__ inline unsigned dematch_linear(const DematchGeom& g, unsigne
   return (p < g.info) ? p : p - (g.sys - g.info);
 }
 
-// k0 = floor(c_rv * Ncb / N) * Z computed in double as the reference does (ldpc_rate_dematcher_impl.cpp:101-102).
+// k0 = floor(c_rv * Ncb / N) * Z (ldpc_rate_dematcher_impl.cpp:101-102).
 __host__ __device__ inline DematchGeom make_dematch_geom(int bg, unsigned Z, unsigned F, unsigned rv, unsigned Qm,
                                                          unsigned Nref, unsigned E, unsigned new_data)
 {
@@ -47,9 +47,12 @@ __host__ __device__ inline DematchGeom make_dematch_geom(int bg, unsigned Z, uns
   g.Ncb = (Nref > 0) ? (Nref < g.N ? Nref : g.N) : g.N;
   g.sys = (K - 2) * Z;
   g.info = g.sys - F;
-  const double f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
-  const double factor = (bg == 2) ? f2[rv & 3] : f1[rv & 3];
-  g.k0 = (unsigned)((unsigned short)floor((factor * g.Ncb) / g.N)) * Z;
+  // The reference computes floor(c_rv * Ncb / N) in double (ldpc_rate_dematcher_impl.cpp:101-102). The integer quotient is
+  // the same number: c_rv * Ncb < 2^21 is exact, and a non-integer quotient of integers with a divisor <= 25 344 is at
+  // least 1 / 25 344 away from an integer, far more than the rounding error of one double division of values below 64.
+  const unsigned f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
+  const unsigned factor = (bg == 2) ? f2[rv & 3] : f1[rv & 3];
+  g.k0 = ((factor * g.Ncb) / g.N) * Z;
   g.E = E;
   g.Qm = Qm;
   g.new_data = new_data;
