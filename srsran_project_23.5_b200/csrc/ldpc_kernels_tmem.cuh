@@ -816,7 +816,30 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       const unsigned nzA = useA ? (dematch_is_fresh(gA) ? gA.zero_from : gA.N) : 0u;
       const unsigned nzB = useB ? (dematch_is_fresh(gB) ? gB.zero_from : gB.N) : 0u;
       const int n_hi = min(K + M, max(HRR, (int)((max(nzA, nzB) + Z - 1) / Z) + 2));
-      if (c.active) {
+      if (tm::uniform((Z & 15) == 0 ? 1 : 0)) {
+        // as in the decode-only load: a thread converts 16 consecutive lanes of one column of both codeblocks (two
+        // 16-byte shared-memory loads, four 16-byte stores) instead of one lane of every column
+        const unsigned V = (unsigned)Z >> 4, nvec = (unsigned)(n_hi - 2) * V;
+        for (unsigned v = (unsigned)t; v < nvec; v += (unsigned)zpad) {
+          const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+          const uint4 a = useA ? *reinterpret_cast<const uint4*>(stA + 16u * v) : zero4;
+          const uint4 b = useB ? *reinterpret_cast<const uint4*>(stB + 16u * v) : zero4;
+          lastA = ((a.x | a.y) | (a.z | a.w)) ? 16u * (v + 1) : lastA;
+          lastB = ((b.x | b.y) | (b.z | b.w)) ? 16u * (v + 1) : lastB;
+          const unsigned n = 2u + v / V, lane0 = 16u * (v - (n - 2u) * V);
+          unsigned* dst = (n < (unsigned)HRR) ? soft_w + n * (unsigned)Z + lane0 : ext_soft_w + (n - HRR) * (unsigned)zpad + lane0;
+          const unsigned aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            o.x = tm::convert_bytes(aw[q], bw[q], 0x0400);
+            o.y = tm::convert_bytes(aw[q], bw[q], 0x0501);
+            o.z = tm::convert_bytes(aw[q], bw[q], 0x0602);
+            o.w = tm::convert_bytes(aw[q], bw[q], 0x0703);
+            *reinterpret_cast<uint4*>(dst + 4 * q) = o;
+          }
+        }
+      } else if (c.active) {
 #pragma unroll 6
         for (int n = 2; n < n_hi; ++n) {
           const unsigned i = (unsigned)(n - 2) * Z + t;
