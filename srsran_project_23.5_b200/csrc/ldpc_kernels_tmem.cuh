@@ -47,9 +47,14 @@
 namespace ldpc_b200 {
 
 enum { TM_SCALE_NONE = 0, TM_SCALE_GENERIC_08 = 1, TM_SCALE_AVX_08 = 2, TM_SCALE_LUT = 3 };
+// Kernel flavour: GENERAL (any Z, <= 384 threads), FULL (Z = 384 folded at compile time), WIDE (decode-only blocks of up to
+// 512 threads: 128 registers, 128 TMEM columns per warp, overflow message words in shared memory).
+enum { TM_MODE_GENERAL = 0, TM_MODE_FULL = 1, TM_MODE_WIDE = 2 };
 
-constexpr int TM_THREADS = 384;       // threads per block at full occupancy of the TMEM lanes (12 warps)
-constexpr int TM_COLS_PER_WARP = 170; // 512 TMEM columns / 3 warps per lane quadrant
+constexpr int TM_THREADS = 384;       // threads of a block whose lifting size fills it (Z = 384), and of every fused block
+constexpr int TM_THREADS_WIDE = 512;  // decode-only blocks of smaller lifting sizes hold floor(512 / roundup32(Z)) groups
+constexpr int TM_COLS_PER_WARP = 170; // 512 TMEM columns / 3 warps per lane quadrant (<= 12 warps)
+constexpr int TM_COLS_PER_WARP_WIDE = 128;  // 4 warps per lane quadrant (13 .. 16 warps); messages beyond go to shared memory
 
 struct __align__(8) TmEdge {
   unsigned s4;  // 4 * (shift % Z): rotation in bytes
@@ -98,6 +103,9 @@ struct TmemParams {
   unsigned rowdesc[LDPC_BG1_M + 2];    // per row: rowcls | rowedge << 8 | rowtm << 20 (one uniform load per row)
   unsigned pairdesc[LDPC_BG1_M + 2];   // per row r: 0, or the descriptor of the pair (r, r + 1) that starts at r (pair_dispatch)
   unsigned short tm_words;             // TMEM words used per thread
+  unsigned short tm_cap;               // TMEM words a thread owns (rowtm >= tm_cap: overflow word rowtm - tm_cap in shared memory)
+  unsigned short ovf_words;            // overflow words per thread
+  unsigned ovf_stride;                 // bytes between consecutive overflow words of one thread (4 x threads per block)
   unsigned char scale_lut[LLR_MAX + 1 + 3];  // TM_SCALE_LUT: scaled magnitude for m in [0, 120] (any factor, any rounding mode)
   TmEdge edge[LDPC_BG1_EDGES];         // high-rate edges only, row after row (extension edges are implicit)
 };
@@ -313,6 +321,9 @@ struct Ctx {
   unsigned Z4;
   unsigned zpad4;
   unsigned tm_addr;    // TMEM address of this warp's column block (lane base in the upper half)
+  unsigned tm_cap;     // words of that block; message words beyond it live in shared memory:
+  unsigned ovf;        //   shared address of this thread's overflow word 0, word i at + i * ovf_stride
+  unsigned ovf_stride;
   unsigned lut;        // TM_SCALE_LUT: shared address of the scaling table (fp16 bit patterns of 544 * lut[m])
   bool active;         // lane < Z
 };
@@ -321,8 +332,9 @@ struct Ctx {
 // private extension node. Split into the part that does not touch shared soft values (pre: runs while slower warps finish
 // the previous row), the loads and the arithmetic, so that two rows without a common column can be interleaved between
 // one pair of barriers (pair_body). e0 / r / tmw are warp-uniform.
-template <int D, bool EXT, int SCALE, bool FULL>
+template <int D, bool EXT, int SCALE, int MODE>
 struct Row {
+  static constexpr bool FULL = MODE == TM_MODE_FULL, WIDE = MODE == TM_MODE_WIDE;
   static constexpr int NV = D + (EXT ? 1 : 0);  // values entering the check
   static constexpr int W = (D + 1) / 2;         // message words of the row
   unsigned addr[D], u[NV], cw[W];
@@ -330,9 +342,18 @@ struct Row {
 
   __device__ __forceinline__ void pre(const Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
   {
-    // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads
-    tma = c.tm_addr + tmw;
-    tm_load<W>(tma, cw);
+    // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads. Blocks of
+    // more than 12 warps own 128 columns per warp: the last rows' messages are thread-private shared-memory words then.
+    if (WIDE && tmw >= c.tm_cap) {
+      tma = 0x80000000u | (c.ovf + (tmw - c.tm_cap) * c.ovf_stride);
+#pragma unroll
+      for (int i = 0; i < W; ++i) {
+        cw[i] = lds32((tma & 0x7fffffffu) + (unsigned)i * c.ovf_stride);
+      }
+    } else {
+      tma = c.tm_addr + tmw;
+      tm_load<W>(tma, cw);
+    }
     // addresses: lane j of column n talks to check lane (j - shift) mod Z (ldpc_decoder_generic.cpp:66)
 #pragma unroll
     for (int k = 0; k < D; ++k) {
@@ -429,14 +450,22 @@ struct Row {
     for (int i = 0; i < W; ++i) {
       wv[i] = __byte_perm(tn[2 * i], tn[2 * i + 1], 0x6420);
     }
-    tm_store<W>(tma, wv);
+    if (WIDE && (tma & 0x80000000u)) {
+#pragma unroll
+      for (int i = 0; i < W; ++i) {
+        sts32((tma & 0x7fffffffu) + (unsigned)i * c.ovf_stride, wv[i]);
+      }
+    } else {
+      tm_store<W>(tma, wv);
+    }
   }
 };
 
-template <int D, bool EXT, int SCALE, bool FULL>
+template <int D, bool EXT, int SCALE, int MODE>
 __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw, int bar_id, int zpad)
 {
-  Row<D, EXT, SCALE, FULL> R;
+  constexpr bool FULL = MODE == TM_MODE_FULL;
+  Row<D, EXT, SCALE, MODE> R;
   R.pre(c, p, r, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
@@ -451,12 +480,13 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
 // running them one after the other - two independent dependency chains per thread, half the barriers and half the loop /
 // dispatch work for these (short) rows. In both 5G base graphs most rows of the extension part are pairwise orthogonal
 // to their successor (BG1: 14 pairs among rows 16-45, BG2: 13).
-template <int DA, int DB, int SCALE, bool FULL>
+template <int DA, int DB, int SCALE, int MODE>
 __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, int e0A, unsigned tmwA, int rB, int e0B,
                                           unsigned tmwB, int bar_id, int zpad)
 {
-  Row<DA, true, SCALE, FULL> A;
-  Row<DB, true, SCALE, FULL> B;
+  constexpr bool FULL = MODE == TM_MODE_FULL;
+  Row<DA, true, SCALE, MODE> A;
+  Row<DB, true, SCALE, MODE> B;
   A.pre(c, p, rA, e0A, tmwA);
   B.pre(c, p, rB, e0B, tmwB);
   group_barrier<FULL>(bar_id, zpad);
@@ -467,7 +497,7 @@ __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, i
   B.compute(c);
 }
 
-template <int SCALE, bool FULL>
+template <int SCALE, int MODE>
 __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad, unsigned rd)
 {
   const int cls = rd & 0xffu;
@@ -476,7 +506,7 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
   switch (cls) {
 #define LDPC_TM_CASE(D, EXT)                        \
   case 2 * (D) + (EXT):                             \
-    row_body<D, (EXT) != 0, SCALE, FULL>(c, p, r, e0, tmw, bar_id, zpad); \
+    row_body<D, (EXT) != 0, SCALE, MODE>(c, p, r, e0, tmw, bar_id, zpad); \
     break;
     LDPC_TM_CASE(2, 1)
     LDPC_TM_CASE(3, 1)
@@ -497,7 +527,7 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
 
 // pd: pair class (16 * DA + DB, DA >= DB) | row index of A << 8 | row index of B << 16; the rows' own descriptors give
 // their edge / TMEM offsets.
-template <int SCALE, bool FULL>
+template <int SCALE, int MODE>
 __device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int bar_id, int zpad, unsigned pd, unsigned rdA,
                                               unsigned rdB)
 {
@@ -507,7 +537,7 @@ __device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int b
   switch (cls) {
 #define LDPC_TM_PAIR(DA, DB)                                                                   \
   case 16 * (DA) + (DB):                                                                       \
-    pair_body<DA, DB, SCALE, FULL>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
+    pair_body<DA, DB, SCALE, MODE>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
     break;
     LDPC_TM_PAIR(5, 5)
     LDPC_TM_PAIR(5, 4)
@@ -584,9 +614,12 @@ constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base ad
 // buffer is read once and written once).
 // FULL: Z = 384 (one group of 12 warps, every lane live) with Z, the barrier operands and the all-lanes-active predicate
 // folded at compile time - the configuration BASELINE.json's metric is quoted on.
-template <int BG, int SCALE, bool FUSED, bool FULL>
-__global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
+// WIDE: decode-only blocks of up to 512 threads for lifting sizes that leave room for more groups.
+template <int BG, int SCALE, bool FUSED, int MODE>
+__global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_THREADS, 1)
+    ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
 {
+  constexpr bool FULL = MODE == TM_MODE_FULL;
   constexpr int K = (BG == 2) ? 10 : 22, M = (BG == 2) ? LDPC_BG2_M : LDPC_BG1_M, HRR = K + 4;
   extern __shared__ __align__(16) unsigned char smem[];
   const int Z = FULL ? MAX_Z : p.Z, zpad = FULL ? MAX_Z : p.zpad, tid = threadIdx.x;
@@ -625,7 +658,12 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
   c.Z4 = (unsigned)p.Z4;
   c.zpad4 = 4u * (unsigned)zpad;
   const unsigned tmem_base = *reinterpret_cast<volatile unsigned*>(smem + 3 * 256 * 4);
-  c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * TM_COLS_PER_WARP;
+  c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * (unsigned)p.tm_cap;
+  c.tm_cap = p.tm_cap;
+  c.ovf_stride = p.ovf_stride;
+  // overflow message words (blocks of more than 12 warps): behind the groups' buffers, word i of thread tid at
+  // (i * threads + tid) * 4 - consecutive threads, consecutive banks
+  c.ovf = (unsigned)__cvta_generic_to_shared(smem + TM_CRC_TABLE_BYTES + (size_t)p.groups * p.group_stride) + 4u * (unsigned)tid;
   c.lut = (unsigned)__cvta_generic_to_shared(smem);
   c.active = FULL || t < Z;
 
@@ -901,9 +939,14 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
       for (int i = 0; i < 8; ++i) {
         init[i] = 0x80808080u;
       }
-      const int words = (nof_layers < M) ? (int)(p.rowdesc[nof_layers] >> 20) : (int)p.tm_words;
+      // first message word behind the layers that run: a TMEM word, or tm_cap + an overflow word
+      const int first_free = (nof_layers < M) ? (int)(p.rowdesc[nof_layers] >> 20) : (int)p.tm_cap + (int)p.ovf_words;
+      const int words = min(first_free, (int)p.tm_words);
       for (int w = 0; w < words; w += 8) {
         tm::tm_st8(c.tm_addr + w, init);
+      }
+      for (int w = 0; w < first_free - (int)p.tm_cap; ++w) {
+        tm::sts32(c.ovf + (unsigned)w * c.ovf_stride, 0x80808080u);
       }
       tm::tm_wait_st();
     }
@@ -934,10 +977,10 @@ __global__ void __launch_bounds__(TM_THREADS, 1) ldpc_decode_tmem_kernel(const _
         // the barrier that orders a row after its predecessor is inside the bodies
         const unsigned rd = p.rowdesc[r], pd = p.pairdesc[r];
         if (pd != 0 && r + 1 < nof_layers) {
-          tm::pair_dispatch<SCALE, FULL>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
+          tm::pair_dispatch<SCALE, MODE>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
           r += 2;
         } else {
-          tm::row_dispatch<SCALE, FULL>(c, p, r, bar_id, zpad, rd);
+          tm::row_dispatch<SCALE, MODE>(c, p, r, bar_id, zpad, rd);
           r += 1;
         }
       }
@@ -1177,17 +1220,19 @@ static inline int tm_scale_selfcheck(int variant, const unsigned char* lut, cuda
 }
 
 // Fills the row / edge tables of a (base graph, lifting size) group. Returns false when a row shape has no kernel case.
-static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p)
+// tm_cap: message words a thread owns in TMEM (a multiple of 8 is used); rows that do not fit get shared-memory words.
+static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p, unsigned tm_cap = TM_COLS_PER_WARP)
 {
   const int M = (bg == 2) ? LDPC_BG2_M : LDPC_BG1_M, K = (bg == 2) ? 10 : 22, hrr = K + 4;
   const uint16_t* row_ptr = (bg == 2) ? LDPC_BG2_ROW_PTR : LDPC_BG1_ROW_PTR;
   const uint8_t* col = (bg == 2) ? LDPC_BG2_COL : LDPC_BG1_COL;
   const uint16_t* shift = (bg == 2) ? LDPC_BG2_SHIFT[lifting_set] : LDPC_BG1_SHIFT[lifting_set];
-  unsigned ne = 0, tmw = 0;
+  unsigned ne = 0, tmw = 0, ovf = 0;
+  bool spilled = false;  // once a row went to shared memory all later ones do (the reset loop relies on the order)
+  p.tm_cap = (unsigned short)tm_cap;
   for (int r = 0; r != M; ++r) {
     unsigned d = 0, ext = 0;
     p.rowedge[r] = (unsigned short)ne;
-    p.rowtm[r] = (unsigned short)tmw;
     for (int e = row_ptr[r]; e != row_ptr[r + 1]; ++e) {
       if (col[e] < hrr) {
         p.edge[ne].s4 = 4u * (shift[e] % (unsigned)Z);
@@ -1206,10 +1251,19 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
       return false;
     }
     p.rowcls[r] = (unsigned char)(2 * d + ext);
+    const unsigned w = (d + 1) / 2;
+    spilled = spilled || tmw + w > (tm_cap & ~7u);
+    if (spilled) {
+      p.rowtm[r] = (unsigned short)(tm_cap + ovf);
+      ovf += w;
+    } else {
+      p.rowtm[r] = (unsigned short)tmw;
+      tmw += w;
+    }
     p.rowdesc[r] = (unsigned)p.rowcls[r] | ((unsigned)p.rowedge[r] << 8) | ((unsigned)p.rowtm[r] << 20);
-    tmw += (d + 1) / 2;
   }
   p.tm_words = (unsigned short)tmw;
+  p.ovf_words = (unsigned short)ovf;
   // pairs of consecutive rows (both with an extension node) that share no high-rate column, chosen greedily in row order;
   // A is the row with the larger high-rate degree (the order inside a pair does not matter)
   for (int r = 4; r + 1 < M;) {
@@ -1229,7 +1283,7 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
       r += 1;
     }
   }
-  return ((tmw + 7) & ~7u) <= (unsigned)TM_COLS_PER_WARP;
+  return ((tmw + 7) & ~7u) <= tm_cap;
 }
 
 constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100
@@ -1239,10 +1293,10 @@ constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block
 // several GPUs, and several host threads may launch at once).
 constexpr int TM_MAX_DEVICES = 64;
 
-template <int BG, int SCALE, bool FUSED, bool FULL>
+template <int BG, int SCALE, bool FUSED, int MODE>
 static inline int tm_launch_full(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
 {
-  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED, FULL>;
+  auto kernel = ldpc_decode_tmem_kernel<BG, SCALE, FUSED, MODE>;
   static std::atomic<bool> attr_set[TM_MAX_DEVICES];
   if (device < 0 || device >= TM_MAX_DEVICES || !attr_set[device].load(std::memory_order_acquire)) {
     const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TM_SMEM_LIMIT);
@@ -1266,8 +1320,15 @@ static inline int tm_launch_full(const TmemParams& p, size_t smem, unsigned grid
 template <int BG, int SCALE, bool FUSED>
 static inline int tm_launch_variant(const TmemParams& p, size_t smem, unsigned grid, int device, cudaStream_t stream)
 {
-  return (p.Z == MAX_Z && p.groups == 1) ? tm_launch_full<BG, SCALE, FUSED, true>(p, smem, grid, device, stream)
-                                         : tm_launch_full<BG, SCALE, FUSED, false>(p, smem, grid, device, stream);
+  if (p.Z == MAX_Z && p.groups == 1) {
+    return tm_launch_full<BG, SCALE, FUSED, TM_MODE_FULL>(p, smem, grid, device, stream);
+  }
+  if constexpr (!FUSED) {
+    if (p.groups * p.zpad > TM_THREADS) {
+      return tm_launch_full<BG, SCALE, false, TM_MODE_WIDE>(p, smem, grid, device, stream);
+    }
+  }
+  return tm_launch_full<BG, SCALE, FUSED, TM_MODE_GENERAL>(p, smem, grid, device, stream);
 }
 
 template <int BG, int SCALE>
@@ -1290,22 +1351,36 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   }
   TmemParams p;
   std::memset(&p, 0, sizeof(p));
-  if (!tm_build_tables(gp.bg, gp.Z, gp.lifting_set, p)) {
-    return 1;
-  }
   p.work = d_work, p.llr_base = d_llr, p.out_base = d_out, p.results = d_res, p.pair_counter = d_pair_counter;
   p.rm_base = d_rm, p.soft_rw = const_cast<int8_t*>(d_llr);
   const bool fused = d_rm != nullptr;
   p.nof_cbs = n, p.Z = gp.Z, p.Z4 = 4 * gp.Z, p.max_iterations = gp.max_iterations;
   p.zpad = ((gp.Z + 31) / 32) * 32;
-  p.groups = TM_THREADS / p.zpad;
+  // Decode-only blocks run up to 512 threads (the kernel fits 128 registers): floor(512 / roundup32(Z)) groups, e.g. 4
+  // instead of 3 at Z = 128 and 2 instead of 1 for Z in (192, 256]. Above 12 warps a warp owns 128 TMEM columns instead
+  // of 170, and the message words of the last rows go to shared memory. The fused kernel needs 168 registers: 384.
+  // (Single-warp groups, Z <= 32, lose 4 - 12 % with 15 instead of 12 groups: they stay at 384.)
+  const int max_threads = (fused || gp.Z == MAX_Z || p.zpad < 64) ? TM_THREADS : TM_THREADS_WIDE;
+  p.groups = std::min(max_threads / p.zpad, 15);  // named barriers 1 .. 15
   const TmLayout lay = tm_layout(gp.bg, gp.Z, p.zpad, fused);
   p.group_stride = lay.total;
   const unsigned n_pairs = (n + 1) / 2;
   if ((unsigned)p.groups > n_pairs) {
     p.groups = (int)n_pairs;
   }
-  size_t smem = TM_CRC_TABLE_BYTES + (size_t)p.groups * lay.total;
+  size_t smem = 0;
+  for (;; --p.groups) {
+    const unsigned threads = (unsigned)(p.groups * p.zpad);
+    const unsigned cap = threads > (unsigned)TM_THREADS ? TM_COLS_PER_WARP_WIDE : TM_COLS_PER_WARP;
+    if (!tm_build_tables(gp.bg, gp.Z, gp.lifting_set, p, cap)) {
+      return 1;
+    }
+    p.ovf_stride = 4u * threads;
+    smem = TM_CRC_TABLE_BYTES + (size_t)p.groups * lay.total + (size_t)p.ovf_words * p.ovf_stride;
+    if (smem <= TM_SMEM_LIMIT || p.groups == 1) {
+      break;
+    }
+  }
   if (smem > TM_SMEM_LIMIT) {
     return 1;
   }
