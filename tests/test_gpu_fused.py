@@ -327,3 +327,47 @@ def test_no_early_stop_half_beside_an_early_finisher(dec, bg, Z):
             assert (out[i * kb:(i + 1) * kb] == bits).all()
             stopped_early += ok and it < max_iters - 1
         assert stopped_early >= 2 and all(w[1] for w in want)
+
+
+@pytest.mark.parametrize("Qm", [2, 4, 6, 8])
+def test_wordwise_scatter_first_transmissions(dec, Qm):
+    """First transmissions whose geometry is word aligned (E / Qm, the start rank and the filler range multiples of 4) take
+    the word-wise scatter of the fused prologue (four symbols transposed in registers, 32-bit shared-memory stores, both
+    codeblocks of a pair at once); the same shapes with one parameter off by one symbol / one filler bit take the byte-wise
+    scatter. Pairs mix the two. Soft buffers, bits and results equal the oracle's
+    (ldpc_rate_dematcher_impl.cpp:125-254, deinterleave :200-210)."""
+    rng = np.random.default_rng(60 + Qm)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    cbs = []
+    so = oo = ro = 0
+    for bg, Z in [(1, 384), (2, 384), (1, 96), (2, 36), (1, 208)]:
+        K, N = O.BG_K[bg] * Z, O.BG_N_SHORT[bg] * Z
+        for F, extra in [(0, 0), (16, 0), (16, 1), (6, 0), (0, 2), (16, 0)]:
+            E = (int(1.2 * K) // (4 * Qm) + extra) * 4 * Qm if extra != 1 else (int(1.2 * K) // (4 * Qm)) * 4 * Qm + Qm
+            msg, cw = O.make_codeword(rng, bg, Z, F, O.CRC24B if K > 100 else O.CRC16)
+            crc = O.CRC24B if K > 100 else O.CRC16
+            rm = O.awgn_llrs(rng, O.port().rate_match(cw, E, 0, Qm, 0, F), 2.0 + 1.5 * Qm / 2 - (2.5 if bg == 2 else 0))
+            cbs.append(dict(bg=bg, Z=Z, N=N, F=F, E=E, crc=crc, rm=rm, so=so, oo=oo, ro=ro, kb=(K + 7) // 8))
+            so += N
+            oo += (K + 7) // 8
+            ro += E
+    dec.softbuffer_reserve(so)
+    dec.softbuffer_write(0, rng.integers(-120, 121, so).astype(np.int8))  # stale contents must not leak into new data
+    descs = np.zeros(len(cbs), pkg.CB_DESC)
+    for i, c in enumerate(cbs):
+        d = descs[i]
+        d["base_graph"], d["lifting_size"], d["nof_filler_bits"], d["crc_poly"] = c["bg"], c["Z"], c["F"], c["crc"]
+        d["early_stop"], d["rv"], d["mod_order"], d["Nref"], d["new_data"] = 1, 0, Qm, 0, 1
+        d["rm_length"], d["in_offset"], d["out_offset"], d["soft_offset"] = c["E"], c["ro"], c["oo"], c["so"]
+        d["in_length"] = c["N"]
+    out, res = dec.dematch_decode_batch(descs, np.concatenate([c["rm"] for c in cbs]), np.zeros(oo, np.uint8))
+    arena = dec.softbuffer_read(0, so)
+    passed = 0
+    for i, c in enumerate(cbs):
+        soft = np.zeros(c["N"], np.int8)
+        bits, ok, it = _oracle_tx(soft, c["rm"], True, c["bg"], c["Z"], 0, Qm, 0, c["F"], c["crc"], 1)
+        assert (arena[c["so"]:c["so"] + c["N"]] == soft).all(), (i, c["bg"], c["Z"], c["F"], c["E"])
+        assert bool(res["crc_ok"][i]) == ok and int(res["iterations"][i]) == it, (i, res[i], ok, it)
+        assert (out[c["oo"]:c["oo"] + c["kb"]] == bits).all(), i
+        passed += ok
+    assert passed > len(cbs) // 2
