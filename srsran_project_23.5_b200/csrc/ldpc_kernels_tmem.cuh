@@ -262,22 +262,23 @@ constexpr float TM_CAP = 65280.f;      // 544 * 120
 //  LUT     any other table (scaling factor != 0.8, the NEON variant's rounding): m = M / 544 read off the mantissa of
 //          fma(M, 1/544, 1024) = 1024 + m (ulp 1), one 16-bit shared-memory load per half of 544 * lut[m] as fp16 bits
 template <int SCALE>
-__device__ __forceinline__ unsigned scale_q(unsigned M, unsigned lut = 0)
+__device__ __forceinline__ unsigned scale_q(unsigned M, unsigned lut = 0, unsigned fifth = 0x0e060e06u)
 {
-  const unsigned magic = hc(1536.f), fifth = hc(0.2f / TM_S), nS = hc(-TM_S);
+  // |M| throughout (an operand modifier): min1 arrives with the sign parity of the row in its sign bits
+  const unsigned magic = hc(1536.f), nS = hc(-TM_S);
   if (SCALE == TM_SCALE_LUT) {
-    const unsigned idx = hfma(M, hc(1.f / TM_S), hc(1024.f));
+    const unsigned idx = hfma_abs(M, hc(1.f / TM_S), hc(1024.f));
     unsigned qa, qb;
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(qa) : "r"(lut + 2u * (idx & 0x3ffu)));
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(qb) : "r"(lut + 2u * ((idx >> 16) & 0x3ffu)));
     return qa | (qb << 16);
   } else if (SCALE == TM_SCALE_GENERIC_08) {
-    const unsigned r = hsub(hfma(M, fifth, magic), magic);
-    return hfma(r, nS, M);
+    const unsigned r = hsub(hfma_abs(M, fifth, magic), magic);
+    return un(__hfma2(h2(r), h2(nS), __habs2(h2(M))));
   } else {
-    const unsigned r = hsub(hfma(hsub(M, hc(2.f * TM_S)), fifth, magic), magic);
-    const unsigned nz = hfma_sat(M, hc(1.f), hc(0.f));
-    return hfma(nz, nS, hfma(r, nS, M));
+    const unsigned r = hsub(hfma(un(__hsub2(__habs2(h2(M)), h2(hc(2.f * TM_S)))), fifth, magic), magic);
+    const unsigned nz = un(__hfma2_sat(__habs2(h2(M)), h2(hc(1.f)), h2(hc(0.f))));
+    return hfma(nz, nS, un(__hfma2(h2(r), h2(nS), __habs2(h2(M)))));
   }
 }
 
@@ -288,8 +289,10 @@ struct MinPair {
 __device__ __forceinline__ MinPair merge(MinPair a, MinPair b)
 {
   MinPair r;
-  r.m1 = hmin(a.m1, b.m1);  // non-negative halves: fp16 order == integer order; these two go to the FP16 pipe, which
-  r.m2 = umin3(hmax(a.m1, b.m1), a.m2, b.m2);  // is the idler one while the minima are formed
+  // m1 carries the sign parity of its set in its sign bits (XORSIGN), m2 is a non-negative bit pattern (fp16 order ==
+  // integer order)
+  r.m1 = hmin_xorsign_abs(a.m1, b.m1);
+  r.m2 = umin3(hmax_abs(a.m1, b.m1), a.m2, b.m2);
   return r;
 }
 // Tree reduction over N sorted pairs.
@@ -324,6 +327,7 @@ struct Ctx {
   unsigned tm_cap;     // words of that block; message words beyond it live in shared memory:
   unsigned ovf;        //   shared address of this thread's overflow word 0, word i at + i * ovf_stride
   unsigned ovf_stride;
+  unsigned k64, k12, kfifth, kinv;  // constants the row bodies want in registers (see the kernel)
   unsigned lut;        // TM_SCALE_LUT: shared address of the scaling table (fp16 bit patterns of 544 * lut[m])
   bool active;         // lane < Z
 };
@@ -387,40 +391,38 @@ struct Row {
     const unsigned cap = hc(TM_CAP), nS = hc(-TM_S);
 #pragma unroll
     for (int k = 0; k < D; ++k) {
-      const unsigned tb = __byte_perm(cw[k >> 1], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+      const unsigned tb = __byte_perm(cw[k >> 1], c.k64, (k & 1) ? 0x4342 : 0x4140);
       // variable-to-check message (compute_var_to_check_msgs): difference (overflowing beyond +-120), then the clamp of
       // operator- for a finite soft value / the pass-through of an infinite one
       const unsigned d = hfma(hsub(tb, hc(1152.f)), nS, u[k]);
-      const unsigned lim = hfma_abs(u[k], hc(0.000244140625f), cap);  // 65280, or +inf for an infinite soft value
+      const unsigned lim = hfma_abs(u[k], c.k12, cap);  // 65280, or +inf for an infinite soft value
       u[k] = hmin_xorsign_abs(d, lim);
     }
     // analyze_var_to_check_msgs (ldpc_decoder_generic.cpp:53-78): min1, min2 (capped at 120), sign parity
-    constexpr int NP = (NV + 2) / 2;  // sorted pairs, including the cap (120, 120)
+    // Sorted pairs; the sign bits of m1 accumulate the sign parity of the values on the way (min.xorsign.abs), the cap
+    // (120, 120) enters as the partner of an odd last value or as a final clamp.
+    constexpr int NP = (NV + 1) / 2;
     MinPair pr[NP];
 #pragma unroll
     for (int i = 0; i < NV / 2; ++i) {
-      pr[i].m1 = hmin_abs(u[2 * i], u[2 * i + 1]);
+      pr[i].m1 = hmin_xorsign_abs(u[2 * i], u[2 * i + 1]);
       pr[i].m2 = hmax_abs(u[2 * i], u[2 * i + 1]);
     }
     if constexpr (NV & 1) {
-      pr[NP - 1].m1 = hmin_abs(u[NV - 1], cap);
-      pr[NP - 1].m2 = cap;
-    } else {
-      pr[NP - 1].m1 = cap;
+      pr[NP - 1].m1 = hmin_xorsign_abs(u[NV - 1], cap);
       pr[NP - 1].m2 = cap;
     }
-    const MinPair mm = reduce_pairs<NP>(pr);
-    unsigned S = 0;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      S ^= u[k];
+    MinPair mm = reduce_pairs<NP>(pr);
+    if constexpr (!(NV & 1)) {
+      mm.m1 = hmin_xorsign_abs(mm.m1, cap);
+      mm.m2 = hmin(mm.m2, cap);
     }
-    const unsigned T = S & SIGN2;
+    const unsigned T = mm.m1 & SIGN2;
     // scale_llr (ldpc_decoder_generic.cpp:80-89), sign parity folded in
-    const unsigned Q1 = scale_q<SCALE>(mm.m1, c.lut), Q2 = scale_q<SCALE>(mm.m2, c.lut);
+    const unsigned Q1 = scale_q<SCALE>(mm.m1, c.lut, c.kfifth), Q2 = scale_q<SCALE>(mm.m2, c.lut, c.kfifth);
     const unsigned Q2s = Q2 ^ T;
     const unsigned nD = hsub(Q1, Q2) ^ T;
-    const unsigned nM1 = mm.m1 ^ SIGN2;
+    const unsigned nM1 = mm.m1 | SIGN2;
     // compute_check_to_var_msgs (:93-116) + compute_soft_bits (:118-130)
     unsigned tn[D + 1];
 #pragma unroll
@@ -435,7 +437,7 @@ struct Row {
         if (FULL || c.active) {
           sts32(addr[k], n);
         }
-        tn[k] = hfma(cn, hc(1.f / TM_S), hc(1152.f));
+        tn[k] = hfma(cn, c.kinv, hc(1152.f));
       } else {
         // the message becomes +-inf once the soft value is promoted (sign of the sum = sign of the message then)
         const unsigned prom = __heq2_mask(__habs2(h2(n)), h2(0x7c007c00u));
@@ -652,13 +654,13 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
   volatile unsigned* flags = reinterpret_cast<volatile unsigned*>(gsm + lay.flags);
 
   tm::Ctx c;
-  c.soft_base = (unsigned)__cvta_generic_to_shared(soft_w);
+  c.soft_base = (unsigned)tm::uniform((int)(unsigned)__cvta_generic_to_shared(soft_w));
   c.ext_soft = (unsigned)__cvta_generic_to_shared(ext_soft_w + t);
   c.t4 = 4u * (unsigned)t;
   c.Z4 = (unsigned)p.Z4;
   c.zpad4 = 4u * (unsigned)zpad;
   const unsigned tmem_base = *reinterpret_cast<volatile unsigned*>(smem + 3 * 256 * 4);
-  c.tm_addr = tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * (unsigned)p.tm_cap;
+  c.tm_addr = (unsigned)tm::uniform((int)(tmem_base + (((unsigned)(warp & 3) * 32u) << 16) + (unsigned)(warp >> 2) * (unsigned)p.tm_cap));
   c.tm_cap = p.tm_cap;
   c.ovf_stride = p.ovf_stride;
   // overflow message words (blocks of more than 12 warps): behind the groups' buffers, word i of thread tid at
@@ -666,6 +668,15 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
   c.ovf = (unsigned)__cvta_generic_to_shared(smem + TM_CRC_TABLE_BYTES + (size_t)p.groups * p.group_stride) + 4u * (unsigned)tid;
   c.lut = (unsigned)__cvta_generic_to_shared(smem);
   c.active = FULL || t < Z;
+  {
+    // Constants that are the register operand of a PRMT / HFMA2 in every edge: derived from a kernel parameter so that the
+    // compiler keeps them in registers instead of rebuilding them (IMAD.MOV + PRMT) in front of every use.
+    const unsigned zero = (unsigned)p.max_iterations >> 31;
+    c.k64 = 0x64646464u | zero;
+    c.k12 = tm::hc(0.000244140625f) | zero;
+    c.kfifth = tm::hc(0.2f / tm::TM_S) | zero;
+    c.kinv = tm::hc(1.f / tm::TM_S) | zero;
+  }
 
   // FUSED: the pair after the current one is claimed one pair early so that its rate-matched LLRs (and previous soft
   // bits) can be pulled into L2 while this pair is decoded (+3.4 % on the full-slot workload; for the plain decoder the
@@ -1163,6 +1174,7 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
+#ifndef LDPC_TM_DEVICE_ONLY  // development builds of a single kernel instantiation (tools/sass_one.sh) stop here
 static inline int tm_scale_variant(const unsigned char* lut)
 {
   bool gen = true, avx = true;
@@ -1402,5 +1414,6 @@ static inline int launch_tmem_decode(const GroupParams& gp, int scale_variant, c
   return gen ? tm_launch_fused_or_not<2, TM_SCALE_GENERIC_08>(fused, p, smem, grid, device, stream)
              : tm_launch_fused_or_not<2, TM_SCALE_AVX_08>(fused, p, smem, grid, device, stream);
 }
+#endif  // LDPC_TM_DEVICE_ONLY
 
 }  // namespace ldpc_b200
