@@ -136,6 +136,9 @@ void* ldpc_cuda_stream(ldpc_cuda_handle* handle);
 int   ldpc_cuda_synchronize(ldpc_cuda_handle* handle);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches claim). */
 uint64_t ldpc_cuda_launch_count(const ldpc_cuda_handle* handle);
+/* How many of those were launches of the general (one codeblock per block, any configuration) decoder kernel instead of the
+ * tensor-memory kernel: 0 unless LDPC_CUDA_FLAG_FORCE_SCALAR is set or the configuration is not covered (tests assert it). */
+uint64_t ldpc_cuda_general_kernel_launch_count(const ldpc_cuda_handle* handle);
 
 /* ---------------------------------------------------------------------------------------------------------------------
  * Drop-in, one codeblock per call, host buffers, synchronous (what the reference interfaces need).

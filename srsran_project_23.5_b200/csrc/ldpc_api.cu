@@ -67,6 +67,7 @@ struct ldpc_cuda_handle {
   bool arena_owned = false;  // false: attached, belongs to a pool shared between handles
   unsigned* pair_counter = nullptr;  // packed kernel: dynamic work distribution
   uint64_t launches = 0;
+  uint64_t general_launches = 0;  // of those: the general decoder kernel (fallback)
   // transport-block assembly: work records + accumulators, and the output staging of the host entry
   uint8_t* d_tbwork = nullptr;
   size_t d_tbwork_cap = 0;
@@ -366,6 +367,7 @@ int launch_decode_group(ldpc_cuda_handle* h, int bg, int Z, const CbWork* d_work
   ldpc_decode_scalar_kernel<<<grid, threads, smem, stream>>>(gp, d_work, n, d_llr, d_out, d_res);
   CUDA_TRY(cudaGetLastError());
   h->launches += 1;
+  h->general_launches += 1;
   return LDPC_CUDA_OK;
 }
 
@@ -1012,6 +1014,7 @@ int ldpc_cuda_synchronize(ldpc_cuda_handle* h)
 }
 
 uint64_t ldpc_cuda_launch_count(const ldpc_cuda_handle* h) { return h ? h->launches : 0; }
+uint64_t ldpc_cuda_general_kernel_launch_count(const ldpc_cuda_handle* h) { return h ? h->general_launches : 0; }
 
 // ---- batched, device buffers ----------------------------------------------------------------------------------------
 int ldpc_cuda_decode_batch_device(ldpc_cuda_handle* h, uint32_t n, const ldpc_cuda_cb_desc* descs, const int8_t* llrs_d,

@@ -97,11 +97,18 @@ struct TmemParams {
   int groups;       // codeblock pairs processed concurrently by one block
   int max_iterations;
   unsigned group_stride;  // bytes of shared memory per group
-  unsigned char rowcls[LDPC_BG1_M];    // per row: 2 * (number of high-rate edges) + (1 if the row has an extension node)
-  unsigned short rowedge[LDPC_BG1_M];  // per row: index of its first entry in edge[]
-  unsigned short rowtm[LDPC_BG1_M];    // per row: first TMEM word (relative to the warp's column block)
-  unsigned rowdesc[LDPC_BG1_M + 2];    // per row: rowcls | rowedge << 8 | rowtm << 20 (one uniform load per row)
-  unsigned pairdesc[LDPC_BG1_M + 2];   // per row r: 0, or the descriptor of the pair (r, r + 1) that starts at r (pair_dispatch)
+  // per row: class | first entry in edge[] << 8 | first message word << 20. class = 2 * (number of high-rate edges) + (1 if
+  // the row has an extension node); message word: TMEM word relative to the warp's column block (see tm_cap)
+  unsigned rowdesc[LDPC_BG1_M + 2];
+  // The schedule of one iteration: a step is one row, or two consecutive rows without a common high-rate column.
+  //   x = class | rows of the step << 8                               (pair class: 16 * DA + DB, DA >= DB)
+  //   y = first edge | first message word << 16 of row A, z = the same of row B
+  //   w = byte offset of the extension node's word of row A | of row B << 16 (behind the thread's word of row 4)
+  // One 16-byte uniform load per step, fetched one step ahead; a zero sentinel follows the last step.
+  uint4 steps[LDPC_BG1_M + 1];
+  // per number of layers L: steps that cover rows [0, L) | rows they cover << 8. A layer limit inside a pair runs the whole
+  // pair: the surplus row sees an all-zero extension node (the kernel clears its word) and leaves every soft value as it is.
+  unsigned short layer_steps[LDPC_BG1_M + 2];
   unsigned short tm_words;             // TMEM words used per thread
   unsigned short tm_cap;               // TMEM words a thread owns (rowtm >= tm_cap: overflow word rowtm - tm_cap in shared memory)
   unsigned short ovf_words;            // overflow words per thread
@@ -344,7 +351,7 @@ struct Row {
   unsigned addr[D], u[NV], cw[W];
   unsigned xaddr, tma;
 
-  __device__ __forceinline__ void pre(const Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw)
+  __device__ __forceinline__ void pre(const Ctx& c, const TmemParams& p, unsigned xoff, int e0, unsigned tmw)
   {
     // previous messages of the row (thread-private TMEM columns); the latency overlaps the shared-memory loads. Blocks of
     // more than 12 warps own 128 columns per warp: the last rows' messages are thread-private shared-memory words then.
@@ -371,7 +378,7 @@ struct Row {
     // stored check-to-variable message.
     xaddr = 0;
     if constexpr (EXT) {
-      xaddr = c.ext_soft + (unsigned)(r - 4) * (FULL ? 4u * MAX_Z : c.zpad4);
+      xaddr = c.ext_soft + xoff;
       u[D] = lds32(xaddr);  // thread-private: no ordering with other threads needed
     }
   }
@@ -464,11 +471,11 @@ struct Row {
 };
 
 template <int D, bool EXT, int SCALE, int MODE>
-__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int e0, unsigned tmw, int bar_id, int zpad)
+__device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, unsigned xoff, int e0, unsigned tmw, int bar_id, int zpad)
 {
   constexpr bool FULL = MODE == TM_MODE_FULL;
   Row<D, EXT, SCALE, MODE> R;
-  R.pre(c, p, r, e0, tmw);
+  R.pre(c, p, xoff, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
   group_barrier<FULL>(bar_id, zpad);
@@ -483,14 +490,14 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, int r, int
 // dispatch work for these (short) rows. In both 5G base graphs most rows of the extension part are pairwise orthogonal
 // to their successor (BG1: 14 pairs among rows 16-45, BG2: 13).
 template <int DA, int DB, int SCALE, int MODE>
-__device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, int e0A, unsigned tmwA, int rB, int e0B,
+__device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, unsigned xoffA, int e0A, unsigned tmwA, unsigned xoffB, int e0B,
                                           unsigned tmwB, int bar_id, int zpad)
 {
   constexpr bool FULL = MODE == TM_MODE_FULL;
   Row<DA, true, SCALE, MODE> A;
   Row<DB, true, SCALE, MODE> B;
-  A.pre(c, p, rA, e0A, tmwA);
-  B.pre(c, p, rB, e0B, tmwB);
+  A.pre(c, p, xoffA, e0A, tmwA);
+  B.pre(c, p, xoffB, e0B, tmwB);
   group_barrier<FULL>(bar_id, zpad);
   A.load();
   B.load();
@@ -499,16 +506,38 @@ __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, int rA, i
   B.compute(c);
 }
 
-template <int SCALE, int MODE>
-__device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r, int bar_id, int zpad, unsigned rd)
+// One step of the schedule (TmemParams::steps): single-row classes are < 40, pair classes (16 * DA + DB) >= 50.
+constexpr bool tm_row_used(int bg, int d, bool ext)
 {
-  const int cls = rd & 0xffu;
-  const int e0 = (rd >> 8) & 0xfffu;
-  const unsigned tmw = rd >> 20;
+  return bg == 1 ? (ext ? (d == 2 || (d >= 5 && d <= 9)) : d == 19) : (ext ? (d >= 3 && d <= 5) : (d == 8 || d == 10));
+}
+constexpr bool tm_pair_used(int bg, int da, int db)
+{
+  return bg == 1 ? ((da == 5 && (db == 5 || db == 4)) || (da == 4 && (db == 4 || db == 3)))
+                 : ((da == 4 && (db == 3 || db == 2)) || (da == 3 && (db == 3 || db == 2)));
+}
+
+// Only the row shapes the base graph has are compiled into its kernels (tm_build_tables checks the schedule against the
+// same predicates).
+template <int BG, int SCALE, int MODE>
+__device__ __forceinline__ void step_dispatch(Ctx& c, const TmemParams& p, int bar_id, int zpad, const uint4 st)
+{
+  const int cls = st.x & 0xffu;
+  const unsigned xoffA = st.w & 0xffffu, xoffB = st.w >> 16;
+  const int e0A = st.y & 0xffffu, e0B = st.z & 0xffffu;
+  const unsigned tmwA = st.y >> 16, tmwB = st.z >> 16;
   switch (cls) {
 #define LDPC_TM_CASE(D, EXT)                        \
   case 2 * (D) + (EXT):                             \
-    row_body<D, (EXT) != 0, SCALE, MODE>(c, p, r, e0, tmw, bar_id, zpad); \
+    if constexpr (tm_row_used(BG, D, (EXT) != 0)) {  \
+      row_body<D, (EXT) != 0, SCALE, MODE>(c, p, xoffA, e0A, tmwA, bar_id, zpad); \
+    }                                               \
+    break;
+#define LDPC_TM_PAIR(DA, DB)                                                                   \
+  case 16 * (DA) + (DB):                                                                       \
+    if constexpr (tm_pair_used(BG, DA, DB)) {                                                  \
+      pair_body<DA, DB, SCALE, MODE>(c, p, xoffA, e0A, tmwA, xoffB, e0B, tmwB, bar_id, zpad);  \
+    }                                                                                          \
     break;
     LDPC_TM_CASE(2, 1)
     LDPC_TM_CASE(3, 1)
@@ -521,26 +550,6 @@ __device__ __forceinline__ void row_dispatch(Ctx& c, const TmemParams& p, int r,
     LDPC_TM_CASE(8, 0)
     LDPC_TM_CASE(10, 0)
     LDPC_TM_CASE(19, 0)
-#undef LDPC_TM_CASE
-    default:
-      break;
-  }
-}
-
-// pd: pair class (16 * DA + DB, DA >= DB) | row index of A << 8 | row index of B << 16; the rows' own descriptors give
-// their edge / TMEM offsets.
-template <int SCALE, int MODE>
-__device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int bar_id, int zpad, unsigned pd, unsigned rdA,
-                                              unsigned rdB)
-{
-  const int cls = pd & 0xffu, rA = (pd >> 8) & 0xffu, rB = (pd >> 16) & 0xffu;
-  const int e0A = (rdA >> 8) & 0xfffu, e0B = (rdB >> 8) & 0xfffu;
-  const unsigned tmwA = rdA >> 20, tmwB = rdB >> 20;
-  switch (cls) {
-#define LDPC_TM_PAIR(DA, DB)                                                                   \
-  case 16 * (DA) + (DB):                                                                       \
-    pair_body<DA, DB, SCALE, MODE>(c, p, rA, e0A, tmwA, rB, e0B, tmwB, bar_id, zpad);                \
-    break;
     LDPC_TM_PAIR(5, 5)
     LDPC_TM_PAIR(5, 4)
     LDPC_TM_PAIR(4, 4)
@@ -549,13 +558,10 @@ __device__ __forceinline__ void pair_dispatch(Ctx& c, const TmemParams& p, int b
     LDPC_TM_PAIR(3, 3)
     LDPC_TM_PAIR(3, 2)
 #undef LDPC_TM_PAIR
+#undef LDPC_TM_CASE
     default:
       break;
   }
-}
-constexpr bool tm_pair_supported(int da, int db)
-{
-  return (da == 5 && (db == 5 || db == 4)) || (da == 4 && db >= 2 && db <= 4) || (da == 3 && (db == 3 || db == 2));
 }
 
 // Byte j of a and of b (selector 0x0400 + 0x0101 j) as a scaled half2: byte ^ 0x80 under a 0x64 high byte is the fp16
@@ -943,6 +949,15 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
       return (int)(cb_len / Z) - K;
     };
     const int nof_layers = tm::uniform(max(doneA ? 4 : layers_of(inszA), doneB ? 4 : layers_of(inszB)));
+    // The schedule runs whole steps: when the layer limit falls between the two rows of a pair the second row runs too. Its
+    // extension node lies behind the last non-zero LLR of both codeblocks: with that (thread-private) word at zero the
+    // row's minimum is zero, every message to a high-rate node is zero and no soft value changes - the same argument that
+    // lets the two codeblocks of a pair run the larger of their layer counts.
+    const unsigned lsteps = p.layer_steps[nof_layers];
+    const int nof_steps = (int)(lsteps & 0xffu), layers_run = (int)(lsteps >> 8);
+    if (layers_run > nof_layers && c.active) {
+      ext_soft_w[(nof_layers - 4) * zpad + t] = 0;
+    }
     {
       // all messages of the layers that will run start at zero (biased bytes)
       unsigned init[8];
@@ -951,7 +966,7 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
         init[i] = 0x80808080u;
       }
       // first message word behind the layers that run: a TMEM word, or tm_cap + an overflow word
-      const int first_free = (nof_layers < M) ? (int)(p.rowdesc[nof_layers] >> 20) : (int)p.tm_cap + (int)p.ovf_words;
+      const int first_free = (layers_run < M) ? (int)(p.rowdesc[layers_run] >> 20) : (int)p.tm_cap + (int)p.ovf_words;
       const int words = min(first_free, (int)p.tm_words);
       for (int w = 0; w < words; w += 8) {
         tm::tm_st8(c.tm_addr + w, init);
@@ -984,16 +999,12 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
     TM_PHASE(4);  // input size, layers, TMEM reset, prefetch of the next pair
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
-      for (int r = 0; r < nof_layers;) {
-        // the barrier that orders a row after its predecessor is inside the bodies
-        const unsigned rd = p.rowdesc[r], pd = p.pairdesc[r];
-        if (pd != 0 && r + 1 < nof_layers) {
-          tm::pair_dispatch<SCALE, MODE>(c, p, bar_id, zpad, pd, p.rowdesc[(pd >> 8) & 0xffu], p.rowdesc[(pd >> 16) & 0xffu]);
-          r += 2;
-        } else {
-          tm::row_dispatch<SCALE, MODE>(c, p, r, bar_id, zpad, rd);
-          r += 1;
-        }
+      // the barrier that orders a row after its predecessor is inside the bodies
+      uint4 next = p.steps[0];
+      for (int s = 0; s < nof_steps; ++s) {
+        const uint4 st = next;
+        next = p.steps[s + 1];  // the descriptor of the step after this one travels under this step's arithmetic
+        tm::step_dispatch<BG, SCALE, MODE>(c, p, bar_id, zpad, st);
       }
       tm::group_barrier<FULL>(bar_id, zpad);
       tm::tm_wait_st();
@@ -1244,7 +1255,7 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
   p.tm_cap = (unsigned short)tm_cap;
   for (int r = 0; r != M; ++r) {
     unsigned d = 0, ext = 0;
-    p.rowedge[r] = (unsigned short)ne;
+    const unsigned row_edge = ne;
     for (int e = row_ptr[r]; e != row_ptr[r + 1]; ++e) {
       if (col[e] < hrr) {
         p.edge[ne].s4 = 4u * (shift[e] % (unsigned)Z);
@@ -1262,38 +1273,59 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
     if (!ok) {
       return false;
     }
-    p.rowcls[r] = (unsigned char)(2 * d + ext);
     const unsigned w = (d + 1) / 2;
+    unsigned row_tm;
     spilled = spilled || tmw + w > (tm_cap & ~7u);
     if (spilled) {
-      p.rowtm[r] = (unsigned short)(tm_cap + ovf);
+      row_tm = tm_cap + ovf;
       ovf += w;
     } else {
-      p.rowtm[r] = (unsigned short)tmw;
+      row_tm = tmw;
       tmw += w;
     }
-    p.rowdesc[r] = (unsigned)p.rowcls[r] | ((unsigned)p.rowedge[r] << 8) | ((unsigned)p.rowtm[r] << 20);
+    p.rowdesc[r] = (2 * d + ext) | (row_edge << 8) | (row_tm << 20);
   }
   p.tm_words = (unsigned short)tmw;
   p.ovf_words = (unsigned short)ovf;
   // pairs of consecutive rows (both with an extension node) that share no high-rate column, chosen greedily in row order;
   // A is the row with the larger high-rate degree (the order inside a pair does not matter)
-  for (int r = 4; r + 1 < M;) {
-    bool disjoint = true;
-    for (int a = row_ptr[r]; a != row_ptr[r + 1] && disjoint; ++a) {
+  auto step_words = [&](int r, unsigned& y) { y = ((p.rowdesc[r] >> 8) & 0xfffu) | ((p.rowdesc[r] >> 20) << 16); };
+  const unsigned zpad4 = 4u * (((unsigned)Z + 31u) / 32u) * 32u;
+  auto ext_offset = [&](int r) { return r >= 4 ? (unsigned)(r - 4) * zpad4 : 0u; };  // < 2^16: 41 * 1536
+  unsigned ns = 0;
+  p.layer_steps[0] = 0;
+  for (int r = 0; r < M;) {
+    bool disjoint = r >= 4 && r + 1 < M;
+    for (int a = row_ptr[r]; disjoint && a != row_ptr[r + 1]; ++a) {
       for (int b = row_ptr[r + 1]; b != row_ptr[r + 2] && disjoint; ++b) {
         disjoint = !(col[a] == col[b] && col[a] < hrr);
       }
     }
-    const int d0 = p.rowcls[r] >> 1, d1 = p.rowcls[r + 1] >> 1;
+    const int d0 = (p.rowdesc[r] & 0xffu) >> 1, d1 = (r + 1 < M) ? (int)((p.rowdesc[r + 1] & 0xffu) >> 1) : 0;
     const int da = d0 >= d1 ? d0 : d1, db = d0 >= d1 ? d1 : d0;
-    if (disjoint && tm::tm_pair_supported(da, db)) {
+    uint4& st = p.steps[ns];
+    if (disjoint && tm::tm_pair_used(bg, da, db)) {
       const int rA = d0 >= d1 ? r : r + 1, rB = d0 >= d1 ? r + 1 : r;
-      p.pairdesc[r] = (unsigned)(16 * da + db) | ((unsigned)rA << 8) | ((unsigned)rB << 16);
+      st.x = (unsigned)(16 * da + db) | (2u << 8);
+      step_words(rA, st.y);
+      step_words(rB, st.z);
+      st.w = ext_offset(rA) | (ext_offset(rB) << 16);
+      p.layer_steps[r + 1] = p.layer_steps[r + 2] = (unsigned short)((ns + 1) | ((unsigned)(r + 2) << 8));
       r += 2;
     } else {
+      if (!tm::tm_row_used(bg, d0, r >= 4)) {
+        return false;  // a row shape the kernels of this base graph were not compiled for
+      }
+      st.x = (p.rowdesc[r] & 0xffu) | (1u << 8);
+      step_words(r, st.y);
+      st.z = 0, st.w = ext_offset(r);
+      p.layer_steps[r + 1] = (unsigned short)((ns + 1) | ((unsigned)(r + 1) << 8));
       r += 1;
     }
+    ++ns;
+  }
+  for (unsigned i = ns; i <= (unsigned)LDPC_BG1_M; ++i) {
+    p.steps[i] = make_uint4(0u, 0u, 0u, 0u);
   }
   return ((tmw + 7) & ~7u) <= tm_cap;
 }

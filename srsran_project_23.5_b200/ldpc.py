@@ -92,6 +92,8 @@ def library():
         L.ldpc_cuda_synchronize.argtypes = [vp]
         L.ldpc_cuda_launch_count.argtypes = [vp]
         L.ldpc_cuda_launch_count.restype = u64
+        L.ldpc_cuda_general_kernel_launch_count.argtypes = [vp]
+        L.ldpc_cuda_general_kernel_launch_count.restype = u64
         L.ldpc_cuda_decode.argtypes = [vp, vp, vp, vp, ctypes.POINTER(u32)]
         L.ldpc_cuda_rate_dematch.argtypes = [vp, vp, vp, vp]
         for name in ("ldpc_cuda_decode_batch", "ldpc_cuda_decode_batch_device", "ldpc_cuda_dematch_decode_batch",
@@ -223,6 +225,7 @@ class LdpcCuda:
             raise LdpcCudaError(rc, "ldpc_cuda_create")
         self._h = h
         self.device = device
+        self.flags = flags
         self.set_algorithm(max_iterations, scaling_factor, scale_mode)
 
     def close(self):
@@ -255,6 +258,10 @@ class LdpcCuda:
     @property
     def launch_count(self):
         return self._L.ldpc_cuda_launch_count(self._h)
+
+    @property
+    def general_kernel_launch_count(self):
+        return self._L.ldpc_cuda_general_kernel_launch_count(self._h)
 
     # -- drop-in, one codeblock ----------------------------------------------------------------------------------------
     def decode(self, bg, Z, llrs, fillers=0, crc=CRC_NONE, out=None):

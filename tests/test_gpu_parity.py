@@ -36,6 +36,7 @@ def test_decode_all_lifting_sizes(dec, bg):
     CRC early-stop decode at a shortened length with filler bits."""
     rng = np.random.default_rng(10 + bg)
     K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+    general0 = dec.general_kernel_launch_count
     for Z in O.LIFTING_SIZES:
         msg, cw = O.make_codeword(rng, bg, Z)
         llr = (10 * (1 - 2 * cw.astype(np.int16))).astype(np.int8)
@@ -48,6 +49,8 @@ def test_decode_all_lifting_sizes(dec, bg):
         noisy = O.awgn_llrs(rng, cw, -1.0 if bg == 1 else -3.5)
         n = (K + 2 + int(rng.integers(2, Ns - K - 1))) * Z
         check_decode(dec, bg, Z, noisy[:n], fillers=F, crc=crc, max_iters=6)
+    if not dec.flags & pkg.FLAG_FORCE_SCALAR:
+        assert dec.general_kernel_launch_count == general0, "a (BG, Z) fell back to the general decoder kernel"
 
 
 @pytest.mark.parametrize("bg,Z", [(1, 384), (1, 208), (2, 384), (2, 30)])
@@ -234,6 +237,41 @@ def test_batch_heterogeneous_codeblocks(dec):
         assert (out[o:o + bits.size] == bits).all(), i
         assert int(res["crc_ok"][i]) == int(ok), i
         assert int(res["iterations"][i]) == it, (i, res[i], it)
+
+
+@pytest.mark.parametrize("bg,Z", [(1, 384), (2, 384), (1, 112), (2, 36)])
+def test_batch_every_layer_count(dec, bg, Z):
+    """Every number of layers the input length can select (ldpc_decoder_impl.cpp:105-114), in pairs of unequal lengths:
+    the kernel's schedule runs rows two at a time where they share no column, so a layer limit that falls inside such a pair
+    (and a pair whose halves stop at different rows) must still give the reference's result. The tensor-memory kernel must
+    be the one that ran."""
+    rng = np.random.default_rng(300 + 10 * bg + Z)
+    dec.set_algorithm(6, 0.8, O.SCALE_GENERIC)
+    K, Ns = O.BG_K[bg], O.BG_N_SHORT[bg]
+    nodes = list(range(K + 2, Ns + 1))
+    nodes = nodes + [int(v) for v in rng.permutation(nodes)]  # equal-length pairs first, then mixed ones
+    msg, cw = O.make_codeword(rng, bg, Z, 0, O.CRC24B)
+    full = O.awgn_llrs(rng, cw, -0.5 - (2.5 if bg == 2 else 0))
+    kb = (K * Z + 7) // 8
+    descs = pkg.make_descs(len(nodes), bg, Z, crc_poly=pkg.CRC24B, in_stride=Ns * Z)
+    llrs = np.zeros((len(nodes), Ns * Z), np.int8)
+    for i, n in enumerate(nodes):
+        descs["in_length"][i] = n * Z
+        llrs[i, :n * Z] = full[:n * Z]
+        descs["early_stop"][i] = i % 3 != 0  # some halves run all iterations beside an early finisher
+    general0 = dec.general_kernel_launch_count
+    out, res = dec.decode_batch(descs, llrs.reshape(-1))
+    if not dec.flags & pkg.FLAG_FORCE_SCALAR:
+        assert dec.general_kernel_launch_count == general0
+    for i, n in enumerate(nodes):
+        if descs["early_stop"][i]:
+            bits, it = O.port().decode(bg, Z, llrs[i, :n * Z], crc=O.CRC24B)
+            want_it, ok = (it if it else 6), it > 0
+        else:
+            bits, _ = O.port().decode(bg, Z, llrs[i, :n * Z], crc=O.CRC_NONE)
+            want_it, ok = 6, O.port().crc(O.CRC24B, bits, K * Z) == 0
+        assert (out[i * kb:(i + 1) * kb] == bits).all(), (bg, Z, i, n)
+        assert int(res["iterations"][i]) == want_it and int(res["crc_ok"][i]) == int(ok), (bg, Z, i, n, res[i])
 
 
 def test_batch_many_pairs_iteration_counts(dec):
