@@ -174,6 +174,32 @@ __device__ __forceinline__ void group_barrier(int id, int nthreads)
   }
 }
 
+// ---- the row barrier, split ------------------------------------------------------------------------------------------
+// A row may read the soft values only after every warp of the group has stored the previous row's. With bar.sync a warp
+// that is ahead waits until the LAST warp has reached its own barrier instruction, i.e. has also finished the dispatch and
+// address arithmetic of the next row. An mbarrier separates the two halves: a warp arrives as soon as its stores are
+// out (one elected lane, after __syncwarp), works out the next row, and only then waits - for the arrivals, not for the
+// other warps' progress beyond them.
+__device__ __forceinline__ void row_arrive(unsigned bar, unsigned t4)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void row_wait(unsigned bar, unsigned& parity)
+{
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "ROW_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra ROW_DONE;\n"
+      "bra ROW_WAIT;\n"
+      "ROW_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+  parity ^= 1u;
+}
+
 // ---- tensor memory as thread-private message storage (shape 32x32b: thread i of the warp <-> TMEM lane base + i) -----
 __device__ __forceinline__ void tm_ld8(unsigned ta, unsigned* r)
 {
@@ -335,6 +361,8 @@ struct Ctx {
   unsigned ovf;        //   shared address of this thread's overflow word 0, word i at + i * ovf_stride
   unsigned ovf_stride;
   unsigned k64, k12, kfifth, kinv;  // constants the row bodies want in registers (see the kernel)
+  unsigned row_bar;    // shared address of the group's row mbarrier
+  unsigned row_parity; // phase the next row_wait waits for
   unsigned lut;        // TM_SCALE_LUT: shared address of the scaling table (fp16 bit patterns of 544 * lut[m])
   bool active;         // lane < Z
 };
@@ -478,10 +506,11 @@ __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, unsigned x
   R.pre(c, p, xoff, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
   // message load, addresses, extension node) runs while slower warps finish the previous row.
-  group_barrier<FULL>(bar_id, zpad);
+  row_wait(c.row_bar, c.row_parity);
   R.load();
   tm_wait_ld();
   R.compute(c);
+  row_arrive(c.row_bar, c.t4);
 }
 
 // Two consecutive rows WITHOUT a common high-rate column (their extension columns are private anyway): they read and
@@ -498,12 +527,13 @@ __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, unsigned 
   Row<DB, true, SCALE, MODE> B;
   A.pre(c, p, xoffA, e0A, tmwA);
   B.pre(c, p, xoffB, e0B, tmwB);
-  group_barrier<FULL>(bar_id, zpad);
+  row_wait(c.row_bar, c.row_parity);
   A.load();
   B.load();
   tm_wait_ld();
   A.compute(c);
   B.compute(c);
+  row_arrive(c.row_bar, c.t4);
 }
 
 // One step of the schedule (TmemParams::steps): single-row classes are < 40, pair classes (16 * DA + DB) >= 50.
@@ -674,6 +704,11 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
   c.ovf = (unsigned)__cvta_generic_to_shared(smem + TM_CRC_TABLE_BYTES + (size_t)p.groups * p.group_stride) + 4u * (unsigned)tid;
   c.lut = (unsigned)__cvta_generic_to_shared(smem);
   c.active = FULL || t < Z;
+  c.row_bar = (unsigned)tm::uniform((int)(unsigned)__cvta_generic_to_shared(gsm + lay.flags + 56));  // flags[14..15]
+  c.row_parity = 0;
+  if (t == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(c.row_bar), "r"(zpad) : "memory");
+  }
   {
     // Constants that are the register operand of a PRMT / HFMA2 in every edge: derived from a kernel parameter so that the
     // compiler keeps them in registers instead of rebuilding them (IMAD.MOV + PRMT) in front of every use.
@@ -1000,13 +1035,14 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
     int it = 0;
     while (tm::uniform((it < p.max_iterations && !(doneA && doneB)) ? 1 : 0)) {
       // the barrier that orders a row after its predecessor is inside the bodies
+      tm::row_arrive(c.row_bar, c.t4);  // every row waits for its predecessor's arrivals: these stand in for the first one's
       uint4 next = p.steps[0];
       for (int s = 0; s < nof_steps; ++s) {
         const uint4 st = next;
         next = p.steps[s + 1];  // the descriptor of the step after this one travels under this step's arithmetic
         tm::step_dispatch<BG, SCALE, MODE>(c, p, bar_id, zpad, st);
       }
-      tm::group_barrier<FULL>(bar_id, zpad);
+      tm::row_wait(c.row_bar, c.row_parity);  // the last row's arrivals
       tm::tm_wait_st();
       TM_PHASE(5);  // row passes of one iteration
       ++it;
