@@ -501,7 +501,6 @@ struct Row {
 template <int D, bool EXT, int SCALE, int MODE>
 __device__ __forceinline__ void row_body(Ctx& c, const TmemParams& p, unsigned xoff, int e0, unsigned tmw, int bar_id, int zpad)
 {
-  constexpr bool FULL = MODE == TM_MODE_FULL;
   Row<D, EXT, SCALE, MODE> R;
   R.pre(c, p, xoff, e0, tmw);
   // The layered schedule orders rows through the shared soft values only: everything above (row descriptor, dispatch,
@@ -522,7 +521,6 @@ template <int DA, int DB, int SCALE, int MODE>
 __device__ __forceinline__ void pair_body(Ctx& c, const TmemParams& p, unsigned xoffA, int e0A, unsigned tmwA, unsigned xoffB, int e0B,
                                           unsigned tmwB, int bar_id, int zpad)
 {
-  constexpr bool FULL = MODE == TM_MODE_FULL;
   Row<DA, true, SCALE, MODE> A;
   Row<DB, true, SCALE, MODE> B;
   A.pre(c, p, xoffA, e0A, tmwA);
@@ -590,6 +588,83 @@ __device__ __forceinline__ void step_dispatch(Ctx& c, const TmemParams& p, int b
 #undef LDPC_TM_PAIR
 #undef LDPC_TM_CASE
     default:
+      break;
+  }
+}
+
+// The fused kernels' dispatch. Runs the step `st` (number s). The rows of the high-rate core (no extension node: BG1 4 x 19 edges, BG2 8 / 10) come in runs of
+// one class: a run stays inside the class' code and skips the dispatch - at code rates close to 1 these rows are most of an
+// iteration (`pusch_slot` +1.2 %; at R = 1/3 the loop-carried state costs 2 %, so the decode-only kernels keep the plain
+// dispatch above). `next` is the prefetched descriptor of step s + 1 on entry and on return.
+template <int BG, int SCALE, int MODE>
+__device__ __forceinline__ void step_dispatch_runs(Ctx& c, const TmemParams& p, int bar_id, int zpad, uint4 st, uint4& next, int& s,
+                                              int nof_steps)
+{
+  const unsigned cls = st.x & 0xffu;
+#define LDPC_TM_ONCE(BODY)                                       \
+  {                                                              \
+    const unsigned xoffA = st.w & 0xffffu, xoffB = st.w >> 16;   \
+    const int e0A = st.y & 0xffffu, e0B = st.z & 0xffffu;        \
+    const unsigned tmwA = st.y >> 16, tmwB = st.z >> 16;         \
+    (void)xoffB, (void)e0B, (void)tmwB;                          \
+    BODY;                                                        \
+    ++s;                                                         \
+  }
+#define LDPC_TM_RUN(BODY)                                        \
+  for (;;) {                                                     \
+    const unsigned xoffA = st.w & 0xffffu, xoffB = st.w >> 16;   \
+    const int e0A = st.y & 0xffffu, e0B = st.z & 0xffffu;        \
+    const unsigned tmwA = st.y >> 16, tmwB = st.z >> 16;         \
+    (void)xoffB, (void)e0B, (void)tmwB;                          \
+    BODY;                                                        \
+    ++s;                                                         \
+    if (s >= nof_steps || (next.x & 0xffu) != cls) {             \
+      break;                                                     \
+    }                                                            \
+    st = next;                                                   \
+    next = p.steps[s + 1];                                       \
+  }
+  switch (cls) {
+#define LDPC_TM_CASE(D, EXT)                        \
+  case 2 * (D) + (EXT):                             \
+    if constexpr (tm_row_used(BG, D, (EXT) != 0)) {  \
+      if constexpr ((EXT) == 0) {                    \
+        LDPC_TM_RUN((row_body<D, false, SCALE, MODE>(c, p, xoffA, e0A, tmwA, bar_id, zpad))) \
+      } else {                                       \
+        LDPC_TM_ONCE((row_body<D, true, SCALE, MODE>(c, p, xoffA, e0A, tmwA, bar_id, zpad))) \
+      }                                              \
+    }                                               \
+    break;
+#define LDPC_TM_PAIR(DA, DB)                                                                   \
+  case 16 * (DA) + (DB):                                                                       \
+    if constexpr (tm_pair_used(BG, DA, DB)) {                                                  \
+      LDPC_TM_ONCE((pair_body<DA, DB, SCALE, MODE>(c, p, xoffA, e0A, tmwA, xoffB, e0B, tmwB, bar_id, zpad)))  \
+    }                                                                                          \
+    break;
+    LDPC_TM_CASE(2, 1)
+    LDPC_TM_CASE(3, 1)
+    LDPC_TM_CASE(4, 1)
+    LDPC_TM_CASE(5, 1)
+    LDPC_TM_CASE(6, 1)
+    LDPC_TM_CASE(7, 1)
+    LDPC_TM_CASE(8, 1)
+    LDPC_TM_CASE(9, 1)
+    LDPC_TM_CASE(8, 0)
+    LDPC_TM_CASE(10, 0)
+    LDPC_TM_CASE(19, 0)
+    LDPC_TM_PAIR(5, 5)
+    LDPC_TM_PAIR(5, 4)
+    LDPC_TM_PAIR(4, 4)
+    LDPC_TM_PAIR(4, 3)
+    LDPC_TM_PAIR(4, 2)
+    LDPC_TM_PAIR(3, 3)
+    LDPC_TM_PAIR(3, 2)
+#undef LDPC_TM_PAIR
+#undef LDPC_TM_CASE
+#undef LDPC_TM_RUN
+#undef LDPC_TM_ONCE
+    default:
+      ++s;  // not reached: tm_build_tables only emits classes the kernel has
       break;
   }
 }
@@ -719,10 +794,10 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
     c.kinv = tm::hc(1.f / tm::TM_S) | zero;
   }
 
-  // FUSED: the pair after the current one is claimed one pair early so that its rate-matched LLRs (and previous soft
-  // bits) can be pulled into L2 while this pair is decoded (+3.4 % on the full-slot workload; for the plain decoder the
-  // earlier claim costs more at the tail than the prefetch gains: profiles/r01_icache_microbench.md v17/v18)
-  constexpr bool PREFETCH = FUSED;
+  // The pair after the current one is claimed one pair early: the atomic's round trip runs under this pair's loads instead
+  // of in front of a barrier, and the next pair's inputs (fused: rate-matched LLRs and previous soft bits) are pulled into
+  // L2 while this pair is decoded.
+  constexpr bool PREFETCH = true;
   if (PREFETCH && t == 0) {
     flags[5] = atomicAdd(p.pair_counter, 1u);
   }
@@ -747,11 +822,18 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
     if (2 * pair >= p.nof_cbs) {
       break;
     }
+    unsigned claimed_early = 0;
+    if (!FUSED && t == 0) {
+      claimed_early = atomicAdd(p.pair_counter, 1u);  // consumed behind the loads (fused: issued under the staging phase)
+    }
     const bool hasB = 2 * pair + 1 < p.nof_cbs;
     const CbWork wA = p.work[2 * pair];
     const CbWork wB = p.work[hasB ? 2 * pair + 1 : 2 * pair];
     const bool useA = !wA.skip_decode, useB = hasB && !wB.skip_decode;
     if (!FUSED && !useA && !useB) {
+      if (t == 0) {
+        flags[5] = claimed_early;
+      }
       tm::group_barrier<FULL>(bar_id, zpad);
       continue;
     }
@@ -952,6 +1034,9 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
     if (lastB) {
       atomicMax(const_cast<unsigned*>(&flags[1]), lastB);
     }
+    if (!FUSED && t == 0) {
+      flags[5] = claimed_early;
+    }
     tm::group_barrier<FULL>(bar_id, zpad);
     const unsigned inszA = flags[0], inszB = flags[1];  // one past the last non-zero LLR (ldpc_decoder_impl.cpp:86-94)
     bool doneA = !useA, doneB = !useB;
@@ -1018,6 +1103,13 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
       const unsigned cbn = min(2u, p.nof_cbs - 2 * pair_next);
       for (unsigned h = 0; h < cbn; ++h) {
         const CbWork wn = p.work[2 * pair_next + h];
+        if constexpr (!FUSED) {
+          const char* in = reinterpret_cast<const char*>(p.llr_base + wn.in_offset);
+          for (unsigned o = 128u * t; o < (wn.skip_decode ? 0u : wn.in_length); o += 128u * zpad) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(in + o));
+          }
+          continue;
+        }
         const char* rm = reinterpret_cast<const char*>(p.rm_base + wn.rm_offset);
         for (unsigned o = 128u * t; o < wn.rm_length; o += 128u * zpad) {
           asm volatile("prefetch.global.L2 [%0];" ::"l"(rm + o));
@@ -1037,10 +1129,15 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
       // the barrier that orders a row after its predecessor is inside the bodies
       tm::row_arrive(c.row_bar, c.t4);  // every row waits for its predecessor's arrivals: these stand in for the first one's
       uint4 next = p.steps[0];
-      for (int s = 0; s < nof_steps; ++s) {
+      for (int s = 0; s < nof_steps;) {
         const uint4 st = next;
         next = p.steps[s + 1];  // the descriptor of the step after this one travels under this step's arithmetic
-        tm::step_dispatch<BG, SCALE, MODE>(c, p, bar_id, zpad, st);
+        if constexpr (FUSED) {
+          tm::step_dispatch_runs<BG, SCALE, MODE>(c, p, bar_id, zpad, st, next, s, nof_steps);
+        } else {
+          tm::step_dispatch<BG, SCALE, MODE>(c, p, bar_id, zpad, st);
+          ++s;
+        }
       }
       tm::row_wait(c.row_bar, c.row_parity);  // the last row's arrivals
       tm::tm_wait_st();
@@ -1147,16 +1244,33 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
           // codeblock is four message bytes (bit-reversed: the first bit of a byte is its MSB), stored by one lane. (The
           // byte-wise loop below reads the soft values with a stride of 8 words - an 8-way bank conflict per load - and
           // was 7 % of the fused kernel's time on full-slot transport blocks.)
+          // Columns go in batches: all loads of a batch are in flight together, and lane u of the warp keeps and stores the
+          // two words of the batch's column u (one store instruction per codeblock and batch).
           const unsigned lane = (unsigned)t & 31u;
-#pragma unroll 2
-          for (int n = 0; n < K; ++n) {
-            const unsigned v = soft_w[(unsigned)n * Z + t];
-            const unsigned ba = __ballot_sync(0xffffffffu, (v & 0x7fffu) == 0 || (v & 0x8000u));
-            const unsigned bb = __ballot_sync(0xffffffffu, (v & 0x7fff0000u) == 0 || (v & 0x80000000u));
-            if (lane == 0) {
-              const unsigned o = ((unsigned)n * Z + (unsigned)t) >> 3;  // byte offset of the four bytes (multiple of 4)
-              *reinterpret_cast<unsigned*>(hard + o) = __byte_perm(__brev(ba), 0u, 0x0123);
-              *reinterpret_cast<unsigned*>(hard + msg_bytes16 + o) = __byte_perm(__brev(bb), 0u, 0x0123);
+          constexpr int CB = (K == 22) ? 11 : 10;
+#pragma unroll 1
+          for (int n0 = 0; n0 < K; n0 += CB) {
+            unsigned v[CB];
+#pragma unroll
+            for (int u = 0; u < CB; ++u) {
+              v[u] = soft_w[(unsigned)(n0 + u) * Z + t];
+            }
+            unsigned wa = 0, wb = 0;
+#pragma unroll
+            for (int u = 0; u < CB; ++u) {
+              // get_hard_bits as in the CRC sweep: sign bit set or magnitude zero
+              const unsigned nz = (v[u] & 0x7fff7fffu) + 0x7fff7fffu;
+              const unsigned hb = (v[u] | ~nz) & 0x80008000u;
+              const unsigned ba = __ballot_sync(0xffffffffu, (hb & 0x8000u) != 0);
+              const unsigned bb = __ballot_sync(0xffffffffu, (hb & 0x80000000u) != 0);
+              wa = (lane == (unsigned)u) ? ba : wa;
+              wb = (lane == (unsigned)u) ? bb : wb;
+            }
+            if (lane < (unsigned)CB) {
+              // byte offset of the four bytes of (column n0 + lane, this warp's 32 lanes): a multiple of 4
+              const unsigned o = ((unsigned)(n0 + (int)lane) * Z + ((unsigned)t - lane)) >> 3;
+              *reinterpret_cast<unsigned*>(hard + o) = __byte_perm(__brev(wa), 0u, 0x0123);
+              *reinterpret_cast<unsigned*>(hard + msg_bytes16 + o) = __byte_perm(__brev(wb), 0u, 0x0123);
             }
           }
           tm::group_barrier<FULL>(bar_id, zpad);  // the bytes are read by other threads than the ones that stored them
