@@ -33,9 +33,9 @@ INT_OPS_PER_EMU = 20                  # SURVEY.md 8(d) canonical cost of one edg
 # in profiles/r02_ncu_tmem_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, warp instructions executed, and the
 # share of issue slots that were active.
 NCU_PROFILE = "profiles/r02_ncu_tmem_summary.txt"
-NCU_TRAFFIC_BYTES_PER_CB = 1.7409e9 / 65536
-NCU_WARP_INSTR_PER_CB = 20.057e9 / 65536
-NCU_ISSUE_SLOTS_ACTIVE = 0.624
+NCU_TRAFFIC_BYTES_PER_CB = 1.7368e9 / 65536
+NCU_WARP_INSTR_PER_CB = 17.992e9 / 65536
+NCU_ISSUE_SLOTS_ACTIVE = 0.738
 REF_BUILD = ("oracle/Makefile: g++ -O3 -DNDEBUG -mavx2 -mfma -mpclmul (+ -mavx512f -mavx512bw in the reference's own avx512 "
              "units), built in the build container and shipped as a binary - portable flags, not -march=native")
 METRIC = "LDPC decoded info Gb/s (BG1 Z=384, 6 iters)"
