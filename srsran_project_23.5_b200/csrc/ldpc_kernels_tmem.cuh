@@ -728,8 +728,10 @@ constexpr unsigned TM_CRC_TABLE_BYTES = 3 * 256 * 4 + 16;  // + the TMEM base ad
 // FULL: Z = 384 (one group of 12 warps, every lane live) with Z, the barrier operands and the all-lanes-active predicate
 // folded at compile time - the configuration BASELINE.json's metric is quoted on.
 // WIDE: decode-only blocks of up to 512 threads for lifting sizes that leave room for more groups.
+// Register cap: the fused kernels need their 168; for the decode-only kernels a cap of 120 makes ptxas settle on 86 registers
+// with a schedule that measures 1 % faster than the 111 it takes when left alone (profiles/r02_kernel_experiments.md).
 template <int BG, int SCALE, bool FUSED, int MODE>
-__global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_THREADS, 1)
+__global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_THREADS, 1) __maxnreg__(FUSED ? 168 : 120)
     ldpc_decode_tmem_kernel(const __grid_constant__ TmemParams p)
 {
   constexpr bool FULL = MODE == TM_MODE_FULL;
