@@ -1337,7 +1337,6 @@ __global__ void __launch_bounds__(MODE == TM_MODE_WIDE ? TM_THREADS_WIDE : TM_TH
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
-#ifndef LDPC_TM_DEVICE_ONLY  // development builds of a single kernel instantiation (tools/sass_one.sh) stop here
 static inline int tm_scale_variant(const unsigned char* lut)
 {
   bool gen = true, avx = true;
@@ -1482,6 +1481,9 @@ static inline bool tm_build_tables(int bg, int Z, int lifting_set, TmemParams& p
   return ((tmw + 7) & ~7u) <= tm_cap;
 }
 
+// Builds that only want the kernels or the table builder (a single instantiation for a SASS listing, the schedule check of
+// tests/test_tm_schedule.py) define LDPC_TM_DEVICE_ONLY and stop here: the launchers below instantiate every kernel.
+#ifndef LDPC_TM_DEVICE_ONLY
 constexpr size_t TM_SMEM_LIMIT = 232448;      // 227 KB opt-in maximum per block on sm_100
 constexpr size_t TM_SMEM_MIN = 120 * 1024;    // more than half an SM: one block per SM owns all 512 TMEM columns
 
