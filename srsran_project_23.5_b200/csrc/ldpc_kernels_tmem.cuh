@@ -2,7 +2,8 @@
 //
 // Work split: one thread per lifted lane, TWO codeblocks per thread (half2: low half = codeblock A, high half = B; both
 // share base graph and lifting size so addresses, rotations and control flow are common). A thread block holds
-// G = 384 / roundup32(Z) independent codeblock pairs ("groups"), each with its own named barrier.
+// G = 384 / roundup32(Z) independent codeblock pairs ("groups"), each with its own named barrier (phases outside the row
+// loop) and its own mbarrier (the row barrier of the layered schedule, split into arrive and wait).
 //
 // Where the data live (per SM, Z = 384: everything on chip, nothing but the input LLRs and output bits touches HBM):
 //   * a-posteriori soft values of the high-rate nodes (bg_K + 4 columns)            shared memory, half2 per lane
@@ -31,8 +32,10 @@
 //         the minimum implies min2 == min1
 //   soft  SOFT' = V + C_new (promotion and stickiness by overflow / inf arithmetic)
 // Messages are stored unscaled as biased bytes: 1152 + c = fma(C, 1/544, 1152) (the rounding absorbs the inexact 1/544).
-// Row structure (degrees, columns, shifts) comes from a per-launch table in the kernel parameters (constant bank,
-// uniform loads); the row bodies are instantiated per number of high-rate edges so that the per-edge loops unroll
+// Row structure (degrees, columns, shifts) comes from per-launch tables in the kernel parameters (constant bank): an
+// iteration is a list of steps (one row, or two rows without a common column), one 16-byte descriptor each, read with
+// uniform loads - descriptors, edge records, TMEM addresses and the class dispatch all stay on the uniform datapath. The
+// row bodies are instantiated per number of high-rate edges so that the per-edge loops unroll
 // while the code stays small enough for the instruction cache (the first packed kernel unrolled all 316 edges and was
 // instruction-fetch bound, profiles/r01_ncu_packed_v1_summary.txt).
 #pragma once
