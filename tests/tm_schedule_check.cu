@@ -1,6 +1,7 @@
 // Host-only check of the decoder kernel's schedule tables (tm_build_tables, csrc/ldpc_kernels_tmem.cuh) for every base graph,
 // lifting size and TMEM budget: compiled and run by tests/test_tm_schedule.py (nvcc, no GPU). Prints "ok <n>" or the first
 // violation.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <map>
