@@ -110,6 +110,9 @@ def test_fused_entry_all_shapes_randomized(flags, per_shape):
     dec = pkg.LdpcCuda(device=0, max_codeblocks=4096, flags=flags)
     try:
         _sweep(dec, per_shape)
+        if not flags & pkg.FLAG_FORCE_SCALAR:
+            # every (BG, Z) of the sweep ran on the fused tensor-memory kernel, none fell back to dematch + general decoder
+            assert dec.general_kernel_launch_count == 0
     finally:
         dec.close()
 
